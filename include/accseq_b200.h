@@ -1,0 +1,161 @@
+/*
+ * include/accseq_b200.h -- C ABI of libaccseq_b200.so: the B200 (sm_100a) implementation of AccSeqV9's
+ * per-read mapping hot path.
+ *
+ * The reference (lisanhu/LongReadMapper) has no plugin/FFI seam for this path: the loop nest is inlined in
+ * `single_end()` (alnmain.c:277-551).  The boundary is therefore cut where SURVEY.md 8(b) puts it --
+ * after `refactor_reads_seq` (alnmain.c:302-303) and before SAM printing (alnmain.c:485) -- and each
+ * entry below names the reference code it replaces.  Plain pointers and sizes only; no CUDA or torch
+ * types.  All functions return 0 on success or a negative AS_E* code (the reference signals no errors).
+ * There is NO CPU fallback: every compute entry fails with AS_ENODEV when no sm_100 device is usable.
+ *
+ * Host pointers may be pageable or pinned (as_host_alloc); pinned buffers reach full PCIe speed.
+ * One host thread per as_gpu handle; results are written in input order.
+ */
+#ifndef ACCSEQ_B200_H
+#define ACCSEQ_B200_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AS_OK        0
+#define AS_EINVAL   -22
+#define AS_ENOMEM   -12
+#define AS_ENODEV   -19
+#define AS_EIO       -5
+#define AS_ECUDA   -200     /* a CUDA runtime call failed; as_last_error() has the text */
+#define AS_ERANGE   -34
+
+typedef struct as_gpu as_gpu;       /* opaque: one per GPU, owns the device copy of the index */
+
+/* ---- the index as the reference holds it in host memory after init() (alnmain.c:179-256) ---- */
+typedef struct as_mta {             /* mta_entry (accaln.h:67-71) without the name string */
+    uint64_t offset;                /* start of the forward copy inside .cat */
+    uint64_t seq_len;
+} as_mta;
+
+typedef struct as_index_view {
+    uint64_t        length;         /* dna_fmi.length = N (fmidx.h:16-21) */
+    const uint64_t *C;              /* dna_fmi.c, 256 entries indexed by ASCII code */
+    const uint64_t *O;              /* dna_fmi.o, o_len entries, 4 per block of o_ratio rows */
+    uint64_t        o_len;
+    int             o_ratio;
+    const char     *bwt;            /* dna_fmi.bwt, one byte per row: A C G T $ */
+    const uint64_t *lc;             /* lc_hash.lc (lchash.h:12-16): (k,l) pairs, 2*4^hlen entries */
+    uint64_t        lc_len;
+    int             hlen;
+    const void     *sa;             /* suffix array, N entries */
+    int             sa_entry_bytes; /* 8: sa_buf->mem (ui40_t structs, sa_use.h:17-20) or u64;  5: raw .sa5 bytes;  4: u32 */
+    const char     *content;        /* context.content: the .cat text, con_len bytes */
+    uint64_t        con_len;
+    const as_mta   *mta;            /* context.mta */
+    int             mta_len;
+} as_index_view;
+
+/* Upload the index once and repack it into the device layouts (DESIGN.md "HBM layout").
+ * Replaces nothing in the reference (it keeps host arrays); lookups return identical values. */
+int  as_gpu_open(as_gpu **h, int device, const as_index_view *ix);
+void as_gpu_close(as_gpu *h);
+/* Route all work of this handle to a caller-owned CUDA stream (a cudaStream_t cast to void*); NULL = the
+ * handle's own stream.  Lets a host framework time/overlap the calls on its own stream. */
+int  as_gpu_set_stream(as_gpu *h, void *cuda_stream);
+const char *as_last_error(void);
+int  as_device_count(void);
+
+/* ---- parameters of the path ---- */
+typedef struct as_params {
+    uint32_t seed_len;   /* context.seed_len, default 20 (alnmain.c:577-580) */
+    uint32_t thres;      /* context.uninformative_thres == histo_cap, default 300 */
+    int32_t  gact_T;     /* GACT tile size (DESIGN.md GACT spec), default 320 */
+    int32_t  gact_O;     /* GACT overlap, default 120 */
+    uint32_t flags;      /* AS_F_* */
+} as_params;
+#define AS_F_MYERS        1u   /* also run the edlib-equivalent NW distance with k=(int)(0.05*len*2) per read */
+#define AS_F_NO_ALIGN     2u   /* stop after PART 1+2 (no GACT): results carry loc/off/strand/flag only */
+void as_params_default(as_params *p);
+
+/* ---- per-read output: the fields of `result` (accaln.h:95-103) that the path computes ---- */
+typedef struct as_result {
+    uint64_t loc;         /* best.key: voted .cat coordinate (alnmain.c:427) */
+    uint64_t off;         /* result.off: 0-based forward offset in the sequence; SAM POS = off+1 */
+    int32_t  seq_id;      /* g_name = mta[seq_id].seq_name; -1 when seq_lookup fails (reference: UB) */
+    int32_t  strand;      /* seq_meta.strand */
+    int32_t  flag;        /* 0, 16 or 4   (alnmain.c:466-474) */
+    int32_t  mapq;        /* 255 or 0 */
+    int32_t  ed;          /* result.ed = GACT score */
+    int32_t  valid;
+    int32_t  n_cigar_op;  /* cigar.n_cigar_op: columns written to the read's slice of store_mem */
+    int32_t  myers;       /* edlib NW distance (-1 above k), or -2 when AS_F_MYERS is off */
+    int32_t  phases;      /* value of `iter` when the phase loop ended (parity aid) */
+    int32_t  from_outer;  /* 1 when best came from the outer vote list (alnmain.c:400-403) */
+} as_result;
+
+/*
+ * as_map_batch -- replaces alnmain.c:330-479 (PART 1-3) for n reads.
+ *   reads      host buffer in refactor_reads_seq layout (alnmain.c:87-103): read i at reads + i*stride,
+ *              upper-case ACGT, lens[i] bases.  Reads mapped to strand 1 are reverse-complemented IN
+ *              PLACE, as alnmain.c:433-438 does (the OpenACC region's copy(reads_mem)).
+ *   results    n entries.
+ *   store_mem  caller-owned CIGAR column storage, read i at store_mem + i*store_stride, one op byte per
+ *              column (alnmain.c:314-325 uses store_stride = 2*max_read_len); may be NULL.
+ */
+int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t stride, const uint32_t *lens, size_t n,
+                 as_result *results, uint8_t *store_mem, size_t store_stride);
+
+/* Same path with every buffer already resident in device memory (pointers are device addresses); used to
+ * time the kernels without PCIe and by frameworks that keep reads on the GPU. */
+int as_map_batch_device(as_gpu *h, const as_params *p, char *d_reads, size_t stride, const uint32_t *d_lens,
+                        size_t n, uint32_t max_len, as_result *d_results, uint8_t *d_store, size_t store_stride);
+
+/* Per-shard counters for the end-of-run statistics (alnmain.c:541 "Sensitivity: valid/total"). */
+typedef struct as_stats {
+    uint64_t total, valid, n_flag4, n_flag16, sum_ed, dp_cells, seeds, sa_hits, bs_steps, overflow_reads;
+} as_stats;
+int as_gpu_stats(as_gpu *h, as_stats *out);          /* accumulated since open / last reset */
+int as_gpu_stats_reset(as_gpu *h);
+/* Device time of the stages of the last as_map_batch* call, milliseconds (CUDA events on the call's stream):
+ * [0] pack+seed+vote (PART 1)  [1] locus/strand (PART 2)  [2] GACT  [3] Myers  [4] result fill  [5] H2D  [6] D2H */
+int as_gpu_last_timing(as_gpu *h, float ms[8]);
+
+/* ---- batched forms of the lookup primitives (parity tests, other callers) ---- */
+/* lc_aln (lchash.c:89-104) on n seeds of qlen bases each, seeds + i*qlen; k,l,r as lc_aln leaves them
+ * (k,l start at 1, N-1 as alnmain.c:354 does). */
+int as_lc_aln_batch(as_gpu *h, const char *seeds, int qlen, size_t n, uint64_t *k, uint64_t *l, uint64_t *r);
+/* fmi_aln (fmidx.c:295-313) from the full range. */
+int as_fmi_aln_batch(as_gpu *h, const char *qry, int qlen, size_t n, uint64_t *k, uint64_t *l, uint64_t *r);
+/* sa_access (fmidx.c:18-33) */
+int as_sa_access_batch(as_gpu *h, const uint64_t *rows, size_t n, uint64_t *pos);
+/* PART 1 only (alnmain.c:333-405): best.key / best.val / phases / from_outer per read. */
+int as_vote_batch(as_gpu *h, const as_params *p, const char *reads, size_t stride, const uint32_t *lens,
+                  size_t n, uint64_t *best_key, uint64_t *best_val, int32_t *phases, int32_t *from_outer);
+/* cigar_align (mutils.c:94-105) on n (query,target) pairs: pair i is q + i*q_stride (qlens[i] bases) vs
+ * t + i*t_stride (tlens[i] bases), ASCII ACGT.  ops + i*ops_stride receives the column ops. */
+int as_cigar_align_batch(as_gpu *h, const as_params *p, const char *q, size_t q_stride, const uint32_t *qlens,
+                         const char *t, size_t t_stride, const uint32_t *tlens, size_t n,
+                         uint8_t *ops, size_t ops_stride, int32_t *n_ops, int32_t *score);
+/* edlib-equivalent NW edit distance (edlib.cpp:694-895): dist[i] = distance, or -1 if ks[i] >= 0 and the
+ * distance exceeds ks[i].  ks may be NULL (no bound). */
+int as_edit_distance_batch(as_gpu *h, const char *q, size_t q_stride, const uint32_t *qlens,
+                           const char *t, size_t t_stride, const uint32_t *tlens, size_t n,
+                           const int32_t *ks, int32_t *dist);
+
+/* ---- index construction on the GPU (asindex.c:78-153) ---- */
+/* Build .cat/.mta content, suffix array, BWT, O, CSA and the 4^hlen interval table for nseq sequences and
+ * write <fasta_path>.mta .cat .cat.sa5 .cat.mfi .cat.lch in the reference's formats (Notes.txt:6-25). */
+int as_index_build_files(int device, const char *fasta_path, int nseq, const char *const *names,
+                         const char *const *seqs, const uint64_t *lens, int o_ratio, int hlen);
+/* Suffix array of text[0,n) (last byte unique smallest), u64 entries. */
+int as_suffix_array(int device, const uint8_t *text, uint64_t n, uint64_t *sa);
+
+/* pinned host memory helpers */
+void *as_host_alloc(size_t bytes);
+void  as_host_free(void *p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

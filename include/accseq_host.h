@@ -1,0 +1,71 @@
+/*
+ * include/accseq_host.h -- host-side C helpers around the hot path (libaccseq_host.so, no CUDA needed):
+ * seeded synthetic inputs, the reference's on-disk index formats, FASTQ ingest and SAM emit.
+ */
+#ifndef ACCSEQ_HOST_H
+#define ACCSEQ_HOST_H
+
+#include <stdint.h>
+#include <stddef.h>
+#include <stdio.h>
+#include "accseq_b200.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- synthetic inputs (distribution of scripts/dna_txt_gen.py:12, seeded) ---- */
+void   as_sim_genome(uint64_t seed, uint64_t n, char *out);                 /* upper-case ACGT, no terminator */
+void   as_sim_plant_repeats(uint64_t seed, char *g, uint64_t n, int n_families, uint64_t unit_len,
+                            int copies, double divergence);
+/* n_reads reads sampled uniformly over positions and strands; length uniform in [len_min,len_max]; per-read
+ * error rate uniform in [err_min,err_max], split sub_frac substitutions, the rest half insertions half
+ * deletions.  out: stride bytes per read, zero padded (refactor_reads_seq layout). Returns reads written. */
+size_t as_sim_reads(uint64_t seed, const char *genome, uint64_t glen, size_t n_reads,
+                    uint32_t len_min, uint32_t len_max, double err_min, double err_max, double sub_frac,
+                    char *out, size_t stride, uint32_t *lens, uint64_t *truth_pos, uint8_t *truth_strand);
+
+/* ---- the reference's index files (Notes.txt:6-25; readers: fmidx.c:246-275, lchash.c:114-127,
+ *      alnmain.c:125-140,237-252) ---- */
+typedef struct as_host_index {
+    as_index_view view;        /* pointers into the owned buffers below */
+    uint64_t *C, *O, *lc, *csa;
+    char     *bwt, *content;
+    uint8_t  *sa5;             /* raw 5-byte entries as on disk */
+    as_mta   *mta;
+    char    **names;           /* mta_len NUL-terminated sequence names */
+    uint64_t  csa_len;
+    int       csa_ratio;
+} as_host_index;
+int  as_index_load(const char *fasta_path, as_host_index **out);   /* <fa>.mta, <fa>.cat{,.mfi,.lch,.sa5} */
+void as_index_free(as_host_index *ix);
+
+/* ---- SAM emit (alnmain.c:62-75, 485-526) ---- */
+int  as_sam_header(FILE *out, const as_host_index *ix, long rg_id);
+/* CIGAR text of the column ops, STANDARD M/I/D (parse_cigar contract); returns length or -1 if it does not fit */
+int  as_cigar_text(const uint8_t *ops, int n_ops, char *buf, size_t buflen);
+int  as_sam_record(FILE *out, const as_host_index *ix, const char *qname, size_t qname_len,
+                   const char *seq, const char *qual, uint32_t len, const as_result *r,
+                   const uint8_t *ops);
+
+/* ---- FASTQ ingest (accaln.c:45-58 reads_load + alnmain.c:87-103 refactor_reads_seq) ---- */
+typedef struct as_read_batch {
+    size_t    n;
+    size_t    stride;          /* max_len + 1 */
+    uint32_t  max_len;
+    char     *seqs;            /* n * stride, zero padded */
+    uint32_t *lens;
+    char    **names;
+    char    **quals;
+} as_read_batch;
+typedef struct as_fastq as_fastq;
+as_fastq *as_fastq_open(const char *path);       /* plain or gzip */
+/* loads up to max_reads records into a fresh batch (seqs from alloc(bytes) if given, else malloc) */
+int  as_fastq_next_batch(as_fastq *fq, size_t max_reads, as_read_batch *b, void *(*alloc)(size_t));
+void as_read_batch_free(as_read_batch *b, void (*dealloc)(void *));
+void as_fastq_close(as_fastq *fq);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
