@@ -111,6 +111,12 @@ int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t stride, cons
 int as_map_batch_device(as_gpu *h, const as_params *p, char *d_reads, size_t stride, const uint32_t *d_lens,
                         size_t n, uint32_t max_len, as_result *d_results, uint8_t *d_store, size_t store_stride);
 
+/* as_map_batch_device only enqueues work on the handle's stream; this (or a synchronize of the caller's
+ * stream) completes it. */
+int as_gpu_sync(as_gpu *h);
+/* Number of CUDA kernels this handle has launched since as_gpu_open (bench.py's gpu_launches). */
+uint64_t as_gpu_launch_count(as_gpu *h);
+
 /* Per-shard counters for the end-of-run statistics (alnmain.c:541 "Sensitivity: valid/total"). */
 typedef struct as_stats {
     uint64_t total, valid, n_flag4, n_flag16, sum_ed, dp_cells, seeds, sa_hits, bs_steps, overflow_reads;
@@ -118,7 +124,8 @@ typedef struct as_stats {
 int as_gpu_stats(as_gpu *h, as_stats *out);          /* accumulated since open / last reset */
 int as_gpu_stats_reset(as_gpu *h);
 /* Device time of the stages of the last as_map_batch* call, milliseconds (CUDA events on the call's stream):
- * [0] pack+seed+vote (PART 1)  [1] locus/strand (PART 2)  [2] GACT  [3] Myers  [4] result fill  [5] H2D  [6] D2H */
+ * [0] pack+seed+vote (PART 1)  [1] locus/strand (PART 2)  [2] GACT (+ result fill, PART 3)  [3] Myers  [4] unused
+ * [5] H2D  [6] counters + D2H  [7] whole call */
 int as_gpu_last_timing(as_gpu *h, float ms[8]);
 
 /* ---- batched forms of the lookup primitives (parity tests, other callers) ---- */
@@ -142,14 +149,6 @@ int as_cigar_align_batch(as_gpu *h, const as_params *p, const char *q, size_t q_
 int as_edit_distance_batch(as_gpu *h, const char *q, size_t q_stride, const uint32_t *qlens,
                            const char *t, size_t t_stride, const uint32_t *tlens, size_t n,
                            const int32_t *ks, int32_t *dist);
-
-/* ---- index construction on the GPU (asindex.c:78-153) ---- */
-/* Build .cat/.mta content, suffix array, BWT, O, CSA and the 4^hlen interval table for nseq sequences and
- * write <fasta_path>.mta .cat .cat.sa5 .cat.mfi .cat.lch in the reference's formats (Notes.txt:6-25). */
-int as_index_build_files(int device, const char *fasta_path, int nseq, const char *const *names,
-                         const char *const *seqs, const uint64_t *lens, int o_ratio, int hlen);
-/* Suffix array of text[0,n) (last byte unique smallest), u64 entries. */
-int as_suffix_array(int device, const uint8_t *text, uint64_t n, uint64_t *sa);
 
 /* pinned host memory helpers */
 void *as_host_alloc(size_t bytes);

@@ -1,0 +1,11 @@
+"""longreadmapper_b200 -- B200 (sm_100a) implementation of AccSeqV9's per-read mapping hot path.
+
+The product is the C-ABI library ``libaccseq_b200.so`` (include/accseq_b200.h) plus the plain-C host helpers
+``libaccseq_host.so`` (include/accseq_host.h).  This package is only the ctypes view of both that the tests,
+``bench.py`` and ``__graft_entry__`` use; there is no CPU fallback behind it.
+"""
+from .capi import (AS_F_MYERS, AS_F_NO_ALIGN, RESULT_DTYPE, AccSeqError, GpuMapper, Params, build_native,
+                   cuda_lib, device_count, host_lib, sim_genome, sim_plant_repeats, sim_reads)
+
+__all__ = ["AS_F_MYERS", "AS_F_NO_ALIGN", "RESULT_DTYPE", "AccSeqError", "GpuMapper", "Params", "build_native",
+           "cuda_lib", "device_count", "host_lib", "sim_genome", "sim_plant_repeats", "sim_reads"]

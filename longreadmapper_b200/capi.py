@@ -1,0 +1,349 @@
+"""ctypes bindings of libaccseq_b200.so / libaccseq_host.so (see include/*.h for the contracts)."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+CSRC_DIR = os.path.join(PKG_DIR, "csrc")
+CUDA_LIB = os.path.join(PKG_DIR, "libaccseq_b200.so")
+HOST_LIB = os.path.join(PKG_DIR, "libaccseq_host.so")
+
+AS_F_MYERS = 1
+AS_F_NO_ALIGN = 2
+
+# as_result (include/accseq_b200.h)
+RESULT_DTYPE = np.dtype([("loc", "<u8"), ("off", "<u8"), ("seq_id", "<i4"), ("strand", "<i4"), ("flag", "<i4"),
+                         ("mapq", "<i4"), ("ed", "<i4"), ("valid", "<i4"), ("n_cigar_op", "<i4"), ("myers", "<i4"),
+                         ("phases", "<i4"), ("from_outer", "<i4")])
+assert RESULT_DTYPE.itemsize == 56
+
+
+class AccSeqError(RuntimeError):
+    pass
+
+
+class AsMta(C.Structure):
+    _fields_ = [("offset", C.c_uint64), ("seq_len", C.c_uint64)]
+
+
+class AsIndexView(C.Structure):
+    _fields_ = [("length", C.c_uint64), ("C", C.c_void_p), ("O", C.c_void_p), ("o_len", C.c_uint64),
+                ("o_ratio", C.c_int), ("bwt", C.c_void_p), ("lc", C.c_void_p), ("lc_len", C.c_uint64),
+                ("hlen", C.c_int), ("sa", C.c_void_p), ("sa_entry_bytes", C.c_int), ("content", C.c_void_p),
+                ("con_len", C.c_uint64), ("mta", C.c_void_p), ("mta_len", C.c_int)]
+
+
+class Params(C.Structure):
+    _fields_ = [("seed_len", C.c_uint32), ("thres", C.c_uint32), ("gact_T", C.c_int32), ("gact_O", C.c_int32),
+                ("flags", C.c_uint32)]
+
+
+class AsStats(C.Structure):
+    _fields_ = [(k, C.c_uint64) for k in ("total", "valid", "n_flag4", "n_flag16", "sum_ed", "dp_cells", "seeds",
+                                           "sa_hits", "bs_steps", "overflow_reads")]
+
+
+class AsHostIndex(C.Structure):
+    _fields_ = [("view", AsIndexView), ("C", C.c_void_p), ("O", C.c_void_p), ("lc", C.c_void_p), ("csa", C.c_void_p),
+                ("bwt", C.c_void_p), ("content", C.c_void_p), ("sa5", C.c_void_p), ("mta", C.c_void_p),
+                ("names", C.POINTER(C.c_char_p)), ("csa_len", C.c_uint64), ("csa_ratio", C.c_int)]
+
+
+def build_native(verbose=False):
+    """Compile both libraries in-tree (nvcc cross-compiles sm_100a without a GPU)."""
+    out = None if verbose else subprocess.DEVNULL
+    subprocess.run(["make", "-s", "-j8", "-C", CSRC_DIR, "all"], check=True, stdout=out)
+
+
+_cuda = None
+_host = None
+
+
+def cuda_lib():
+    """libaccseq_b200.so; raises if it is not built -- there is no fallback path."""
+    global _cuda
+    if _cuda is not None:
+        return _cuda
+    if not os.path.exists(CUDA_LIB):
+        raise AccSeqError(f"{CUDA_LIB} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(make -C longreadmapper_b200/csrc). There is no CPU fallback.")
+    L = C.CDLL(CUDA_LIB)
+    vp, u64, sz, i32 = C.c_void_p, C.c_uint64, C.c_size_t, C.c_int
+    L.as_last_error.restype = C.c_char_p
+    L.as_device_count.restype = i32
+    L.as_gpu_open.argtypes = [C.POINTER(vp), i32, C.POINTER(AsIndexView)]
+    L.as_gpu_close.argtypes = [vp]
+    L.as_gpu_close.restype = None
+    L.as_gpu_set_stream.argtypes = [vp, vp]
+    L.as_gpu_sync.argtypes = [vp]
+    L.as_gpu_launch_count.argtypes = [vp]
+    L.as_gpu_launch_count.restype = u64
+    L.as_params_default.argtypes = [C.POINTER(Params)]
+    L.as_params_default.restype = None
+    L.as_map_batch.argtypes = [vp, C.POINTER(Params), vp, sz, vp, sz, vp, vp, sz]
+    L.as_map_batch_device.argtypes = [vp, C.POINTER(Params), vp, sz, vp, sz, C.c_uint32, vp, vp, sz]
+    L.as_gpu_stats.argtypes = [vp, C.POINTER(AsStats)]
+    L.as_gpu_stats_reset.argtypes = [vp]
+    L.as_gpu_last_timing.argtypes = [vp, C.POINTER(C.c_float * 8)]
+    L.as_lc_aln_batch.argtypes = [vp, vp, i32, sz, vp, vp, vp]
+    L.as_fmi_aln_batch.argtypes = [vp, vp, i32, sz, vp, vp, vp]
+    L.as_sa_access_batch.argtypes = [vp, vp, sz, vp]
+    L.as_vote_batch.argtypes = [vp, C.POINTER(Params), vp, sz, vp, sz, vp, vp, vp, vp]
+    L.as_cigar_align_batch.argtypes = [vp, C.POINTER(Params), vp, sz, vp, vp, sz, vp, sz, vp, sz, vp, vp]
+    L.as_edit_distance_batch.argtypes = [vp, vp, sz, vp, vp, sz, vp, sz, vp, vp]
+    L.as_host_alloc.argtypes = [sz]
+    L.as_host_alloc.restype = vp
+    L.as_host_free.argtypes = [vp]
+    L.as_host_free.restype = None
+    _cuda = L
+    return L
+
+
+def host_lib():
+    global _host
+    if _host is not None:
+        return _host
+    if not os.path.exists(HOST_LIB):
+        raise AccSeqError(f"{HOST_LIB} is missing: run make -C longreadmapper_b200/csrc host")
+    L = C.CDLL(HOST_LIB)
+    vp, u64, sz = C.c_void_p, C.c_uint64, C.c_size_t
+    L.as_sim_genome.argtypes = [u64, u64, vp]
+    L.as_sim_genome.restype = None
+    L.as_sim_plant_repeats.argtypes = [u64, vp, u64, C.c_int, u64, C.c_int, C.c_double]
+    L.as_sim_plant_repeats.restype = None
+    L.as_sim_reads.argtypes = [u64, vp, u64, sz, C.c_uint32, C.c_uint32, C.c_double, C.c_double, C.c_double, vp, sz,
+                               vp, vp, vp]
+    L.as_sim_reads.restype = sz
+    if hasattr(L, "as_index_load"):
+        L.as_index_load.argtypes = [C.c_char_p, C.POINTER(C.POINTER(AsHostIndex))]
+        L.as_index_free.argtypes = [C.POINTER(AsHostIndex)]
+        L.as_index_free.restype = None
+    _host = L
+    return L
+
+
+def device_count():
+    return int(cuda_lib().as_device_count())
+
+
+# ---------------------------------------------------------------------------------------------------
+# synthetic inputs (distribution of the reference's scripts/dna_txt_gen.py:12, seeded)
+# ---------------------------------------------------------------------------------------------------
+def sim_genome(seed, n):
+    g = np.empty(n, dtype=np.uint8)
+    host_lib().as_sim_genome(seed, n, g.ctypes.data)
+    return g
+
+
+def sim_plant_repeats(seed, genome, n_families=8, unit_len=1500, copies=6, divergence=0.01):
+    host_lib().as_sim_plant_repeats(seed, genome.ctypes.data, genome.size, n_families, unit_len, copies, divergence)
+    return genome
+
+
+def sim_reads(seed, genome, n_reads, len_min, len_max, err_min, err_max, sub_frac, out=None):
+    """Returns (reads[n, stride] uint8 zero padded, lens uint32, truth_pos uint64, truth_strand uint8)."""
+    stride = len_max + 1
+    reads = out if out is not None else np.zeros((n_reads, stride), dtype=np.uint8)
+    lens = np.zeros(n_reads, dtype=np.uint32)
+    pos = np.zeros(n_reads, dtype=np.uint64)
+    strand = np.zeros(n_reads, dtype=np.uint8)
+    got = host_lib().as_sim_reads(seed, genome.ctypes.data, genome.size, n_reads, len_min, len_max, err_min, err_max,
+                                  sub_frac, reads.ctypes.data, stride, lens.ctypes.data, pos.ctypes.data,
+                                  strand.ctypes.data)
+    if got != n_reads:
+        raise AccSeqError("as_sim_reads: genome too short for these reads")
+    return reads, lens, pos, strand
+
+
+# ---------------------------------------------------------------------------------------------------
+def _ptr(a):
+    return a.ctypes.data if a is not None else None
+
+
+class GpuMapper:
+    """One as_gpu handle: the index resident on one B200, mirrors the calls alnmain.c makes per batch."""
+
+    def __init__(self, device, *, length, C_table, O, o_ratio, bwt, lc, hlen, sa, sa_entry_bytes, content, mta):
+        L = cuda_lib()
+        self._keep = [np.ascontiguousarray(x) for x in (C_table, O, bwt, lc, sa, content)]
+        Ct, Ot, bw, lcv, sav, con = self._keep
+        mta_arr = (AsMta * max(1, len(mta)))(*[AsMta(int(o), int(s)) for (o, s) in mta])
+        v = AsIndexView(int(length), Ct.ctypes.data, Ot.ctypes.data, Ot.size, int(o_ratio), bw.ctypes.data,
+                        lcv.ctypes.data, lcv.size, int(hlen), sav.ctypes.data, int(sa_entry_bytes), con.ctypes.data,
+                        con.size, C.cast(mta_arr, C.c_void_p), len(mta))
+        h = C.c_void_p()
+        rc = L.as_gpu_open(C.byref(h), device, C.byref(v))
+        if rc != 0:
+            raise AccSeqError(f"as_gpu_open failed ({rc}): {L.as_last_error().decode()}")
+        self.h = h
+        self.L = L
+        self.device = device
+        self.N = int(length)
+        self._keep = None          # the device copy is complete; host arrays are no longer referenced
+
+    @classmethod
+    def from_oracle_index(cls, ox, device=0):
+        """ox: tests/oracle_lib.OracleIndex (the reference's in-memory layout)."""
+        return cls(device, length=ox.n, C_table=ox.Ctab, O=ox.O, o_ratio=ox.s.o_ratio, bwt=ox.bwt, lc=ox.lc,
+                   hlen=ox.s.hlen, sa=ox.sa, sa_entry_bytes=8, content=ox.cat,
+                   mta=[(o, s) for (_, o, s) in ox.mta])
+
+    @classmethod
+    def from_index_files(cls, fasta_path, device=0):
+        """Loads <fa>.mta/.cat/.cat.mfi/.cat.lch/.cat.sa5 with the C loader (libaccseq_host.so) and uploads."""
+        H = host_lib()
+        L = cuda_lib()
+        p = C.POINTER(AsHostIndex)()
+        rc = H.as_index_load(fasta_path.encode(), C.byref(p))
+        if rc != 0:
+            raise AccSeqError(f"as_index_load({fasta_path}) failed: {rc}")
+        try:
+            h = C.c_void_p()
+            rc = L.as_gpu_open(C.byref(h), device, C.byref(p.contents.view))
+            if rc != 0:
+                raise AccSeqError(f"as_gpu_open failed ({rc}): {L.as_last_error().decode()}")
+            names = [p.contents.names[i].decode() for i in range(p.contents.view.mta_len)]
+            n = int(p.contents.view.length)
+        finally:
+            H.as_index_free(p)
+        self = cls.__new__(cls)
+        self.h, self.L, self.device, self.N, self._keep, self.names = h, L, device, n, None, names
+        return self
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise AccSeqError(f"{what} failed ({rc}): {self.L.as_last_error().decode()}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.as_gpu_close(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def params(self, seed_len=20, thres=300, T=None, O=None, flags=0):
+        p = Params()
+        self.L.as_params_default(C.byref(p))
+        p.seed_len, p.thres, p.flags = seed_len, thres, flags
+        if T is not None:
+            p.gact_T = T
+        if O is not None:
+            p.gact_O = O
+        return p
+
+    # -- whole path -------------------------------------------------------------------------------
+    def map_batch(self, reads, lens, params=None, want_ops=True, store_stride=None):
+        """reads: uint8 [n, stride] (strand-1 reads are reverse-complemented in place). Returns (results, ops)."""
+        p = params or self.params()
+        reads = np.ascontiguousarray(reads)
+        assert reads.dtype == np.uint8 and reads.ndim == 2
+        n, stride = reads.shape
+        lens = np.ascontiguousarray(lens, dtype=np.uint32)
+        res = np.zeros(n, dtype=RESULT_DTYPE)
+        ops = None
+        if want_ops:
+            if store_stride is None:
+                store_stride = 2 * int(lens.max()) if n else 2
+            ops = np.zeros((n, store_stride), dtype=np.uint8)
+        self._check(self.L.as_map_batch(self.h, C.byref(p), reads.ctypes.data, stride, lens.ctypes.data, n,
+                                        res.ctypes.data, _ptr(ops), store_stride or 0), "as_map_batch")
+        return res, ops
+
+    def map_batch_device(self, d_reads_ptr, stride, d_lens_ptr, n, max_len, d_res_ptr, d_store_ptr, store_stride,
+                         params=None):
+        p = params or self.params()
+        self._check(self.L.as_map_batch_device(self.h, C.byref(p), d_reads_ptr, stride, d_lens_ptr, n, max_len,
+                                               d_res_ptr, d_store_ptr, store_stride), "as_map_batch_device")
+
+    def set_stream(self, cuda_stream_ptr):
+        self._check(self.L.as_gpu_set_stream(self.h, cuda_stream_ptr), "as_gpu_set_stream")
+
+    def sync(self):
+        self._check(self.L.as_gpu_sync(self.h), "as_gpu_sync")
+
+    def launch_count(self):
+        return int(self.L.as_gpu_launch_count(self.h))
+
+    def stats(self):
+        s = AsStats()
+        self._check(self.L.as_gpu_stats(self.h, C.byref(s)), "as_gpu_stats")
+        return {k: int(getattr(s, k)) for k, _ in AsStats._fields_}
+
+    def stats_reset(self):
+        self._check(self.L.as_gpu_stats_reset(self.h), "as_gpu_stats_reset")
+
+    def last_timing(self):
+        ms = (C.c_float * 8)()
+        self._check(self.L.as_gpu_last_timing(self.h, C.byref(ms)), "as_gpu_last_timing")
+        k = ("part1", "part2", "gact", "myers", "unused", "h2d", "d2h", "total")
+        return dict(zip(k, [float(x) for x in ms]))
+
+    # -- single stages ----------------------------------------------------------------------------
+    def _aln(self, fn, seeds, qlen):
+        seeds = np.ascontiguousarray(seeds, dtype=np.uint8)
+        n = seeds.size // qlen if qlen else 0
+        k = np.zeros(n, np.uint64); l = np.zeros(n, np.uint64); r = np.zeros(n, np.uint64)
+        self._check(fn(self.h, seeds.ctypes.data, qlen, n, k.ctypes.data, l.ctypes.data, r.ctypes.data), "aln_batch")
+        return k, l, r
+
+    def lc_aln_batch(self, seeds, qlen):
+        return self._aln(self.L.as_lc_aln_batch, seeds, qlen)
+
+    def fmi_aln_batch(self, seeds, qlen):
+        return self._aln(self.L.as_fmi_aln_batch, seeds, qlen)
+
+    def sa_access_batch(self, rows):
+        rows = np.ascontiguousarray(rows, dtype=np.uint64)
+        pos = np.zeros(rows.size, np.uint64)
+        self._check(self.L.as_sa_access_batch(self.h, rows.ctypes.data, rows.size, pos.ctypes.data), "as_sa_access_batch")
+        return pos
+
+    def vote_batch(self, reads, lens, params=None):
+        p = params or self.params()
+        reads = np.ascontiguousarray(reads)
+        n, stride = reads.shape
+        lens = np.ascontiguousarray(lens, dtype=np.uint32)
+        key = np.zeros(n, np.uint64); val = np.zeros(n, np.uint64)
+        ph = np.zeros(n, np.int32); fo = np.zeros(n, np.int32)
+        self._check(self.L.as_vote_batch(self.h, C.byref(p), reads.ctypes.data, stride, lens.ctypes.data, n,
+                                         key.ctypes.data, val.ctypes.data, ph.ctypes.data, fo.ctypes.data), "as_vote_batch")
+        return key, val, ph, fo
+
+    @staticmethod
+    def _pairs(seqs):
+        lens = np.array([len(s) for s in seqs], dtype=np.uint32)
+        stride = int(lens.max()) + 1 if len(seqs) else 1
+        buf = np.zeros((len(seqs), stride), dtype=np.uint8)
+        for i, s in enumerate(seqs):
+            buf[i, : len(s)] = np.frombuffer(bytes(s), dtype=np.uint8) if not isinstance(s, np.ndarray) else s
+        return buf, stride, lens
+
+    def cigar_align_batch(self, queries, targets, params=None):
+        """queries/targets: lists of bytes / uint8 arrays. Returns (scores, [ops arrays])."""
+        p = params or self.params()
+        n = len(queries)
+        qb, qs, ql = self._pairs(queries)
+        tb, tstr, tl = self._pairs(targets)
+        ostride = int(ql.max() + tl.max()) + 2 if n else 2
+        ops = np.zeros((n, ostride), dtype=np.uint8)
+        n_ops = np.zeros(n, np.int32); score = np.zeros(n, np.int32)
+        self._check(self.L.as_cigar_align_batch(self.h, C.byref(p), qb.ctypes.data, qs, ql.ctypes.data, tb.ctypes.data, tstr,
+                                                tl.ctypes.data, n, ops.ctypes.data, ostride, n_ops.ctypes.data,
+                                                score.ctypes.data), "as_cigar_align_batch")
+        return score, [ops[i, : n_ops[i]].copy() for i in range(n)]
+
+    def edit_distance_batch(self, queries, targets, ks=None):
+        n = len(queries)
+        qb, qs, ql = self._pairs(queries)
+        tb, tstr, tl = self._pairs(targets)
+        dist = np.zeros(n, np.int32)
+        kk = None if ks is None else np.ascontiguousarray(ks, dtype=np.int32)
+        self._check(self.L.as_edit_distance_batch(self.h, qb.ctypes.data, qs, ql.ctypes.data, tb.ctypes.data, tstr,
+                                                  tl.ctypes.data, n, _ptr(kk), dist.ctypes.data), "as_edit_distance_batch")
+        return dist

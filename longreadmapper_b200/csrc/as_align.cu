@@ -1,0 +1,344 @@
+/*
+ * as_align.cu -- PART 2 and PART 3 of the per-read loop and the aligner behind cigar_align:
+ *   locus/strand   seq_lookup alnmain.c:151-176, _rev_comp_in_place alnmain.c:27-60, alnmain.c:425-438
+ *   GACT           cigar_align mutils.c:94-105 -> simple_gact (un-vendored lisanhu/GACT; spec: DESIGN.md)
+ *   result fill    alnmain.c:458-477
+ *
+ * GACT kernel: one warp per read, tiles of the read processed in sequence (each tile's anchor is where the
+ * previous traceback stopped).  Inside a tile lane L owns R = T/32 consecutive query rows and sweeps the
+ * target columns on a skewed anti-diagonal schedule (lane L is at column s-L in step s): the R cell values
+ * of the previous column live in registers, the strip boundary moves between lanes with one __shfl_up_sync
+ * per step, and 2-bit traceback codes (the column's op codes, packed R per word) are staged in shared
+ * memory, laid out [lane][column] so that a step's 32 stores hit 32 different banks.
+ */
+#include "as_common.cuh"
+
+/* ---------------------------------------------------------------------------------------------- */
+/* PART 2: locus lookup + strand fix                                                               */
+/* ---------------------------------------------------------------------------------------------- */
+__device__ __forceinline__ uint32_t comp_ascii(uint32_t c) {             /* alnmain.c:31-51 */
+    switch (c) {
+    case 'A': case 'a': return 'T';
+    case 'C': case 'c': return 'G';
+    case 'G': case 'g': return 'C';
+    case 'T': case 't': return 'A';
+    default: return 'N';
+    }
+}
+
+#define AS_TOFF_NONE 0xFFFFFFFFFFFFFFFFULL
+
+__global__ void __launch_bounds__(256) k_locus(DevIndex ix, char *__restrict__ ascii, size_t stride,
+                                               const uint32_t *__restrict__ lens, size_t n, uint32_t *__restrict__ pack,
+                                               size_t wstride, const VoteOut *__restrict__ vote,
+                                               as_result *__restrict__ res, uint64_t *__restrict__ toff) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint64_t warp0 = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
+    const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+    for (uint64_t r = warp0; r < n; r += nwarps) {
+        const VoteOut v = vote[r];
+        const uint32_t len = lens[r];
+        const uint64_t loc = v.best_key;
+        /* seq_lookup: the entries tile .cat, so only the last one starting at or before loc can match */
+        int lo = 0, hi = ix.mta_len;     /* first entry with offset > loc */
+        while (lo < hi) {
+            int mid = (lo + hi) >> 1;
+            if (ix.mta[mid].offset <= loc) lo = mid + 1; else hi = mid;
+        }
+        int seq_id = -1, strand = 0;
+        uint64_t off = 0, fwd = 0;
+        if (lo > 0 && v.phases >= 0 && loc + len >= loc) {               /* u64 wrap of loc+len: reference UB, unmapped here */
+            const int i = lo - 1;
+            const uint64_t start = ix.mta[i].offset, sl = ix.mta[i].seq_len, end = start + 2 * sl;
+            if (loc >= start && loc + len <= start + sl) {               /* alnmain.c:158-164 */
+                seq_id = i; strand = 0; fwd = loc; off = loc - start;
+            } else if (loc >= start + sl && loc + len <= end) {          /* alnmain.c:165-172 */
+                seq_id = i; strand = 1; off = end - loc - len; fwd = off + start;
+            }
+        }
+        if (lane == 0) {
+            as_result o;
+            o.loc = loc;
+            o.off = off;
+            o.seq_id = seq_id;
+            o.strand = strand;
+            o.flag = seq_id < 0 ? 4 : (strand ? 16 : 0);                 /* alnmain.c:466-474; GACT may still fail it */
+            o.mapq = seq_id < 0 ? 0 : 255;
+            o.ed = -1;
+            o.valid = seq_id >= 0;
+            o.n_cigar_op = 0;
+            o.myers = -2;
+            o.phases = v.phases;
+            o.from_outer = v.from_outer;
+            res[r] = o;
+            toff[r] = seq_id < 0 ? AS_TOFF_NONE : fwd;
+        }
+        if (strand == 1) {                                               /* alnmain.c:433-438 */
+            uint8_t *s = (uint8_t *)ascii + r * stride;
+            const uint32_t half = len >> 1;
+            for (uint32_t i = lane; i < half; i += 32) {
+                uint32_t a = s[i], b = s[len - 1 - i];
+                s[i] = (uint8_t)comp_ascii(b);
+                s[len - 1 - i] = (uint8_t)comp_ascii(a);
+            }
+            if ((len & 1u) && lane == 0) s[half] = (uint8_t)comp_ascii(s[half]);
+            __syncwarp();
+            uint32_t *pw = pack + r * wstride;
+            const uint32_t nw = (len + 15) >> 4;
+            for (uint32_t w = lane; w < nw; w += 32) {
+                uint32_t b0 = w << 4, lim = len - b0 < 16 ? len - b0 : 16, val = 0;
+                for (uint32_t t = 0; t < lim; t++) val |= as_base_code(s[b0 + t]) << (2 * t);
+                pw[w] = val;
+            }
+        }
+    }
+}
+
+int as_launch_locus(as_gpu *h, char *d_ascii, size_t stride, const uint32_t *d_lens, size_t n,
+                    uint32_t *d_pack, size_t wstride, const VoteOut *d_vote, as_result *d_res, uint64_t *d_toff) {
+    if (n == 0) return AS_OK;
+    uint64_t blocks = (n + 7) / 8, cap = (uint64_t)h->sm_count * 8;
+    k_locus<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(h->ix, d_ascii, stride, d_lens, n, d_pack, wstride,
+                                                                          d_vote, d_res, d_toff);
+    h->launches++;
+    AS_CUDA(cudaGetLastError());
+    return AS_OK;
+}
+
+/* ---------------------------------------------------------------------------------------------- */
+/* GACT                                                                                            */
+/* ---------------------------------------------------------------------------------------------- */
+struct GactArgs {
+    const uint32_t *qpack;
+    size_t q_wstride;
+    const uint32_t *qlens;
+    const uint32_t *tbase;
+    const uint64_t *toff;        /* per read base offset into tbase, AS_TOFF_NONE = skip */
+    const uint32_t *tlens;       /* NULL: tlen = qlen (alnmain.c:440-446) */
+    size_t n;
+    int T, O;
+    int TS;                      /* columns kept per lane in shared memory: even, >= min(T, longest target) */
+    int TQ;                      /* min(T, longest query) */
+    uint8_t *ops;
+    size_t ops_stride;
+    int32_t *n_ops, *score;      /* pair mode outputs (may be NULL) */
+    as_result *res;              /* map mode output (may be NULL) */
+    unsigned int *work_counter;
+    unsigned long long *stats;
+};
+
+template <int R, typename PT>
+__global__ void __launch_bounds__(32) k_gact(GactArgs a) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int T = a.T, inner = a.T - a.O, TS = a.TS;
+    PT *ptr = reinterpret_cast<PT *>(smem);                    /* [32][TS] */
+    uint8_t *ts = smem + (size_t)32 * TS * sizeof(PT);         /* [TS] target codes of the tile */
+    uint8_t *tmp = ts + TS;                                    /* [TS+TQ] committed ops, reversed */
+    const int L = threadIdx.x;
+    PT *myptr = ptr + (size_t)L * TS;
+    unsigned long long st_cells = 0;
+
+    for (;;) {
+        uint32_t read = 0;
+        if (L == 0) read = atomicAdd(a.work_counter, 1u);
+        read = __shfl_sync(0xFFFFFFFFu, read, 0);
+        if (read >= a.n) break;
+        const int qlen = (int)a.qlens[read];
+        const int tlen = a.tlens ? (int)a.tlens[read] : qlen;
+        const uint64_t toff = a.toff ? a.toff[read] : 0;
+        uint8_t *ops = a.ops ? a.ops + (size_t)read * a.ops_stride : nullptr;
+        int n = 0, score = 0;
+        if (toff == AS_TOFF_NONE) {
+            /* seq_lookup failed: flag 4 was set by PART 2; reference behaviour is undefined (alnmain.c:409,430-446) */
+            continue;
+        }
+        const uint32_t *qp = a.qpack + (size_t)read * a.q_wstride;
+        int i0 = 0, j0 = 0;
+        while (i0 < qlen || j0 < tlen) {
+            const int Tq = qlen - i0 < T ? qlen - i0 : T;
+            const int Tt = tlen - j0 < T ? tlen - j0 : T;
+            const bool q_done = (i0 + Tq == qlen), t_done = (j0 + Tt == tlen);
+            const bool last = q_done && t_done;
+            /* stage the target codes of the tile */
+            for (int x = L; x < Tt; x += 32) ts[x] = (uint8_t)as_base_at(a.tbase, toff + (uint64_t)(j0 + x));
+            /* this lane's query rows */
+            int qv[R], h[R];
+            {
+                const int row0 = L * R;
+                uint32_t w = row0 < Tq ? as_bases16(qp, (uint64_t)(i0 + row0)) : 0u;
+#pragma unroll
+                for (int r = 0; r < R; r++) {
+                    qv[r] = (row0 + r < Tq) ? (int)((w >> (2 * r)) & 3u) : 4;
+                    h[r] = row0 + r + 1;                         /* D[i][0] = i */
+                }
+            }
+            __syncwarp();
+            int prev_recv = L * R;                               /* D[L*R][0] */
+            int rowmin_key = (Tq << 12) | (Tt << 1);             /* bottom-row candidates, column 0 first */
+            const int nsteps = Tt + 31;
+            for (int s = 1; s <= nsteps; s++) {
+                int recv = __shfl_up_sync(0xFFFFFFFFu, h[R - 1], 1);
+                const int j = s - L;
+                if (j >= 1 && j <= Tt) {
+                    const int tc = ts[j - 1];
+                    int up = L == 0 ? j : recv;
+                    int diag = L == 0 ? j - 1 : prev_recv;
+                    prev_recv = recv;
+                    uint32_t word = 0;
+#pragma unroll
+                    for (int r = 0; r < R; r++) {
+                        const int left = h[r];
+                        const int neq = qv[r] != tc;
+                        const int d = diag + neq;
+                        const int u1 = up + 1, l1 = left + 1;
+                        const int m = min(u1, l1);
+                        const int best = min(d, m);
+                        /* op code of the step taken into this cell: 0 '=', 3 'X', 1 up ('I'), 2 left ('D') */
+                        const uint32_t code = d <= m ? (neq ? 3u : 0u) : (u1 <= l1 ? 1u : 2u);
+                        word |= code << (2 * r);
+                        diag = left;
+                        up = best;
+                        h[r] = best;
+                    }
+                    myptr[j - 1] = (PT)word;
+                    const int key = (h[R - 1] << 12) | ((Tt - j) << 1);
+                    rowmin_key = min(rowmin_key, key);
+                }
+            }
+            __syncwarp();
+            st_cells += (unsigned long long)Tq * (unsigned long long)Tt;
+            /* ---- end cell ---- */
+            int ei = Tq, ej = Tt;
+            if (!last) {
+                int best = 0x7FFFFFFF;
+                if (!q_done) best = __shfl_sync(0xFFFFFFFFu, rowmin_key, 31);   /* Tq == T == 32R: row T is lane 31's last */
+                if (!t_done) {
+                    int ck = 0x7FFFFFFF;
+#pragma unroll
+                    for (int r = 0; r < R; r++) {
+                        const int i = L * R + r + 1;
+                        if (i <= Tq) ck = min(ck, (h[r] << 12) | ((Tq - i) << 1) | 1);
+                    }
+                    if (L == 0) ck = min(ck, (Tt << 12) | (Tq << 1) | 1);       /* i = 0: D[0][Tt] = Tt */
+#pragma unroll
+                    for (int d = 16; d >= 1; d >>= 1) ck = min(ck, __shfl_xor_sync(0xFFFFFFFFu, ck, d));
+                    best = min(best, ck);
+                }
+                const int dist = (best >> 1) & 0x7FF;
+                if (best & 1) { ei = Tq - dist; ej = Tt; } else { ei = Tq; ej = Tt - dist; }
+            }
+            /* ---- traceback (uniform across the warp; lane 0 records) ---- */
+            int ci = ei, cj = ej, m = 0, ai = ei, aj = ej;
+            bool anchored = false;
+            while (ci > 0 || cj > 0) {
+                uint32_t op;
+                if (ci == 0) op = 2;
+                else if (cj == 0) op = 1;
+                else {
+                    const int rl = (ci - 1) / R, rr = (ci - 1) - rl * R;
+                    op = ((uint32_t)ptr[(size_t)rl * TS + (cj - 1)] >> (2 * rr)) & 3u;
+                }
+                const int si = ci - (op != 2u), sj = cj - (op != 1u);
+                if (last || (si < inner && sj < inner)) {
+                    if (!anchored) { ai = ci; aj = cj; anchored = true; }
+                    if (L == 0) tmp[m] = (uint8_t)op;
+                    m++;
+                    score += (op != 0u);
+                }
+                ci = si;
+                cj = sj;
+            }
+            __syncwarp();
+            if (m == 0 && !last) { score = -1; break; }
+            if (ops) {
+                for (int x = L; x < m; x += 32)
+                    if ((size_t)(n + x) < a.ops_stride) ops[n + x] = tmp[m - 1 - x];
+            }
+            n += m;
+            i0 += ai;
+            j0 += aj;
+            __syncwarp();
+            if (last) break;
+        }
+        if (L == 0) {
+            if (a.res) {                                        /* PART 3, alnmain.c:458-477 */
+                as_result *o = a.res + read;
+                o->ed = score;
+                o->n_cigar_op = n;
+                if (score == -1) { o->valid = 0; o->flag = 4; o->mapq = 0; }
+            }
+            if (a.n_ops) a.n_ops[read] = n;
+            if (a.score) a.score[read] = score;
+        }
+    }
+    if (L == 0 && st_cells) atomicAdd(a.stats + 5, st_cells);
+}
+
+template <int R>
+static int launch_gact_r(as_gpu *h, const GactArgs &a, size_t n) {
+    int rc;
+    uint64_t cap = (uint64_t)h->sm_count * 32;
+    unsigned grid = (unsigned)(n < cap ? n : cap);
+    if constexpr (R <= 8) {
+        size_t smem = (size_t)32 * a.TS * 2 + 2 * (size_t)a.TS + a.TQ + 16;
+        rc = cudaFuncSetAttribute(k_gact<R, uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (rc != cudaSuccess) { as_set_error("cudaFuncSetAttribute(gact): %s", cudaGetErrorString((cudaError_t)rc)); return AS_ECUDA; }
+        k_gact<R, uint16_t><<<grid, 32, smem, h->stream>>>(a);
+    } else {
+        size_t smem = (size_t)32 * a.TS * 4 + 2 * (size_t)a.TS + a.TQ + 16;
+        rc = cudaFuncSetAttribute(k_gact<R, uint32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (rc != cudaSuccess) { as_set_error("cudaFuncSetAttribute(gact): %s", cudaGetErrorString((cudaError_t)rc)); return AS_ECUDA; }
+        k_gact<R, uint32_t><<<grid, 32, smem, h->stream>>>(a);
+    }
+    h->launches++;
+    AS_CUDA(cudaGetLastError());
+    return AS_OK;
+}
+
+int as_launch_gact(as_gpu *h, const as_params *p, const uint32_t *d_qpack, size_t q_wstride, const uint32_t *d_qlens,
+                   const uint32_t *d_tbase, const uint64_t *d_toff, const uint32_t *d_tlens, size_t n,
+                   uint32_t max_qlen, uint32_t max_tlen, uint8_t *d_ops, size_t ops_stride, int32_t *d_nops,
+                   int32_t *d_score, as_result *d_res) {
+    if (n == 0) return AS_OK;
+    const int T = p->gact_T, O = p->gact_O;
+    if (T < 32 || T > 512 || (T & 31) || O < 0 || O >= T) {
+        as_set_error("GACT: tile size T=%d must be a multiple of 32 in [32,512] and 0 <= O=%d < T", T, O);
+        return AS_EINVAL;
+    }
+    GactArgs a;
+    a.qpack = d_qpack; a.q_wstride = q_wstride; a.qlens = d_qlens;
+    a.tbase = d_tbase; a.toff = d_toff; a.tlens = d_tlens;
+    a.n = n; a.T = T; a.O = O;
+    a.TS = (int)(max_tlen < (uint32_t)T ? max_tlen : (uint32_t)T);
+    a.TS = (a.TS + 2) & ~1;      /* even: lane stride TS-1 is odd, so a step's stores hit distinct banks */
+    a.TQ = (int)(max_qlen < (uint32_t)T ? max_qlen : (uint32_t)T);
+    a.ops = d_ops; a.ops_stride = ops_stride; a.n_ops = d_nops; a.score = d_score; a.res = d_res;
+    AS_TRY(as_scratch(h, &h->misc[5], 64));
+    AS_CUDA(cudaMemsetAsync(h->misc[5].p, 0, 64, h->stream));
+    a.work_counter = (unsigned int *)h->misc[5].p;
+    a.stats = h->d_stats;
+    /* rows per lane: the whole tile when some query reaches T rows, else just enough for the longest query */
+    int rows = (int)(max_qlen < (uint32_t)T ? max_qlen : (uint32_t)T);
+    int R = (rows + 31) / 32;
+    if (max_qlen >= (uint32_t)T) R = T / 32;
+    if (R < 1) R = 1;
+    /* a shorter tile buffer for short queries would not change results: T only bounds Tq/Tt */
+    switch (R) {
+    case 1: return launch_gact_r<1>(h, a, n);
+    case 2: return launch_gact_r<2>(h, a, n);
+    case 3: return launch_gact_r<3>(h, a, n);
+    case 4: return launch_gact_r<4>(h, a, n);
+    case 5: return launch_gact_r<5>(h, a, n);
+    case 6: return launch_gact_r<6>(h, a, n);
+    case 7: return launch_gact_r<7>(h, a, n);
+    case 8: return launch_gact_r<8>(h, a, n);
+    case 9: return launch_gact_r<9>(h, a, n);
+    case 10: return launch_gact_r<10>(h, a, n);
+    case 11: return launch_gact_r<11>(h, a, n);
+    case 12: return launch_gact_r<12>(h, a, n);
+    case 13: return launch_gact_r<13>(h, a, n);
+    case 14: return launch_gact_r<14>(h, a, n);
+    case 15: return launch_gact_r<15>(h, a, n);
+    default: return launch_gact_r<16>(h, a, n);
+    }
+}

@@ -1,0 +1,324 @@
+/*
+ * as_api.cu -- the batched entry points of include/accseq_b200.h: as_map_batch replaces the loop nest
+ * alnmain.c:330-479 for one batch; the *_batch primitives expose single stages for parity tests.
+ */
+#include "as_common.cuh"
+
+extern "C" void as_params_default(as_params *p) {
+    if (!p) return;
+    p->seed_len = 20;      /* alnmain.c:577-580 */
+    p->thres = 300;
+    p->gact_T = 320;       /* Darwin GACT operating point (README.md:5; DESIGN.md "GACT spec") */
+    p->gact_O = 120;
+    p->flags = 0;
+}
+
+static size_t pack_wstride(uint32_t max_len) { return ((size_t)max_len + 15) / 16 + 3; }
+
+/* all device-side stages of one batch, asynchronous on h->stream; events 1..5 bracket the stages */
+static int run_stages(as_gpu *h, const as_params *p, char *d_reads, size_t stride, const uint32_t *d_lens, size_t n,
+                      uint32_t max_len, as_result *d_res, uint8_t *d_store, size_t store_stride, bool stop_after_vote,
+                      VoteOut **vote_out) {
+    const size_t ws = pack_wstride(max_len);
+    AS_TRY(as_scratch(h, &h->qpack, n * ws * sizeof(uint32_t)));
+    AS_TRY(as_scratch(h, &h->vote, n * sizeof(VoteOut)));
+    AS_TRY(as_scratch(h, &h->toff, n * sizeof(uint64_t)));
+    uint32_t *d_pack = (uint32_t *)h->qpack.p;
+    VoteOut *d_vote = (VoteOut *)h->vote.p;
+    uint64_t *d_toff = (uint64_t *)h->toff.p;
+    if (vote_out) *vote_out = d_vote;
+    AS_CUDA(cudaEventRecord(h->ev[1], h->stream));
+    AS_TRY(as_launch_pack(h, d_reads, stride, d_lens, n, d_pack, ws));
+    AS_TRY(as_launch_vote(h, p, d_pack, ws, d_lens, n, max_len, d_vote));
+    AS_CUDA(cudaEventRecord(h->ev[2], h->stream));
+    if (stop_after_vote) return AS_OK;
+    AS_TRY(as_launch_locus(h, d_reads, stride, d_lens, n, d_pack, ws, d_vote, d_res, d_toff));
+    AS_CUDA(cudaEventRecord(h->ev[3], h->stream));
+    if (!(p->flags & AS_F_NO_ALIGN))
+        AS_TRY(as_launch_gact(h, p, d_pack, ws, d_lens, h->ix.text2, d_toff, nullptr, n, max_len, max_len, d_store,
+                              store_stride, nullptr, nullptr, d_res));
+    AS_CUDA(cudaEventRecord(h->ev[4], h->stream));
+    if ((p->flags & AS_F_MYERS) && !(p->flags & AS_F_NO_ALIGN))
+        AS_TRY(as_launch_myers(h, d_pack, ws, d_lens, h->ix.text2, d_toff, nullptr, n, max_len, nullptr, nullptr, d_res));
+    AS_CUDA(cudaEventRecord(h->ev[5], h->stream));
+    return AS_OK;
+}
+
+/* per-batch counters that are cheap to take from the results on the device */
+__global__ void __launch_bounds__(256) k_count_results(const as_result *__restrict__ res, size_t n,
+                                                       unsigned long long *__restrict__ stats) {
+    unsigned long long valid = 0, f4 = 0, f16 = 0, sed = 0;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const as_result r = res[i];
+        valid += r.valid != 0;
+        f4 += (r.flag & 4) != 0;
+        f16 += (r.flag & 16) != 0;
+        if (r.valid && r.ed > 0) sed += (unsigned long long)r.ed;
+    }
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) {
+        valid += __shfl_xor_sync(0xFFFFFFFFu, valid, d);
+        f4 += __shfl_xor_sync(0xFFFFFFFFu, f4, d);
+        f16 += __shfl_xor_sync(0xFFFFFFFFu, f16, d);
+        sed += __shfl_xor_sync(0xFFFFFFFFu, sed, d);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (valid) atomicAdd(stats + 1, valid);
+        if (f4) atomicAdd(stats + 2, f4);
+        if (f16) atomicAdd(stats + 3, f16);
+        if (sed) atomicAdd(stats + 4, sed);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(stats + 0, (unsigned long long)n);
+}
+
+static int count_results(as_gpu *h, const as_result *d_res, size_t n) {
+    uint64_t blocks = (n + 255) / 256, cap = (uint64_t)h->sm_count * 4;
+    k_count_results<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(d_res, n, h->d_stats);
+    h->launches++;
+    AS_CUDA(cudaGetLastError());
+    return AS_OK;
+}
+
+static int check_map_args(as_gpu *h, const as_params *p, const void *reads, size_t stride, const uint32_t *lens,
+                          const as_result *results) {
+    if (!h || !p || !reads || !lens || !results || stride == 0) {
+        as_set_error("as_map_batch: NULL argument");
+        return AS_EINVAL;
+    }
+    return AS_OK;
+}
+
+static int finish_timing(as_gpu *h) {
+    /* ms: [0] PART 1, [1] PART 2, [2] GACT, [3] Myers, [4] result fill (fused, 0), [5] H2D, [6] D2H, [7] total */
+    float v;
+    for (int i = 0; i < 8; i++) h->last_ms[i] = 0.f;
+    if (cudaEventElapsedTime(&v, h->ev[0], h->ev[1]) == cudaSuccess) h->last_ms[5] = v;
+    if (cudaEventElapsedTime(&v, h->ev[1], h->ev[2]) == cudaSuccess) h->last_ms[0] = v;
+    if (cudaEventElapsedTime(&v, h->ev[2], h->ev[3]) == cudaSuccess) h->last_ms[1] = v;
+    if (cudaEventElapsedTime(&v, h->ev[3], h->ev[4]) == cudaSuccess) h->last_ms[2] = v;
+    if (cudaEventElapsedTime(&v, h->ev[4], h->ev[5]) == cudaSuccess) h->last_ms[3] = v;
+    if (cudaEventElapsedTime(&v, h->ev[5], h->ev[6]) == cudaSuccess) h->last_ms[6] = v;
+    if (cudaEventElapsedTime(&v, h->ev[0], h->ev[6]) == cudaSuccess) h->last_ms[7] = v;
+    cudaGetLastError();
+    return AS_OK;
+}
+
+extern "C" int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t stride, const uint32_t *lens, size_t n,
+                            as_result *results, uint8_t *store_mem, size_t store_stride) {
+    AS_TRY(check_map_args(h, p, reads, stride, lens, results));
+    if (n == 0) return AS_OK;
+    AS_CUDA(cudaSetDevice(h->device));
+    uint32_t max_len = 0;
+    for (size_t i = 0; i < n; i++) {
+        if (lens[i] > max_len) max_len = lens[i];
+    }
+    if ((size_t)max_len + 1 > stride) {
+        as_set_error("as_map_batch: a read of %u bases does not fit stride %zu", max_len, stride);
+        return AS_EINVAL;
+    }
+    const bool want_ops = store_mem != nullptr && !(p->flags & AS_F_NO_ALIGN);
+    if (want_ops && store_stride < 2 * (size_t)max_len) {
+        as_set_error("as_map_batch: store_stride %zu < 2*max_read_len (alnmain.c:316-320)", store_stride);
+        return AS_EINVAL;
+    }
+    AS_TRY(as_scratch(h, &h->reads, n * stride));
+    AS_TRY(as_scratch(h, &h->lens, n * sizeof(uint32_t)));
+    AS_TRY(as_scratch(h, &h->results, n * sizeof(as_result)));
+    if (want_ops) AS_TRY(as_scratch(h, &h->store, n * store_stride));
+    char *d_reads = (char *)h->reads.p;
+    uint32_t *d_lens = (uint32_t *)h->lens.p;
+    as_result *d_res = (as_result *)h->results.p;
+    uint8_t *d_store = want_ops ? (uint8_t *)h->store.p : nullptr;
+
+    AS_CUDA(cudaEventRecord(h->ev[0], h->stream));
+    AS_CUDA(cudaMemcpyAsync(d_reads, reads, n * stride, cudaMemcpyHostToDevice, h->stream));
+    AS_CUDA(cudaMemcpyAsync(d_lens, lens, n * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+    AS_TRY(run_stages(h, p, d_reads, stride, d_lens, n, max_len, d_res, d_store, store_stride, false, nullptr));
+    AS_TRY(count_results(h, d_res, n));
+    AS_CUDA(cudaMemcpyAsync(results, d_res, n * sizeof(as_result), cudaMemcpyDeviceToHost, h->stream));
+    if (want_ops) AS_CUDA(cudaMemcpyAsync(store_mem, d_store, n * store_stride, cudaMemcpyDeviceToHost, h->stream));
+    /* strand-1 reads were reverse-complemented in place (alnmain.c:433-438; the OpenACC copy(reads_mem) :421) */
+    AS_CUDA(cudaMemcpyAsync(reads, d_reads, n * stride, cudaMemcpyDeviceToHost, h->stream));
+    AS_CUDA(cudaEventRecord(h->ev[6], h->stream));
+    AS_CUDA(cudaStreamSynchronize(h->stream));
+    return finish_timing(h);
+}
+
+extern "C" int as_map_batch_device(as_gpu *h, const as_params *p, char *d_reads, size_t stride, const uint32_t *d_lens,
+                                   size_t n, uint32_t max_len, as_result *d_results, uint8_t *d_store, size_t store_stride) {
+    AS_TRY(check_map_args(h, p, d_reads, stride, d_lens, d_results));
+    if (n == 0) return AS_OK;
+    AS_CUDA(cudaSetDevice(h->device));
+    if ((size_t)max_len + 1 > stride) return AS_EINVAL;
+    if (d_store && !(p->flags & AS_F_NO_ALIGN) && store_stride < 2 * (size_t)max_len) return AS_EINVAL;
+    AS_CUDA(cudaEventRecord(h->ev[0], h->stream));
+    AS_TRY(run_stages(h, p, d_reads, stride, d_lens, n, max_len, d_results, d_store, store_stride, false, nullptr));
+    AS_TRY(count_results(h, d_results, n));
+    AS_CUDA(cudaEventRecord(h->ev[6], h->stream));
+    return AS_OK;                     /* asynchronous: as_gpu_sync() or the caller's stream sync completes it */
+}
+
+extern "C" int as_gpu_sync(as_gpu *h) {
+    if (!h) return AS_EINVAL;
+    AS_CUDA(cudaSetDevice(h->device));
+    AS_CUDA(cudaStreamSynchronize(h->stream));
+    return AS_OK;
+}
+
+extern "C" int as_gpu_last_timing(as_gpu *h, float ms[8]) {
+    if (!h || !ms) return AS_EINVAL;
+    AS_CUDA(cudaSetDevice(h->device));
+    AS_CUDA(cudaStreamSynchronize(h->stream));
+    finish_timing(h);
+    for (int i = 0; i < 8; i++) ms[i] = h->last_ms[i];
+    return AS_OK;
+}
+
+extern "C" int as_gpu_stats(as_gpu *h, as_stats *out) {
+    if (!h || !out) return AS_EINVAL;
+    AS_CUDA(cudaSetDevice(h->device));
+    AS_CUDA(cudaStreamSynchronize(h->stream));
+    unsigned long long v[10];
+    AS_CUDA(cudaMemcpy(v, h->d_stats, sizeof v, cudaMemcpyDeviceToHost));
+    out->total = v[0]; out->valid = v[1]; out->n_flag4 = v[2]; out->n_flag16 = v[3]; out->sum_ed = v[4];
+    out->dp_cells = v[5]; out->seeds = v[6]; out->sa_hits = v[7]; out->bs_steps = v[8]; out->overflow_reads = v[9];
+    return AS_OK;
+}
+
+extern "C" int as_gpu_stats_reset(as_gpu *h) {
+    if (!h) return AS_EINVAL;
+    AS_CUDA(cudaSetDevice(h->device));
+    AS_CUDA(cudaMemsetAsync(h->d_stats, 0, 16 * sizeof(unsigned long long), h->stream));
+    return AS_OK;
+}
+
+extern "C" uint64_t as_gpu_launch_count(as_gpu *h) { return h ? h->launches : 0; }
+
+/* ---------------------------------------------------------------------------------------------- */
+/* PART 1 only                                                                                     */
+/* ---------------------------------------------------------------------------------------------- */
+extern "C" int as_vote_batch(as_gpu *h, const as_params *p, const char *reads, size_t stride, const uint32_t *lens,
+                             size_t n, uint64_t *best_key, uint64_t *best_val, int32_t *phases, int32_t *from_outer) {
+    if (!h || !p || !reads || !lens || stride == 0) return AS_EINVAL;
+    if (n == 0) return AS_OK;
+    AS_CUDA(cudaSetDevice(h->device));
+    uint32_t max_len = 0;
+    for (size_t i = 0; i < n; i++)
+        if (lens[i] > max_len) max_len = lens[i];
+    if ((size_t)max_len + 1 > stride) return AS_EINVAL;
+    AS_TRY(as_scratch(h, &h->reads, n * stride));
+    AS_TRY(as_scratch(h, &h->lens, n * sizeof(uint32_t)));
+    AS_CUDA(cudaMemcpyAsync(h->reads.p, reads, n * stride, cudaMemcpyHostToDevice, h->stream));
+    AS_CUDA(cudaMemcpyAsync(h->lens.p, lens, n * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+    VoteOut *d_vote = nullptr;
+    AS_TRY(run_stages(h, p, (char *)h->reads.p, stride, (const uint32_t *)h->lens.p, n, max_len, nullptr, nullptr, 0, true, &d_vote));
+    AS_TRY(as_pinned(h, n * sizeof(VoteOut)));
+    AS_CUDA(cudaMemcpyAsync(h->h_pin, d_vote, n * sizeof(VoteOut), cudaMemcpyDeviceToHost, h->stream));
+    AS_CUDA(cudaStreamSynchronize(h->stream));
+    const VoteOut *v = (const VoteOut *)h->h_pin;
+    for (size_t i = 0; i < n; i++) {
+        if (best_key) best_key[i] = v[i].best_key;
+        if (best_val) best_val[i] = v[i].best_val;
+        if (phases) phases[i] = v[i].phases;
+        if (from_outer) from_outer[i] = v[i].from_outer;
+    }
+    return AS_OK;
+}
+
+/* ---------------------------------------------------------------------------------------------- */
+/* aligner on explicit (query, target) pairs                                                       */
+/* ---------------------------------------------------------------------------------------------- */
+static int upload_pairs(as_gpu *h, const char *q, size_t q_stride, const uint32_t *qlens, const char *t, size_t t_stride,
+                        const uint32_t *tlens, size_t n, uint32_t *max_q, uint32_t *max_t, size_t *qws, size_t *tws) {
+    uint32_t mq = 0, mt = 0;
+    for (size_t i = 0; i < n; i++) {
+        if (qlens[i] > mq) mq = qlens[i];
+        if (tlens[i] > mt) mt = tlens[i];
+    }
+    if (mq > q_stride || mt > t_stride) {
+        as_set_error("pair batch: a sequence is longer than its stride");
+        return AS_EINVAL;
+    }
+    *max_q = mq;
+    *max_t = mt;
+    *qws = pack_wstride(mq);
+    *tws = pack_wstride(mt);
+    AS_TRY(as_scratch(h, &h->misc[0], n * q_stride + 16));
+    AS_TRY(as_scratch(h, &h->misc[1], n * t_stride + 16));
+    AS_TRY(as_scratch(h, &h->misc[2], 2 * n * sizeof(uint32_t)));
+    AS_TRY(as_scratch(h, &h->qpack, n * *qws * sizeof(uint32_t)));
+    AS_TRY(as_scratch(h, &h->tpack, n * *tws * sizeof(uint32_t)));
+    AS_CUDA(cudaMemcpyAsync(h->misc[0].p, q, n * q_stride, cudaMemcpyHostToDevice, h->stream));
+    AS_CUDA(cudaMemcpyAsync(h->misc[1].p, t, n * t_stride, cudaMemcpyHostToDevice, h->stream));
+    uint32_t *d_l = (uint32_t *)h->misc[2].p;
+    AS_CUDA(cudaMemcpyAsync(d_l, qlens, n * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+    AS_CUDA(cudaMemcpyAsync(d_l + n, tlens, n * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+    AS_TRY(as_launch_pack(h, (const char *)h->misc[0].p, q_stride, d_l, n, (uint32_t *)h->qpack.p, *qws));
+    AS_TRY(as_launch_pack(h, (const char *)h->misc[1].p, t_stride, d_l + n, n, (uint32_t *)h->tpack.p, *tws));
+    return AS_OK;
+}
+
+__global__ void k_pair_offsets(uint64_t *toff, size_t n, size_t bases_per_pair) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        toff[i] = (uint64_t)i * bases_per_pair;
+}
+
+static int pair_offsets(as_gpu *h, size_t n, size_t tws) {
+    AS_TRY(as_scratch(h, &h->toff, n * sizeof(uint64_t)));
+    uint64_t blocks = (n + 255) / 256;
+    k_pair_offsets<<<(unsigned)(blocks < 1024 ? blocks : 1024), 256, 0, h->stream>>>((uint64_t *)h->toff.p, n, tws * 16);
+    h->launches++;
+    AS_CUDA(cudaGetLastError());
+    return AS_OK;
+}
+
+extern "C" int as_cigar_align_batch(as_gpu *h, const as_params *p, const char *q, size_t q_stride, const uint32_t *qlens,
+                                    const char *t, size_t t_stride, const uint32_t *tlens, size_t n, uint8_t *ops,
+                                    size_t ops_stride, int32_t *n_ops, int32_t *score) {
+    if (!h || !p || !q || !t || !qlens || !tlens || !n_ops || !score) return AS_EINVAL;
+    if (n == 0) return AS_OK;
+    AS_CUDA(cudaSetDevice(h->device));
+    uint32_t mq, mt;
+    size_t qws, tws;
+    AS_TRY(upload_pairs(h, q, q_stride, qlens, t, t_stride, tlens, n, &mq, &mt, &qws, &tws));
+    if (ops && ops_stride < (size_t)mq + mt) {
+        as_set_error("as_cigar_align_batch: ops_stride %zu < max qlen + max tlen", ops_stride);
+        return AS_EINVAL;
+    }
+    AS_TRY(pair_offsets(h, n, tws));
+    AS_TRY(as_scratch(h, &h->misc[3], 2 * n * sizeof(int32_t)));
+    if (ops) AS_TRY(as_scratch(h, &h->store, n * ops_stride));
+    int32_t *d_no = (int32_t *)h->misc[3].p;
+    const uint32_t *d_l = (const uint32_t *)h->misc[2].p;
+    AS_TRY(as_launch_gact(h, p, (const uint32_t *)h->qpack.p, qws, d_l, (const uint32_t *)h->tpack.p, (const uint64_t *)h->toff.p,
+                          d_l + n, n, mq, mt, ops ? (uint8_t *)h->store.p : nullptr, ops_stride, d_no, d_no + n, nullptr));
+    AS_CUDA(cudaMemcpyAsync(n_ops, d_no, n * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    AS_CUDA(cudaMemcpyAsync(score, d_no + n, n * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    if (ops) AS_CUDA(cudaMemcpyAsync(ops, h->store.p, n * ops_stride, cudaMemcpyDeviceToHost, h->stream));
+    AS_CUDA(cudaStreamSynchronize(h->stream));
+    return AS_OK;
+}
+
+extern "C" int as_edit_distance_batch(as_gpu *h, const char *q, size_t q_stride, const uint32_t *qlens, const char *t,
+                                      size_t t_stride, const uint32_t *tlens, size_t n, const int32_t *ks, int32_t *dist) {
+    if (!h || !q || !t || !qlens || !tlens || !dist) return AS_EINVAL;
+    if (n == 0) return AS_OK;
+    AS_CUDA(cudaSetDevice(h->device));
+    uint32_t mq, mt;
+    size_t qws, tws;
+    AS_TRY(upload_pairs(h, q, q_stride, qlens, t, t_stride, tlens, n, &mq, &mt, &qws, &tws));
+    AS_TRY(pair_offsets(h, n, tws));
+    AS_TRY(as_scratch(h, &h->misc[3], 2 * n * sizeof(int32_t)));
+    int32_t *d_d = (int32_t *)h->misc[3].p;
+    int32_t *d_k = nullptr;
+    if (ks) {
+        d_k = d_d + n;
+        AS_CUDA(cudaMemcpyAsync(d_k, ks, n * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+    }
+    const uint32_t *d_l = (const uint32_t *)h->misc[2].p;
+    AS_TRY(as_launch_myers(h, (const uint32_t *)h->qpack.p, qws, d_l, (const uint32_t *)h->tpack.p, (const uint64_t *)h->toff.p,
+                           d_l + n, n, mq, d_k, d_d, nullptr));
+    AS_CUDA(cudaMemcpyAsync(dist, d_d, n * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    AS_CUDA(cudaStreamSynchronize(h->stream));
+    return AS_OK;
+}

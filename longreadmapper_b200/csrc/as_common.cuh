@@ -1,0 +1,174 @@
+/*
+ * as_common.cuh -- internal declarations shared by the translation units of libaccseq_b200.so.
+ * sm_100a only.  Nothing here is part of the public C ABI (include/accseq_b200.h).
+ */
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "accseq_b200.h"
+
+/* ------------------------------------------------------------------------------------------------
+ * HBM layout of the index (DESIGN.md "HBM layout")
+ * ---------------------------------------------------------------------------------------------- */
+
+/* One 32-byte sector per 64 BWT rows: occurrence counts at the block start (relative to the enclosing
+ * super block) and the 64 rows as two bit planes.  One occ() = one sector.  Replaces the reference's
+ * O table (4 x u64 per 32 rows) + byte-per-row BWT (fmidx.h:16-21; occ at fmidx.c:277-293). */
+struct __align__(32) FmBlock {
+    uint32_t cnt[4];   /* # of A,C,G,T in rows [sb_start, 64*blk) */
+    uint64_t lo;       /* bit r = low bit of the code of row 64*blk + r */
+    uint64_t hi;       /* bit r = high bit                                 */
+};
+#define AS_SB_SHIFT 30 /* super block = 2^30 rows; absolute counts as u64[4] per super block */
+
+struct DevIndex {
+    uint64_t N;                 /* rows = .cat length (fmi->length) */
+    uint64_t primary;           /* row whose BWT char is '$' (coded as A in the planes) */
+    uint64_t C[4];              /* dna_fmi.c['A'],['C'],['G'],['T'] */
+    const FmBlock *fm;
+    const uint64_t *super;      /* [n_super][4] */
+    const ulonglong2 *lc;       /* (k,l) per 12-mer, indexed by the LSB-first code of the k-mer */
+    int hlen;
+    const uint32_t *sa_lo;      /* low 32 bits of SA[row] */
+    const uint8_t *sa_hi;       /* bits 32..39, NULL when N <= 2^32 */
+    const uint32_t *text2;      /* .cat text, 2 bits per base, 16 bases per word, LSB first */
+    const as_mta *mta;
+    int mta_len;
+};
+
+struct ScratchBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+};
+
+struct as_gpu {
+    int device = 0;
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr;
+    DevIndex ix{};
+    /* owned device allocations of the index */
+    void *d_fm = nullptr, *d_super = nullptr, *d_lc = nullptr, *d_sa_lo = nullptr, *d_sa_hi = nullptr,
+         *d_text2 = nullptr, *d_mta = nullptr;
+    /* device scratch, grown on demand */
+    ScratchBuf reads, lens, results, store, qpack, tpack, toff, vote, counters, ovf_list, ovf_table, misc[6];
+    /* pinned staging for small D2H/H2D */
+    void *h_pin = nullptr;
+    size_t h_pin_cap = 0;
+    /* stats: device accumulators (as_stats layout, u64 x 10) */
+    unsigned long long *d_stats = nullptr;
+    cudaEvent_t ev[10]{};
+    float last_ms[8]{};
+    int sm_count = 148;
+    uint64_t launches = 0;      /* kernels launched by this handle since open */
+};
+
+/* error plumbing */
+void as_set_error(const char *fmt, ...);
+#define AS_CUDA(call)                                                                               \
+    do {                                                                                            \
+        cudaError_t e_ = (call);                                                                    \
+        if (e_ != cudaSuccess) {                                                                    \
+            as_set_error("%s:%d: %s failed: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+            return AS_ECUDA;                                                                        \
+        }                                                                                           \
+    } while (0)
+#define AS_TRY(call)              \
+    do {                          \
+        int r_ = (call);          \
+        if (r_ != AS_OK) return r_; \
+    } while (0)
+
+int as_scratch(as_gpu *h, ScratchBuf *b, size_t bytes);   /* ensure capacity (device memory) */
+int as_pinned(as_gpu *h, size_t bytes);                   /* ensure h->h_pin capacity */
+
+/* stage launchers (as_lookup.cu / as_vote.cu / as_align.cu); all asynchronous on h->stream */
+struct VoteOut {
+    uint64_t best_key, best_val;
+    int32_t phases, from_outer;
+};
+int as_launch_pack(as_gpu *h, const char *d_ascii, size_t stride, const uint32_t *d_lens, size_t n,
+                   uint32_t *d_pack, size_t wstride);
+int as_launch_vote(as_gpu *h, const as_params *p, const uint32_t *d_pack, size_t wstride, const uint32_t *d_lens,
+                   size_t n, uint32_t max_len, VoteOut *d_vote);
+int as_launch_locus(as_gpu *h, char *d_ascii, size_t stride, const uint32_t *d_lens, size_t n,
+                    uint32_t *d_pack, size_t wstride, const VoteOut *d_vote, as_result *d_res, uint64_t *d_toff);
+int as_launch_gact(as_gpu *h, const as_params *p, const uint32_t *d_qpack, size_t q_wstride, const uint32_t *d_qlens,
+                   const uint32_t *d_tbase, const uint64_t *d_toff, const uint32_t *d_tlens, size_t n,
+                   uint32_t max_qlen, uint32_t max_tlen, uint8_t *d_ops, size_t ops_stride, int32_t *d_nops,
+                   int32_t *d_score, as_result *d_res);
+int as_launch_myers(as_gpu *h, const uint32_t *d_qpack, size_t q_wstride, const uint32_t *d_qlens,
+                    const uint32_t *d_tbase, const uint64_t *d_toff, const uint32_t *d_tlens, size_t n,
+                    uint32_t max_qlen, const int32_t *d_ks, int32_t *d_dist, as_result *d_res);
+
+/* ------------------------------------------------------------------------------------------------
+ * device helpers
+ * ---------------------------------------------------------------------------------------------- */
+#ifdef __CUDACC__
+
+/* A0 C1 G2 T3 for upper or lower case ASCII (lchash.c:38-45, fmidx.c:278-282 mapper[]) */
+__device__ __forceinline__ uint32_t as_base_code(uint32_t c) { return ((c >> 1) & 3u) ^ ((c >> 2) & 1u); }
+
+__device__ __forceinline__ void as_ld_block(const FmBlock *b, uint4 &cnt, uint64_t &lo, uint64_t &hi) {
+    /* one 32-byte sector, two 16-byte read-only loads */
+    const uint4 *p = reinterpret_cast<const uint4 *>(b);
+    cnt = __ldg(p);
+    uint4 w = __ldg(p + 1);
+    lo = ((uint64_t)w.y << 32) | w.x;
+    hi = ((uint64_t)w.w << 32) | w.z;
+}
+
+/* occ(c, loc) = #{ rows r <= loc : bwt[r] == c }   (fmidx.c:277-293 _occ_access, inclusive of loc) */
+__device__ __forceinline__ uint64_t as_occ(const DevIndex &ix, uint32_t c, uint64_t loc) {
+    uint64_t blk = loc >> 6;
+    uint32_t r = (uint32_t)loc & 63u;
+    uint4 cnt;
+    uint64_t lo, hi;
+    as_ld_block(ix.fm + blk, cnt, lo, hi);
+    uint64_t m = ((c & 1u) ? lo : ~lo) & ((c & 2u) ? hi : ~hi);
+    m &= (r == 63u) ? ~0ULL : ((1ULL << (r + 1)) - 1ULL);
+    uint32_t base = c == 0 ? cnt.x : c == 1 ? cnt.y : c == 2 ? cnt.z : cnt.w;
+    uint64_t v = __ldg(ix.super + 4 * (loc >> AS_SB_SHIFT) + c) + base + (uint64_t)__popcll(m);
+    /* the '$' row is stored as code 0 */
+    if (c == 0 && (ix.primary >> 6) == blk && ((uint32_t)ix.primary & 63u) <= r) v -= 1;
+    return v;
+}
+
+/* one backward-search step for character code c (fmidx.c:300-307) */
+__device__ __forceinline__ void as_bs_step(const DevIndex &ix, uint32_t c, uint64_t &k, uint64_t &l) {
+    uint64_t ok = as_occ(ix, c, k - 1);
+    uint64_t ol = as_occ(ix, c, l);
+    /* select chain: a dynamic index into the by-value kernel parameter would force a local-memory copy */
+    const uint64_t cc = c == 0 ? ix.C[0] : c == 1 ? ix.C[1] : c == 2 ? ix.C[2] : ix.C[3];
+    k = cc + ok + 1;
+    l = cc + ol;
+}
+
+__device__ __forceinline__ uint64_t as_sa(const DevIndex &ix, uint64_t row) {
+    uint64_t v = __ldg(ix.sa_lo + row);
+    if (ix.sa_hi) v |= (uint64_t)__ldg(ix.sa_hi + row) << 32;
+    return v;
+}
+
+/* 2-bit packed sequences: 16 bases per u32, base i at bits [2(i&15), 2(i&15)+1] of word i>>4 */
+__device__ __forceinline__ uint32_t as_base_at(const uint32_t *w, uint64_t i) {
+    return (__ldg(w + (i >> 4)) >> (2u * ((uint32_t)i & 15u))) & 3u;
+}
+/* up to 16 bases starting at base offset i (needs one word of slack past the end) */
+__device__ __forceinline__ uint32_t as_bases16(const uint32_t *w, uint64_t i) {
+    uint32_t a = __ldg(w + (i >> 4)), b = __ldg(w + (i >> 4) + 1);
+    return __funnelshift_r(a, b, 2u * ((uint32_t)i & 15u));
+}
+/* 32 bases starting at base offset i as a u64 (needs two words of slack) */
+__device__ __forceinline__ uint64_t as_bases32(const uint32_t *w, uint64_t i) {
+    const uint32_t *p = w + (i >> 4);
+    uint32_t a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+    uint32_t s = 2u * ((uint32_t)i & 15u);
+    return ((uint64_t)__funnelshift_r(b, c, s) << 32) | __funnelshift_r(a, b, s);
+}
+
+#endif /* __CUDACC__ */

@@ -1,0 +1,134 @@
+/*
+ * as_lookup.cu -- read packing and the batched forms of the reference's lookup primitives:
+ *   lc_aln   lchash.c:89-104  (+ lc_access :12-16, _num_from_seq :36-49)
+ *   fmi_aln  fmidx.c:295-313  (+ _occ_access :277-293)
+ *   sa_access fmidx.c:18-33
+ * One thread per query; every lookup is a chain of dependent 32-byte sector gathers, so the kernels are
+ * sized for memory-level parallelism (many resident warps), not arithmetic.
+ */
+#include "as_common.cuh"
+
+/* ---------------------------------------------------------------------------------------------- */
+/* 2-bit packing of a read batch (refactor_reads_seq layout in, alnmain.c:87-103)                  */
+/* ---------------------------------------------------------------------------------------------- */
+__global__ void __launch_bounds__(256) k_pack_reads(const char *__restrict__ ascii, size_t stride,
+                                                    const uint32_t *__restrict__ lens, size_t n,
+                                                    uint32_t *__restrict__ pack, size_t wstride) {
+    /* one thread per output word; consecutive threads write consecutive words of a read */
+    uint64_t total = (uint64_t)n * wstride;
+    for (uint64_t g = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; g < total; g += (uint64_t)gridDim.x * blockDim.x) {
+        uint64_t r = g / wstride;
+        uint32_t w = (uint32_t)(g - r * wstride);
+        uint32_t len = lens[r];
+        uint32_t b0 = w << 4;
+        uint32_t v = 0;
+        if (b0 < len) {
+            const uint8_t *src = (const uint8_t *)ascii + r * stride + b0;
+            uint32_t lim = len - b0 < 16 ? len - b0 : 16;
+            for (uint32_t t = 0; t < lim; t++) v |= as_base_code(src[t]) << (2 * t);
+        }
+        pack[g] = v;
+    }
+}
+
+int as_launch_pack(as_gpu *h, const char *d_ascii, size_t stride, const uint32_t *d_lens, size_t n,
+                   uint32_t *d_pack, size_t wstride) {
+    if (n == 0) return AS_OK;
+    uint64_t total = (uint64_t)n * wstride;
+    uint64_t blocks = (total + 255) / 256;
+    uint64_t cap = (uint64_t)h->sm_count * 32;
+    k_pack_reads<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(d_ascii, stride, d_lens, n, d_pack, wstride);
+    h->launches++;
+    AS_CUDA(cudaGetLastError());
+    return AS_OK;
+}
+
+/* ---------------------------------------------------------------------------------------------- */
+/* batched primitives on ASCII queries                                                             */
+/* ---------------------------------------------------------------------------------------------- */
+__global__ void __launch_bounds__(128) k_lc_aln_ascii(DevIndex ix, const char *__restrict__ q, int qlen, size_t n,
+                                                      int use_table, uint64_t *__restrict__ ko, uint64_t *__restrict__ lo,
+                                                      uint64_t *__restrict__ ro) {
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint8_t *s = (const uint8_t *)q + i * (uint64_t)qlen;
+        uint64_t k = 1, l = ix.N - 1;                                   /* alnmain.c:354 */
+        int left = qlen;
+        bool absent = false;
+        if (use_table && qlen >= ix.hlen) {                             /* lchash.c:93-96 */
+            left = qlen - ix.hlen;
+            uint64_t code = 0;
+            for (int t = 0; t < ix.hlen; t++) code |= (uint64_t)as_base_code(s[left + t]) << (2 * t);
+            ulonglong2 kl = __ldg(ix.lc + code);
+            k = kl.x;
+            l = kl.y;
+            absent = (k == 0 && l == 0);                                /* lchash.c:101 */
+        } else if (use_table) {
+            left = qlen - ix.hlen;                                      /* negative: no steps (lchash.c:90,103) */
+        }
+        uint64_t r = 0;
+        if (!absent) {
+            for (int t = left - 1; t >= 0; t--) {                       /* fmidx.c:300-310 */
+                as_bs_step(ix, as_base_code(s[t]), k, l);
+                if (k > l) break;
+            }
+            r = k > l ? 0 : l - k + 1;
+        }
+        ko[i] = k;
+        lo[i] = l;
+        ro[i] = r;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_sa_access(DevIndex ix, const uint64_t *__restrict__ rows, size_t n,
+                                                   uint64_t *__restrict__ pos) {
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        uint64_t r = rows[i];
+        pos[i] = r < ix.N ? as_sa(ix, r) : 0;                           /* fmidx.c:20-23: out of scope -> 0 */
+    }
+}
+
+static int aln_batch(as_gpu *h, const char *q, int qlen, size_t n, int use_table, uint64_t *k, uint64_t *l, uint64_t *r) {
+    if (!h || !q || !k || !l || !r || qlen < 0) return AS_EINVAL;
+    if (n == 0) return AS_OK;
+    AS_CUDA(cudaSetDevice(h->device));
+    size_t qb = n * (size_t)qlen;
+    AS_TRY(as_scratch(h, &h->misc[0], qb + 16));
+    AS_TRY(as_scratch(h, &h->misc[1], n * 3 * sizeof(uint64_t)));
+    uint64_t *d_out = (uint64_t *)h->misc[1].p;
+    AS_CUDA(cudaMemcpyAsync(h->misc[0].p, q, qb, cudaMemcpyHostToDevice, h->stream));
+    uint64_t blocks = (n + 127) / 128, cap = (uint64_t)h->sm_count * 16;
+    k_lc_aln_ascii<<<(unsigned)(blocks < cap ? blocks : cap), 128, 0, h->stream>>>(h->ix, (const char *)h->misc[0].p, qlen, n,
+                                                                                 use_table, d_out, d_out + n, d_out + 2 * n);
+    h->launches++;
+    AS_CUDA(cudaGetLastError());
+    AS_CUDA(cudaMemcpyAsync(k, d_out, n * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+    AS_CUDA(cudaMemcpyAsync(l, d_out + n, n * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+    AS_CUDA(cudaMemcpyAsync(r, d_out + 2 * n, n * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+    AS_CUDA(cudaStreamSynchronize(h->stream));
+    return AS_OK;
+}
+
+extern "C" int as_lc_aln_batch(as_gpu *h, const char *seeds, int qlen, size_t n, uint64_t *k, uint64_t *l, uint64_t *r) {
+    return aln_batch(h, seeds, qlen, n, 1, k, l, r);
+}
+
+extern "C" int as_fmi_aln_batch(as_gpu *h, const char *qry, int qlen, size_t n, uint64_t *k, uint64_t *l, uint64_t *r) {
+    return aln_batch(h, qry, qlen, n, 0, k, l, r);
+}
+
+extern "C" int as_sa_access_batch(as_gpu *h, const uint64_t *rows, size_t n, uint64_t *pos) {
+    if (!h || !rows || !pos) return AS_EINVAL;
+    if (n == 0) return AS_OK;
+    AS_CUDA(cudaSetDevice(h->device));
+    AS_TRY(as_scratch(h, &h->misc[0], n * sizeof(uint64_t)));
+    AS_TRY(as_scratch(h, &h->misc[1], n * sizeof(uint64_t)));
+    AS_CUDA(cudaMemcpyAsync(h->misc[0].p, rows, n * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
+    uint64_t blocks = (n + 255) / 256, cap = (uint64_t)h->sm_count * 16;
+    k_sa_access<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(h->ix, (const uint64_t *)h->misc[0].p, n,
+                                                                              (uint64_t *)h->misc[1].p);
+    h->launches++;
+    AS_CUDA(cudaGetLastError());
+    AS_CUDA(cudaMemcpyAsync(pos, h->misc[1].p, n * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+    AS_CUDA(cudaStreamSynchronize(h->stream));
+    return AS_OK;
+}

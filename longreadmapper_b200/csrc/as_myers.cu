@@ -1,0 +1,262 @@
+/*
+ * as_myers.cu -- edlib-equivalent global (NW) edit distance, the verification path beside GACT.
+ * Semantics of edlibAlign(mode NW, task DISTANCE): edlib.cpp:141-260 -> myersCalcEditDistanceNW
+ * (edlib.cpp:694-895): unit costs, result = distance, or -1 when k >= 0 and the distance exceeds k.
+ * Arithmetic: Myers 1999 / Hyyro 2001 bit-vector column update as in calculateBlock (edlib.cpp:373-408),
+ * 64 query rows per word.
+ *
+ *   k_myers_short  one thread per pair, query <= 256 bases: all words in registers, no band.
+ *   k_myers_band   one warp per pair, Ukkonen band |i-j| <= k (edlib.cpp:730-790 keeps the same cells
+ *                  alive block-wise): word b of the band is owned by lane b%32 and runs column s-b in
+ *                  step s, so the horizontal carry of word b-1 reaches word b by one rotate-shuffle per
+ *                  step.  Cells outside the band are bounded from above by +1 deltas exactly as edlib does
+ *                  for blocks entering its band, so every distance <= k is exact.
+ */
+#include "as_common.cuh"
+
+__device__ __forceinline__ uint32_t compress_even(uint32_t x) {
+    x &= 0x55555555u;
+    x = (x | (x >> 1)) & 0x33333333u;
+    x = (x | (x >> 2)) & 0x0F0F0F0Fu;
+    x = (x | (x >> 4)) & 0x00FF00FFu;
+    x = (x | (x >> 8)) & 0x0000FFFFu;
+    return x;
+}
+
+/* bit planes of query rows [64b, 64b+64): p0 bit r = low bit of base 64b+r, p1 = high bit; vm = rows < qlen */
+__device__ __forceinline__ void query_planes(const uint32_t *qp, int b, int qlen, uint64_t &p0, uint64_t &p1, uint64_t &vm) {
+    p0 = 0;
+    p1 = 0;
+#pragma unroll
+    for (int w = 0; w < 4; w++) {
+        uint32_t x = __ldg(qp + 4 * b + w);
+        p0 |= (uint64_t)compress_even(x) << (16 * w);
+        p1 |= (uint64_t)compress_even(x >> 1) << (16 * w);
+    }
+    int valid = qlen - 64 * b;
+    vm = valid >= 64 ? ~0ULL : (valid <= 0 ? 0ULL : ((1ULL << valid) - 1ULL));
+}
+
+__device__ __forceinline__ uint64_t eq_mask(uint32_t c, uint64_t p0, uint64_t p1, uint64_t vm) {
+    return ((c & 1u) ? p0 : ~p0) & ((c & 2u) ? p1 : ~p1) & vm;
+}
+
+/* one word, one column (edlib.cpp:373-408); returns hout in {-1,0,1} taken at bit 63 */
+__device__ __forceinline__ int myers_block(uint64_t Eq, uint64_t &Pv, uint64_t &Mv, int hin) {
+    const uint64_t hneg = hin < 0 ? 1ULL : 0ULL;
+    const uint64_t Xv = Eq | Mv;
+    Eq |= hneg;
+    const uint64_t Xh = (((Eq & Pv) + Pv) ^ Pv) | Eq;
+    uint64_t Ph = Mv | ~(Xh | Pv);
+    uint64_t Mh = Pv & Xh;
+    const int hout = (int)(Ph >> 63) - (int)(Mh >> 63);
+    Ph <<= 1;
+    Mh <<= 1;
+    Mh |= hneg;
+    if (hin > 0) Ph |= 1ULL;
+    Pv = Mh | ~(Xv | Ph);
+    Mv = Ph & Xv;
+    return hout;
+}
+
+struct MyersArgs {
+    const uint32_t *qpack;
+    size_t q_wstride;
+    const uint32_t *qlens;
+    const uint32_t *tbase;
+    const uint64_t *toff;
+    const uint32_t *tlens;       /* NULL: tlen = qlen */
+    size_t n;
+    const int32_t *ks;           /* NULL with k_from_len: k = (int)(0.05*len*2) (alnmain.c:428); NULL otherwise: unbounded */
+    int k_from_len;
+    int32_t *dist;               /* may be NULL */
+    as_result *res;              /* may be NULL; writes .myers */
+    unsigned int *work_counter;
+};
+
+__device__ __forceinline__ int pair_k(const MyersArgs &a, size_t i, int qlen) {
+    if (a.ks) return a.ks[i];
+    if (a.k_from_len) return (int)(0.05 * (double)qlen * 2);
+    return -1;
+}
+
+__global__ void __launch_bounds__(128) k_myers_short(MyersArgs a) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < a.n; i += (size_t)gridDim.x * blockDim.x) {
+        const uint64_t toff = a.toff ? a.toff[i] : 0;
+        if (toff == 0xFFFFFFFFFFFFFFFFULL) continue;
+        const int qlen = (int)a.qlens[i];
+        const int tlen = a.tlens ? (int)a.tlens[i] : qlen;
+        const int k = pair_k(a, i, qlen);
+        const uint32_t *qp = a.qpack + i * a.q_wstride;
+        int d;
+        if (qlen == 0) d = tlen;
+        else if (tlen == 0) d = qlen;
+        else {
+            const int nb = (qlen + 63) >> 6;
+            uint64_t p0[4], p1[4], vm[4], Pv[4], Mv[4];
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
+                if (b < nb) query_planes(qp, b, qlen, p0[b], p1[b], vm[b]);
+                else { p0[b] = p1[b] = vm[b] = 0; }
+                Pv[b] = ~0ULL;
+                Mv[b] = 0;
+            }
+            int score = 64 * nb;                         /* D at the last row of the last word, column 0 */
+            uint32_t tw = 0;
+            for (int j = 0; j < tlen; j++) {
+                const uint64_t tp = toff + (uint64_t)j;
+                if ((tp & 15u) == 0 || j == 0) tw = __ldg(a.tbase + (tp >> 4));
+                const uint32_t c = (tw >> (2u * ((uint32_t)tp & 15u))) & 3u;
+                int h = 1;                               /* D[0][j] - D[0][j-1] */
+#pragma unroll
+                for (int b = 0; b < 4; b++)
+                    if (b < nb) h = myers_block(eq_mask(c, p0[b], p1[b], vm[b]), Pv[b], Mv[b], h);
+                score += h;
+            }
+            /* walk up from the word's last row to row qlen */
+            const int lastbit = (qlen - 1) & 63;
+            const uint64_t above = lastbit == 63 ? 0ULL : (~0ULL << (lastbit + 1));
+            uint64_t pv = Pv[0], mv = Mv[0];
+#pragma unroll
+            for (int b = 1; b < 4; b++)
+                if (b == nb - 1) { pv = Pv[b]; mv = Mv[b]; }
+            d = score - (__popcll(pv & above) - __popcll(mv & above));
+        }
+        const int out = (k >= 0 && d > k) ? -1 : d;
+        if (a.dist) a.dist[i] = out;
+        if (a.res) a.res[i].myers = out;
+    }
+}
+
+template <int W>
+__global__ void __launch_bounds__(128) k_myers_band(MyersArgs a) {
+    const int l = threadIdx.x & 31;
+    for (;;) {
+        uint32_t pi = 0;
+        if (l == 0) pi = atomicAdd(a.work_counter, 1u);
+        pi = __shfl_sync(0xFFFFFFFFu, pi, 0);
+        if (pi >= a.n) break;
+        const uint64_t toff = a.toff ? a.toff[pi] : 0;
+        if (toff == 0xFFFFFFFFFFFFFFFFULL) continue;
+        const int qlen = (int)a.qlens[pi];
+        const int tlen = a.tlens ? (int)a.tlens[pi] : qlen;
+        const int kin = pair_k(a, pi, qlen);
+        const uint32_t *qp = a.qpack + (size_t)pi * a.q_wstride;
+        int out;
+        const int diff = qlen > tlen ? qlen - tlen : tlen - qlen;
+        if (qlen == 0 || tlen == 0) {
+            const int d = qlen + tlen;
+            out = (kin >= 0 && d > kin) ? -1 : d;
+        } else if (kin >= 0 && diff > kin) {
+            out = -1;
+        } else {
+            const int k = kin >= 0 ? kin : (qlen > tlen ? qlen : tlen);
+            const int nb = (qlen + 63) >> 6;
+            const int B = nb - 1;
+            uint64_t p0[W], p1[W], vm[W], Pv[W], Mv[W];
+            int cur[W], score[W], hout[W];
+#pragma unroll
+            for (int w = 0; w < W; w++) {
+                cur[w] = l + 32 * w;
+                score[w] = 0;
+                hout[w] = 0;
+                p0[w] = p1[w] = vm[w] = Mv[w] = 0;
+                Pv[w] = ~0ULL;
+            }
+            int d_final = 0;
+            const int last_step = tlen + B;
+            for (int s = 1; s <= last_step; s++) {
+                /* carry of word b-1 (same column, previous step): rotate by one lane; lane 0 takes the previous slot */
+                int rh[W];
+#pragma unroll
+                for (int w = 0; w < W; w++) rh[w] = __shfl_sync(0xFFFFFFFFu, (score[w] << 2) | (hout[w] + 1), (l + 31) & 31);
+#pragma unroll
+                for (int w = 0; w < W; w++) {
+                    const int b = cur[w];
+                    if (b > B) continue;
+                    const int j = s - b;
+                    const int jf = 64 * b + 1 - k < 1 ? 1 : 64 * b + 1 - k;
+                    int jl = 64 * b + 64 + k;
+                    if (jl > tlen || jl < 0) jl = tlen;
+                    if (j < jf) continue;
+                    if (j > jl) {                        /* this word left the band: hand the slot to word b + 32W */
+                        cur[w] = b + 32 * W;
+                        hout[w] = 0;
+                        continue;
+                    }
+                    int rv = rh[w];
+                    if (l == 0) rv = rh[(w + W - 1) % W];
+                    if (j == jf) {
+                        query_planes(qp, b, qlen, p0[w], p1[w], vm[w]);
+                        Pv[w] = ~0ULL;
+                        Mv[w] = 0;
+                        /* D at this word's last row, column jf-1 (edlib.cpp:757-763) */
+                        score[w] = (jf == 1) ? 64 * (b + 1) : (rv >> 2) - ((rv & 3) - 1) + 64;
+                    }
+                    const int top = j - k - 1;
+                    const int fb = top <= 0 ? 0 : top >> 6;
+                    const int hin = (b == fb) ? 1 : (rv & 3) - 1;
+                    const uint32_t c = as_base_at(a.tbase, toff + (uint64_t)(j - 1));
+                    const int ho = myers_block(eq_mask(c, p0[w], p1[w], vm[w]), Pv[w], Mv[w], hin);
+                    hout[w] = ho;
+                    score[w] += ho;
+                    if (b == B && j == tlen) {
+                        const int lastbit = (qlen - 1) & 63;
+                        const uint64_t above = lastbit == 63 ? 0ULL : (~0ULL << (lastbit + 1));
+                        d_final = score[w] - (__popcll(Pv[w] & above) - __popcll(Mv[w] & above));
+                    }
+                }
+            }
+            const int d = __shfl_sync(0xFFFFFFFFu, d_final, B & 31);
+            out = (kin >= 0 && d > kin) ? -1 : d;
+        }
+        if (l == 0) {
+            if (a.dist) a.dist[pi] = out;
+            if (a.res) a.res[pi].myers = out;
+        }
+    }
+}
+
+int as_launch_myers(as_gpu *h, const uint32_t *d_qpack, size_t q_wstride, const uint32_t *d_qlens,
+                    const uint32_t *d_tbase, const uint64_t *d_toff, const uint32_t *d_tlens, size_t n,
+                    uint32_t max_qlen, const int32_t *d_ks, int32_t *d_dist, as_result *d_res) {
+    /* d_ks == NULL && d_res != NULL: map mode, k from the read length.  max band half-width for sizing: */
+    if (n == 0) return AS_OK;
+    MyersArgs a;
+    a.qpack = d_qpack; a.q_wstride = q_wstride; a.qlens = d_qlens;
+    a.tbase = d_tbase; a.toff = d_toff; a.tlens = d_tlens; a.n = n;
+    a.ks = d_ks; a.k_from_len = (d_ks == nullptr && d_res != nullptr);
+    a.dist = d_dist; a.res = d_res;
+    AS_TRY(as_scratch(h, &h->misc[4], 64));
+    AS_CUDA(cudaMemsetAsync(h->misc[4].p, 0, 64, h->stream));
+    a.work_counter = (unsigned int *)h->misc[4].p;
+    if (max_qlen <= 256) {
+        uint64_t blocks = (n + 127) / 128, cap = (uint64_t)h->sm_count * 16;
+        k_myers_short<<<(unsigned)(blocks < cap ? blocks : cap), 128, 0, h->stream>>>(a);
+    } else {
+        /* band words: map mode k = 0.1*len; otherwise assume the full matrix (exact for any k) */
+        uint64_t nb = ((uint64_t)max_qlen + 63) / 64;
+        uint64_t band_words = nb;
+        if (a.k_from_len) {
+            uint64_t k = (uint64_t)(0.05 * (double)max_qlen * 2);
+            uint64_t bw = (2 * k + 1) / 64 + 2;
+            if (bw < band_words) band_words = bw;
+        }
+        int W = (int)((band_words + 31) / 32) + 1;
+        uint64_t blocks = (n + 3) / 4, cap = (uint64_t)h->sm_count * 8;
+        unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
+        if (W <= 2) k_myers_band<2><<<grid, 128, 0, h->stream>>>(a);
+        else if (W <= 3) k_myers_band<3><<<grid, 128, 0, h->stream>>>(a);
+        else if (W <= 4) k_myers_band<4><<<grid, 128, 0, h->stream>>>(a);
+        else if (W <= 6) k_myers_band<6><<<grid, 128, 0, h->stream>>>(a);
+        else if (W <= 9) k_myers_band<9><<<grid, 128, 0, h->stream>>>(a);
+        else {
+            as_set_error("edit distance: query of %u bases needs a %llu-word band; at most 256 words are supported",
+                         max_qlen, (unsigned long long)band_words);
+            return AS_ERANGE;
+        }
+    }
+    h->launches++;
+    AS_CUDA(cudaGetLastError());
+    return AS_OK;
+}

@@ -1,0 +1,452 @@
+/*
+ * as_vote.cu -- PART 1 of the per-read loop (alnmain.c:333-405): phase-by-phase seeding, SA-hit voting
+ * into 16-bp buckets (histo.c:26-56), top-2 selection (histo.c:84-96) and the phase control with its
+ * last-phase override (alnmain.c:371-404).
+ *
+ * Mapping: a group of G lanes (8, 16 or 32, chosen from the longest read of the batch) owns one read and
+ * walks its phases; within a phase every lane owns one seed at a time: lc-table gather, then up to
+ * seed_len-hlen backward-search steps (two 32-byte sector gathers each), then the group spreads the SA
+ * rows of all surviving seeds over its lanes and votes into a shared-memory hash table keyed by bucket
+ * (atomicCAS claim, atomicAdd count, atomicMin key / first-seen order).  The reference's vote list is
+ * order-dependent only through tie-breaks in TOP2; `ord` = (seed index in phase, SA row offset) restores
+ * that order exactly.  Reads whose distinct buckets overflow the shared table are
+ * queued and redone by the same code over a large table in global memory (BIG instantiation).
+ */
+#include "as_common.cuh"
+
+#define VOTE_THREADS 128
+#define MAXP 34                      /* seed_len <= 32 -> at most 33 phases */
+#define EMPTY_BUCKET 0xFFFFFFFFFFFFFFFFULL
+
+struct VoteTable {
+    unsigned long long *bucket;
+    uint32_t *val, *ord, *low, *used;   /* used: BIG only */
+    uint32_t *n_used;                   /* BIG only */
+    uint32_t cap, shift;                /* cap = 1 << (64 - shift) */
+};
+
+struct VoteArgs {
+    const uint32_t *pack;
+    size_t wstride;
+    const uint32_t *lens;
+    size_t n;
+    int sl;
+    uint32_t thres;
+    VoteOut *out;
+    unsigned int *work_counter;
+    /* overflow queue */
+    unsigned int *ovf_count;
+    uint32_t *ovf_list;
+    /* BIG */
+    unsigned char *big_mem;
+    size_t big_stride;
+    uint32_t big_cap;
+    unsigned long long *stats;   /* as_stats layout */
+};
+
+__device__ __forceinline__ uint32_t hash_bucket(uint64_t b, uint32_t shift) {
+    return (uint32_t)((b * 0x9E3779B97F4A7C15ULL) >> shift);
+}
+
+template <bool BIG>
+__device__ __forceinline__ bool table_insert(const VoteTable &t, uint64_t bucket, uint32_t low, uint32_t ord) {
+    uint32_t slot = hash_bucket(bucket, t.shift);
+    for (uint32_t probes = 0; probes < t.cap; probes++) {
+        unsigned long long prev = atomicCAS(t.bucket + slot, EMPTY_BUCKET, (unsigned long long)bucket);
+        if (prev == EMPTY_BUCKET || prev == bucket) {
+            if (BIG && prev == EMPTY_BUCKET) t.used[atomicAdd(t.n_used, 1u)] = slot;
+            atomicAdd(t.val + slot, 1u);
+            atomicMin(t.ord + slot, ord);
+            atomicMin(t.low + slot, low);
+            return true;
+        }
+        slot = (slot + 1) & (t.cap - 1);
+    }
+    return false;
+}
+
+/* top-2 under (val desc, ord asc), as histo_find_2_max leaves them (histo.c:84-96) */
+__device__ __forceinline__ void top2_push(uint64_t &a0, uint64_t &a1, uint64_t c) {
+    if (c > a0) {
+        a1 = a0;
+        a0 = c;
+    } else if (c > a1) {
+        a1 = c;
+    }
+}
+
+template <int G, bool BIG>
+__global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, VoteArgs a) {
+    constexpr int CAP = 8 * G;
+    constexpr int GROUPS = VOTE_THREADS / G;
+    __shared__ unsigned long long s_bucket[BIG ? 1 : GROUPS * CAP];
+    __shared__ uint32_t s_val[BIG ? 1 : GROUPS * CAP], s_ord[BIG ? 1 : GROUPS * CAP], s_low[BIG ? 1 : GROUPS * CAP];
+    __shared__ unsigned long long s_okey[(BIG ? 1 : GROUPS) * MAXP];
+    __shared__ uint32_t s_oval[(BIG ? 1 : GROUPS) * MAXP];
+
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t g = lane & (G - 1);
+    const uint32_t gmask = (G == 32) ? 0xFFFFFFFFu : (((1u << G) - 1u) << (lane & ~(uint32_t)(G - 1)));
+    const int grp = threadIdx.x / G;
+
+    VoteTable t;
+    if (BIG) {
+        unsigned char *m = a.big_mem + (size_t)blockIdx.x * a.big_stride;
+        t.cap = a.big_cap;
+        t.bucket = (unsigned long long *)m;
+        t.val = (uint32_t *)(m + (size_t)t.cap * 8);
+        t.ord = t.val + t.cap;
+        t.low = t.ord + t.cap;
+        t.used = t.low + t.cap;
+        t.n_used = t.used + t.cap;
+    } else {
+        t.cap = CAP;
+        t.bucket = s_bucket + grp * CAP;
+        t.val = s_val + grp * CAP;
+        t.ord = s_ord + grp * CAP;
+        t.low = s_low + grp * CAP;
+        t.used = nullptr;
+        t.n_used = nullptr;
+    }
+    t.shift = 64 - (31 - __clz(t.cap));
+    unsigned long long *okey = s_okey + (BIG ? 0 : grp) * MAXP;
+    uint32_t *oval = s_oval + (BIG ? 0 : grp) * MAXP;
+
+    if (BIG) {
+        for (uint32_t s = g; s < t.cap; s += G) {
+            t.bucket[s] = EMPTY_BUCKET;
+            t.val[s] = 0;
+            t.ord[s] = 0xFFFFFFFFu;
+            t.low[s] = 0xFFFFFFFFu;
+        }
+        if (g == 0) *t.n_used = 0;
+        __syncwarp(gmask);
+    }
+
+    const int sl = a.sl, P = sl + 1;
+    const int left0 = sl - ix.hlen;
+    const uint64_t hmask = (1ULL << (2 * ix.hlen)) - 1ULL;
+    unsigned long long st_seeds = 0, st_steps = 0, st_hits = 0, st_ovf = 0;
+
+    for (;;) {
+        /* next read of this group */
+        uint32_t widx = 0;
+        if (g == 0) widx = atomicAdd(a.work_counter, 1u);
+        widx = __shfl_sync(gmask, widx, 0, G);
+        uint32_t read;
+        if (BIG) {
+            if (widx >= *a.ovf_count) break;
+            read = a.ovf_list[widx];
+        } else {
+            if (widx >= a.n) break;
+            read = widx;
+        }
+        const uint32_t len = a.lens[read];
+        const uint32_t *pr = a.pack + (size_t)read * a.wstride;
+        const uint32_t num_seeds = len / (uint32_t)P;                   /* alnmain.c:371 */
+        const uint32_t span = len > (uint32_t)sl ? len - (uint32_t)sl : 0;   /* seeds start at j < len - sl (:353) */
+
+        uint32_t n_outer = 0;
+        uint64_t best_key = 0, best_val = 0;
+        int iter;
+        bool overflow = false;
+        for (iter = 0; iter < P; ++iter) {
+            /* ---- clear the table ---- */
+            if (!BIG) {
+                for (uint32_t s = g; s < (uint32_t)CAP; s += G) {
+                    t.bucket[s] = EMPTY_BUCKET;
+                    t.val[s] = 0;
+                    t.ord[s] = 0xFFFFFFFFu;
+                    t.low[s] = 0xFFFFFFFFu;
+                }
+            }
+            __syncwarp(gmask);
+            const uint32_t m_count = (uint32_t)iter < span ? (span - (uint32_t)iter + (uint32_t)P - 1) / (uint32_t)P : 0;
+            bool ok = true;
+            for (uint32_t c0 = 0; c0 < m_count; c0 += G) {
+                const uint32_t m = c0 + g;
+                const uint32_t j = (uint32_t)iter + m * (uint32_t)P;
+                uint64_t kk = 1, ll = ix.N - 1, rr = 0;                 /* alnmain.c:354 */
+                if (m < m_count) {
+                    const uint64_t seed = as_bases32(pr, j);
+                    bool absent = false;
+                    int left = left0;
+                    if (left0 >= 0) {                                   /* lchash.c:93-101 */
+                        ulonglong2 kl = __ldg(ix.lc + ((seed >> (2 * left0)) & hmask));
+                        kk = kl.x;
+                        ll = kl.y;
+                        absent = (kk == 0 && ll == 0);
+                    }
+                    st_seeds++;
+                    if (!absent) {
+                        for (int tt = left - 1; tt >= 0; tt--) {        /* fmidx.c:300-310 */
+                            as_bs_step(ix, (uint32_t)(seed >> (2 * tt)) & 3u, kk, ll);
+                            st_steps++;
+                            if (kk > ll) break;
+                        }
+                        rr = kk > ll ? 0 : ll - kk + 1;
+                    }
+                }
+                const uint32_t rr_eff = (rr > 0 && rr < a.thres) ? (uint32_t)rr : 0u;   /* alnmain.c:360 */
+                const uint32_t multi = __ballot_sync(gmask, rr_eff > 1) & gmask;
+                if (multi == 0) {
+                    /* common case: every surviving seed has exactly one SA row */
+                    if (rr_eff) {
+                        uint64_t key = as_sa(ix, kk) - (uint64_t)j;     /* alnmain.c:363-365, u64 wrap kept */
+                        st_hits++;
+                        if (!table_insert<BIG>(t, key >> 4, (uint32_t)key & 15u, m * a.thres)) ok = false;
+                    }
+                } else {
+                    /* spread all SA rows of the chunk over the lanes of the group */
+                    uint32_t incl = rr_eff;
+#pragma unroll
+                    for (int d = 1; d < G; d <<= 1) {
+                        uint32_t o = __shfl_up_sync(gmask, incl, d, G);
+                        if ((int)g >= d) incl += o;
+                    }
+                    const uint32_t base = incl - rr_eff;
+                    const uint32_t V = __shfl_sync(gmask, incl, G - 1, G);
+                    for (uint32_t v0 = 0; v0 < V; v0 += G) {
+                        const uint32_t v = v0 + g;
+                        /* owner = largest lane whose exclusive base <= v */
+                        uint32_t lo = 0;
+#pragma unroll
+                        for (int d = G >> 1; d >= 1; d >>= 1) {
+                            uint32_t b = __shfl_sync(gmask, base, lo + d, G);
+                            if (b <= v) lo += d;
+                        }
+                        const uint32_t ob = __shfl_sync(gmask, base, lo, G);
+                        const uint32_t okl = __shfl_sync(gmask, (uint32_t)kk, lo, G);
+                        const uint32_t okh = __shfl_sync(gmask, (uint32_t)(kk >> 32), lo, G);
+                        if (v < V) {
+                            const uint32_t om = c0 + lo;
+                            const uint32_t oj = (uint32_t)iter + om * (uint32_t)P;
+                            const uint32_t off = v - ob;
+                            uint64_t row = (((uint64_t)okh << 32) | okl) + off;
+                            uint64_t key = as_sa(ix, row) - (uint64_t)oj;
+                            st_hits++;
+                            if (!table_insert<BIG>(t, key >> 4, (uint32_t)key & 15u, om * a.thres + off)) ok = false;
+                        }
+                    }
+                }
+            }
+            __syncwarp(gmask);
+            if (__ballot_sync(gmask, !ok) & gmask) {
+                overflow = true;
+                break;
+            }
+            /* ---- TOP2 of the phase (histo.c:84-96) ---- */
+            uint64_t a0 = 0, a1 = 0;
+            uint32_t slot0 = 0;
+            if (BIG) {
+                const uint32_t nu = *t.n_used;
+                for (uint32_t u = g; u < nu; u += G) {
+                    uint32_t s = t.used[u];
+                    uint64_t c = ((uint64_t)t.val[s] << 32) | (0xFFFFFFFFu - t.ord[s]);
+                    if (c > a0) slot0 = s;
+                    top2_push(a0, a1, c);
+                }
+            } else {
+                for (uint32_t s = g; s < (uint32_t)CAP; s += G) {
+                    uint32_t vv = t.val[s];
+                    uint64_t c = vv ? (((uint64_t)vv << 32) | (0xFFFFFFFFu - t.ord[s])) : 0;
+                    if (c > a0) slot0 = s;
+                    top2_push(a0, a1, c);
+                }
+            }
+#pragma unroll
+            for (int d = G >> 1; d >= 1; d >>= 1) {
+                uint64_t b0 = __shfl_xor_sync(gmask, a0, d, G);
+                uint64_t b1 = __shfl_xor_sync(gmask, a1, d, G);
+                uint32_t bs = __shfl_xor_sync(gmask, slot0, d, G);
+                uint64_t mn = a0 < b0 ? a0 : b0;
+                uint64_t mx1 = a1 > b1 ? a1 : b1;
+                if (b0 > a0) {
+                    a0 = b0;
+                    slot0 = bs;
+                }
+                a1 = mn > mx1 ? mn : mx1;
+            }
+            const uint32_t v0val = (uint32_t)(a0 >> 32), v1val = (uint32_t)(a1 >> 32);
+            uint64_t c0key = 0;
+            if (v0val) c0key = ((uint64_t)t.bucket[slot0] << 4) | t.low[slot0];
+            __syncwarp(gmask);
+            if (BIG) {
+                /* reset only the used slots */
+                const uint32_t nu = *t.n_used;
+                __syncwarp(gmask);
+                for (uint32_t u = g; u < nu; u += G) {
+                    uint32_t s = t.used[u];
+                    t.bucket[s] = EMPTY_BUCKET;
+                    t.val[s] = 0;
+                    t.ord[s] = 0xFFFFFFFFu;
+                    t.low[s] = 0xFFFFFFFFu;
+                }
+                __syncwarp(gmask);
+                if (g == 0) *t.n_used = 0;
+                __syncwarp(gmask);
+            }
+            if (num_seeds > 0) {                                        /* alnmain.c:373 */
+                const uint64_t v = (uint64_t)v0val + v1val;
+                const double score = (double)v / (double)(int)num_seeds;
+                if (score > 0.6) {                                      /* :378-384 */
+                    best_key = c0key;
+                    best_val = v0val;
+                    break;
+                } else if (v0val != 0) {                                /* :386-388 histo_add(outer, cand[0].key) */
+                    const uint64_t b = c0key >> 4;
+                    uint32_t found = n_outer;
+                    for (uint32_t e = 0; e < n_outer; e++)
+                        if ((okey[e] >> 4) == b) found = e;
+                    __syncwarp(gmask);
+                    if (g == 0) {
+                        if (found < n_outer) {
+                            oval[found] += 1;
+                            if (c0key < okey[found]) okey[found] = c0key;
+                        } else {
+                            okey[n_outer] = c0key;
+                            oval[n_outer] = 1;
+                        }
+                    }
+                    if (found == n_outer) n_outer++;
+                    __syncwarp(gmask);
+                }
+            }
+        }
+        if (overflow) {
+            if (BIG) {
+                /* cannot happen: the big table holds every possible vote of a phase; flag it loudly */
+                st_ovf++;
+                if (g == 0) {
+                    VoteOut o;
+                    o.best_key = 0;
+                    o.best_val = 0;
+                    o.phases = -1;
+                    o.from_outer = -1;
+                    a.out[read] = o;
+                }
+                /* table state is unknown: wipe it */
+                for (uint32_t s = g; s < t.cap; s += G) {
+                    t.bucket[s] = EMPTY_BUCKET;
+                    t.val[s] = 0;
+                    t.ord[s] = 0xFFFFFFFFu;
+                    t.low[s] = 0xFFFFFFFFu;
+                }
+                if (g == 0) *t.n_used = 0;
+                __syncwarp(gmask);
+            } else if (g == 0) {
+                a.ovf_list[atomicAdd(a.ovf_count, 1u)] = read;
+            }
+            continue;
+        }
+        int from_outer = 0;
+        if (iter >= P - 1) {                                            /* alnmain.c:400-403 */
+            uint64_t bk = 0;
+            uint32_t bv = 0;
+            for (uint32_t e = 0; e < n_outer; e++) {
+                if (oval[e] > bv) {
+                    bv = oval[e];
+                    bk = okey[e];
+                }
+            }
+            best_key = bk;
+            best_val = bv;
+            from_outer = 1;
+        }
+        if (g == 0) {
+            VoteOut o;
+            o.best_key = best_key;
+            o.best_val = best_val;
+            o.phases = iter;
+            o.from_outer = from_outer;
+            a.out[read] = o;
+        }
+        __syncwarp(gmask);
+    }
+
+    /* stats: one atomic per warp and counter */
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) {
+        st_seeds += __shfl_xor_sync(0xFFFFFFFFu, st_seeds, d);
+        st_steps += __shfl_xor_sync(0xFFFFFFFFu, st_steps, d);
+        st_hits += __shfl_xor_sync(0xFFFFFFFFu, st_hits, d);
+        st_ovf += __shfl_xor_sync(0xFFFFFFFFu, st_ovf, d);
+    }
+    if (lane == 0) {
+        if (st_seeds) atomicAdd(a.stats + 6, st_seeds);
+        if (st_hits) atomicAdd(a.stats + 7, st_hits);
+        if (st_steps) atomicAdd(a.stats + 8, st_steps);
+        if (st_ovf) atomicAdd(a.stats + 9, st_ovf);
+    }
+}
+
+static uint32_t next_pow2(uint64_t v) {
+    uint32_t p = 64;
+    while (p < v && p < (1u << 30)) p <<= 1;
+    return p;
+}
+
+int as_launch_vote(as_gpu *h, const as_params *p, const uint32_t *d_pack, size_t wstride, const uint32_t *d_lens,
+                   size_t n, uint32_t max_len, VoteOut *d_vote) {
+    if (n == 0) return AS_OK;
+    if (p->seed_len < 1 || p->seed_len > 32 || p->thres < 1 || p->thres > 65535) {
+        as_set_error("as_map_batch: seed_len must be in [1,32] and thres in [1,65535]");
+        return AS_EINVAL;
+    }
+    if (n >= 0xFFFFFFFFull) return AS_ERANGE;
+    const int sl = (int)p->seed_len, P = sl + 1;
+    /* counters: [0] work counter, [1] overflow count, [2] work counter of the BIG pass */
+    AS_TRY(as_scratch(h, &h->counters, 64));
+    AS_TRY(as_scratch(h, &h->ovf_list, n * sizeof(uint32_t)));
+    AS_CUDA(cudaMemsetAsync(h->counters.p, 0, 64, h->stream));
+
+    /* BIG table: every vote of one phase fits at load factor <= 1/2 */
+    uint64_t seeds_per_phase = max_len > (uint32_t)sl ? ((uint64_t)(max_len - sl) + P - 1) / P : 1;
+    uint64_t max_votes = seeds_per_phase * (uint64_t)(p->thres > 1 ? p->thres - 1 : 1);
+    uint32_t big_cap = next_pow2(2 * max_votes);
+    size_t big_stride = ((size_t)big_cap * 24 + 64 + 255) & ~(size_t)255;
+    size_t budget = (size_t)2 << 30;
+    size_t big_warps = budget / big_stride;
+    if (big_warps > (size_t)h->sm_count * 4) big_warps = (size_t)h->sm_count * 4;
+    if (big_warps > n) big_warps = n;
+    if (big_warps < 1) big_warps = 1;
+    AS_TRY(as_scratch(h, &h->ovf_table, big_warps * big_stride));
+
+    VoteArgs a;
+    a.pack = d_pack;
+    a.wstride = wstride;
+    a.lens = d_lens;
+    a.n = n;
+    a.sl = sl;
+    a.thres = p->thres;
+    a.out = d_vote;
+    a.work_counter = (unsigned int *)h->counters.p;
+    a.ovf_count = (unsigned int *)h->counters.p + 1;
+    a.ovf_list = (uint32_t *)h->ovf_list.p;
+    a.big_mem = (unsigned char *)h->ovf_table.p;
+    a.big_stride = big_stride;
+    a.big_cap = big_cap;
+    a.stats = h->d_stats;
+
+    /* lanes per read from the seeds of one phase of the longest read */
+    int G = seeds_per_phase <= 8 ? 8 : seeds_per_phase <= 16 ? 16 : 32;
+    uint64_t groups_needed = n;
+    uint64_t groups_per_block = VOTE_THREADS / G;
+    uint64_t blocks = (groups_needed + groups_per_block - 1) / groups_per_block;
+    uint64_t cap = (uint64_t)h->sm_count * 8;          /* 8 blocks of <= 27 KB shared memory per SM */
+    unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
+    if (G == 8)
+        k_vote<8, false><<<grid, VOTE_THREADS, 0, h->stream>>>(h->ix, a);
+    else if (G == 16)
+        k_vote<16, false><<<grid, VOTE_THREADS, 0, h->stream>>>(h->ix, a);
+    else
+        k_vote<32, false><<<grid, VOTE_THREADS, 0, h->stream>>>(h->ix, a);
+    h->launches++;
+    AS_CUDA(cudaGetLastError());
+    /* overflow pass: exits at once when the queue is empty */
+    a.work_counter = (unsigned int *)h->counters.p + 2;
+    k_vote<32, true><<<(unsigned)big_warps, 32, 0, h->stream>>>(h->ix, a);
+    h->launches++;
+    AS_CUDA(cudaGetLastError());
+    return AS_OK;
+}
