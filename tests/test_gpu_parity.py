@@ -1,0 +1,309 @@
+"""Parity of the CUDA path (through the C ABI, libaccseq_b200.so) with the oracle: bit-exact on every
+integer field -- SA intervals, SA values, voted locus, phases, strand, offset, FLAG, MAPQ, ED, CIGAR ops,
+Myers distance.  The oracle itself is pinned against the compiled reference in test_oracle_vs_ref.py."""
+import numpy as np
+import pytest
+
+from conftest import reads_from
+
+pytestmark = pytest.mark.gpu
+
+FIELDS = ("loc", "off", "seq_id", "strand", "flag", "mapq", "ed", "valid", "myers", "phases", "from_outer")
+
+
+@pytest.fixture(scope="module")
+def gpu_uniform(native, idx_uniform):
+    ix, _ = idx_uniform
+    m = native.GpuMapper.from_oracle_index(ix, 0)
+    yield m
+    m.close()
+
+
+@pytest.fixture(scope="module")
+def gpu_repeat(native, idx_repeat):
+    ix, _ = idx_repeat
+    m = native.GpuMapper.from_oracle_index(ix, 0)
+    yield m
+    m.close()
+
+
+def compare_map(native, mapper, ix, reads, lens, stride, **kw):
+    seed_len = kw.get("seed_len", 20)
+    thres = kw.get("thres", 300)
+    T = kw.get("T", 320)
+    O = kw.get("O", 120)
+    r_cpu = reads.copy()
+    r_gpu = reads.copy()
+    exp, exp_ops, cells = ix.map_batch(r_cpu, stride, lens, seed_len=seed_len, thres=thres, T=T, O=O, myers=True)
+    p = mapper.params(seed_len=seed_len, thres=thres, T=T, O=O, flags=native.AS_F_MYERS)
+    mapper.stats_reset()
+    got, got_ops = mapper.map_batch(r_gpu, lens, params=p)
+    for f in FIELDS:
+        bad = np.nonzero(exp[f] != got[f])[0]
+        assert bad.size == 0, f"{f}: {bad.size} reads differ, first {bad[0]}: exp {exp[f][bad[0]]} got {got[f][bad[0]]}"
+    assert np.array_equal(exp["n_ops"], got["n_cigar_op"])
+    for i in range(len(lens)):
+        n = int(exp["n_ops"][i])
+        assert np.array_equal(exp_ops[i, :n], got_ops[i, :n]), f"CIGAR ops differ on read {i}"
+    assert np.array_equal(r_cpu, r_gpu), "in-place reverse complement differs"
+    st = mapper.stats()
+    assert st["total"] == len(lens)
+    assert st["valid"] == int(exp["valid"].sum())
+    assert st["dp_cells"] == cells
+    return exp, st
+
+
+# ---------------------------------------------------------------------------------------------------
+# lookups (lchash.c:89-104, fmidx.c:295-313, fmidx.c:18-33)
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("qlen", [20, 12, 13, 32, 8])
+def test_lc_aln_matches_oracle(gpu_uniform, idx_uniform, qlen):
+    ix, (g,) = idx_uniform
+    rng = np.random.default_rng(qlen)
+    n = 4000
+    pos = rng.integers(0, g.size - 64, n)
+    seeds = np.stack([g[p:p + qlen] for p in pos])
+    # half of them get one substitution so that many intervals die part-way
+    mut = rng.integers(0, 2, n).astype(bool)
+    where = rng.integers(0, qlen, n)
+    seeds[mut, where[mut]] = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, int(mut.sum()))]
+    k, l, r = gpu_uniform.lc_aln_batch(seeds, qlen)
+    ek, el, er = ix.lc_aln_batch(seeds, qlen)
+    assert np.array_equal(r, er)
+    live = er > 0
+    assert np.array_equal(k[live], ek[live]) and np.array_equal(l[live], el[live])
+    # dead intervals: the reference leaves (k,l) wherever the search stopped; same here
+    assert np.array_equal(k, ek) and np.array_equal(l, el)
+
+
+def test_lc_aln_equals_fmi_aln(gpu_uniform, idx_uniform):
+    """The invariant test/test-lchash.cc:30-48 checks: table-accelerated == plain backward search, and the
+    SA position spells the query."""
+    ix, (g,) = idx_uniform
+    rng = np.random.default_rng(5)
+    pos = rng.integers(0, g.size - 64, 2000)
+    q = np.stack([g[p:p + 64] for p in pos])
+    k1, l1, r1 = gpu_uniform.lc_aln_batch(q, 64)
+    k2, l2, r2 = gpu_uniform.fmi_aln_batch(q, 64)
+    assert np.array_equal(r1, r2) and np.array_equal(k1, k2) and np.array_equal(l1, l2)
+    assert (r1 >= 1).all()
+    sa = gpu_uniform.sa_access_batch(k1)
+    cat = ix.cat
+    for i in range(0, 2000, 97):
+        assert bytes(cat[int(sa[i]):int(sa[i]) + 64]) == bytes(q[i])
+
+
+def test_sa_access(gpu_uniform, idx_uniform):
+    ix, _ = idx_uniform
+    rows = np.random.default_rng(1).integers(0, ix.n, 100000).astype(np.uint64)
+    assert np.array_equal(gpu_uniform.sa_access_batch(rows), ix.sa[rows])
+    assert np.array_equal(gpu_uniform.sa_access_batch(np.arange(ix.n, dtype=np.uint64)), ix.sa)
+
+
+# ---------------------------------------------------------------------------------------------------
+# PART 1 (alnmain.c:333-405)
+# ---------------------------------------------------------------------------------------------------
+def check_vote(mapper, ix, reads, lens, seed_len=20, thres=300):
+    key, val, ph, fo = mapper.vote_batch(reads, lens, mapper.params(seed_len=seed_len, thres=thres))
+    for i in range(len(lens)):
+        v = ix.vote(reads[i, : lens[i]], seed_len, thres)
+        assert (int(key[i]), int(val[i]), int(ph[i]), int(fo[i])) == (v.best_key, v.best_val, v.phases, v.from_outer), i
+
+
+def test_vote_uniform_short(native, gpu_uniform, idx_uniform):
+    ix, gs = idx_uniform
+    reads, lens, _ = reads_from(native, 100, gs, 3000, 150, 150, 0.01, 0.01, 0.9)
+    check_vote(gpu_uniform, ix, reads, lens)
+
+
+def test_vote_repeat_rich(native, gpu_repeat, idx_repeat):
+    ix, gs = idx_repeat
+    for k, (lmin, lmax, e) in enumerate([(100, 100, 0.0), (150, 150, 0.02), (250, 250, 0.05), (100, 250, 0.08)]):
+        reads, lens, _ = reads_from(native, 200 + k, gs, 750, lmin, lmax, e, e, 0.7)
+        check_vote(gpu_repeat, ix, reads, lens)
+
+
+@pytest.mark.parametrize("seed_len,thres", [(12, 300), (16, 50), (24, 300), (32, 1000), (20, 2)])
+def test_vote_parameters(native, gpu_repeat, idx_repeat, seed_len, thres):
+    ix, gs = idx_repeat
+    reads, lens, _ = reads_from(native, 300 + seed_len, gs, 300, 60, 260, 0.0, 0.06, 0.8)
+    check_vote(gpu_repeat, ix, reads, lens, seed_len, thres)
+
+
+def test_vote_long_reads(native, gpu_repeat, idx_repeat):
+    ix, gs = idx_repeat
+    reads, lens, _ = reads_from(native, 400, gs, 40, 1000, 6000, 0.05, 0.15, 0.34)
+    check_vote(gpu_repeat, ix, reads, lens)
+
+
+# ---------------------------------------------------------------------------------------------------
+# whole path (alnmain.c:330-479)
+# ---------------------------------------------------------------------------------------------------
+def test_map_uniform_short(native, gpu_uniform, idx_uniform):
+    ix, gs = idx_uniform
+    reads, lens, stride = reads_from(native, 500, gs, 4000, 150, 150, 0.01, 0.01, 0.9)
+    exp, st = compare_map(native, gpu_uniform, ix, reads, lens, stride)
+    assert exp["valid"].mean() > 0.95
+
+
+def test_map_repeat_rich_mixed(native, gpu_repeat, idx_repeat):
+    ix, gs = idx_repeat
+    reads, lens, stride = reads_from(native, 600, gs, 1500, 100, 250, 0.0, 0.08, 0.6)
+    compare_map(native, gpu_repeat, ix, reads, lens, stride)
+
+
+def test_map_long_reads_tiled(native, gpu_repeat, idx_repeat):
+    """reads longer than the GACT tile: several tiles per read, indels."""
+    ix, gs = idx_repeat
+    reads, lens, stride = reads_from(native, 700, gs, 60, 400, 5000, 0.05, 0.15, 0.34)
+    compare_map(native, gpu_repeat, ix, reads, lens, stride)
+
+
+@pytest.mark.parametrize("T,O", [(64, 16), (128, 120), (320, 0), (512, 128), (32, 31)])
+def test_map_tile_parameters(native, gpu_repeat, idx_repeat, T, O):
+    ix, gs = idx_repeat
+    reads, lens, stride = reads_from(native, 800 + T, gs, 100, 50, 900, 0.0, 0.12, 0.4)
+    compare_map(native, gpu_repeat, ix, reads, lens, stride, T=T, O=O)
+
+
+def test_map_edge_cases(native, gpu_repeat, idx_repeat):
+    """ragged batch: reads at the sequence boundaries (seq_lookup straddles -> unmapped), reads shorter than
+    one phase (num_seeds == 0), reads of pure garbage (no votes -> key 0), a read of len == seed_len + 1."""
+    ix, (a, b) = idx_repeat
+    rng = np.random.default_rng(9)
+    seqs = [a[:150], a[-150:], b[:150], b[-150:],                    # at the ends
+            np.concatenate([a[-75:], b[:75]]),                       # straddles A.fwd|A.rev? (no: A.fwd end + junk)
+            a[1000:1021], a[1000:1022], a[1000:1041], a[1000:1042],   # 21, 22, 41, 42 bases
+            np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, 150)],  # random: no hits
+            a[5000:5150][::-1].copy(),                               # reversed, not complemented
+            np.full(150, ord("A"), np.uint8),                        # homopolymer
+            np.tile(np.frombuffer(b"ACGTTGCA", np.uint8), 18)]       # tandem unit
+    comp = np.zeros(256, np.uint8)
+    comp[list(b"ACGT")] = list(b"TGCA")
+    seqs.append(comp[a[-150:]][::-1].copy())                         # start of A's reverse copy
+    seqs.append(comp[a[:150]][::-1].copy())                          # end of A's reverse copy
+    stride = 151
+    reads = np.zeros((len(seqs), stride), np.uint8)
+    lens = np.zeros(len(seqs), np.uint32)
+    for i, s in enumerate(seqs):
+        reads[i, : len(s)] = s
+        lens[i] = len(s)
+    compare_map(native, gpu_repeat, ix, reads, lens, stride)
+
+
+def test_map_empty_and_single(native, gpu_uniform, idx_uniform):
+    ix, (g,) = idx_uniform
+    res, ops = gpu_uniform.map_batch(np.zeros((0, 151), np.uint8), np.zeros(0, np.uint32))
+    assert res.size == 0
+    reads = np.zeros((1, 151), np.uint8)
+    reads[0, :150] = g[777:927]
+    exp, _ = compare_map(native, gpu_uniform, ix, reads, np.array([150], np.uint32), 151)
+    assert exp["off"][0] == 777 and exp["flag"][0] == 0 and exp["ed"][0] == 0
+
+
+def test_map_batch_split_invariance(native, gpu_uniform, idx_uniform):
+    """results do not depend on batching (rid/batch never enter the arithmetic)."""
+    ix, gs = idx_uniform
+    reads, lens, stride = reads_from(native, 900, gs, 1000, 150, 150, 0.02, 0.02, 0.8)
+    p = gpu_uniform.params()
+    whole, wops = gpu_uniform.map_batch(reads.copy(), lens, params=p)
+    parts = [gpu_uniform.map_batch(reads[s:e].copy(), lens[s:e], params=p) for s, e in ((0, 1), (1, 500), (500, 1000))]
+    assert np.array_equal(whole, np.concatenate([x[0] for x in parts]))
+    assert np.array_equal(wops, np.concatenate([x[1] for x in parts]))
+
+
+def test_truth_recovered(native, gpu_uniform, idx_uniform):
+    """size-independent property: substitution-only reads land on the simulated position and strand."""
+    ix, (g,) = idx_uniform
+    reads, lens, pos, strand = native.sim_reads(77, g, 5000, 150, 150, 0.02, 0.02, 1.0)
+    res, _ = gpu_uniform.map_batch(reads, lens, params=gpu_uniform.params(flags=native.AS_F_MYERS))
+    ok = res["valid"] == 1
+    assert ok.mean() > 0.99
+    assert (res["off"][ok] == pos[ok]).mean() > 0.99
+    assert np.array_equal(res["strand"][ok] == 1, strand[ok] == 1)
+    # single-tile reads: GACT ED equals the exact NW distance
+    both = ok & (res["myers"] >= 0)
+    assert both.sum() > 4000 and np.array_equal(res["ed"][both], res["myers"][both])
+
+
+# ---------------------------------------------------------------------------------------------------
+# aligners on explicit pairs (mutils.c:94-105; edlib.cpp:694-895)
+# ---------------------------------------------------------------------------------------------------
+def mutate(rng, s, err, sub_frac=0.34):
+    out = []
+    alpha = b"ACGT"
+    for c in s:
+        x = rng.random()
+        if x < err:
+            y = rng.random()
+            if y < sub_frac:
+                out.append(alpha[rng.integers(0, 4)])
+            elif y < sub_frac + (1 - sub_frac) / 2:
+                out.append(alpha[rng.integers(0, 4)])
+                out.append(c)
+            else:
+                continue
+        else:
+            out.append(c)
+    return bytes(out)
+
+
+def random_pairs(seed, n, lmin, lmax, emax):
+    rng = np.random.default_rng(seed)
+    qs, ts = [], []
+    for _ in range(n):
+        L = int(rng.integers(lmin, lmax + 1))
+        t = bytes(np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, L)])
+        q = mutate(rng, t, rng.random() * emax)
+        qs.append(q)
+        ts.append(t)
+    return qs, ts
+
+
+@pytest.mark.parametrize("T,O,lmax", [(320, 120, 300), (320, 120, 2500), (64, 20, 700), (32, 8, 300), (512, 200, 3000)])
+def test_gact_pairs(orc, gpu_uniform, T, O, lmax):
+    qs, ts = random_pairs(T + lmax, 120, 1, lmax, 0.2)
+    qs += [b"A", b"ACGT", b"A" * 50, b"ACGT" * 30]
+    ts += [b"C", b"ACGT", b"A" * 80, b"TGCA" * 30]
+    score, ops = gpu_uniform.cigar_align_batch(qs, ts, gpu_uniform.params(T=T, O=O))
+    for i, (q, t) in enumerate(zip(qs, ts)):
+        es, eops, _ = orc.gact(np.frombuffer(q, np.uint8), np.frombuffer(t, np.uint8), T, O)
+        assert es == score[i], (i, len(q), len(t))
+        assert np.array_equal(eops, ops[i]), i
+        if es >= 0:   # every path consumes exactly the two sequences
+            assert int(np.isin(ops[i], (0, 1, 3)).sum()) == len(q) and int(np.isin(ops[i], (0, 2, 3)).sum()) == len(t)
+
+
+def test_gact_single_tile_is_exact_nw(orc, gpu_uniform):
+    qs, ts = random_pairs(3, 200, 20, 320, 0.25)
+    score, _ = gpu_uniform.cigar_align_batch(qs, ts)
+    dist = gpu_uniform.edit_distance_batch(qs, ts)
+    assert np.array_equal(score, dist)
+
+
+def test_edlib_known_answer(gpu_uniform):
+    """edlib/ed_test.c:14-19: two 100-mers differing at 2 positions -> 2 / 100M."""
+    rng = np.random.default_rng(0)
+    t = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, 100)].copy()
+    q = t.copy()
+    q[10] = ord("A") if q[10] != ord("A") else ord("C")
+    q[60] = ord("G") if q[60] != ord("G") else ord("T")
+    d = gpu_uniform.edit_distance_batch([q.tobytes()], [t.tobytes()], [5000000])
+    assert d[0] == 2
+    s, ops = gpu_uniform.cigar_align_batch([q.tobytes()], [t.tobytes()])
+    assert s[0] == 2 and len(ops[0]) == 100 and set(ops[0].tolist()) <= {0, 3}
+
+
+@pytest.mark.parametrize("lmax,emax", [(256, 0.3), (2000, 0.15), (12000, 0.12)])
+def test_myers_pairs(orc, gpu_uniform, lmax, emax):
+    n = 150 if lmax <= 2000 else 24
+    qs, ts = random_pairs(lmax, n, 1, lmax, emax)
+    rng = np.random.default_rng(lmax)
+    # unbounded
+    d = gpu_uniform.edit_distance_batch(qs, ts)
+    exp = np.array([orc.edit_distance(np.frombuffer(q, np.uint8), np.frombuffer(t, np.uint8), -1) for q, t in zip(qs, ts)])
+    assert np.array_equal(d, exp)
+    # bounded: k around the true distance exercises the -1 verdict and the band
+    ks = np.maximum(0, exp + rng.integers(-5, 6, len(qs))).astype(np.int32)
+    d = gpu_uniform.edit_distance_batch(qs, ts, ks)
+    assert np.array_equal(d, np.where(exp > ks, -1, exp))
