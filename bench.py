@@ -1,0 +1,469 @@
+#!/usr/bin/env python
+"""bench.py -- mapped reads/s of the AccSeqV9 per-read mapping hot path on B200 (BASELINE.json's metric).
+
+A step = one pass of the hot path (alnmain.c:330-479: seeding + voting, locus/strand, GACT, result fill) over
+one batch of synthetic reads.  N=1 workload = BASELINE.json configs[1]: 4.6 Mbp uniform synthetic genome
+(distribution of scripts/dna_txt_gen.py), 1M x 150 bp reads at 2 % error; with N ranks every rank maps its
+own 1M-read shard against its own replica of the index (weak scaling, no data-path collective; one
+all-reduce of the shard statistics at the end).
+
+  value        whole-job reads/s with the batch resident in HBM (as_map_batch_device), CUDA-event timed
+  e2e          the same through as_map_batch with pinned HOST buffers (H2D + kernels + D2H in the timed region)
+  roofline     the dominant kernel of the step against its bound (GACT: INT32 ALU; seeding/voting: memory)
+  cpu_baseline the reference's CPU code (oracle/_ref/accaln_ref, P single-thread processes on P read
+               slices -- the reference's mapping loop is single-threaded) on a bounded sample
+  --impl reference   times only that CPU arm.
+
+Only the cpu legs touch oracle/ (to write the index files accaln_ref loads and to run it).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: genome bases, reads per rank, read length range, error range, substitution fraction
+    "c1": dict(genome=1_000_000, reads=10_000, len=(150, 150), err=(0.01, 0.01), sub=0.9),
+    "c2": dict(genome=4_600_000, reads=1_000_000, len=(150, 150), err=(0.02, 0.02), sub=0.8),
+    "c3": dict(genome=100_000_000, reads=100_000, len=(10_000, 10_000), err=(0.10, 0.10), sub=1 / 3),
+}
+GENOME_SEED = 20240
+READS_SEED = 777
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--reads", type=int, default=0, help="override reads per rank (smaller = NOT the named config)")
+    ap.add_argument("--cpu-sample", type=int, default=0, help="reads in the CPU baseline sample (0 = auto)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------------------------
+# clocks: nvidia-smi sampled during the timed region (B200_PROFILING.md)
+# ---------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        rows = [l for (t, l) in self.lines if t0 <= t <= t1 + 0.2] or [l for (_, l) in self.lines]
+        for l in rows:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU arm: the reference's own code (oracle/_ref/accaln_ref), P processes on P disjoint read slices
+# ---------------------------------------------------------------------------------------------------
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def write_fastq(path, reads, lens, start=0):
+    stride = reads.shape[1]
+    with open(path, "wb") as f:
+        for i in range(reads.shape[0]):
+            L = int(lens[i])
+            f.write(b"@r%d\n" % (start + i))
+            f.write(reads[i, :L].tobytes())
+            f.write(b"\n+\n")
+            f.write(b"I" * L)
+            f.write(b"\n")
+    return stride
+
+
+def parse_mlog_seconds(text, begin_key, end_key):
+    """mlog lines look like `[ Verbose     0.25 ] msg` (mlog/logger.c:75); returns t(end) - t(begin)."""
+    tb = te = None
+    for line in text.splitlines():
+        if "]" not in line or "[" not in line:
+            continue
+        head, msg = line.split("]", 1)
+        try:
+            t = float(head.replace("[", " ").split()[-1])
+        except (ValueError, IndexError):
+            continue
+        if begin_key in msg and tb is None:
+            tb = t
+        if end_key in msg:
+            te = t
+    if tb is None or te is None:
+        return None
+    return te - tb
+
+
+def cpu_reference_run(wl_name, sample_reads, procs, workdir):
+    """Runs the compiled reference (or, when oracle/_ref is absent, the oracle port) on `sample_reads` reads of the
+    workload.  Returns dict(value reads/s, cores, kind, sample, seconds)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib
+    import longreadmapper_b200 as lm
+    wl = WORKLOADS[wl_name]
+    g = lm.sim_genome(GENOME_SEED, wl["genome"])
+    reads, lens, _, _ = lm.sim_reads(READS_SEED, g, sample_reads, wl["len"][0], wl["len"][1], wl["err"][0], wl["err"][1],
+                                     wl["sub"])
+    t0 = time.time()
+    ix = oracle_lib.OracleIndex.build(["chr1"], [g.tobytes()])
+    t_index = time.time() - t0
+    if oracle_lib.have_ref():
+        fa = os.path.join(workdir, "g.fa")
+        with open(fa, "wb") as f:
+            f.write(b">chr1\n")
+            f.write(g.tobytes())
+            f.write(b"\n")
+        ix.write(fa)
+        ix.close()
+        procs = max(1, min(procs, sample_reads))
+        per = (sample_reads + procs - 1) // procs
+        fqs = []
+        for p in range(procs):
+            s, e = p * per, min(sample_reads, (p + 1) * per)
+            if s >= e:
+                break
+            fq = os.path.join(workdir, f"r{p}.fq")
+            write_fastq(fq, reads[s:e], lens[s:e], s)
+            fqs.append((fq, e - s))
+        exe = os.path.join(oracle_lib.REF_DIR, "accaln_ref")
+        t0 = time.time()
+        ps = [subprocess.Popen([exe, fa, fq, str(n), "20", "300"], stdout=subprocess.DEVNULL, stderr=subprocess.PIPE,
+                               text=True) for fq, n in fqs]
+        errs = [p.communicate()[1] for p in ps]
+        wall = time.time() - t0
+        if any(p.returncode != 0 for p in ps):
+            raise RuntimeError("accaln_ref failed: " + errs[0][-400:])
+        # mapping-only time per process: "Begin processing queries" -> "Done aligning" (alnmain.c:311,540)
+        secs = [parse_mlog_seconds(e, "Begin processing", "Done aligning") for e in errs]
+        secs = [s if s and s > 0 else wall for s in secs]
+        t = max(secs)
+        return dict(value=sample_reads / t, unit="reads/s", cores=len(fqs), kind="reference",
+                    sample=f"{sample_reads} reads of {wl_name} ({len(fqs)} accaln_ref processes, 1 thread each; index load "
+                           f"excluded; GACT = the oracle stand-in linked behind gact.h, the original submodule is absent)",
+                    seconds=t, wall_seconds=wall, index_build_seconds=t_index)
+    # port: the oracle's restatement, one thread
+    stride = reads.shape[1]
+    t0 = time.time()
+    ix.map_batch(reads, stride, lens, myers=False)
+    t = time.time() - t0
+    ix.close()
+    return dict(value=sample_reads / t, unit="reads/s", cores=1, kind="port",
+                sample=f"{sample_reads} reads of {wl_name} (oracle/oracle.c orc_map_batch, 1 thread)", seconds=t)
+
+
+def auto_cpu_sample(wl_name, cores, budget_s):
+    # measured single-thread rates of the reference build (SURVEY 6 + GACT stand-in): ~6k reads/s at 150 bp, ~8/s at 10 kbp
+    rate = {"c1": 6000.0, "c2": 6000.0, "c3": 8.0}[wl_name]
+    return int(max(cores * 50, min(WORKLOADS[wl_name]["reads"], rate * cores * budget_s)))
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    cores = host_cores()
+    wl = args.workload
+    sample = args.cpu_sample or auto_cpu_sample(wl, cores, 20.0)
+    per_step = []
+    with tempfile.TemporaryDirectory(prefix="accseq_ref_") as wd:
+        for i in range(args.warmup + args.steps):
+            if i < args.warmup and i > 0:
+                continue                      # one warm-up pass is enough to page the binaries and files in
+            r = cpu_reference_run(wl, sample, cores, wd)
+            if i >= args.warmup:
+                per_step.append(r)
+    t = float(np.mean([r["seconds"] for r in per_step]))
+    v = sample / t
+    r0 = per_step[0]
+    line = {"impl": "reference", "metric": "mapped reads/sec", "value": v, "unit": "reads/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * t, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u64/i32", "data": "synthetic",
+            "config": {"workload": workload_name(wl, args), "reads_per_step": sample, "seed_len": 20, "thres": 300},
+            "cpu_baseline": {"value": v, "unit": "reads/s", "cores": r0["cores"], "kind": r0["kind"], "sample": r0["sample"]},
+            "e2e": {"value": v, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+def workload_name(wl, args):
+    w = WORKLOADS[wl]
+    n = args.reads or w["reads"]
+    return (f"{wl}: {w['genome'] / 1e6:g} Mbp uniform synthetic genome (dna_txt_gen.py distribution, seeded), "
+            f"{n} reads/GPU of {w['len'][0]}-{w['len'][1]} bp at {w['err'][0] * 100:g}-{w['err'][1] * 100:g}% error")
+
+
+# ---------------------------------------------------------------------------------------------------
+# B200 arm
+# ---------------------------------------------------------------------------------------------------
+INT_OPS_PER_CELL = 9.0   # SASS count of the GACT inner cell (DESIGN.md "GACT kernel"), used for the INT32 roofline
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    import longreadmapper_b200 as lm
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if lm.device_count() < 1 or not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the hot path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    wl = WORKLOADS[args.workload]
+    n = args.reads or wl["reads"]
+
+    # ---- inputs: the index replica of this rank (built on the GPU) and this rank's read shard ----
+    g = lm.sim_genome(GENOME_SEED, wl["genome"])
+    t0 = time.time()
+    mapper = lm.GpuMapper.build([g], local)
+    t_index = time.time() - t0
+    dev = torch.device("cuda", local)
+    reads, lens, truth_pos, truth_strand = lm.sim_reads(READS_SEED + 1000 * rank, g, n, wl["len"][0], wl["len"][1],
+                                                        wl["err"][0], wl["err"][1], wl["sub"])
+    stride = reads.shape[1]
+    max_len = int(lens.max())
+    store_stride = 2 * max_len
+    params = mapper.params()
+
+    # one non-default stream for everything that is timed: the library launches on it (as_gpu_set_stream), the
+    # restore copy and the CUDA events are issued on it
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    mapper.set_stream(stream.cuda_stream)
+    d_pristine = torch.from_numpy(reads).to(dev)
+    d_reads = torch.empty_like(d_pristine)
+    d_lens = torch.from_numpy(lens.view(np.int32)).to(dev)
+    d_res = torch.empty(n * lm.RESULT_DTYPE.itemsize, dtype=torch.uint8, device=dev)
+    d_store = torch.empty(n * store_stride, dtype=torch.uint8, device=dev)
+    torch.cuda.synchronize()
+
+    def step_device():
+        d_reads.copy_(d_pristine)            # strand-1 reads are reverse-complemented in place by every pass
+        mapper.map_batch_device(d_reads.data_ptr(), stride, d_lens.data_ptr(), n, max_len, d_res.data_ptr(),
+                                d_store.data_ptr(), store_stride, params)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+    mapper.stats_reset()
+    launches0 = mapper.launch_count()
+    stage_ms = {}
+    sampler = ClockSampler(local)
+    sampler.start()
+    time.sleep(0.25)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t_wall0 = time.time()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_device()
+    e1.record(stream)
+    barrier()
+    t_wall1 = time.time()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop(t_wall0, t_wall1)
+    launches = mapper.launch_count() - launches0 + args.steps       # + the restore copy of every step
+    tm = mapper.last_timing()
+    st = mapper.stats()
+    if world > 1:
+        tmax = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        ms = float(tmax.item())
+        # the one collective of the design: shard statistics (alnmain.c:541 Sensitivity line)
+        keys = sorted(st)
+        sv = torch.tensor([st[k] for k in keys], dtype=torch.int64, device=dev)
+        dist.all_reduce(sv, op=dist.ReduceOp.SUM)
+        st = dict(zip(keys, [int(x) for x in sv.tolist()]))
+    ms_per_step = ms / args.steps
+    value = world * n / (ms_per_step / 1e3)
+
+    # correctness of what was timed: the results of the last step against the simulated truth
+    res = np.frombuffer(d_res.cpu().numpy().tobytes(), dtype=lm.RESULT_DTYPE)
+    ok = res["valid"] == 1
+    exact = float(((res["off"] == truth_pos) & ok & ((res["strand"] == 1) == (truth_strand == 1))).mean())
+
+    # ---- e2e: host buffers through the C ABI ----
+    e2e = None
+    if not args.no_e2e:
+        L = mapper.L
+        import ctypes as C
+        nb_reads, nb_res, nb_store = n * stride, n * lm.RESULT_DTYPE.itemsize, n * store_stride
+        hp = [L.as_host_alloc(x) for x in (nb_reads, 4 * n, nb_res, nb_store, nb_reads)]
+        if not all(hp):
+            raise SystemExit("bench.py: pinned allocation failed")
+        h_reads = np.ctypeslib.as_array(C.cast(hp[0], C.POINTER(C.c_uint8)), shape=(n, stride))
+        h_lens = np.ctypeslib.as_array(C.cast(hp[1], C.POINTER(C.c_uint32)), shape=(n,))
+        h_src = np.ctypeslib.as_array(C.cast(hp[4], C.POINTER(C.c_uint8)), shape=(n, stride))
+        h_src[:] = reads
+        h_lens[:] = lens
+
+        def step_e2e():
+            h_reads[:] = h_src             # host-side restore of the batch (host memcpy, part of the user's step)
+            rc = L.as_map_batch(mapper.h, C.byref(params), hp[0], stride, hp[1], n, hp[2], hp[3], store_stride)
+            if rc != 0:
+                raise SystemExit(f"as_map_batch failed ({rc}): {L.as_last_error().decode()}")
+
+        for _ in range(max(1, min(args.warmup, 2))):
+            step_e2e()
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record(stream)
+        for _ in range(args.steps):
+            step_e2e()
+        f1.record(stream)
+        barrier()
+        ems = f0.elapsed_time(f1)
+        if world > 1:
+            tmax = torch.tensor([ems], dtype=torch.float64, device=dev)
+            dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+            ems = float(tmax.item())
+        e2e_tm = mapper.last_timing()
+        hres = np.ctypeslib.as_array(C.cast(hp[2], C.POINTER(C.c_uint8)), shape=(nb_res,)).view(lm.RESULT_DTYPE)
+        same = bool(np.array_equal(hres, res))
+        e2e = {"value": world * n / (ems / args.steps / 1e3), "unit": "reads/s",
+               "h2d_bytes_per_step": nb_reads + 4 * n, "d2h_bytes_per_step": nb_res + nb_store + nb_reads,
+               "ms_per_step": ems / args.steps, "same_results_as_device_path": same,
+               "stage_ms_last_step": {k: round(v, 3) for k, v in e2e_tm.items()}}
+        for p in hp:
+            L.as_host_free(p)
+
+    # ---- roofline of the dominant kernel (stage times: CUDA events inside the library, on the timing stream) ----
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
+    steps = args.steps
+    per_step = {k: st[k] / steps / world for k in st}
+    # algorithmic bytes of seeding+voting per SURVEY 8(d): 16 B lc pair per seed + 49 B per backward step + 5 B per SA hit
+    vote_bytes = per_step["seeds"] * 16 + per_step["bs_steps"] * 49 + per_step["sa_hits"] * 5 + n * max_len / 4
+    sm_clock = (clocks.get("sm_mhz") or 1965.0) * 1e6
+    int_peak = 148 * 128 * 1965.0e6 / 1e12          # lanes x max clock, Tops/s
+    stages = {
+        "part1_seed_vote": {"ms": tm["part1"], "bound": "hbm", "achieved": vote_bytes / (tm["part1"] / 1e3) / 1e9 if tm["part1"] else None,
+                            "peak": hbm_peak, "unit": "GB/s"},
+        "part2_locus": {"ms": tm["part2"]},
+        "gact": {"ms": tm["gact"], "bound": "int32",
+                 "gcups": per_step["dp_cells"] / (tm["gact"] / 1e3) / 1e9 if tm["gact"] else None,
+                 "achieved": per_step["dp_cells"] * INT_OPS_PER_CELL / (tm["gact"] / 1e3) / 1e12 if tm["gact"] else None,
+                 "peak": int_peak, "unit": "Tops/s"},
+    }
+    for s in stages.values():
+        if s.get("achieved") is not None:
+            s["frac"] = s["achieved"] / s["peak"]
+    dom = max(("part1_seed_vote", "gact"), key=lambda k: stages[k]["ms"])
+    d = stages[dom]
+    roofline = {"kernel": "k_gact" if dom == "gact" else "k_vote", "bound": d["bound"], "achieved": d["achieved"],
+                "peak": d["peak"], "unit": d["unit"], "frac": d.get("frac"), "traffic": None,
+                "peak_source": peak_src if d["bound"] == "hbm" else "148 SMs x 128 INT32 lanes x clocks.max.sm 1965 MHz",
+                "ms_per_launch": d["ms"], "share_of_step": d["ms"] / tm["total"] if tm["total"] else None,
+                "stages": stages, "sm_clock_mhz_under_load": sm_clock / 1e6}
+
+    line = {"metric": "mapped reads/sec", "value": value, "unit": "reads/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u64/i32", "data": "synthetic",
+            "config": {"workload": workload_name(args.workload, args), "reads_per_step_per_gpu": n, "seed_len": 20,
+                       "thres": 300, "gact_T": int(params.gact_T), "gact_O": int(params.gact_O),
+                       "l2": "inputs exceed L2 (reads 151 MB + lc table 256 MB + SA 37 MB per pass > 126 MB)",
+                       "index": "built on the GPU (as_gpu_build), replicated per rank", "index_build_s": round(t_index, 2)},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+            "roofline": roofline,
+            "gcups": stages["gact"]["gcups"],
+            "quality": {"mapped_frac": float(ok.mean()), "exact_pos_strand_frac": exact,
+                        "valid_total": [st["valid"], st["total"]]},
+            "stats_per_step_per_gpu": {k: per_step[k] for k in ("seeds", "bs_steps", "sa_hits", "dp_cells", "overflow_reads")}}
+
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cores = host_cores()
+        sample = args.cpu_sample or auto_cpu_sample(args.workload, cores, 12.0)
+        try:
+            with tempfile.TemporaryDirectory(prefix="accseq_cpu_") as wd:
+                cb = cpu_reference_run(args.workload, sample, cores, wd)
+            line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        except Exception as ex:          # the CPU leg must not lose the GPU numbers
+            line["cpu_baseline"] = {"value": None, "unit": "reads/s", "cores": cores, "kind": "reference", "sample": f"failed: {ex}"}
+    elif rank == 0:
+        line["cpu_baseline"] = None
+    if rank == 0:
+        print(json.dumps(line))
+    mapper.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_b200(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

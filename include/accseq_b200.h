@@ -60,6 +60,28 @@ typedef struct as_index_view {
  * Replaces nothing in the reference (it keeps host arrays); lookups return identical values. */
 int  as_gpu_open(as_gpu **h, int device, const as_index_view *ix);
 void as_gpu_close(as_gpu *h);
+
+/* Build the index ON the GPU from the .cat text (asindex.c:97-110: forward + reverse complement per sequence,
+ * one final '$') -- replaces fmi_build (fmidx.c:166-199: pSAscan suffix sort psascan/sa_use.cc:8-18, BWT
+ * :76-98, C table :101-125, O table :128-150) and lc_build (lchash.c:52-73) of the reference's `accidx`.
+ * Requires con_len < 2^32-1.  The handle is ready for as_map_batch; as_gpu_export returns the same index in
+ * the reference's layouts, byte-identical to the files accidx writes. */
+int  as_gpu_build(as_gpu **h, int device, const char *content, uint64_t con_len, const as_mta *mta, int mta_len,
+                  int hlen);
+typedef struct as_index_out {       /* caller-owned buffers; a NULL member is skipped */
+    uint64_t *C;                    /* 256 entries */
+    uint64_t *O;                    /* 4*(N/o_ratio+1) entries (fmidx.c:128-150) */
+    int       o_ratio;              /* must divide 64; the reference uses 32 (asindex.c:138) */
+    char     *bwt;                  /* N bytes */
+    uint64_t *lc;                   /* 2*4^hlen entries, MSB-first code order (lchash.c:36-49) */
+    void     *sa;                   /* N entries of sa_entry_bytes (5 = .sa5 bytes, 8 = u64 / ui40_t structs) */
+    int       sa_entry_bytes;
+    uint64_t *csa;                  /* ceil(N/csa_ratio) entries written: SA[csa_ratio*i] (fmidx.c:153-163) */
+    int       csa_ratio;
+} as_index_out;
+int  as_gpu_export(as_gpu *h, as_index_out *out);
+/* rows of the index (dna_fmi.length) and the hash length of a handle */
+uint64_t as_gpu_index_length(as_gpu *h);
 /* Route all work of this handle to a caller-owned CUDA stream (a cudaStream_t cast to void*); NULL = the
  * handle's own stream.  Lets a host framework time/overlap the calls on its own stream. */
 int  as_gpu_set_stream(as_gpu *h, void *cuda_stream);

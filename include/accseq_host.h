@@ -39,6 +39,12 @@ typedef struct as_host_index {
 } as_host_index;
 int  as_index_load(const char *fasta_path, as_host_index **out);   /* <fa>.mta, <fa>.cat{,.mfi,.lch,.sa5} */
 void as_index_free(as_host_index *ix);
+/* construction side (asindex.c:78-153): the .cat image of a set of sequences, buffers for as_gpu_export,
+ * and the writer of the five files */
+char *as_cat_build(int nseq, const char *const *seqs, const uint64_t *lens, as_mta *mta, uint64_t *con_len);
+as_host_index *as_index_alloc(uint64_t n, int hlen, int o_ratio, int csa_ratio, int mta_len);
+void as_index_out_of(as_host_index *ix, as_index_out *out);
+int  as_index_write(const char *fasta_path, const as_host_index *ix);
 
 /* ---- SAM emit (alnmain.c:62-75, 485-526) ---- */
 int  as_sam_header(FILE *out, const as_host_index *ix, long rg_id);

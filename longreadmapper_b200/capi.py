@@ -35,6 +35,11 @@ class AsIndexView(C.Structure):
                 ("con_len", C.c_uint64), ("mta", C.c_void_p), ("mta_len", C.c_int)]
 
 
+class AsIndexOut(C.Structure):
+    _fields_ = [("C", C.c_void_p), ("O", C.c_void_p), ("o_ratio", C.c_int), ("bwt", C.c_void_p), ("lc", C.c_void_p),
+                ("sa", C.c_void_p), ("sa_entry_bytes", C.c_int), ("csa", C.c_void_p), ("csa_ratio", C.c_int)]
+
+
 class Params(C.Structure):
     _fields_ = [("seed_len", C.c_uint32), ("thres", C.c_uint32), ("gact_T", C.c_int32), ("gact_O", C.c_int32),
                 ("flags", C.c_uint32)]
@@ -74,6 +79,10 @@ def cuda_lib():
     L.as_last_error.restype = C.c_char_p
     L.as_device_count.restype = i32
     L.as_gpu_open.argtypes = [C.POINTER(vp), i32, C.POINTER(AsIndexView)]
+    L.as_gpu_build.argtypes = [C.POINTER(vp), i32, vp, u64, vp, i32, i32]
+    L.as_gpu_export.argtypes = [vp, C.POINTER(AsIndexOut)]
+    L.as_gpu_index_length.argtypes = [vp]
+    L.as_gpu_index_length.restype = u64
     L.as_gpu_close.argtypes = [vp]
     L.as_gpu_close.restype = None
     L.as_gpu_set_stream.argtypes = [vp, vp]
@@ -116,10 +125,17 @@ def host_lib():
     L.as_sim_reads.argtypes = [u64, vp, u64, sz, C.c_uint32, C.c_uint32, C.c_double, C.c_double, C.c_double, vp, sz,
                                vp, vp, vp]
     L.as_sim_reads.restype = sz
-    if hasattr(L, "as_index_load"):
-        L.as_index_load.argtypes = [C.c_char_p, C.POINTER(C.POINTER(AsHostIndex))]
-        L.as_index_free.argtypes = [C.POINTER(AsHostIndex)]
-        L.as_index_free.restype = None
+    L.as_index_load.argtypes = [C.c_char_p, C.POINTER(C.POINTER(AsHostIndex))]
+    L.as_index_free.argtypes = [C.POINTER(AsHostIndex)]
+    L.as_index_free.restype = None
+    L.as_cat_build.argtypes = [C.c_int, C.POINTER(C.c_char_p), C.POINTER(u64), vp, C.POINTER(u64)]
+    L.as_cat_build.restype = vp
+    L.as_index_alloc.argtypes = [u64, C.c_int, C.c_int, C.c_int, C.c_int]
+    L.as_index_alloc.restype = C.POINTER(AsHostIndex)
+    L.as_index_out_of.argtypes = [C.POINTER(AsHostIndex), vp]
+    L.as_index_out_of.restype = None
+    L.as_index_write.argtypes = [C.c_char_p, C.POINTER(AsHostIndex)]
+    L.as_cigar_text.argtypes = [vp, C.c_int, C.c_char_p, sz]
     _host = L
     return L
 
@@ -157,6 +173,33 @@ def sim_reads(seed, genome, n_reads, len_min, len_max, err_min, err_max, sub_fra
     return reads, lens, pos, strand
 
 
+def cat_image(seqs):
+    """The .cat text of a list of sequences (uint8 arrays / bytes): forward + reverse complement each, final '$'
+    (asindex.c:97-110).  Returns (cat uint8[N], [(offset, seq_len)])."""
+    comp = np.zeros(256, np.uint8)
+    comp[:] = ord("N")
+    for a, b in zip(b"ACGT", b"TGCA"):
+        comp[a] = b
+    parts, mta, off = [], [], 0
+    for s in seqs:
+        s = np.frombuffer(bytes(s), np.uint8) if not isinstance(s, np.ndarray) else s
+        s = np.where(s > 0x60, s - 0x20, s).astype(np.uint8)
+        parts += [s, comp[s][::-1]]
+        mta.append((off, int(s.size)))
+        off += 2 * int(s.size)
+    parts.append(np.frombuffer(b"$", np.uint8))
+    return np.ascontiguousarray(np.concatenate(parts)), mta
+
+
+def cigar_text(ops):
+    ops = np.ascontiguousarray(ops, dtype=np.uint8)
+    buf = C.create_string_buffer(4 * ops.size + 16)
+    n = host_lib().as_cigar_text(ops.ctypes.data, ops.size, buf, len(buf))
+    if n < 0:
+        raise AccSeqError("bad column ops")
+    return buf.value.decode()
+
+
 # ---------------------------------------------------------------------------------------------------
 def _ptr(a):
     return a.ctypes.data if a is not None else None
@@ -189,6 +232,35 @@ class GpuMapper:
         return cls(device, length=ox.n, C_table=ox.Ctab, O=ox.O, o_ratio=ox.s.o_ratio, bwt=ox.bwt, lc=ox.lc,
                    hlen=ox.s.hlen, sa=ox.sa, sa_entry_bytes=8, content=ox.cat,
                    mta=[(o, s) for (_, o, s) in ox.mta])
+
+    @classmethod
+    def build(cls, seqs, device=0, hlen=12, names=None):
+        """Index construction on the GPU from raw sequences (the accidx path: asindex.c:129-153)."""
+        L = cuda_lib()
+        cat, mta = cat_image(seqs)
+        mta_arr = (AsMta * max(1, len(mta)))(*[AsMta(o, s) for (o, s) in mta])
+        h = C.c_void_p()
+        rc = L.as_gpu_build(C.byref(h), device, cat.ctypes.data, cat.size, C.cast(mta_arr, C.c_void_p), len(mta), hlen)
+        if rc != 0:
+            raise AccSeqError(f"as_gpu_build failed ({rc}): {L.as_last_error().decode()}")
+        self = cls.__new__(cls)
+        self.h, self.L, self.device, self.N, self._keep = h, L, device, int(cat.size), None
+        self.names = list(names) if names else [f"seq{i}" for i in range(len(mta))]
+        self.mta, self.hlen = mta, hlen
+        return self
+
+    def export(self, o_ratio=32, csa_ratio=4, hlen=None, sa_entry_bytes=8):
+        """The index in the reference's in-memory layouts: dict of numpy arrays C, O, bwt, lc, sa, csa."""
+        hlen = hlen if hlen is not None else getattr(self, "hlen", 12)
+        N = self.N
+        out = dict(C=np.zeros(256, np.uint64), O=np.zeros(4 * (N // o_ratio + 1), np.uint64), bwt=np.zeros(N, np.uint8),
+                   lc=np.zeros(2 * 4 ** hlen, np.uint64),
+                   sa=np.zeros(N, np.uint64) if sa_entry_bytes == 8 else np.zeros(N * 5, np.uint8),
+                   csa=np.zeros(N // csa_ratio + 1, np.uint64))
+        o = AsIndexOut(out["C"].ctypes.data, out["O"].ctypes.data, o_ratio, out["bwt"].ctypes.data, out["lc"].ctypes.data,
+                       out["sa"].ctypes.data, sa_entry_bytes, out["csa"].ctypes.data, csa_ratio)
+        self._check(self.L.as_gpu_export(self.h, C.byref(o)), "as_gpu_export")
+        return out
 
     @classmethod
     def from_index_files(cls, fasta_path, device=0):

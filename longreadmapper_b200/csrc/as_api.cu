@@ -34,6 +34,9 @@ static int run_stages(as_gpu *h, const as_params *p, char *d_reads, size_t strid
     if (stop_after_vote) return AS_OK;
     AS_TRY(as_launch_locus(h, d_reads, stride, d_lens, n, d_pack, ws, d_vote, d_res, d_toff));
     AS_CUDA(cudaEventRecord(h->ev[3], h->stream));
+    /* columns past n_cigar_op stay zero, so equal inputs give equal bytes whatever ran before (the reference
+     * leaves them uninitialised, alnmain.c:316-320) */
+    if (!(p->flags & AS_F_NO_ALIGN) && d_store) AS_CUDA(cudaMemsetAsync(d_store, 0, n * store_stride, h->stream));
     if (!(p->flags & AS_F_NO_ALIGN))
         AS_TRY(as_launch_gact(h, p, d_pack, ws, d_lens, h->ix.text2, d_toff, nullptr, n, max_len, max_len, d_store,
                               store_stride, nullptr, nullptr, d_res));
@@ -193,6 +196,7 @@ extern "C" int as_gpu_stats_reset(as_gpu *h) {
 }
 
 extern "C" uint64_t as_gpu_launch_count(as_gpu *h) { return h ? h->launches : 0; }
+extern "C" uint64_t as_gpu_index_length(as_gpu *h) { return h ? h->ix.N : 0; }
 
 /* ---------------------------------------------------------------------------------------------- */
 /* PART 1 only                                                                                     */

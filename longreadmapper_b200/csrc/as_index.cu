@@ -308,6 +308,56 @@ out:
     return rc;
 }
 
+/* device checks, stream, events, stats buffer; NULL (with as_last_error set) when the device is unusable */
+as_gpu *as_handle_new(int device) {
+    int ndev = as_device_count();
+    if (ndev <= 0 || device < 0 || device >= ndev) {
+        as_set_error("as_gpu_open: no usable CUDA device %d (found %d); there is no CPU fallback", device, ndev);
+        return nullptr;
+    }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) {
+        as_set_error("as_gpu_open: cudaGetDeviceProperties(%d) failed", device);
+        return nullptr;
+    }
+    if (prop.major != 10) {
+        as_set_error("as_gpu_open: device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+        return nullptr;
+    }
+    if (cudaSetDevice(device) != cudaSuccess) {
+        as_set_error("as_gpu_open: cudaSetDevice(%d) failed", device);
+        return nullptr;
+    }
+    as_gpu *h = new (std::nothrow) as_gpu();
+    if (!h) return nullptr;
+    h->device = device;
+    h->sm_count = prop.multiProcessorCount;
+    cudaError_t e = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        as_set_error("cudaStreamCreate: %s", cudaGetErrorString(e));
+        delete h;
+        return nullptr;
+    }
+    h->stream = h->own_stream;
+    for (cudaEvent_t &ev : h->ev) cudaEventCreate(&ev);
+    if (cudaMalloc((void **)&h->d_stats, 16 * sizeof(unsigned long long)) != cudaSuccess ||
+        cudaMemset(h->d_stats, 0, 16 * sizeof(unsigned long long)) != cudaSuccess) {
+        as_set_error("as_gpu_open: cudaMalloc(stats) failed");
+        as_gpu_close(h);
+        return nullptr;
+    }
+    return h;
+}
+
+int as_launch_pack_text(as_gpu *h, const uint8_t *d_in, uint64_t n, uint32_t *d_out) {
+    uint64_t nw = (n + 15) >> 4;
+    int grid = (int)((nw + 255) / 256 < 148 * 16 ? (nw + 255) / 256 : 148 * 16);
+    k_pack_text<<<grid ? grid : 1, 256, 0, h->stream>>>(d_in, n, d_out);
+    h->launches++;
+    AS_CUDA(cudaGetLastError());
+    return AS_OK;
+}
+
 extern "C" int as_gpu_open(as_gpu **out, int device, const as_index_view *v) {
     if (!out || !v) return AS_EINVAL;
     *out = nullptr;
@@ -332,36 +382,8 @@ extern "C" int as_gpu_open(as_gpu **out, int device, const as_index_view *v) {
         as_set_error("as_gpu_open: bad length/con_len");
         return AS_EINVAL;
     }
-    int ndev = as_device_count();
-    if (ndev <= 0 || device < 0 || device >= ndev) {
-        as_set_error("as_gpu_open: no usable CUDA device %d (found %d); there is no CPU fallback", device, ndev);
-        return AS_ENODEV;
-    }
-    cudaDeviceProp prop;
-    AS_CUDA(cudaGetDeviceProperties(&prop, device));
-    if (prop.major != 10) {
-        as_set_error("as_gpu_open: device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
-        return AS_ENODEV;
-    }
-    AS_CUDA(cudaSetDevice(device));
-    as_gpu *h = new (std::nothrow) as_gpu();
-    if (!h) return AS_ENOMEM;
-    h->device = device;
-    h->sm_count = prop.multiProcessorCount;
-    cudaError_t e = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking);
-    if (e != cudaSuccess) {
-        as_set_error("cudaStreamCreate: %s", cudaGetErrorString(e));
-        delete h;
-        return AS_ECUDA;
-    }
-    h->stream = h->own_stream;
-    for (cudaEvent_t &ev : h->ev) cudaEventCreate(&ev);
-    if (cudaMalloc((void **)&h->d_stats, 16 * sizeof(unsigned long long)) != cudaSuccess ||
-        cudaMemset(h->d_stats, 0, 16 * sizeof(unsigned long long)) != cudaSuccess) {
-        as_set_error("as_gpu_open: cudaMalloc(stats) failed");
-        as_gpu_close(h);
-        return AS_ENOMEM;
-    }
+    as_gpu *h = as_handle_new(device);
+    if (!h) return AS_ENODEV;
     int rc = build_index(h, v);
     if (rc != AS_OK) {
         as_gpu_close(h);
