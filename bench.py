@@ -329,15 +329,10 @@ def run_b200(args):
     launches = mapper.launch_count() - launches0 + args.steps       # + the restore copy of every step
     tm = mapper.last_timing()
     st = mapper.stats()
-    if world > 1:
-        tmax = torch.tensor([ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        ms = float(tmax.item())
-        # the one collective of the design: shard statistics (alnmain.c:541 Sensitivity line)
-        keys = sorted(st)
-        sv = torch.tensor([st[k] for k in keys], dtype=torch.int64, device=dev)
-        dist.all_reduce(sv, op=dist.ReduceOp.SUM)
-        st = dict(zip(keys, [int(x) for x in sv.tolist()]))
+    from longreadmapper_b200 import shard
+    ms = shard.max_over_ranks(ms, dev)
+    # the one collective of the design: shard statistics (alnmain.c:541 Sensitivity line)
+    st = shard.reduce_stats(st, dev)
     ms_per_step = ms / args.steps
     value = world * n / (ms_per_step / 1e3)
 
@@ -377,10 +372,7 @@ def run_b200(args):
         f1.record(stream)
         barrier()
         ems = f0.elapsed_time(f1)
-        if world > 1:
-            tmax = torch.tensor([ems], dtype=torch.float64, device=dev)
-            dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-            ems = float(tmax.item())
+        ems = shard.max_over_ranks(ems, dev)
         e2e_tm = mapper.last_timing()
         hres = np.ctypeslib.as_array(C.cast(hp[2], C.POINTER(C.c_uint8)), shape=(nb_res,)).view(lm.RESULT_DTYPE)
         same = bool(np.array_equal(hres, res))

@@ -4,6 +4,7 @@ The product is the C-ABI library ``libaccseq_b200.so`` (include/accseq_b200.h) p
 ``libaccseq_host.so`` (include/accseq_host.h).  This package is only the ctypes view of both that the tests,
 ``bench.py`` and ``__graft_entry__`` use; there is no CPU fallback behind it.
 """
+from . import capi, shard
 from .capi import (AS_F_MYERS, AS_F_NO_ALIGN, RESULT_DTYPE, AccSeqError, GpuMapper, Params, build_native,
                    cat_image, cigar_text, cuda_lib, device_count, host_lib, sim_genome, sim_plant_repeats, sim_reads)
 

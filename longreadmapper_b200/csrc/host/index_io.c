@@ -269,7 +269,21 @@ int as_index_write(const char *fa, const as_host_index *ix) {
     if (!fp) return AS_EIO;
     bad = wr(fp, ix->C, 256 * 8) | wr(fp, &ix->view.o_ratio, sizeof(int)) | wr(fp, &ix->view.o_len, 8) |
           wr(fp, ix->O, ix->view.o_len * 8) | wr(fp, &n, 8) | wr(fp, ix->bwt, n) | wr(fp, &ix->csa_ratio, sizeof(int)) |
-          wr(fp, &ix->csa_len, 8) | wr(fp, ix->csa, ix->csa_len * 8);
+          wr(fp, &ix->csa_len, 8);
+    if (ix->csa) {
+        bad |= wr(fp, ix->csa, ix->csa_len * 8);
+    } else {
+        /* an index loaded by as_index_load does not keep the sampled SA: csa[i] = SA[csa_ratio*i] (fmidx.c:153-163) */
+        for (uint64_t i = 0; i < ix->csa_len && !bad; i++) {
+            const uint64_t row = i * (uint64_t)ix->csa_ratio;
+            uint64_t v = 0;
+            if (row < n) {
+                const uint8_t *e = ix->sa5 + 5 * row;
+                v = (uint64_t)e[0] | (uint64_t)e[1] << 8 | (uint64_t)e[2] << 16 | (uint64_t)e[3] << 24 | (uint64_t)e[4] << 32;
+            }
+            bad |= wr(fp, &v, 8);
+        }
+    }
     bad |= fclose(fp);
     if (bad) return AS_EIO;
     fp = create2(fa, ".cat.lch");

@@ -1,0 +1,192 @@
+"""CPU tests (-m "not gpu") of the drop-in boundary and the host helpers: the C-ABI libraries load and export
+every symbol include/*.h declares, compute entries fail loudly without a GPU (no CPU fallback), and the plain-C
+host side (index files, FASTQ ingest, SAM emit) agrees with the files/records the compiled reference wrote."""
+import ctypes as C
+import gzip
+import os
+import re
+
+import numpy as np
+import pytest
+
+import oracle_lib
+from test_oracle_vs_ref import GOLD, read_fasta_gz, read_fastq_gz
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared(header):
+    text = open(os.path.join(ROOT, "include", header)).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(as_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_cuda_library_exports_every_declared_symbol(native):
+    L = native.cuda_lib()
+    names = declared("accseq_b200.h")
+    assert len(names) >= 24
+    for n in names:
+        assert hasattr(L, n), f"libaccseq_b200.so does not export {n}"
+
+
+def test_host_library_exports_every_declared_symbol(native):
+    L = native.host_lib()
+    names = declared("accseq_host.h")
+    assert len(names) >= 15
+    for n in names:
+        assert hasattr(L, n), f"libaccseq_host.so does not export {n}"
+
+
+def test_gact_header_names_are_defined_by_the_oracle_glue():
+    """the reference's own sources compile against include/gact/gact.h (oracle/Makefile); the names it needs"""
+    text = open(os.path.join(ROOT, "include", "gact", "gact.h")).read()
+    for n in ("mmstring", "cigar", "ms_borrow", "simple_gact", "parse_cigar", "n_cigar_op", "score"):
+        assert n in text
+
+
+def test_no_cpu_fallback(native):
+    """without a device every compute entry fails with AS_ENODEV and says why"""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    L = native.cuda_lib()
+    assert native.device_count() == 0
+    g = native.sim_genome(1, 2000)
+    cat, mta = native.cat_image([g])
+    arr = (native.capi.AsMta * 1)(native.capi.AsMta(mta[0][0], mta[0][1]))
+    h = C.c_void_p()
+    rc = L.as_gpu_build(C.byref(h), 0, cat.ctypes.data, cat.size, C.cast(arr, C.c_void_p), 1, 12)
+    assert rc == -19 and not h.value
+    assert b"device" in L.as_last_error().lower() or b"cuda" in L.as_last_error().lower()
+    with pytest.raises(native.AccSeqError):
+        native.GpuMapper.build([g], 0)
+
+
+def test_params_default(native):
+    p = native.Params()
+    native.cuda_lib().as_params_default(C.byref(p))
+    assert (p.seed_len, p.thres, p.gact_T, p.gact_O, p.flags) == (20, 300, 320, 120, 0)   # alnmain.c:577-580
+
+
+# ------------------------------------------------------------------------------------------------
+# host helpers
+# ------------------------------------------------------------------------------------------------
+def test_cat_image_matches_oracle(native, orc):
+    names, seqs = read_fasta_gz(os.path.join(GOLD, "repeat.fa.gz"))
+    ix = orc.OracleIndex.build(names, seqs)
+    cat, mta = native.cat_image(seqs)
+    assert np.array_equal(cat, ix.cat)
+    assert mta == [(o, s) for (_, o, s) in ix.mta]
+    # and the C builder (asindex.c:97-110)
+    H = native.host_lib()
+    n = len(seqs)
+    out_mta = (native.capi.AsMta * n)()
+    con_len = C.c_uint64(0)
+    p = H.as_cat_build(n, (C.c_char_p * n)(*seqs), (C.c_uint64 * n)(*[len(s) for s in seqs]), C.cast(out_mta, C.c_void_p),
+                       C.byref(con_len))
+    assert p and con_len.value == ix.n
+    assert C.string_at(p, con_len.value) == ix.cat.tobytes()
+    assert [(m.offset, m.seq_len) for m in out_mta] == mta
+    C.CDLL(None).free(C.c_void_p(p))
+    ix.close()
+
+
+def test_index_loader_reads_reference_files(native, orc, tmp_path):
+    """as_index_load reads the five files in the reference's formats (fmidx.c:246-275, lchash.c:114-127,
+    alnmain.c:125-140,237-252); the files here are sha256-identical to accidx_ref's (test_oracle_vs_ref)."""
+    names, seqs = read_fasta_gz(os.path.join(GOLD, "repeat.fa.gz"))
+    ix = orc.OracleIndex.build(names, seqs)
+    fa = str(tmp_path / "g.fa")
+    ix.write(fa)
+    H = native.host_lib()
+    p = C.POINTER(native.capi.AsHostIndex)()
+    assert H.as_index_load(fa.encode(), C.byref(p)) == 0
+    v = p.contents.view
+    assert v.length == ix.n and v.o_ratio == 32 and v.hlen == 12 and v.mta_len == 2 and v.sa_entry_bytes == 5
+    view = oracle_lib._np_view
+    assert np.array_equal(view(v.bwt, np.uint8, ix.n), ix.bwt)
+    assert np.array_equal(view(v.C, np.uint64, 256), ix.Ctab)
+    assert np.array_equal(view(v.O, np.uint64, v.o_len), ix.O)
+    assert np.array_equal(view(v.lc, np.uint64, v.lc_len), ix.lc)
+    assert np.array_equal(view(v.content, np.uint8, v.con_len), ix.cat)
+    sa5 = view(v.sa, np.uint8, 5 * ix.n).reshape(-1, 5)
+    assert np.array_equal(sa5[:, :4].copy().view("<u4").ravel().astype(np.uint64) | (sa5[:, 4].astype(np.uint64) << 32), ix.sa)
+    assert [p.contents.names[i].decode() for i in range(2)] == names
+    # write them back with the C writer: identical bytes
+    fb = str(tmp_path / "h.fa")
+    assert H.as_index_write(fb.encode(), p) == 0
+    for ext in (".mta", ".cat", ".cat.sa5", ".cat.mfi", ".cat.lch"):
+        assert open(fa + ext, "rb").read() == open(fb + ext, "rb").read(), ext
+    H.as_index_free(p)
+    assert H.as_index_load(str(tmp_path / "missing.fa").encode(), C.byref(p)) != 0
+    ix.close()
+
+
+class ReadBatch(C.Structure):
+    _fields_ = [("n", C.c_size_t), ("stride", C.c_size_t), ("max_len", C.c_uint32), ("seqs", C.c_void_p),
+                ("lens", C.POINTER(C.c_uint32)), ("names", C.POINTER(C.c_char_p)), ("quals", C.POINTER(C.c_char_p))]
+
+
+def fastq_api(H):
+    H.as_fastq_open.restype = C.c_void_p
+    H.as_fastq_open.argtypes = [C.c_char_p]
+    H.as_fastq_next_batch.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(ReadBatch), C.c_void_p]
+    H.as_read_batch_free.argtypes = [C.POINTER(ReadBatch), C.c_void_p]
+    H.as_read_batch_free.restype = None
+    H.as_fastq_close.argtypes = [C.c_void_p]
+    H.as_fastq_close.restype = None
+    return H
+
+
+@pytest.mark.parametrize("gz", [True, False])
+def test_fastq_batches(native, tmp_path, gz):
+    """reads_load + refactor_reads_seq (accaln.c:45-58, alnmain.c:87-103): batches of <= max_reads, one zero
+    padded buffer of stride max_len+1"""
+    H = fastq_api(native.host_lib())
+    recs = read_fastq_gz(os.path.join(GOLD, "reads.fq.gz"))
+    path = os.path.join(GOLD, "reads.fq.gz")
+    if not gz:
+        path = str(tmp_path / "r.fq")
+        open(path, "wb").write(gzip.open(os.path.join(GOLD, "reads.fq.gz"), "rb").read())
+    fq = H.as_fastq_open(path.encode())
+    assert fq
+    seen = 0
+    while True:
+        b = ReadBatch()
+        assert H.as_fastq_next_batch(fq, 100, C.byref(b), None) == 0
+        if b.n == 0:
+            break
+        assert b.n <= 100 and b.stride == b.max_len + 1
+        buf = oracle_lib._np_view(b.seqs, np.uint8, b.n * b.stride).reshape(b.n, b.stride)
+        for i in range(b.n):
+            name, s, q = recs[seen + i]
+            assert b.lens[i] == len(s) and buf[i, :len(s)].tobytes() == s and not buf[i, len(s):].any()
+            assert b.names[i].decode() == name and b.quals[i] == q
+        assert b.max_len == max(len(recs[seen + i][1]) for i in range(b.n))
+        seen += b.n
+        H.as_read_batch_free(C.byref(b), None)
+    assert seen == len(recs)
+    H.as_fastq_close(fq)
+    assert not H.as_fastq_open(str(tmp_path / "nope.fq").encode())
+
+
+def test_cigar_text(native):
+    assert native.cigar_text(np.array([0, 3, 0, 1, 2, 2, 0], np.uint8)) == "3M1I2D1M"      # edlib.cpp:262-311 STANDARD
+    assert native.cigar_text(np.array([], np.uint8)) == ""
+    buf = C.create_string_buffer(4)
+    ops = np.array([0, 1] * 10, np.uint8)
+    assert native.host_lib().as_cigar_text(ops.ctypes.data, ops.size, buf, 4) == -1
+
+
+def test_sim_reads_are_seeded_and_truthful(native):
+    g = native.sim_genome(3, 50_000)
+    assert set(np.unique(g)) <= set(b"ACGT") and np.array_equal(g, native.sim_genome(3, 50_000))
+    r1, l1, p1, s1 = native.sim_reads(9, g, 200, 100, 200, 0.0, 0.0, 1.0)
+    r2, l2, p2, s2 = native.sim_reads(9, g, 200, 100, 200, 0.0, 0.0, 1.0)
+    assert np.array_equal(r1, r2) and np.array_equal(p1, p2)
+    comp = np.zeros(256, np.uint8)
+    comp[list(b"ACGT")] = list(b"TGCA")
+    for i in range(200):
+        ref = g[int(p1[i]):int(p1[i]) + int(l1[i])]
+        rd = r1[i, :l1[i]]
+        assert np.array_equal(rd, ref if s1[i] == 0 else comp[ref][::-1])
