@@ -98,6 +98,8 @@ typedef struct as_params {
 } as_params;
 #define AS_F_MYERS        1u   /* also run the edlib-equivalent NW distance with k=(int)(0.05*len*2) per read */
 #define AS_F_NO_ALIGN     2u   /* stop after PART 1+2 (no GACT): results carry loc/off/strand/flag only */
+#define AS_F_GACT_WARP    4u   /* force the one-read-per-warp anti-diagonal GACT kernel (default for n < 2048) */
+#define AS_F_GACT_BITPAR  8u   /* force the bit-parallel one-read-per-lane GACT kernel (default for n >= 2048) */
 void as_params_default(as_params *p);
 
 /* ---- per-read output: the fields of `result` (accaln.h:95-103) that the path computes ---- */

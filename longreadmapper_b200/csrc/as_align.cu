@@ -26,7 +26,6 @@ __device__ __forceinline__ uint32_t comp_ascii(uint32_t c) {             /* alnm
     }
 }
 
-#define AS_TOFF_NONE 0xFFFFFFFFFFFFFFFFULL
 
 __global__ void __launch_bounds__(256) k_locus(DevIndex ix, char *__restrict__ ascii, size_t stride,
                                                const uint32_t *__restrict__ lens, size_t n, uint32_t *__restrict__ pack,
@@ -108,25 +107,6 @@ int as_launch_locus(as_gpu *h, char *d_ascii, size_t stride, const uint32_t *d_l
 /* ---------------------------------------------------------------------------------------------- */
 /* GACT                                                                                            */
 /* ---------------------------------------------------------------------------------------------- */
-struct GactArgs {
-    const uint32_t *qpack;
-    size_t q_wstride;
-    const uint32_t *qlens;
-    const uint32_t *tbase;
-    const uint64_t *toff;        /* per read base offset into tbase, AS_TOFF_NONE = skip */
-    const uint32_t *tlens;       /* NULL: tlen = qlen (alnmain.c:440-446) */
-    size_t n;
-    int T, O;
-    int TS;                      /* columns kept per lane in shared memory: even, >= min(T, longest target) */
-    int TQ;                      /* min(T, longest query) */
-    uint8_t *ops;
-    size_t ops_stride;
-    int32_t *n_ops, *score;      /* pair mode outputs (may be NULL) */
-    as_result *res;              /* map mode output (may be NULL) */
-    unsigned int *work_counter;
-    unsigned long long *stats;
-};
-
 template <int R, typename PT>
 __global__ void __launch_bounds__(32) k_gact(GactArgs a) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -317,6 +297,10 @@ int as_launch_gact(as_gpu *h, const as_params *p, const uint32_t *d_qpack, size_
     AS_CUDA(cudaMemsetAsync(h->misc[5].p, 0, 64, h->stream));
     a.work_counter = (unsigned int *)h->misc[5].p;
     a.stats = h->d_stats;
+    /* two implementations of the same tile DP: bit-parallel, one read per lane (as_gact_bp.cu) for batches that fill
+     * the GPU with lanes; anti-diagonal, one read per warp (below) for small batches */
+    const bool force_warp = (p->flags & AS_F_GACT_WARP) != 0, force_bp = (p->flags & AS_F_GACT_BITPAR) != 0;
+    if (!force_warp && (force_bp || n >= 2048)) return as_launch_gact_bp(h, a, n, max_qlen, max_tlen);
     /* rows per lane: the whole tile when some query reaches T rows, else just enough for the longest query */
     int rows = (int)(max_qlen < (uint32_t)T ? max_qlen : (uint32_t)T);
     int R = (rows + 31) / 32;

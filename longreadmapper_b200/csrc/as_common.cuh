@@ -56,6 +56,7 @@ struct as_gpu {
          *d_text2 = nullptr, *d_mta = nullptr;
     /* device scratch, grown on demand */
     ScratchBuf reads, lens, results, store, qpack, tpack, toff, vote, counters, ovf_list, ovf_table, misc[6];
+    ScratchBuf gact_planes, gact_tb;     /* bit-parallel GACT: traceback planes / packed tile ops, per resident warp */
     /* pinned staging for small D2H/H2D */
     void *h_pin = nullptr;
     size_t h_pin_cap = 0;
@@ -103,6 +104,28 @@ int as_launch_gact(as_gpu *h, const as_params *p, const uint32_t *d_qpack, size_
                    const uint32_t *d_tbase, const uint64_t *d_toff, const uint32_t *d_tlens, size_t n,
                    uint32_t max_qlen, uint32_t max_tlen, uint8_t *d_ops, size_t ops_stride, int32_t *d_nops,
                    int32_t *d_score, as_result *d_res);
+#define AS_TOFF_NONE 0xFFFFFFFFFFFFFFFFULL
+struct GactArgs {
+    const uint32_t *qpack;
+    size_t q_wstride;
+    const uint32_t *qlens;
+    const uint32_t *tbase;
+    const uint64_t *toff;        /* per read base offset into tbase, AS_TOFF_NONE = skip */
+    const uint32_t *tlens;       /* NULL: tlen = qlen (alnmain.c:440-446) */
+    size_t n;
+    int T, O;
+    int TS;                      /* columns kept per lane in shared memory: even, >= min(T, longest target) */
+    int TQ;                      /* min(T, longest query) */
+    uint8_t *ops;
+    size_t ops_stride;
+    int32_t *n_ops, *score;      /* pair mode outputs (may be NULL) */
+    as_result *res;              /* map mode output (may be NULL) */
+    unsigned int *work_counter;
+    unsigned long long *stats;
+};
+
+/* bit-parallel GACT (as_gact_bp.cu): one read per lane; `a` is filled by as_launch_gact */
+int as_launch_gact_bp(as_gpu *h, GactArgs &a, size_t n, uint32_t max_qlen, uint32_t max_tlen);
 int as_launch_myers(as_gpu *h, const uint32_t *d_qpack, size_t q_wstride, const uint32_t *d_qlens,
                     const uint32_t *d_tbase, const uint64_t *d_toff, const uint32_t *d_tlens, size_t n,
                     uint32_t max_qlen, const int32_t *d_ks, int32_t *d_dist, as_result *d_res);

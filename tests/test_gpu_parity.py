@@ -8,6 +8,7 @@ from conftest import reads_from
 
 pytestmark = pytest.mark.gpu
 
+GACT_IMPL = {"warp": 4, "bitpar": 8}      # AS_F_GACT_WARP / AS_F_GACT_BITPAR: both kernels must agree with the oracle
 FIELDS = ("loc", "off", "seq_id", "strand", "flag", "mapq", "ed", "valid", "myers", "phases", "from_outer")
 
 
@@ -35,7 +36,7 @@ def compare_map(native, mapper, ix, reads, lens, stride, **kw):
     r_cpu = reads.copy()
     r_gpu = reads.copy()
     exp, exp_ops, cells = ix.map_batch(r_cpu, stride, lens, seed_len=seed_len, thres=thres, T=T, O=O, myers=True)
-    p = mapper.params(seed_len=seed_len, thres=thres, T=T, O=O, flags=native.AS_F_MYERS)
+    p = mapper.params(seed_len=seed_len, thres=thres, T=T, O=O, flags=native.AS_F_MYERS | GACT_IMPL.get(kw.get("gact"), 0))
     mapper.stats_reset()
     got, got_ops = mapper.map_batch(r_gpu, lens, params=p)
     for f in FIELDS:
@@ -146,27 +147,31 @@ def test_map_uniform_short(native, gpu_uniform, idx_uniform):
     assert exp["valid"].mean() > 0.95
 
 
-def test_map_repeat_rich_mixed(native, gpu_repeat, idx_repeat):
+@pytest.mark.parametrize("gact", ["warp", "bitpar"])
+def test_map_repeat_rich_mixed(native, gpu_repeat, idx_repeat, gact):
     ix, gs = idx_repeat
     reads, lens, stride = reads_from(native, 600, gs, 1500, 100, 250, 0.0, 0.08, 0.6)
-    compare_map(native, gpu_repeat, ix, reads, lens, stride)
+    compare_map(native, gpu_repeat, ix, reads, lens, stride, gact=gact)
 
 
-def test_map_long_reads_tiled(native, gpu_repeat, idx_repeat):
+@pytest.mark.parametrize("gact", ["warp", "bitpar"])
+def test_map_long_reads_tiled(native, gpu_repeat, idx_repeat, gact):
     """reads longer than the GACT tile: several tiles per read, indels."""
     ix, gs = idx_repeat
     reads, lens, stride = reads_from(native, 700, gs, 60, 400, 5000, 0.05, 0.15, 0.34)
-    compare_map(native, gpu_repeat, ix, reads, lens, stride)
+    compare_map(native, gpu_repeat, ix, reads, lens, stride, gact=gact)
 
 
+@pytest.mark.parametrize("gact", ["warp", "bitpar"])
 @pytest.mark.parametrize("T,O", [(64, 16), (128, 120), (320, 0), (512, 128), (32, 31)])
-def test_map_tile_parameters(native, gpu_repeat, idx_repeat, T, O):
+def test_map_tile_parameters(native, gpu_repeat, idx_repeat, T, O, gact):
     ix, gs = idx_repeat
     reads, lens, stride = reads_from(native, 800 + T, gs, 100, 50, 900, 0.0, 0.12, 0.4)
-    compare_map(native, gpu_repeat, ix, reads, lens, stride, T=T, O=O)
+    compare_map(native, gpu_repeat, ix, reads, lens, stride, T=T, O=O, gact=gact)
 
 
-def test_map_edge_cases(native, gpu_repeat, idx_repeat):
+@pytest.mark.parametrize("gact", ["warp", "bitpar"])
+def test_map_edge_cases(native, gpu_repeat, idx_repeat, gact):
     """ragged batch: reads at the sequence boundaries (seq_lookup straddles -> unmapped), reads shorter than
     one phase (num_seeds == 0), reads of pure garbage (no votes -> key 0), a read of len == seed_len + 1."""
     ix, (a, b) = idx_repeat
@@ -188,7 +193,7 @@ def test_map_edge_cases(native, gpu_repeat, idx_repeat):
     for i, s in enumerate(seqs):
         reads[i, : len(s)] = s
         lens[i] = len(s)
-    compare_map(native, gpu_repeat, ix, reads, lens, stride)
+    compare_map(native, gpu_repeat, ix, reads, lens, stride, gact=gact)
 
 
 def test_map_empty_and_single(native, gpu_uniform, idx_uniform):
@@ -260,12 +265,15 @@ def random_pairs(seed, n, lmin, lmax, emax):
     return qs, ts
 
 
+@pytest.mark.parametrize("gact", ["warp", "bitpar"])
 @pytest.mark.parametrize("T,O,lmax", [(320, 120, 300), (320, 120, 2500), (64, 20, 700), (32, 8, 300), (512, 200, 3000)])
-def test_gact_pairs(orc, gpu_uniform, T, O, lmax):
+def test_gact_pairs(orc, gpu_uniform, T, O, lmax, gact):
     qs, ts = random_pairs(T + lmax, 120, 1, lmax, 0.2)
     qs += [b"A", b"ACGT", b"A" * 50, b"ACGT" * 30]
     ts += [b"C", b"ACGT", b"A" * 80, b"TGCA" * 30]
-    score, ops = gpu_uniform.cigar_align_batch(qs, ts, gpu_uniform.params(T=T, O=O))
+    qs += [b"", b"ACG", b""]
+    ts += [b"ACGTA", b"", b""]
+    score, ops = gpu_uniform.cigar_align_batch(qs, ts, gpu_uniform.params(T=T, O=O, flags=GACT_IMPL[gact]))
     for i, (q, t) in enumerate(zip(qs, ts)):
         es, eops, _ = orc.gact(np.frombuffer(q, np.uint8), np.frombuffer(t, np.uint8), T, O)
         assert es == score[i], (i, len(q), len(t))
@@ -274,9 +282,10 @@ def test_gact_pairs(orc, gpu_uniform, T, O, lmax):
             assert int(np.isin(ops[i], (0, 1, 3)).sum()) == len(q) and int(np.isin(ops[i], (0, 2, 3)).sum()) == len(t)
 
 
-def test_gact_single_tile_is_exact_nw(orc, gpu_uniform):
+@pytest.mark.parametrize("gact", ["warp", "bitpar"])
+def test_gact_single_tile_is_exact_nw(orc, gpu_uniform, gact):
     qs, ts = random_pairs(3, 200, 20, 320, 0.25)
-    score, _ = gpu_uniform.cigar_align_batch(qs, ts)
+    score, _ = gpu_uniform.cigar_align_batch(qs, ts, gpu_uniform.params(flags=GACT_IMPL[gact]))
     dist = gpu_uniform.edit_distance_batch(qs, ts)
     assert np.array_equal(score, dist)
 
