@@ -125,7 +125,11 @@ typedef struct as_result {
  *              PLACE, as alnmain.c:433-438 does (the OpenACC region's copy(reads_mem)).
  *   results    n entries.
  *   store_mem  caller-owned CIGAR column storage, read i at store_mem + i*store_stride, one op byte per
- *              column (alnmain.c:314-325 uses store_stride = 2*max_read_len); may be NULL.
+ *              column (alnmain.c:314-325 uses store_stride = 2*max_read_len); may be NULL.  Columns at and past
+ *              results[i].n_cigar_op are unspecified, as in the reference (it never initialises `store`): only the
+ *              columns some read of the chunk uses are copied back.
+ * The batch is processed in chunks (AS_CHUNK_READS overrides the size) pipelined over three streams; results do
+ * not depend on the chunking.
  */
 int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t stride, const uint32_t *lens, size_t n,
                  as_result *results, uint8_t *store_mem, size_t store_stride);
@@ -147,10 +151,14 @@ typedef struct as_stats {
 } as_stats;
 int as_gpu_stats(as_gpu *h, as_stats *out);          /* accumulated since open / last reset */
 int as_gpu_stats_reset(as_gpu *h);
-/* Device time of the stages of the last as_map_batch* call, milliseconds (CUDA events on the call's stream):
+/* Device time of the stages of the last as_map_batch* call, milliseconds (CUDA events on the call's streams):
  * [0] pack+seed+vote (PART 1)  [1] locus/strand (PART 2)  [2] GACT (+ result fill, PART 3)  [3] Myers  [4] unused
- * [5] H2D  [6] counters + D2H  [7] whole call */
+ *     -- kernel time, summed over the chunks of the call
+ * [5] span of the H2D copies  [6] span of the D2H copies (as_map_batch pipelines chunks: H2D of chunk i+1, kernels of
+ *     chunk i and D2H of chunk i-1 overlap, so [5] and [6] overlap the kernel time)  [7] whole call */
 int as_gpu_last_timing(as_gpu *h, float ms[8]);
+/* Bytes the last as_map_batch moved over PCIe in each direction. */
+int as_gpu_last_transfer(as_gpu *h, uint64_t *h2d_bytes, uint64_t *d2h_bytes);
 
 /* ---- batched forms of the lookup primitives (parity tests, other callers) ---- */
 /* lc_aln (lchash.c:89-104) on n seeds of qlen bases each, seeds + i*qlen; k,l,r as lc_aln leaves them

@@ -98,6 +98,7 @@ def cuda_lib():
     L.as_gpu_stats.argtypes = [vp, C.POINTER(AsStats)]
     L.as_gpu_stats_reset.argtypes = [vp]
     L.as_gpu_last_timing.argtypes = [vp, C.POINTER(C.c_float * 8)]
+    L.as_gpu_last_transfer.argtypes = [vp, C.POINTER(u64), C.POINTER(u64)]
     L.as_lc_aln_batch.argtypes = [vp, vp, i32, sz, vp, vp, vp]
     L.as_fmi_aln_batch.argtypes = [vp, vp, i32, sz, vp, vp, vp]
     L.as_sa_access_batch.argtypes = [vp, vp, sz, vp]
@@ -357,6 +358,11 @@ class GpuMapper:
         self._check(self.L.as_gpu_last_timing(self.h, C.byref(ms)), "as_gpu_last_timing")
         k = ("part1", "part2", "gact", "myers", "unused", "h2d", "d2h", "total")
         return dict(zip(k, [float(x) for x in ms]))
+
+    def last_transfer(self):
+        a, b = C.c_uint64(0), C.c_uint64(0)
+        self._check(self.L.as_gpu_last_transfer(self.h, C.byref(a), C.byref(b)), "as_gpu_last_transfer")
+        return int(a.value), int(b.value)
 
     # -- single stages ----------------------------------------------------------------------------
     def _aln(self, fn, seeds, qlen):

@@ -3,6 +3,7 @@
  * alnmain.c:330-479 for one batch; the *_batch primitives expose single stages for parity tests.
  */
 #include "as_common.cuh"
+#include <stdlib.h>
 
 extern "C" void as_params_default(as_params *p) {
     if (!p) return;
@@ -15,48 +16,51 @@ extern "C" void as_params_default(as_params *p) {
 
 static size_t pack_wstride(uint32_t max_len) { return ((size_t)max_len + 15) / 16 + 3; }
 
-/* all device-side stages of one batch, asynchronous on h->stream; events 1..5 bracket the stages */
+/* all device-side stages of n reads, asynchronous on h->stream; ev[0..4] bracket the stages.  `slot0` is the index
+ * of the first read inside the handle's per-read scratch (qpack / vote / toff), so chunks of one batch do not overlap. */
 static int run_stages(as_gpu *h, const as_params *p, char *d_reads, size_t stride, const uint32_t *d_lens, size_t n,
                       uint32_t max_len, as_result *d_res, uint8_t *d_store, size_t store_stride, bool stop_after_vote,
-                      VoteOut **vote_out) {
+                      VoteOut **vote_out, cudaEvent_t *ev, size_t slot0, size_t slots) {
     const size_t ws = pack_wstride(max_len);
-    AS_TRY(as_scratch(h, &h->qpack, n * ws * sizeof(uint32_t)));
-    AS_TRY(as_scratch(h, &h->vote, n * sizeof(VoteOut)));
-    AS_TRY(as_scratch(h, &h->toff, n * sizeof(uint64_t)));
-    uint32_t *d_pack = (uint32_t *)h->qpack.p;
-    VoteOut *d_vote = (VoteOut *)h->vote.p;
-    uint64_t *d_toff = (uint64_t *)h->toff.p;
+    AS_TRY(as_scratch(h, &h->qpack, slots * ws * sizeof(uint32_t)));
+    AS_TRY(as_scratch(h, &h->vote, slots * sizeof(VoteOut)));
+    AS_TRY(as_scratch(h, &h->toff, slots * sizeof(uint64_t)));
+    uint32_t *d_pack = (uint32_t *)h->qpack.p + slot0 * ws;
+    VoteOut *d_vote = (VoteOut *)h->vote.p + slot0;
+    uint64_t *d_toff = (uint64_t *)h->toff.p + slot0;
     if (vote_out) *vote_out = d_vote;
-    AS_CUDA(cudaEventRecord(h->ev[1], h->stream));
+    AS_CUDA(cudaEventRecord(ev[0], h->stream));
     AS_TRY(as_launch_pack(h, d_reads, stride, d_lens, n, d_pack, ws));
     AS_TRY(as_launch_vote(h, p, d_pack, ws, d_lens, n, max_len, d_vote));
-    AS_CUDA(cudaEventRecord(h->ev[2], h->stream));
+    AS_CUDA(cudaEventRecord(ev[1], h->stream));
     if (stop_after_vote) return AS_OK;
     AS_TRY(as_launch_locus(h, d_reads, stride, d_lens, n, d_pack, ws, d_vote, d_res, d_toff));
-    AS_CUDA(cudaEventRecord(h->ev[3], h->stream));
-    /* columns past n_cigar_op stay zero, so equal inputs give equal bytes whatever ran before (the reference
-     * leaves them uninitialised, alnmain.c:316-320) */
+    AS_CUDA(cudaEventRecord(ev[2], h->stream));
+    /* columns past n_cigar_op stay zero in DEVICE storage, so equal inputs give equal bytes whatever ran before
+     * (the reference leaves them uninitialised, alnmain.c:316-320) */
     if (!(p->flags & AS_F_NO_ALIGN) && d_store) AS_CUDA(cudaMemsetAsync(d_store, 0, n * store_stride, h->stream));
     if (!(p->flags & AS_F_NO_ALIGN))
         AS_TRY(as_launch_gact(h, p, d_pack, ws, d_lens, h->ix.text2, d_toff, nullptr, n, max_len, max_len, d_store,
                               store_stride, nullptr, nullptr, d_res));
-    AS_CUDA(cudaEventRecord(h->ev[4], h->stream));
+    AS_CUDA(cudaEventRecord(ev[3], h->stream));
     if ((p->flags & AS_F_MYERS) && !(p->flags & AS_F_NO_ALIGN))
         AS_TRY(as_launch_myers(h, d_pack, ws, d_lens, h->ix.text2, d_toff, nullptr, n, max_len, nullptr, nullptr, d_res));
-    AS_CUDA(cudaEventRecord(h->ev[5], h->stream));
+    AS_CUDA(cudaEventRecord(ev[4], h->stream));
     return AS_OK;
 }
 
 /* per-batch counters that are cheap to take from the results on the device */
 __global__ void __launch_bounds__(256) k_count_results(const as_result *__restrict__ res, size_t n,
-                                                       unsigned long long *__restrict__ stats) {
+                                                       unsigned long long *__restrict__ stats, int *__restrict__ max_ops) {
     unsigned long long valid = 0, f4 = 0, f16 = 0, sed = 0;
+    int mx = 0;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
         const as_result r = res[i];
         valid += r.valid != 0;
         f4 += (r.flag & 4) != 0;
         f16 += (r.flag & 16) != 0;
         if (r.valid && r.ed > 0) sed += (unsigned long long)r.ed;
+        mx = max(mx, r.n_cigar_op);
     }
 #pragma unroll
     for (int d = 16; d >= 1; d >>= 1) {
@@ -64,8 +68,10 @@ __global__ void __launch_bounds__(256) k_count_results(const as_result *__restri
         f4 += __shfl_xor_sync(0xFFFFFFFFu, f4, d);
         f16 += __shfl_xor_sync(0xFFFFFFFFu, f16, d);
         sed += __shfl_xor_sync(0xFFFFFFFFu, sed, d);
+        mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, d));
     }
     if ((threadIdx.x & 31) == 0) {
+        if (max_ops && mx) atomicMax(max_ops, mx);
         if (valid) atomicAdd(stats + 1, valid);
         if (f4) atomicAdd(stats + 2, f4);
         if (f16) atomicAdd(stats + 3, f16);
@@ -74,9 +80,9 @@ __global__ void __launch_bounds__(256) k_count_results(const as_result *__restri
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(stats + 0, (unsigned long long)n);
 }
 
-static int count_results(as_gpu *h, const as_result *d_res, size_t n) {
+static int count_results(as_gpu *h, const as_result *d_res, size_t n, int *d_max_ops) {
     uint64_t blocks = (n + 255) / 256, cap = (uint64_t)h->sm_count * 4;
-    k_count_results<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(d_res, n, h->d_stats);
+    k_count_results<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(d_res, n, h->d_stats, d_max_ops);
     h->launches++;
     AS_CUDA(cudaGetLastError());
     return AS_OK;
@@ -91,19 +97,60 @@ static int check_map_args(as_gpu *h, const as_params *p, const void *reads, size
     return AS_OK;
 }
 
+static float ev_ms(cudaEvent_t a, cudaEvent_t b) {
+    float v = 0.f;
+    if (cudaEventElapsedTime(&v, a, b) != cudaSuccess) {
+        cudaGetLastError();
+        return 0.f;
+    }
+    return v;
+}
+
+/* ms: [0] PART 1, [1] PART 2, [2] GACT, [3] Myers, [4] unused -- kernel stage times summed over the chunks of the call;
+ * [5] span of the H2D copies, [6] span of the D2H copies (both overlap the kernels when the call was chunked), [7] whole call */
 static int finish_timing(as_gpu *h) {
-    /* ms: [0] PART 1, [1] PART 2, [2] GACT, [3] Myers, [4] result fill (fused, 0), [5] H2D, [6] D2H, [7] total */
-    float v;
     for (int i = 0; i < 8; i++) h->last_ms[i] = 0.f;
-    if (cudaEventElapsedTime(&v, h->ev[0], h->ev[1]) == cudaSuccess) h->last_ms[5] = v;
-    if (cudaEventElapsedTime(&v, h->ev[1], h->ev[2]) == cudaSuccess) h->last_ms[0] = v;
-    if (cudaEventElapsedTime(&v, h->ev[2], h->ev[3]) == cudaSuccess) h->last_ms[1] = v;
-    if (cudaEventElapsedTime(&v, h->ev[3], h->ev[4]) == cudaSuccess) h->last_ms[2] = v;
-    if (cudaEventElapsedTime(&v, h->ev[4], h->ev[5]) == cudaSuccess) h->last_ms[3] = v;
-    if (cudaEventElapsedTime(&v, h->ev[5], h->ev[6]) == cudaSuccess) h->last_ms[6] = v;
-    if (cudaEventElapsedTime(&v, h->ev[0], h->ev[6]) == cudaSuccess) h->last_ms[7] = v;
-    cudaGetLastError();
+    const int nc = h->n_chunks_last;
+    for (int c = 0; c < nc; c++) {
+        cudaEvent_t *e = h->cev[c];
+        h->last_ms[0] += ev_ms(e[0], e[1]);
+        h->last_ms[1] += ev_ms(e[1], e[2]);
+        h->last_ms[2] += ev_ms(e[2], e[3]);
+        h->last_ms[3] += ev_ms(e[3], e[4]);
+    }
+    h->last_ms[7] = ev_ms(h->ev[0], h->ev[6]);
+    h->timing_pending = false;
     return AS_OK;
+}
+
+static int ensure_pipeline(as_gpu *h) {
+    if (h->cev_ready) return AS_OK;
+    AS_CUDA(cudaStreamCreateWithFlags(&h->s_h2d, cudaStreamNonBlocking));
+    AS_CUDA(cudaStreamCreateWithFlags(&h->s_d2h, cudaStreamNonBlocking));
+    for (auto &row : h->cev)
+        for (cudaEvent_t &e : row) AS_CUDA(cudaEventCreate(&e));
+    AS_CUDA(cudaEventCreate(&h->ev_d2h0));
+    AS_CUDA(cudaMalloc((void **)&h->d_chunk_max, AS_MAX_CHUNKS * sizeof(int)));
+    AS_CUDA(cudaMallocHost((void **)&h->h_chunk_max, AS_MAX_CHUNKS * sizeof(int)));
+    h->cev_ready = true;
+    return AS_OK;
+}
+
+/* reads per chunk: enough chunks to overlap the copies with the kernels, each still filling the GPU */
+static size_t chunk_reads(size_t n, size_t stride) {
+    if (const char *e = getenv("AS_CHUNK_READS")) {
+        long v = atol(e);
+        if (v > 0) return (size_t)v;
+    }
+    const size_t min_reads = 32768;
+    size_t c = (n + 7) / 8;
+    /* long reads: cap a chunk at ~256 MB of sequence so that the first kernels start early */
+    const size_t by_bytes = ((size_t)256 << 20) / (stride ? stride : 1);
+    if (c > by_bytes) c = by_bytes;
+    if (c < min_reads) c = min_reads;
+    if ((n + c - 1) / c > AS_MAX_CHUNKS) c = (n + AS_MAX_CHUNKS - 1) / AS_MAX_CHUNKS;
+    if (c > n) c = n;
+    return c ? c : 1;
 }
 
 extern "C" int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t stride, const uint32_t *lens, size_t n,
@@ -111,6 +158,7 @@ extern "C" int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t s
     AS_TRY(check_map_args(h, p, reads, stride, lens, results));
     if (n == 0) return AS_OK;
     AS_CUDA(cudaSetDevice(h->device));
+    AS_TRY(ensure_pipeline(h));
     uint32_t max_len = 0;
     for (size_t i = 0; i < n; i++) {
         if (lens[i] > max_len) max_len = lens[i];
@@ -133,18 +181,71 @@ extern "C" int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t s
     as_result *d_res = (as_result *)h->results.p;
     uint8_t *d_store = want_ops ? (uint8_t *)h->store.p : nullptr;
 
+    const size_t cr = chunk_reads(n, stride);
+    const int nc = (int)((n + cr - 1) / cr);
+    h->n_chunks_last = nc;
+    /* per-read scratch of every chunk is carved out of one allocation made before anything is enqueued */
+    {
+        VoteOut *unused;
+        (void)unused;
+        const size_t ws = pack_wstride(max_len);
+        AS_TRY(as_scratch(h, &h->qpack, n * ws * sizeof(uint32_t)));
+        AS_TRY(as_scratch(h, &h->vote, n * sizeof(VoteOut)));
+        AS_TRY(as_scratch(h, &h->toff, n * sizeof(uint64_t)));
+    }
+    h->last_h2d_bytes = n * stride + n * sizeof(uint32_t);
+    h->last_d2h_bytes = n * sizeof(as_result) + n * stride + (size_t)nc * sizeof(int);
     AS_CUDA(cudaEventRecord(h->ev[0], h->stream));
-    AS_CUDA(cudaMemcpyAsync(d_reads, reads, n * stride, cudaMemcpyHostToDevice, h->stream));
-    AS_CUDA(cudaMemcpyAsync(d_lens, lens, n * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
-    AS_TRY(run_stages(h, p, d_reads, stride, d_lens, n, max_len, d_res, d_store, store_stride, false, nullptr));
-    AS_TRY(count_results(h, d_res, n));
-    AS_CUDA(cudaMemcpyAsync(results, d_res, n * sizeof(as_result), cudaMemcpyDeviceToHost, h->stream));
-    if (want_ops) AS_CUDA(cudaMemcpyAsync(store_mem, d_store, n * store_stride, cudaMemcpyDeviceToHost, h->stream));
-    /* strand-1 reads were reverse-complemented in place (alnmain.c:433-438; the OpenACC copy(reads_mem) :421) */
-    AS_CUDA(cudaMemcpyAsync(reads, d_reads, n * stride, cudaMemcpyDeviceToHost, h->stream));
+    AS_CUDA(cudaStreamWaitEvent(h->s_h2d, h->ev[0], 0));
+    AS_CUDA(cudaStreamWaitEvent(h->s_d2h, h->ev[0], 0));
+    AS_CUDA(cudaMemsetAsync(h->d_chunk_max, 0, AS_MAX_CHUNKS * sizeof(int), h->stream));
+    /* every H2D copy is queued up front: they stream in order while the kernels of earlier chunks run */
+    for (int c = 0; c < nc; c++) {
+        const size_t r0 = (size_t)c * cr, cn = (n - r0 < cr) ? n - r0 : cr;
+        AS_CUDA(cudaMemcpyAsync(d_reads + r0 * stride, reads + r0 * stride, cn * stride, cudaMemcpyHostToDevice, h->s_h2d));
+        AS_CUDA(cudaMemcpyAsync(d_lens + r0, lens + r0, cn * sizeof(uint32_t), cudaMemcpyHostToDevice, h->s_h2d));
+        AS_CUDA(cudaEventRecord(h->cev[c][5], h->s_h2d));
+    }
+    /* the CIGAR columns of chunk c are copied once the chunk's widest row is known: only that many columns of
+     * every row cross PCIe (the reference leaves columns >= n_cigar_op uninitialised, alnmain.c:316-320) */
+    auto finish_chunk = [&](int c) -> int {
+        const size_t r0 = (size_t)c * cr, cn = (n - r0 < cr) ? n - r0 : cr;
+        AS_CUDA(cudaEventSynchronize(h->cev[c][7]));
+        size_t w = (size_t)(h->h_chunk_max[c] > 0 ? h->h_chunk_max[c] : 0);
+        w = (w + 15) & ~(size_t)15;
+        if (w > store_stride) w = store_stride;
+        h->last_d2h_bytes += w * cn;
+        if (w)
+            AS_CUDA(cudaMemcpy2DAsync(store_mem + r0 * store_stride, store_stride, d_store + r0 * store_stride, store_stride,
+                                      w, cn, cudaMemcpyDeviceToHost, h->s_d2h));
+        return AS_OK;
+    };
+    for (int c = 0; c < nc; c++) {
+        const size_t r0 = (size_t)c * cr, cn = (n - r0 < cr) ? n - r0 : cr;
+        AS_CUDA(cudaStreamWaitEvent(h->stream, h->cev[c][5], 0));
+        AS_TRY(run_stages(h, p, d_reads + r0 * stride, stride, d_lens + r0, cn, max_len, d_res + r0,
+                          d_store ? d_store + r0 * store_stride : nullptr, store_stride, false, nullptr, h->cev[c], r0, n));
+        AS_TRY(count_results(h, d_res + r0, cn, h->d_chunk_max + c));
+        AS_CUDA(cudaEventRecord(h->cev[c][6], h->stream));
+        if (want_ops && c > 0) AS_TRY(finish_chunk(c - 1));
+        AS_CUDA(cudaStreamWaitEvent(h->s_d2h, h->cev[c][6], 0));
+        if (c == 0) AS_CUDA(cudaEventRecord(h->ev_d2h0, h->s_d2h));
+        AS_CUDA(cudaMemcpyAsync(h->h_chunk_max + c, h->d_chunk_max + c, sizeof(int), cudaMemcpyDeviceToHost, h->s_d2h));
+        AS_CUDA(cudaEventRecord(h->cev[c][7], h->s_d2h));
+        AS_CUDA(cudaMemcpyAsync(results + r0, d_res + r0, cn * sizeof(as_result), cudaMemcpyDeviceToHost, h->s_d2h));
+        /* strand-1 reads were reverse-complemented in place (alnmain.c:433-438; the OpenACC copy(reads_mem) :421) */
+        AS_CUDA(cudaMemcpyAsync(reads + r0 * stride, d_reads + r0 * stride, cn * stride, cudaMemcpyDeviceToHost, h->s_d2h));
+    }
+    if (want_ops) AS_TRY(finish_chunk(nc - 1));
+    AS_CUDA(cudaEventRecord(h->ev[7], h->s_d2h));
+    AS_CUDA(cudaStreamWaitEvent(h->stream, h->ev[7], 0));
     AS_CUDA(cudaEventRecord(h->ev[6], h->stream));
     AS_CUDA(cudaStreamSynchronize(h->stream));
-    return finish_timing(h);
+    finish_timing(h);
+    h->last_ms[5] = ev_ms(h->ev[0], h->cev[nc - 1][5]);
+    h->last_ms[6] = ev_ms(h->ev_d2h0, h->ev[7]);
+    h->last_ms[7] = ev_ms(h->ev[0], h->ev[6]);
+    return AS_OK;
 }
 
 extern "C" int as_map_batch_device(as_gpu *h, const as_params *p, char *d_reads, size_t stride, const uint32_t *d_lens,
@@ -152,12 +253,15 @@ extern "C" int as_map_batch_device(as_gpu *h, const as_params *p, char *d_reads,
     AS_TRY(check_map_args(h, p, d_reads, stride, d_lens, d_results));
     if (n == 0) return AS_OK;
     AS_CUDA(cudaSetDevice(h->device));
+    AS_TRY(ensure_pipeline(h));
     if ((size_t)max_len + 1 > stride) return AS_EINVAL;
     if (d_store && !(p->flags & AS_F_NO_ALIGN) && store_stride < 2 * (size_t)max_len) return AS_EINVAL;
+    h->n_chunks_last = 1;
     AS_CUDA(cudaEventRecord(h->ev[0], h->stream));
-    AS_TRY(run_stages(h, p, d_reads, stride, d_lens, n, max_len, d_results, d_store, store_stride, false, nullptr));
-    AS_TRY(count_results(h, d_results, n));
+    AS_TRY(run_stages(h, p, d_reads, stride, d_lens, n, max_len, d_results, d_store, store_stride, false, nullptr, h->cev[0], 0, n));
+    AS_TRY(count_results(h, d_results, n, nullptr));
     AS_CUDA(cudaEventRecord(h->ev[6], h->stream));
+    h->timing_pending = true;
     return AS_OK;                     /* asynchronous: as_gpu_sync() or the caller's stream sync completes it */
 }
 
@@ -172,8 +276,15 @@ extern "C" int as_gpu_last_timing(as_gpu *h, float ms[8]) {
     if (!h || !ms) return AS_EINVAL;
     AS_CUDA(cudaSetDevice(h->device));
     AS_CUDA(cudaStreamSynchronize(h->stream));
-    finish_timing(h);
+    if (h->timing_pending) finish_timing(h);
     for (int i = 0; i < 8; i++) ms[i] = h->last_ms[i];
+    return AS_OK;
+}
+
+extern "C" int as_gpu_last_transfer(as_gpu *h, uint64_t *h2d_bytes, uint64_t *d2h_bytes) {
+    if (!h) return AS_EINVAL;
+    if (h2d_bytes) *h2d_bytes = h->last_h2d_bytes;
+    if (d2h_bytes) *d2h_bytes = h->last_d2h_bytes;
     return AS_OK;
 }
 
@@ -215,7 +326,9 @@ extern "C" int as_vote_batch(as_gpu *h, const as_params *p, const char *reads, s
     AS_CUDA(cudaMemcpyAsync(h->reads.p, reads, n * stride, cudaMemcpyHostToDevice, h->stream));
     AS_CUDA(cudaMemcpyAsync(h->lens.p, lens, n * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
     VoteOut *d_vote = nullptr;
-    AS_TRY(run_stages(h, p, (char *)h->reads.p, stride, (const uint32_t *)h->lens.p, n, max_len, nullptr, nullptr, 0, true, &d_vote));
+    AS_TRY(ensure_pipeline(h));
+    AS_TRY(run_stages(h, p, (char *)h->reads.p, stride, (const uint32_t *)h->lens.p, n, max_len, nullptr, nullptr, 0, true, &d_vote,
+                      h->cev[0], 0, n));
     AS_TRY(as_pinned(h, n * sizeof(VoteOut)));
     AS_CUDA(cudaMemcpyAsync(h->h_pin, d_vote, n * sizeof(VoteOut), cudaMemcpyDeviceToHost, h->stream));
     AS_CUDA(cudaStreamSynchronize(h->stream));

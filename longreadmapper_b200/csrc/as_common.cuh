@@ -24,6 +24,7 @@ struct __align__(32) FmBlock {
     uint64_t lo;       /* bit r = low bit of the code of row 64*blk + r */
     uint64_t hi;       /* bit r = high bit                                 */
 };
+#define AS_MAX_CHUNKS 32
 #define AS_SB_SHIFT 30 /* super block = 2^30 rows; absolute counts as u64[4] per super block */
 
 struct DevIndex {
@@ -64,6 +65,16 @@ struct as_gpu {
     unsigned long long *d_stats = nullptr;
     cudaEvent_t ev[10]{};
     float last_ms[8]{};
+    /* chunked pipeline of as_map_batch: H2D of chunk i+1 | kernels of chunk i | D2H of chunk i-1 */
+    cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+    cudaEvent_t cev[AS_MAX_CHUNKS][8]{};   /* per chunk: [0..4] stage marks, [5] H2D done, [6] kernels done, [7] fixed D2H done */
+    cudaEvent_t ev_d2h0 = nullptr;         /* first D2H issued */
+    bool cev_ready = false;
+    int n_chunks_last = 0;
+    uint64_t last_h2d_bytes = 0, last_d2h_bytes = 0;   /* bytes the last as_map_batch moved over PCIe */
+    bool timing_pending = false;           /* as_map_batch_device enqueued a call whose events were not read yet */
+    int *d_chunk_max = nullptr;            /* per chunk: max n_cigar_op (trims the CIGAR-column D2H) */
+    int *h_chunk_max = nullptr;            /* pinned mirror */
     int sm_count = 148;
     uint64_t launches = 0;      /* kernels launched by this handle since open */
 };

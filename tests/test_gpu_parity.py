@@ -217,6 +217,21 @@ def test_map_batch_split_invariance(native, gpu_uniform, idx_uniform):
     assert np.array_equal(wops, np.concatenate([x[1] for x in parts]))
 
 
+def test_map_chunked_pipeline(native, gpu_uniform, idx_uniform, monkeypatch):
+    """as_map_batch pipelines chunks over three streams and trims the CIGAR-column copy per chunk: a ragged last
+    chunk, chunk-local scratch and the trimmed 2D copy must leave results identical to the oracle's."""
+    ix, gs = idx_uniform
+    reads, lens, stride = reads_from(native, 950, gs, 4099, 100, 180, 0.0, 0.05, 0.6)
+    monkeypatch.setenv("AS_CHUNK_READS", "1000")
+    compare_map(native, gpu_uniform, ix, reads, lens, stride)
+    h2d, d2h = gpu_uniform.last_transfer()
+    assert h2d == 4099 * (stride + 4) and d2h < 4099 * (56 + stride + 2 * 180)
+    tm = gpu_uniform.last_timing()
+    assert tm["total"] > 0 and tm["part1"] > 0 and tm["gact"] > 0
+    monkeypatch.setenv("AS_CHUNK_READS", "5")
+    compare_map(native, gpu_uniform, ix, reads[:100], lens[:100], stride)   # 20 chunks of 5 reads
+
+
 def test_truth_recovered(native, gpu_uniform, idx_uniform):
     """size-independent property: substitution-only reads land on the simulated position and strand."""
     ix, (g,) = idx_uniform
