@@ -14,6 +14,7 @@ AS_F_MYERS = 1
 AS_F_NO_ALIGN = 2
 AS_F_GACT_WARP = 4
 AS_F_GACT_BITPAR = 8
+AS_F_WIDE_INDEX = 16
 
 # as_result (include/accseq_b200.h)
 RESULT_DTYPE = np.dtype([("loc", "<u8"), ("off", "<u8"), ("seq_id", "<i4"), ("strand", "<i4"), ("flag", "<i4"),

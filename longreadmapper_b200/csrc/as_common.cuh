@@ -184,6 +184,51 @@ __device__ __forceinline__ void as_bs_step(const DevIndex &ix, uint32_t c, uint6
     l = cc + ol;
 }
 
+/* ---- 32-bit fast path: indexes of at most 2^30 rows (one super block, so the block counts are absolute and every
+ * row number fits a register).  Same values as as_occ / as_bs_step, about a third of the instructions. ---- */
+struct BsChar32 {           /* per-character constants of one backward-search step */
+    uint32_t xlo, xhi;      /* xor masks that turn the two planes into "row holds c" */
+    uint32_t C;             /* dna_fmi.c[c] */
+    uint32_t c;
+};
+__device__ __forceinline__ BsChar32 as_bs_char32(const DevIndex &ix, uint32_t c) {
+    BsChar32 b;
+    b.c = c;
+    b.xlo = (c & 1u) ? 0u : 0xFFFFFFFFu;
+    b.xhi = (c & 2u) ? 0u : 0xFFFFFFFFu;
+    b.C = (uint32_t)(c == 0 ? ix.C[0] : c == 1 ? ix.C[1] : c == 2 ? ix.C[2] : ix.C[3]);
+    return b;
+}
+__device__ __forceinline__ uint32_t as_shr_clamp(uint32_t v, uint32_t s) {   /* PTX shr: shifts >= 32 give 0 */
+    uint32_t r;
+    asm("shr.b32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(s));
+    return r;
+}
+__device__ __forceinline__ uint32_t as_shl_clamp(uint32_t v, uint32_t s) {
+    uint32_t r;
+    asm("shl.b32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(s));
+    return r;
+}
+__device__ __forceinline__ uint32_t as_occ32(const DevIndex &ix, const BsChar32 &b, uint32_t loc) {
+    const uint32_t blk = loc >> 6, r = loc & 63u;
+    const uint32_t *p = reinterpret_cast<const uint32_t *>(ix.fm + blk);
+    const uint32_t base = __ldg(p + b.c);                                   /* same 32-byte sector as the planes */
+    const uint4 w = __ldg(reinterpret_cast<const uint4 *>(p) + 1);          /* lo.x lo.y hi.x hi.y */
+    const uint32_t m0 = (w.x ^ b.xlo) & (w.z ^ b.xhi), m1 = (w.y ^ b.xlo) & (w.w ^ b.xhi);
+    const uint32_t k0 = ~as_shl_clamp(0xFFFFFFFEu, r);                       /* rows 0..r of the low half */
+    const uint32_t k1 = as_shr_clamp(0xFFFFFFFFu, 63u - r);                  /* rows 32..r of the high half */
+    uint32_t v = base + __popc(m0 & k0) + __popc(m1 & k1);
+    /* the '$' row is stored as code 0 */
+    if (b.c == 0 && loc >= (uint32_t)ix.primary && blk == (uint32_t)(ix.primary >> 6)) v -= 1;
+    return v;
+}
+__device__ __forceinline__ void as_bs_step32(const DevIndex &ix, uint32_t c, uint32_t &k, uint32_t &l) {
+    const BsChar32 b = as_bs_char32(ix, c);
+    const uint32_t ok = as_occ32(ix, b, k - 1), ol = as_occ32(ix, b, l);
+    k = b.C + ok + 1;
+    l = b.C + ol;
+}
+
 __device__ __forceinline__ uint64_t as_sa(const DevIndex &ix, uint64_t row) {
     uint64_t v = __ldg(ix.sa_lo + row);
     if (ix.sa_hi) v |= (uint64_t)__ldg(ix.sa_hi + row) << 32;

@@ -13,15 +13,18 @@
  * queued and redone by the same code over a large table in global memory (BIG instantiation).
  */
 #include "as_common.cuh"
+#include <type_traits>
 
 #define VOTE_THREADS 128
 #define MAXP 34                      /* seed_len <= 32 -> at most 33 phases */
 #define EMPTY_BUCKET 0xFFFFFFFFFFFFFFFFULL
 
-struct VoteTable {
+template <typename USED_T>
+struct VoteTableT {
     unsigned long long *bucket;
-    uint32_t *val, *ord, *low, *used;   /* used: BIG only */
-    uint32_t *n_used;                   /* BIG only */
+    uint32_t *val, *ord, *low;
+    USED_T *used;                       /* slots claimed in this phase, in claim order */
+    uint32_t *n_used;
     uint32_t cap, shift;                /* cap = 1 << (64 - shift) */
 };
 
@@ -48,13 +51,13 @@ __device__ __forceinline__ uint32_t hash_bucket(uint64_t b, uint32_t shift) {
     return (uint32_t)((b * 0x9E3779B97F4A7C15ULL) >> shift);
 }
 
-template <bool BIG>
-__device__ __forceinline__ bool table_insert(const VoteTable &t, uint64_t bucket, uint32_t low, uint32_t ord) {
+template <typename USED_T, typename VT>
+__device__ __forceinline__ bool table_insert(const VT &t, uint64_t bucket, uint32_t low, uint32_t ord) {
     uint32_t slot = hash_bucket(bucket, t.shift);
     for (uint32_t probes = 0; probes < t.cap; probes++) {
         unsigned long long prev = atomicCAS(t.bucket + slot, EMPTY_BUCKET, (unsigned long long)bucket);
         if (prev == EMPTY_BUCKET || prev == bucket) {
-            if (BIG && prev == EMPTY_BUCKET) t.used[atomicAdd(t.n_used, 1u)] = slot;
+            if (prev == EMPTY_BUCKET) t.used[atomicAdd(t.n_used, 1u)] = (USED_T)slot;
             atomicAdd(t.val + slot, 1u);
             atomicMin(t.ord + slot, ord);
             atomicMin(t.low + slot, low);
@@ -75,10 +78,13 @@ __device__ __forceinline__ void top2_push(uint64_t &a0, uint64_t &a1, uint64_t c
     }
 }
 
-template <int G, bool BIG>
+template <int G, bool BIG, bool SMALL>
 __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, VoteArgs a) {
     constexpr int CAP = 8 * G;
     constexpr int GROUPS = VOTE_THREADS / G;
+    typedef typename std::conditional<BIG, uint32_t, uint8_t>::type USED_T;
+    __shared__ uint8_t s_used[BIG ? 1 : GROUPS * CAP];
+    __shared__ uint32_t s_nused[BIG ? 1 : GROUPS];
     __shared__ unsigned long long s_bucket[BIG ? 1 : GROUPS * CAP];
     __shared__ uint32_t s_val[BIG ? 1 : GROUPS * CAP], s_ord[BIG ? 1 : GROUPS * CAP], s_low[BIG ? 1 : GROUPS * CAP];
     __shared__ unsigned long long s_okey[(BIG ? 1 : GROUPS) * MAXP];
@@ -89,7 +95,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
     const uint32_t gmask = (G == 32) ? 0xFFFFFFFFu : (((1u << G) - 1u) << (lane & ~(uint32_t)(G - 1)));
     const int grp = threadIdx.x / G;
 
-    VoteTable t;
+    VoteTableT<USED_T> t;
     if (BIG) {
         unsigned char *m = a.big_mem + (size_t)blockIdx.x * a.big_stride;
         t.cap = a.big_cap;
@@ -97,31 +103,30 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
         t.val = (uint32_t *)(m + (size_t)t.cap * 8);
         t.ord = t.val + t.cap;
         t.low = t.ord + t.cap;
-        t.used = t.low + t.cap;
-        t.n_used = t.used + t.cap;
+        t.used = (USED_T *)(t.low + t.cap);
+        t.n_used = (uint32_t *)(t.low + 2 * (size_t)t.cap);
     } else {
         t.cap = CAP;
         t.bucket = s_bucket + grp * CAP;
         t.val = s_val + grp * CAP;
         t.ord = s_ord + grp * CAP;
         t.low = s_low + grp * CAP;
-        t.used = nullptr;
-        t.n_used = nullptr;
+        t.used = (USED_T *)(s_used + grp * CAP);
+        t.n_used = s_nused + grp;
     }
     t.shift = 64 - (31 - __clz(t.cap));
     unsigned long long *okey = s_okey + (BIG ? 0 : grp) * MAXP;
     uint32_t *oval = s_oval + (BIG ? 0 : grp) * MAXP;
 
-    if (BIG) {
-        for (uint32_t s = g; s < t.cap; s += G) {
-            t.bucket[s] = EMPTY_BUCKET;
-            t.val[s] = 0;
-            t.ord[s] = 0xFFFFFFFFu;
-            t.low[s] = 0xFFFFFFFFu;
-        }
-        if (g == 0) *t.n_used = 0;
-        __syncwarp(gmask);
+    /* the table starts empty and every phase resets exactly the slots it claimed */
+    for (uint32_t s = g; s < t.cap; s += G) {
+        t.bucket[s] = EMPTY_BUCKET;
+        t.val[s] = 0;
+        t.ord[s] = 0xFFFFFFFFu;
+        t.low[s] = 0xFFFFFFFFu;
     }
+    if (g == 0) *t.n_used = 0;
+    __syncwarp(gmask);
 
     const int sl = a.sl, P = sl + 1;
     const int left0 = sl - ix.hlen;
@@ -151,16 +156,6 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
         int iter;
         bool overflow = false;
         for (iter = 0; iter < P; ++iter) {
-            /* ---- clear the table ---- */
-            if (!BIG) {
-                for (uint32_t s = g; s < (uint32_t)CAP; s += G) {
-                    t.bucket[s] = EMPTY_BUCKET;
-                    t.val[s] = 0;
-                    t.ord[s] = 0xFFFFFFFFu;
-                    t.low[s] = 0xFFFFFFFFu;
-                }
-            }
-            __syncwarp(gmask);
             const uint32_t m_count = (uint32_t)iter < span ? (span - (uint32_t)iter + (uint32_t)P - 1) / (uint32_t)P : 0;
             bool ok = true;
             for (uint32_t c0 = 0; c0 < m_count; c0 += G) {
@@ -179,10 +174,21 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
                     }
                     st_seeds++;
                     if (!absent) {
-                        for (int tt = left - 1; tt >= 0; tt--) {        /* fmidx.c:300-310 */
-                            as_bs_step(ix, (uint32_t)(seed >> (2 * tt)) & 3u, kk, ll);
-                            st_steps++;
-                            if (kk > ll) break;
+                        if (SMALL) {
+                            uint32_t k32 = (uint32_t)kk, l32 = (uint32_t)ll;
+                            for (int tt = left - 1; tt >= 0; tt--) {    /* fmidx.c:300-310 */
+                                as_bs_step32(ix, (uint32_t)(seed >> (2 * tt)) & 3u, k32, l32);
+                                st_steps++;
+                                if (k32 > l32) break;
+                            }
+                            kk = k32;
+                            ll = l32;
+                        } else {
+                            for (int tt = left - 1; tt >= 0; tt--) {    /* fmidx.c:300-310 */
+                                as_bs_step(ix, (uint32_t)(seed >> (2 * tt)) & 3u, kk, ll);
+                                st_steps++;
+                                if (kk > ll) break;
+                            }
                         }
                         rr = kk > ll ? 0 : ll - kk + 1;
                     }
@@ -194,7 +200,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
                     if (rr_eff) {
                         uint64_t key = as_sa(ix, kk) - (uint64_t)j;     /* alnmain.c:363-365, u64 wrap kept */
                         st_hits++;
-                        if (!table_insert<BIG>(t, key >> 4, (uint32_t)key & 15u, m * a.thres)) ok = false;
+                        if (!table_insert<USED_T>(t, key >> 4, (uint32_t)key & 15u, m * a.thres)) ok = false;
                     }
                 } else {
                     /* spread all SA rows of the chunk over the lanes of the group */
@@ -225,7 +231,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
                             uint64_t row = (((uint64_t)okh << 32) | okl) + off;
                             uint64_t key = as_sa(ix, row) - (uint64_t)oj;
                             st_hits++;
-                            if (!table_insert<BIG>(t, key >> 4, (uint32_t)key & 15u, om * a.thres + off)) ok = false;
+                            if (!table_insert<USED_T>(t, key >> 4, (uint32_t)key & 15u, om * a.thres + off)) ok = false;
                         }
                     }
                 }
@@ -238,21 +244,12 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
             /* ---- TOP2 of the phase (histo.c:84-96) ---- */
             uint64_t a0 = 0, a1 = 0;
             uint32_t slot0 = 0;
-            if (BIG) {
-                const uint32_t nu = *t.n_used;
-                for (uint32_t u = g; u < nu; u += G) {
-                    uint32_t s = t.used[u];
-                    uint64_t c = ((uint64_t)t.val[s] << 32) | (0xFFFFFFFFu - t.ord[s]);
-                    if (c > a0) slot0 = s;
-                    top2_push(a0, a1, c);
-                }
-            } else {
-                for (uint32_t s = g; s < (uint32_t)CAP; s += G) {
-                    uint32_t vv = t.val[s];
-                    uint64_t c = vv ? (((uint64_t)vv << 32) | (0xFFFFFFFFu - t.ord[s])) : 0;
-                    if (c > a0) slot0 = s;
-                    top2_push(a0, a1, c);
-                }
+            const uint32_t nu = *t.n_used;
+            for (uint32_t u = g; u < nu; u += G) {
+                uint32_t s = t.used[u];
+                uint64_t c = ((uint64_t)t.val[s] << 32) | (0xFFFFFFFFu - t.ord[s]);
+                if (c > a0) slot0 = s;
+                top2_push(a0, a1, c);
             }
 #pragma unroll
             for (int d = G >> 1; d >= 1; d >>= 1) {
@@ -271,21 +268,17 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
             uint64_t c0key = 0;
             if (v0val) c0key = ((uint64_t)t.bucket[slot0] << 4) | t.low[slot0];
             __syncwarp(gmask);
-            if (BIG) {
-                /* reset only the used slots */
-                const uint32_t nu = *t.n_used;
-                __syncwarp(gmask);
-                for (uint32_t u = g; u < nu; u += G) {
-                    uint32_t s = t.used[u];
-                    t.bucket[s] = EMPTY_BUCKET;
-                    t.val[s] = 0;
-                    t.ord[s] = 0xFFFFFFFFu;
-                    t.low[s] = 0xFFFFFFFFu;
-                }
-                __syncwarp(gmask);
-                if (g == 0) *t.n_used = 0;
-                __syncwarp(gmask);
+            /* reset only the slots this phase claimed */
+            for (uint32_t u = g; u < nu; u += G) {
+                uint32_t s = t.used[u];
+                t.bucket[s] = EMPTY_BUCKET;
+                t.val[s] = 0;
+                t.ord[s] = 0xFFFFFFFFu;
+                t.low[s] = 0xFFFFFFFFu;
             }
+            __syncwarp(gmask);
+            if (g == 0) *t.n_used = 0;
+            __syncwarp(gmask);
             if (num_seeds > 0) {                                        /* alnmain.c:373 */
                 const uint64_t v = (uint64_t)v0val + v1val;
                 const double score = (double)v / (double)(int)num_seeds;
@@ -325,18 +318,19 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
                     o.from_outer = -1;
                     a.out[read] = o;
                 }
-                /* table state is unknown: wipe it */
-                for (uint32_t s = g; s < t.cap; s += G) {
-                    t.bucket[s] = EMPTY_BUCKET;
-                    t.val[s] = 0;
-                    t.ord[s] = 0xFFFFFFFFu;
-                    t.low[s] = 0xFFFFFFFFu;
-                }
-                if (g == 0) *t.n_used = 0;
-                __syncwarp(gmask);
             } else if (g == 0) {
                 a.ovf_list[atomicAdd(a.ovf_count, 1u)] = read;
             }
+            /* the phase did not reach its reset: wipe the whole table */
+            __syncwarp(gmask);
+            for (uint32_t s = g; s < t.cap; s += G) {
+                t.bucket[s] = EMPTY_BUCKET;
+                t.val[s] = 0;
+                t.ord[s] = 0xFFFFFFFFu;
+                t.low[s] = 0xFFFFFFFFu;
+            }
+            if (g == 0) *t.n_used = 0;
+            __syncwarp(gmask);
             continue;
         }
         int from_outer = 0;
@@ -435,17 +429,23 @@ int as_launch_vote(as_gpu *h, const as_params *p, const uint32_t *d_pack, size_t
     uint64_t blocks = (groups_needed + groups_per_block - 1) / groups_per_block;
     uint64_t cap = (uint64_t)h->sm_count * 8;          /* 8 blocks of <= 27 KB shared memory per SM */
     unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
-    if (G == 8)
-        k_vote<8, false><<<grid, VOTE_THREADS, 0, h->stream>>>(h->ix, a);
-    else if (G == 16)
-        k_vote<16, false><<<grid, VOTE_THREADS, 0, h->stream>>>(h->ix, a);
-    else
-        k_vote<32, false><<<grid, VOTE_THREADS, 0, h->stream>>>(h->ix, a);
+    /* indexes of one super block (<= 2^30 rows) take the 32-bit backward-search path */
+    const bool small = h->ix.N <= (1ULL << AS_SB_SHIFT) && !(p->flags & AS_F_WIDE_INDEX);
+#define VOTE_LAUNCH(GG)                                                                      \
+    do {                                                                                     \
+        if (small) k_vote<GG, false, true><<<grid, VOTE_THREADS, 0, h->stream>>>(h->ix, a);  \
+        else k_vote<GG, false, false><<<grid, VOTE_THREADS, 0, h->stream>>>(h->ix, a);       \
+    } while (0)
+    if (G == 8) VOTE_LAUNCH(8);
+    else if (G == 16) VOTE_LAUNCH(16);
+    else VOTE_LAUNCH(32);
+#undef VOTE_LAUNCH
     h->launches++;
     AS_CUDA(cudaGetLastError());
     /* overflow pass: exits at once when the queue is empty */
     a.work_counter = (unsigned int *)h->counters.p + 2;
-    k_vote<32, true><<<(unsigned)big_warps, 32, 0, h->stream>>>(h->ix, a);
+    if (small) k_vote<32, true, true><<<(unsigned)big_warps, 32, 0, h->stream>>>(h->ix, a);
+    else k_vote<32, true, false><<<(unsigned)big_warps, 32, 0, h->stream>>>(h->ix, a);
     h->launches++;
     AS_CUDA(cudaGetLastError());
     return AS_OK;

@@ -104,8 +104,8 @@ def test_sa_access(gpu_uniform, idx_uniform):
 # ---------------------------------------------------------------------------------------------------
 # PART 1 (alnmain.c:333-405)
 # ---------------------------------------------------------------------------------------------------
-def check_vote(mapper, ix, reads, lens, seed_len=20, thres=300):
-    key, val, ph, fo = mapper.vote_batch(reads, lens, mapper.params(seed_len=seed_len, thres=thres))
+def check_vote(mapper, ix, reads, lens, seed_len=20, thres=300, flags=0):
+    key, val, ph, fo = mapper.vote_batch(reads, lens, mapper.params(seed_len=seed_len, thres=thres, flags=flags))
     for i in range(len(lens)):
         v = ix.vote(reads[i, : lens[i]], seed_len, thres)
         assert (int(key[i]), int(val[i]), int(ph[i]), int(fo[i])) == (v.best_key, v.best_val, v.phases, v.from_outer), i
@@ -117,11 +117,12 @@ def test_vote_uniform_short(native, gpu_uniform, idx_uniform):
     check_vote(gpu_uniform, ix, reads, lens)
 
 
-def test_vote_repeat_rich(native, gpu_repeat, idx_repeat):
+@pytest.mark.parametrize("wide", [0, 16])     # AS_F_WIDE_INDEX: the 64-bit path human-scale indexes take
+def test_vote_repeat_rich(native, gpu_repeat, idx_repeat, wide):
     ix, gs = idx_repeat
     for k, (lmin, lmax, e) in enumerate([(100, 100, 0.0), (150, 150, 0.02), (250, 250, 0.05), (100, 250, 0.08)]):
         reads, lens, _ = reads_from(native, 200 + k, gs, 750, lmin, lmax, e, e, 0.7)
-        check_vote(gpu_repeat, ix, reads, lens)
+        check_vote(gpu_repeat, ix, reads, lens, flags=wide)
 
 
 @pytest.mark.parametrize("seed_len,thres", [(12, 300), (16, 50), (24, 300), (32, 1000), (20, 2)])
@@ -131,10 +132,11 @@ def test_vote_parameters(native, gpu_repeat, idx_repeat, seed_len, thres):
     check_vote(gpu_repeat, ix, reads, lens, seed_len, thres)
 
 
-def test_vote_long_reads(native, gpu_repeat, idx_repeat):
+@pytest.mark.parametrize("wide", [0, 16])
+def test_vote_long_reads(native, gpu_repeat, idx_repeat, wide):
     ix, gs = idx_repeat
     reads, lens, _ = reads_from(native, 400, gs, 40, 1000, 6000, 0.05, 0.15, 0.34)
-    check_vote(gpu_repeat, ix, reads, lens)
+    check_vote(gpu_repeat, ix, reads, lens, flags=wide)
 
 
 # ---------------------------------------------------------------------------------------------------
