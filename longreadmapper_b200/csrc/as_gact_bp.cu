@@ -20,6 +20,7 @@
 #include <stdlib.h>
 
 #define BP_THREADS 128
+#define BP_PREFETCH 12
 
 /* even bits of x (bit 2r) -> bit r of the low word; odd bits -> high word */
 __device__ __forceinline__ uint32_t compress_even(uint64_t x) {
@@ -30,6 +31,14 @@ __device__ __forceinline__ uint32_t compress_even(uint64_t x) {
     x = (x | (x >> 8)) & 0x0000FFFF0000FFFFULL;
     x = (x | (x >> 16));
     return (uint32_t)x;
+}
+
+/* bytes [s0, s1) of `acc` to row offsets pos+s, skipping what falls outside the row */
+__device__ __forceinline__ void put_bytes(uint8_t *ops, long pos, uint32_t acc, int s0, int s1, size_t stride) {
+    for (int s = s0; s < s1; s++) {
+        const long q = pos + s;
+        if (q >= 0 && (size_t)q < stride) ops[q] = (uint8_t)(acc >> (8 * s));
+    }
 }
 
 template <int W>
@@ -62,6 +71,9 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
         const uint32_t *qp = a.qpack + (done ? 0 : read * a.q_wstride);
         uint8_t *ops = (a.ops && !done) ? a.ops + read * a.ops_stride : nullptr;
         int i0 = 0, j0 = 0, n = 0, score = 0;
+        /* column ops leave as aligned 32-bit words: omis = misalignment of the row, oacc = the word being filled */
+        const uint32_t omis = (uint32_t)(reinterpret_cast<uintptr_t>(ops) & 3u);
+        uint32_t oacc = 0;
         if (!done && qlen == 0 && tlen == 0) done = true;
 
         while (__any_sync(0xFFFFFFFFu, !done)) {
@@ -94,6 +106,8 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
             int maxTt = Tt;
 #pragma unroll
             for (int d = 16; d >= 1; d >>= 1) maxTt = max(maxTt, __shfl_xor_sync(0xFFFFFFFFu, maxTt, d));
+            /* the bottom row only matters to tiles that leave query rows behind (never for reads of one tile) */
+            const bool track_row = __any_sync(0xFFFFFFFFu, !done && !q_done);
 
             /* ---- fill: one column per iteration, W words per column ---- */
             uint32_t tw = 0;
@@ -113,7 +127,9 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
                         const uint32_t xh = (((eq2 & pv) + pv) ^ pv) | eq2;
                         uint32_t ph = mv | ~(xh | pv);
                         uint32_t mh = pv & xh;
-                        if (w == wlast && Tq > 0) sc += (int)((ph >> blast) & 1u) - (int)((mh >> blast) & 1u);
+                        if (track_row) {
+                            if (w == wlast && Tq > 0) sc += (int)((ph >> blast) & 1u) - (int)((mh >> blast) & 1u);
+                        }
                         const uint32_t hp_out = ph >> 31, hn_out = mh >> 31;
                         ph = (ph << 1) | hpos;
                         mh = (mh << 1) | hneg;
@@ -128,8 +144,7 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
                         hpos = hp_out;
                         hneg = hn_out;
                     }
-                    const int key = (sc << 12) | ((Tt - j) << 1);
-                    rowkey = min(rowkey, key);
+                    if (track_row) rowkey = min(rowkey, (sc << 12) | ((Tt - j) << 1));
                 }
             }
             __syncwarp();
@@ -176,6 +191,12 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
                         op = ((v.x >> b) & 1u) | (((v.y >> b) & 1u) << 1);
                     }
                     const int si = ci - (op != 2u), sj = cj - (op != 1u);
+                    /* the walk is a chain of dependent loads of planes written long ago: pull the line it will need
+                     * BP_PREFETCH columns further down the diagonal into L2 (lanes of a warp share that line) */
+                    if (sj > BP_PREFETCH && si > BP_PREFETCH) {
+                        const uint2 *pf = planes + ((size_t)(sj - 1 - BP_PREFETCH) * W + ((si - 1 - BP_PREFETCH) >> 5)) * 32;
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(pf));
+                    }
                     if (last || (si < inner && sj < inner)) {
                         if (!anchored) { ai = ci; aj = cj; anchored = true; }
                         acc |= op << (2 * (m & 15));
@@ -205,7 +226,14 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
                     if (x < mym) {
                         const int p = mym - 1 - x;
                         if ((p >> 4) != have) { have = p >> 4; word = tb[(size_t)have * 32]; }
-                        if (ops && (size_t)(n + x) < a.ops_stride) ops[n + x] = (uint8_t)((word >> (2 * (p & 15))) & 3u);
+                        const uint32_t vp = (uint32_t)(n + x) + omis;             /* byte slot counted from the aligned base */
+                        oacc |= ((word >> (2 * (p & 15))) & 3u) << (8 * (vp & 3u));
+                        if ((vp & 3u) == 3u) {
+                            const long pos = (long)(vp & ~3u) - (long)omis;     /* offset of the word inside the row */
+                            if (pos >= 0 && (size_t)pos + 4 <= a.ops_stride) *reinterpret_cast<uint32_t *>(ops + pos) = oacc;
+                            else put_bytes(ops, pos, oacc, 0, 4, a.ops_stride);
+                            oacc = 0;
+                        }
                     }
                 }
             }
@@ -216,6 +244,10 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
                 if (last) done = true;
             }
             __syncwarp();
+        }
+        if (ops && (((uint32_t)n + omis) & 3u)) {                  /* the last, partial word */
+            const uint32_t vp = (uint32_t)n + omis;
+            put_bytes(ops, (long)(vp & ~3u) - (long)omis, oacc, 0, (int)(vp & 3u), a.ops_stride);
         }
         if (!skipped && read < a.n) {
             if (a.res) {                                        /* PART 3, alnmain.c:458-477 */
@@ -239,6 +271,11 @@ static int launch_bp(as_gpu *h, const GactArgs &a, size_t n, int blocks_per_sm) 
     const size_t tb_per_warp = (size_t)((a.TS + a.TQ + 15) / 16 + 1) * 32;  /* u32 */
     size_t warps_needed = (n + 31) / 32;
     size_t blocks = (warps_needed + BP_THREADS / 32 - 1) / (BP_THREADS / 32);
+    if (blocks_per_sm <= 0) {        /* as many resident blocks as the register file allows: the traceback is latency bound */
+        int occ = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_gact_bp<W>, BP_THREADS, 0) != cudaSuccess || occ < 1) occ = 4;
+        blocks_per_sm = occ;
+    }
     size_t cap = (size_t)h->sm_count * blocks_per_sm;
     if (blocks > cap) blocks = cap;
     const size_t warps = blocks * (BP_THREADS / 32);
@@ -256,7 +293,7 @@ int as_launch_gact_bp(as_gpu *h, GactArgs &a, size_t n, uint32_t max_qlen, uint3
     if (n >= 0xFFFFFFE0ull) return AS_ERANGE;
     const int rows = (int)(max_qlen < (uint32_t)a.T ? max_qlen : (uint32_t)a.T);
     const int words = rows > 0 ? (rows + 31) / 32 : 1;
-    int bps = 4;
+    int bps = 0;
     if (const char *e = getenv("AS_GACT_BLOCKS_PER_SM")) {
         int v = atoi(e);
         if (v >= 1 && v <= 16) bps = v;
