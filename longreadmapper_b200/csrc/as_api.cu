@@ -136,21 +136,37 @@ static int ensure_pipeline(as_gpu *h) {
     return AS_OK;
 }
 
-/* reads per chunk: enough chunks to overlap the copies with the kernels, each still filling the GPU */
-static size_t chunk_reads(size_t n, size_t stride) {
+/* Chunk schedule of one as_map_batch call.  The D2H stream is the longest of the three (results + CIGAR columns + the
+ * reverse-complemented reads), so the first chunk is small -- it reaches the D2H stream early -- and the following
+ * ones grow to the size at which the kernels run at full efficiency; AS_CHUNK_READS forces a fixed size. */
+static int plan_chunks(size_t n, size_t stride, size_t *begin /* AS_MAX_CHUNKS + 1 */) {
+    size_t fixed = 0;
     if (const char *e = getenv("AS_CHUNK_READS")) {
         long v = atol(e);
-        if (v > 0) return (size_t)v;
+        if (v > 0) fixed = (size_t)v;
+    }
+    int nc = 0;
+    begin[0] = 0;
+    if (fixed) {
+        if ((n + fixed - 1) / fixed > AS_MAX_CHUNKS) fixed = (n + AS_MAX_CHUNKS - 1) / AS_MAX_CHUNKS;
+        for (size_t r = 0; r < n; r += fixed) begin[++nc] = (r + fixed < n) ? r + fixed : n;
+        return nc;
     }
     const size_t min_reads = 32768;
-    size_t c = (n + 7) / 8;
-    /* long reads: cap a chunk at ~256 MB of sequence so that the first kernels start early */
-    const size_t by_bytes = ((size_t)256 << 20) / (stride ? stride : 1);
-    if (c > by_bytes) c = by_bytes;
-    if (c < min_reads) c = min_reads;
-    if ((n + c - 1) / c > AS_MAX_CHUNKS) c = (n + AS_MAX_CHUNKS - 1) / AS_MAX_CHUNKS;
-    if (c > n) c = n;
-    return c ? c : 1;
+    /* long reads: cap a chunk at ~256 MB of sequence */
+    size_t big = n / 4, by_bytes = ((size_t)256 << 20) / (stride ? stride : 1);
+    if (big > by_bytes) big = by_bytes;
+    if (big < min_reads) big = min_reads;
+    size_t c = big / 4 > min_reads ? big / 4 : min_reads;      /* ramp: big/4, big/2, big, big, ... */
+    size_t r = 0;
+    while (r < n) {
+        size_t take = c;
+        if (nc == AS_MAX_CHUNKS - 1 || n - r < take + min_reads / 2) take = n - r;
+        r += take;
+        begin[++nc] = r;
+        if (c < big) c = (2 * c < big) ? 2 * c : big;
+    }
+    return nc;
 }
 
 extern "C" int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t stride, const uint32_t *lens, size_t n,
@@ -181,8 +197,8 @@ extern "C" int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t s
     as_result *d_res = (as_result *)h->results.p;
     uint8_t *d_store = want_ops ? (uint8_t *)h->store.p : nullptr;
 
-    const size_t cr = chunk_reads(n, stride);
-    const int nc = (int)((n + cr - 1) / cr);
+    size_t cb[AS_MAX_CHUNKS + 1];
+    const int nc = plan_chunks(n, stride, cb);
     h->n_chunks_last = nc;
     /* per-read scratch of every chunk is carved out of one allocation made before anything is enqueued */
     {
@@ -201,7 +217,7 @@ extern "C" int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t s
     AS_CUDA(cudaMemsetAsync(h->d_chunk_max, 0, AS_MAX_CHUNKS * sizeof(int), h->stream));
     /* every H2D copy is queued up front: they stream in order while the kernels of earlier chunks run */
     for (int c = 0; c < nc; c++) {
-        const size_t r0 = (size_t)c * cr, cn = (n - r0 < cr) ? n - r0 : cr;
+        const size_t r0 = cb[c], cn = cb[c + 1] - cb[c];
         AS_CUDA(cudaMemcpyAsync(d_reads + r0 * stride, reads + r0 * stride, cn * stride, cudaMemcpyHostToDevice, h->s_h2d));
         AS_CUDA(cudaMemcpyAsync(d_lens + r0, lens + r0, cn * sizeof(uint32_t), cudaMemcpyHostToDevice, h->s_h2d));
         AS_CUDA(cudaEventRecord(h->cev[c][5], h->s_h2d));
@@ -209,7 +225,7 @@ extern "C" int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t s
     /* the CIGAR columns of chunk c are copied once the chunk's widest row is known: only that many columns of
      * every row cross PCIe (the reference leaves columns >= n_cigar_op uninitialised, alnmain.c:316-320) */
     auto finish_chunk = [&](int c) -> int {
-        const size_t r0 = (size_t)c * cr, cn = (n - r0 < cr) ? n - r0 : cr;
+        const size_t r0 = cb[c], cn = cb[c + 1] - cb[c];
         AS_CUDA(cudaEventSynchronize(h->cev[c][7]));
         size_t w = (size_t)(h->h_chunk_max[c] > 0 ? h->h_chunk_max[c] : 0);
         w = (w + 15) & ~(size_t)15;
@@ -221,7 +237,7 @@ extern "C" int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t s
         return AS_OK;
     };
     for (int c = 0; c < nc; c++) {
-        const size_t r0 = (size_t)c * cr, cn = (n - r0 < cr) ? n - r0 : cr;
+        const size_t r0 = cb[c], cn = cb[c + 1] - cb[c];
         AS_CUDA(cudaStreamWaitEvent(h->stream, h->cev[c][5], 0));
         AS_TRY(run_stages(h, p, d_reads + r0 * stride, stride, d_lens + r0, cn, max_len, d_res + r0,
                           d_store ? d_store + r0 * store_stride : nullptr, store_stride, false, nullptr, h->cev[c], r0, n));

@@ -162,9 +162,12 @@ __device__ __forceinline__ void as_ld_block(const FmBlock *b, uint4 &cnt, uint64
 __device__ __forceinline__ uint64_t as_occ(const DevIndex &ix, uint32_t c, uint64_t loc) {
     uint64_t blk = loc >> 6;
     uint32_t r = (uint32_t)loc & 63u;
-    uint4 cnt;
-    uint64_t lo, hi;
-    as_ld_block(ix.fm + blk, cnt, lo, hi);
+    uint32_t v8[8];
+    asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=r"(v8[0]), "=r"(v8[1]), "=r"(v8[2]), "=r"(v8[3]), "=r"(v8[4]), "=r"(v8[5]), "=r"(v8[6]), "=r"(v8[7])
+        : "l"(ix.fm + blk));
+    uint4 cnt = make_uint4(v8[0], v8[1], v8[2], v8[3]);
+    const uint64_t lo = ((uint64_t)v8[5] << 32) | v8[4], hi = ((uint64_t)v8[7] << 32) | v8[6];
     uint64_t m = ((c & 1u) ? lo : ~lo) & ((c & 2u) ? hi : ~hi);
     m &= (r == 63u) ? ~0ULL : ((1ULL << (r + 1)) - 1ULL);
     uint32_t base = c == 0 ? cnt.x : c == 1 ? cnt.y : c == 2 ? cnt.z : cnt.w;
@@ -186,6 +189,9 @@ __device__ __forceinline__ void as_bs_step(const DevIndex &ix, uint32_t c, uint6
 
 /* ---- 32-bit fast path: indexes of at most 2^30 rows (one super block, so the block counts are absolute and every
  * row number fits a register).  Same values as as_occ / as_bs_step, about a third of the instructions. ---- */
+#ifndef AS_OCC_256
+#define AS_OCC_256 1
+#endif
 struct BsChar32 {           /* per-character constants of one backward-search step */
     uint32_t xlo, xhi;      /* xor masks that turn the two planes into "row holds c" */
     uint32_t C;             /* dna_fmi.c[c] */
@@ -209,12 +215,25 @@ __device__ __forceinline__ uint32_t as_shl_clamp(uint32_t v, uint32_t s) {
     asm("shl.b32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(s));
     return r;
 }
+/* the whole 32-byte FM block in ONE 256-bit request (sm_100: LDG.E.256): one L1 tag lookup per occ instead of two */
+__device__ __forceinline__ void as_ld_block256(const FmBlock *b, uint32_t (&v)[8]) {
+    asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+        : "l"(b));
+}
 __device__ __forceinline__ uint32_t as_occ32(const DevIndex &ix, const BsChar32 &b, uint32_t loc) {
     const uint32_t blk = loc >> 6, r = loc & 63u;
+    uint32_t v8[8];                                                        /* cnt[0..3], lo.x lo.y hi.x hi.y */
+#if AS_OCC_256
+    as_ld_block256(ix.fm + blk, v8);
+    const uint32_t base = b.c == 0 ? v8[0] : b.c == 1 ? v8[1] : b.c == 2 ? v8[2] : v8[3];
+#else
     const uint32_t *p = reinterpret_cast<const uint32_t *>(ix.fm + blk);
     const uint32_t base = __ldg(p + b.c);                                   /* same 32-byte sector as the planes */
-    const uint4 w = __ldg(reinterpret_cast<const uint4 *>(p) + 1);          /* lo.x lo.y hi.x hi.y */
-    const uint32_t m0 = (w.x ^ b.xlo) & (w.z ^ b.xhi), m1 = (w.y ^ b.xlo) & (w.w ^ b.xhi);
+    const uint4 w = __ldg(reinterpret_cast<const uint4 *>(p) + 1);
+    v8[4] = w.x; v8[5] = w.y; v8[6] = w.z; v8[7] = w.w;
+#endif
+    const uint32_t m0 = (v8[4] ^ b.xlo) & (v8[6] ^ b.xhi), m1 = (v8[5] ^ b.xlo) & (v8[7] ^ b.xhi);
     const uint32_t k0 = ~as_shl_clamp(0xFFFFFFFEu, r);                       /* rows 0..r of the low half */
     const uint32_t k1 = as_shr_clamp(0xFFFFFFFFu, 63u - r);                  /* rows 32..r of the high half */
     uint32_t v = base + __popc(m0 & k0) + __popc(m1 & k1);

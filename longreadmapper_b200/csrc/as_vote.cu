@@ -16,6 +16,9 @@
 #include <type_traits>
 
 #define VOTE_THREADS 128
+#ifndef VOTE_CLAIM
+#define VOTE_CLAIM 1
+#endif
 #define MAXP 34                      /* seed_len <= 32 -> at most 33 phases */
 #define EMPTY_BUCKET 0xFFFFFFFFFFFFFFFFULL
 
@@ -78,10 +81,24 @@ __device__ __forceinline__ void top2_push(uint64_t &a0, uint64_t &a1, uint64_t c
     }
 }
 
+/* warp-wide max of a small unsigned value (all 32 lanes take part) */
+__device__ __forceinline__ uint32_t warp_max_u32(uint32_t v) {
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) v = max(v, __shfl_xor_sync(0xFFFFFFFFu, v, d));
+    return v;
+}
+
+/*
+ * The 32/G groups of a warp run as one state machine: every trip of the outer loop is ONE PHASE of the read each
+ * group currently owns (groups that finished a read pick the next one at the top of the trip).  All loop bounds
+ * inside a trip are warp-wide maxima and the per-group work is predicated, so the warp never splits into serial
+ * sub-warps: reads that need 1 phase and reads that need 21 share full-width instructions.
+ */
 template <int G, bool BIG, bool SMALL>
 __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, VoteArgs a) {
     constexpr int CAP = 8 * G;
     constexpr int GROUPS = VOTE_THREADS / G;
+    constexpr uint32_t FULL = 0xFFFFFFFFu;
     typedef typename std::conditional<BIG, uint32_t, uint8_t>::type USED_T;
     __shared__ uint8_t s_used[BIG ? 1 : GROUPS * CAP];
     __shared__ uint32_t s_nused[BIG ? 1 : GROUPS];
@@ -126,236 +143,270 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
         t.low[s] = 0xFFFFFFFFu;
     }
     if (g == 0) *t.n_used = 0;
-    __syncwarp(gmask);
+    __syncwarp();
 
     const int sl = a.sl, P = sl + 1;
     const int left0 = sl - ix.hlen;
     const uint64_t hmask = (1ULL << (2 * ix.hlen)) - 1ULL;
     unsigned long long st_seeds = 0, st_steps = 0, st_hits = 0, st_ovf = 0;
 
-    for (;;) {
-        /* next read of this group */
-        uint32_t widx = 0;
-        if (g == 0) widx = atomicAdd(a.work_counter, 1u);
-        widx = __shfl_sync(gmask, widx, 0, G);
-        uint32_t read;
-        if (BIG) {
-            if (widx >= *a.ovf_count) break;
-            read = a.ovf_list[widx];
-        } else {
-            if (widx >= a.n) break;
-            read = widx;
-        }
-        const uint32_t len = a.lens[read];
-        const uint32_t *pr = a.pack + (size_t)read * a.wstride;
-        const uint32_t num_seeds = len / (uint32_t)P;                   /* alnmain.c:371 */
-        const uint32_t span = len > (uint32_t)sl ? len - (uint32_t)sl : 0;   /* seeds start at j < len - sl (:353) */
+    /* state of the read this group owns */
+    bool have = false, drained = false;
+    uint32_t claim_next = 0, claim_end = 0;
+    uint32_t read = 0, len = 0, num_seeds = 0, span = 0, n_outer = 0;
+    const uint32_t *pr = a.pack;
+    int iter = 0;
 
-        uint32_t n_outer = 0;
-        uint64_t best_key = 0, best_val = 0;
-        int iter;
-        bool overflow = false;
-        for (iter = 0; iter < P; ++iter) {
-            const uint32_t m_count = (uint32_t)iter < span ? (span - (uint32_t)iter + (uint32_t)P - 1) / (uint32_t)P : 0;
-            bool ok = true;
-            for (uint32_t c0 = 0; c0 < m_count; c0 += G) {
-                const uint32_t m = c0 + g;
-                const uint32_t j = (uint32_t)iter + m * (uint32_t)P;
-                uint64_t kk = 1, ll = ix.N - 1, rr = 0;                 /* alnmain.c:354 */
-                if (m < m_count) {
-                    const uint64_t seed = as_bases32(pr, j);
-                    bool absent = false;
-                    int left = left0;
-                    if (left0 >= 0) {                                   /* lchash.c:93-101 */
-                        ulonglong2 kl = __ldg(ix.lc + ((seed >> (2 * left0)) & hmask));
-                        kk = kl.x;
-                        ll = kl.y;
-                        absent = (kk == 0 && ll == 0);
-                    }
-                    st_seeds++;
-                    if (!absent) {
-                        if (SMALL) {
-                            uint32_t k32 = (uint32_t)kk, l32 = (uint32_t)ll;
-                            for (int tt = left - 1; tt >= 0; tt--) {    /* fmidx.c:300-310 */
-                                as_bs_step32(ix, (uint32_t)(seed >> (2 * tt)) & 3u, k32, l32);
-                                st_steps++;
-                                if (k32 > l32) break;
-                            }
-                            kk = k32;
-                            ll = l32;
-                        } else {
-                            for (int tt = left - 1; tt >= 0; tt--) {    /* fmidx.c:300-310 */
-                                as_bs_step(ix, (uint32_t)(seed >> (2 * tt)) & 3u, kk, ll);
-                                st_steps++;
-                                if (kk > ll) break;
-                            }
-                        }
-                        rr = kk > ll ? 0 : ll - kk + 1;
-                    }
+    for (;;) {
+        /* ---- groups without a read take the next one ---- */
+        if (!have && !drained) {
+            /* reads are claimed VOTE_CLAIM at a time: one same-address atomic per group and claim, not per read */
+            if (claim_next == claim_end) {
+                uint32_t w0 = 0;
+                if (g == 0) w0 = atomicAdd(a.work_counter, (uint32_t)VOTE_CLAIM);
+                claim_next = __shfl_sync(gmask, w0, 0, G);
+                claim_end = claim_next + VOTE_CLAIM;
+            }
+            const uint32_t widx = claim_next++;
+            const uint32_t limit = BIG ? *a.ovf_count : (uint32_t)a.n;
+            if (widx < limit) {
+                read = BIG ? a.ovf_list[widx] : widx;
+                len = a.lens[read];
+                pr = a.pack + (size_t)read * a.wstride;
+                num_seeds = len / (uint32_t)P;                                   /* alnmain.c:371 */
+                span = len > (uint32_t)sl ? len - (uint32_t)sl : 0;               /* seeds start at j < len - sl (:353) */
+                n_outer = 0;
+                iter = 0;
+                have = true;
+            } else {
+                drained = true;
+            }
+        }
+        if (!__any_sync(FULL, have)) break;
+
+        /* ---- one phase: seeds iter, iter+P, ... of the read (alnmain.c:353) ---- */
+        const uint32_t m_count =
+            (have && (uint32_t)iter < span) ? (span - (uint32_t)iter + (uint32_t)P - 1) / (uint32_t)P : 0;
+        const uint32_t m_max = warp_max_u32(m_count);
+        bool ok = true;
+        for (uint32_t c0 = 0; c0 < m_max; c0 += G) {
+            const uint32_t m = c0 + g;
+            const uint32_t j = (uint32_t)iter + m * (uint32_t)P;
+            uint64_t kk = 1, ll = ix.N - 1, rr = 0;                             /* alnmain.c:354 */
+            if (m < m_count) {
+                const uint64_t seed = as_bases32(pr, j);
+                bool absent = false;
+                if (left0 >= 0) {                                               /* lchash.c:93-101 */
+                    ulonglong2 kl = __ldg(ix.lc + ((seed >> (2 * left0)) & hmask));
+                    kk = kl.x;
+                    ll = kl.y;
+                    absent = (kk == 0 && ll == 0);
                 }
-                const uint32_t rr_eff = (rr > 0 && rr < a.thres) ? (uint32_t)rr : 0u;   /* alnmain.c:360 */
-                const uint32_t multi = __ballot_sync(gmask, rr_eff > 1) & gmask;
-                if (multi == 0) {
-                    /* common case: every surviving seed has exactly one SA row */
-                    if (rr_eff) {
-                        uint64_t key = as_sa(ix, kk) - (uint64_t)j;     /* alnmain.c:363-365, u64 wrap kept */
+                st_seeds++;
+                if (!absent) {
+                    if (SMALL) {
+                        uint32_t k32 = (uint32_t)kk, l32 = (uint32_t)ll;
+                        for (int tt = left0 - 1; tt >= 0; tt--) {                /* fmidx.c:300-310 */
+                            as_bs_step32(ix, (uint32_t)(seed >> (2 * tt)) & 3u, k32, l32);
+                            st_steps++;
+                            if (k32 > l32) break;
+                        }
+                        kk = k32;
+                        ll = l32;
+                    } else {
+                        for (int tt = left0 - 1; tt >= 0; tt--) {                /* fmidx.c:300-310 */
+                            as_bs_step(ix, (uint32_t)(seed >> (2 * tt)) & 3u, kk, ll);
+                            st_steps++;
+                            if (kk > ll) break;
+                        }
+                    }
+                    rr = kk > ll ? 0 : ll - kk + 1;
+                }
+            }
+            __syncwarp();
+            const uint32_t rr_eff = (rr > 0 && rr < a.thres) ? (uint32_t)rr : 0u;   /* alnmain.c:360 */
+            if (!__any_sync(FULL, rr_eff > 1)) {
+                /* common case: every surviving seed of the warp has exactly one SA row */
+                if (rr_eff) {
+                    uint64_t key = as_sa(ix, kk) - (uint64_t)j;                 /* alnmain.c:363-365, u64 wrap kept */
+                    st_hits++;
+                    if (!table_insert<USED_T>(t, key >> 4, (uint32_t)key & 15u, m * a.thres)) ok = false;
+                }
+            } else {
+                /* spread all SA rows of the group's seeds over its lanes */
+                uint32_t incl = rr_eff;
+#pragma unroll
+                for (int d = 1; d < G; d <<= 1) {
+                    uint32_t o = __shfl_up_sync(gmask, incl, d, G);
+                    if ((int)g >= d) incl += o;
+                }
+                const uint32_t base = incl - rr_eff;
+                const uint32_t V = __shfl_sync(gmask, incl, G - 1, G);
+                const uint32_t V_max = warp_max_u32(V);
+                for (uint32_t v0 = 0; v0 < V_max; v0 += G) {
+                    const uint32_t v = v0 + g;
+                    /* owner = largest lane whose exclusive base <= v */
+                    uint32_t lo = 0;
+#pragma unroll
+                    for (int d = G >> 1; d >= 1; d >>= 1) {
+                        uint32_t b = __shfl_sync(gmask, base, lo + d, G);
+                        if (b <= v) lo += d;
+                    }
+                    const uint32_t ob = __shfl_sync(gmask, base, lo, G);
+                    const uint32_t okl = __shfl_sync(gmask, (uint32_t)kk, lo, G);
+                    const uint32_t okh = __shfl_sync(gmask, (uint32_t)(kk >> 32), lo, G);
+                    if (v < V) {
+                        const uint32_t om = c0 + lo;
+                        const uint32_t oj = (uint32_t)iter + om * (uint32_t)P;
+                        const uint32_t off = v - ob;
+                        uint64_t row = (((uint64_t)okh << 32) | okl) + off;
+                        uint64_t key = as_sa(ix, row) - (uint64_t)oj;
                         st_hits++;
-                        if (!table_insert<USED_T>(t, key >> 4, (uint32_t)key & 15u, m * a.thres)) ok = false;
-                    }
-                } else {
-                    /* spread all SA rows of the chunk over the lanes of the group */
-                    uint32_t incl = rr_eff;
-#pragma unroll
-                    for (int d = 1; d < G; d <<= 1) {
-                        uint32_t o = __shfl_up_sync(gmask, incl, d, G);
-                        if ((int)g >= d) incl += o;
-                    }
-                    const uint32_t base = incl - rr_eff;
-                    const uint32_t V = __shfl_sync(gmask, incl, G - 1, G);
-                    for (uint32_t v0 = 0; v0 < V; v0 += G) {
-                        const uint32_t v = v0 + g;
-                        /* owner = largest lane whose exclusive base <= v */
-                        uint32_t lo = 0;
-#pragma unroll
-                        for (int d = G >> 1; d >= 1; d >>= 1) {
-                            uint32_t b = __shfl_sync(gmask, base, lo + d, G);
-                            if (b <= v) lo += d;
-                        }
-                        const uint32_t ob = __shfl_sync(gmask, base, lo, G);
-                        const uint32_t okl = __shfl_sync(gmask, (uint32_t)kk, lo, G);
-                        const uint32_t okh = __shfl_sync(gmask, (uint32_t)(kk >> 32), lo, G);
-                        if (v < V) {
-                            const uint32_t om = c0 + lo;
-                            const uint32_t oj = (uint32_t)iter + om * (uint32_t)P;
-                            const uint32_t off = v - ob;
-                            uint64_t row = (((uint64_t)okh << 32) | okl) + off;
-                            uint64_t key = as_sa(ix, row) - (uint64_t)oj;
-                            st_hits++;
-                            if (!table_insert<USED_T>(t, key >> 4, (uint32_t)key & 15u, om * a.thres + off)) ok = false;
-                        }
+                        if (!table_insert<USED_T>(t, key >> 4, (uint32_t)key & 15u, om * a.thres + off)) ok = false;
                     }
                 }
             }
-            __syncwarp(gmask);
-            if (__ballot_sync(gmask, !ok) & gmask) {
-                overflow = true;
-                break;
-            }
-            /* ---- TOP2 of the phase (histo.c:84-96) ---- */
-            uint64_t a0 = 0, a1 = 0;
-            uint32_t slot0 = 0;
-            const uint32_t nu = *t.n_used;
-            for (uint32_t u = g; u < nu; u += G) {
+        }
+        __syncwarp();
+        const bool overflow = have && (__ballot_sync(gmask, !ok) & gmask) != 0;
+
+        /* ---- TOP2 of the phase (histo.c:84-96) over the slots the phase claimed ---- */
+        uint64_t a0 = 0, a1 = 0;
+        uint32_t slot0 = 0;
+        const uint32_t nu = *t.n_used;
+        const uint32_t nu_max = warp_max_u32(nu);
+        for (uint32_t u0 = 0; u0 < nu_max; u0 += G) {
+            const uint32_t u = u0 + g;
+            if (u < nu) {
                 uint32_t s = t.used[u];
                 uint64_t c = ((uint64_t)t.val[s] << 32) | (0xFFFFFFFFu - t.ord[s]);
                 if (c > a0) slot0 = s;
                 top2_push(a0, a1, c);
             }
+        }
 #pragma unroll
-            for (int d = G >> 1; d >= 1; d >>= 1) {
-                uint64_t b0 = __shfl_xor_sync(gmask, a0, d, G);
-                uint64_t b1 = __shfl_xor_sync(gmask, a1, d, G);
-                uint32_t bs = __shfl_xor_sync(gmask, slot0, d, G);
-                uint64_t mn = a0 < b0 ? a0 : b0;
-                uint64_t mx1 = a1 > b1 ? a1 : b1;
-                if (b0 > a0) {
-                    a0 = b0;
-                    slot0 = bs;
-                }
-                a1 = mn > mx1 ? mn : mx1;
+        for (int d = G >> 1; d >= 1; d >>= 1) {
+            uint64_t b0 = __shfl_xor_sync(gmask, a0, d, G);
+            uint64_t b1 = __shfl_xor_sync(gmask, a1, d, G);
+            uint32_t bs = __shfl_xor_sync(gmask, slot0, d, G);
+            uint64_t mn = a0 < b0 ? a0 : b0;
+            uint64_t mx1 = a1 > b1 ? a1 : b1;
+            if (b0 > a0) {
+                a0 = b0;
+                slot0 = bs;
             }
-            const uint32_t v0val = (uint32_t)(a0 >> 32), v1val = (uint32_t)(a1 >> 32);
-            uint64_t c0key = 0;
-            if (v0val) c0key = ((uint64_t)t.bucket[slot0] << 4) | t.low[slot0];
-            __syncwarp(gmask);
-            /* reset only the slots this phase claimed */
-            for (uint32_t u = g; u < nu; u += G) {
+            a1 = mn > mx1 ? mn : mx1;
+        }
+        const uint32_t v0val = (uint32_t)(a0 >> 32), v1val = (uint32_t)(a1 >> 32);
+        uint64_t c0key = 0;
+        if (v0val) c0key = ((uint64_t)t.bucket[slot0] << 4) | t.low[slot0];
+        __syncwarp();
+        /* ---- reset: the claimed slots, or the whole table when the phase overflowed it ---- */
+        if (__any_sync(FULL, overflow)) {
+            if (overflow) {
+                for (uint32_t s = g; s < t.cap; s += G) {
+                    t.bucket[s] = EMPTY_BUCKET;
+                    t.val[s] = 0;
+                    t.ord[s] = 0xFFFFFFFFu;
+                    t.low[s] = 0xFFFFFFFFu;
+                }
+            }
+        }
+        for (uint32_t u0 = 0; u0 < nu_max; u0 += G) {
+            const uint32_t u = u0 + g;
+            if (u < nu && !overflow) {
                 uint32_t s = t.used[u];
                 t.bucket[s] = EMPTY_BUCKET;
                 t.val[s] = 0;
                 t.ord[s] = 0xFFFFFFFFu;
                 t.low[s] = 0xFFFFFFFFu;
             }
-            __syncwarp(gmask);
-            if (g == 0) *t.n_used = 0;
-            __syncwarp(gmask);
-            if (num_seeds > 0) {                                        /* alnmain.c:373 */
-                const uint64_t v = (uint64_t)v0val + v1val;
-                const double score = (double)v / (double)(int)num_seeds;
-                if (score > 0.6) {                                      /* :378-384 */
-                    best_key = c0key;
-                    best_val = v0val;
-                    break;
-                } else if (v0val != 0) {                                /* :386-388 histo_add(outer, cand[0].key) */
-                    const uint64_t b = c0key >> 4;
-                    uint32_t found = n_outer;
-                    for (uint32_t e = 0; e < n_outer; e++)
-                        if ((okey[e] >> 4) == b) found = e;
-                    __syncwarp(gmask);
-                    if (g == 0) {
-                        if (found < n_outer) {
-                            oval[found] += 1;
-                            if (c0key < okey[found]) okey[found] = c0key;
-                        } else {
-                            okey[n_outer] = c0key;
-                            oval[n_outer] = 1;
-                        }
-                    }
-                    if (found == n_outer) n_outer++;
-                    __syncwarp(gmask);
-                }
+        }
+        __syncwarp();
+        if (g == 0) *t.n_used = 0;
+        __syncwarp();
+
+        /* ---- phase control (alnmain.c:371-404) ---- */
+        bool finished = false, broke = false;
+        uint64_t best_key = 0, best_val = 0;
+        uint32_t vote_outer = 0;             /* this group adds c0key to its outer list */
+        if (have && !overflow && num_seeds > 0) {                               /* alnmain.c:373 */
+            const uint64_t v = (uint64_t)v0val + v1val;
+            const double score = (double)v / (double)(int)num_seeds;
+            if (score > 0.6) {                                                  /* :378-384 */
+                best_key = c0key;
+                best_val = v0val;
+                broke = true;
+            } else if (v0val != 0) {                                            /* :386-388 histo_add(outer, cand[0].key) */
+                vote_outer = 1;
             }
         }
-        if (overflow) {
-            if (BIG) {
-                /* cannot happen: the big table holds every possible vote of a phase; flag it loudly */
-                st_ovf++;
-                if (g == 0) {
+        if (__any_sync(FULL, vote_outer != 0)) {
+            const uint32_t no_max = warp_max_u32(vote_outer ? n_outer : 0u);
+            const uint64_t b = c0key >> 4;
+            uint32_t found = n_outer;
+            for (uint32_t e = 0; e < no_max; e++)
+                if (vote_outer && e < n_outer && (okey[e] >> 4) == b) found = e;
+            __syncwarp();
+            if (vote_outer && g == 0) {
+                if (found < n_outer) {
+                    oval[found] += 1;
+                    if (c0key < okey[found]) okey[found] = c0key;
+                } else {
+                    okey[n_outer] = c0key;
+                    oval[n_outer] = 1;
+                }
+            }
+            if (vote_outer && found == n_outer) n_outer++;
+            __syncwarp();
+        }
+        if (have) {
+            if (overflow) {
+                finished = true;
+            } else {
+                if (!broke) iter++;                                            /* a break leaves iter where it was */
+                finished = broke || iter >= P;
+            }
+        }
+        if (__any_sync(FULL, finished)) {
+            int from_outer = 0;
+            if (finished && !overflow && iter >= P - 1) {                       /* alnmain.c:400-403 */
+                uint64_t bk = 0;
+                uint32_t bv = 0;
+                for (uint32_t e = 0; e < n_outer; e++) {
+                    if (oval[e] > bv) {
+                        bv = oval[e];
+                        bk = okey[e];
+                    }
+                }
+                best_key = bk;
+                best_val = bv;
+                from_outer = 1;
+            }
+            if (finished && g == 0) {
+                if (!overflow) {
+                    VoteOut o;
+                    o.best_key = best_key;
+                    o.best_val = best_val;
+                    o.phases = iter;
+                    o.from_outer = from_outer;
+                    a.out[read] = o;
+                } else if (BIG) {
+                    /* cannot happen: the big table holds every possible vote of a phase; flag it loudly */
                     VoteOut o;
                     o.best_key = 0;
                     o.best_val = 0;
                     o.phases = -1;
                     o.from_outer = -1;
                     a.out[read] = o;
-                }
-            } else if (g == 0) {
-                a.ovf_list[atomicAdd(a.ovf_count, 1u)] = read;
-            }
-            /* the phase did not reach its reset: wipe the whole table */
-            __syncwarp(gmask);
-            for (uint32_t s = g; s < t.cap; s += G) {
-                t.bucket[s] = EMPTY_BUCKET;
-                t.val[s] = 0;
-                t.ord[s] = 0xFFFFFFFFu;
-                t.low[s] = 0xFFFFFFFFu;
-            }
-            if (g == 0) *t.n_used = 0;
-            __syncwarp(gmask);
-            continue;
-        }
-        int from_outer = 0;
-        if (iter >= P - 1) {                                            /* alnmain.c:400-403 */
-            uint64_t bk = 0;
-            uint32_t bv = 0;
-            for (uint32_t e = 0; e < n_outer; e++) {
-                if (oval[e] > bv) {
-                    bv = oval[e];
-                    bk = okey[e];
+                } else {
+                    a.ovf_list[atomicAdd(a.ovf_count, 1u)] = read;           /* redone by the BIG pass */
                 }
             }
-            best_key = bk;
-            best_val = bv;
-            from_outer = 1;
+            if (finished && overflow && BIG) st_ovf += (g == 0);
+            if (finished) have = false;
+            __syncwarp();
         }
-        if (g == 0) {
-            VoteOut o;
-            o.best_key = best_key;
-            o.best_val = best_val;
-            o.phases = iter;
-            o.from_outer = from_outer;
-            a.out[read] = o;
-        }
-        __syncwarp(gmask);
     }
 
     /* stats: one atomic per warp and counter */
