@@ -342,7 +342,9 @@ def run_b200(args):
     # correctness of what was timed: the results of the last step against the simulated truth
     res = np.frombuffer(d_res.cpu().numpy().tobytes(), dtype=lm.RESULT_DTYPE)
     ok = res["valid"] == 1
-    exact = float(((res["off"] == truth_pos) & ok & ((res["strand"] == 1) == (truth_strand == 1))).mean())
+    same_strand = (res["strand"] == 1) == (truth_strand == 1)
+    exact = float(((res["off"] == truth_pos) & ok & same_strand).mean())
+    near = float(((np.abs(res["off"].astype(np.int64) - truth_pos.astype(np.int64)) <= 50) & ok & same_strand).mean())
 
     # ---- e2e: host buffers through the C ABI ----
     e2e = None
@@ -422,10 +424,19 @@ def run_b200(args):
     for s in stages.values():
         if s.get("achieved") is not None:
             s["frac"] = s["achieved"] / s["peak"]
+    # DRAM bytes per launch of the dominant kernels, from the committed `ncu --set full` capture of this same command
+    # (profiles/ncu_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum); null for workloads it was not taken on
+    traffic = {}
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(args.workload, {})
+    except (OSError, ValueError):
+        pass
     dom = max(("part1_seed_vote", "gact"), key=lambda k: stages[k]["ms"])
     d = stages[dom]
-    roofline = {"kernel": "k_gact" if dom == "gact" else "k_vote", "bound": d["bound"], "achieved": d["achieved"],
-                "peak": d["peak"], "unit": d["unit"], "frac": d.get("frac"), "traffic": None,
+    roofline = {"kernel": "k_gact_bp" if dom == "gact" else "k_vote", "bound": d["bound"], "achieved": d["achieved"],
+                "peak": d["peak"], "unit": d["unit"], "frac": d.get("frac"),
+                "traffic": traffic.get("k_gact_bp" if dom == "gact" else "k_vote") if n == wl["reads"] else None,
+                "algorithmic": vote_bytes if dom != "gact" else per_step["dp_cells"] * INT_OPS_PER_CELL,
                 "peak_source": peak_src if d["bound"] == "hbm" else "148 SMs x 128 INT32 lanes x clocks.max.sm 1965 MHz",
                 "ms_per_launch": d["ms"], "share_of_step": d["ms"] / tm["total"] if tm["total"] else None,
                 "stages": stages, "sm_clock_mhz_under_load": sm_clock / 1e6}
@@ -435,12 +446,13 @@ def run_b200(args):
             "vs_baseline": None, "dtype": "u64/i32", "data": "synthetic",
             "config": {"workload": workload_name(args.workload, args), "reads_per_step_per_gpu": n, "seed_len": 20,
                        "thres": 300, "gact_T": int(params.gact_T), "gact_O": int(params.gact_O),
-                       "l2": "inputs exceed L2 (reads 151 MB + lc table 256 MB + SA 37 MB per pass > 126 MB)",
+                       "l2": f"inputs exceed L2: reads {n * stride / 1e6:.0f} MB + lc table 268 MB + SA {4 * (2 * wl['genome'] + 1) / 1e6:.0f} MB "
+                             f"+ GACT planes per pass > 126 MB, no flush needed",
                        "index": "built on the GPU (as_gpu_build), replicated per rank", "index_build_s": round(t_index, 2)},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
             "roofline": roofline,
             "gcups": stages["gact"]["gcups"],
-            "quality": {"mapped_frac": float(ok.mean()), "exact_pos_strand_frac": exact,
+            "quality": {"mapped_frac": float(ok.mean()), "exact_pos_strand_frac": exact, "within_50bp_strand_frac": near,
                         "valid_total": [st["valid"], st["total"]]},
             "stats_per_step_per_gpu": {k: per_step[k] for k in ("seeds", "bs_steps", "sa_hits", "dp_cells", "overflow_reads")}}
 
