@@ -248,6 +248,69 @@ __device__ __forceinline__ void as_bs_step32(const DevIndex &ix, uint32_t c, uin
     l = b.C + ol;
 }
 
+/* ---- table-driven backward search (k_vote): the per-character constants of a step live in a 4-entry shared-memory
+ * table, so a step costs one LDS.128 instead of three select chains over kernel parameters, and the block count of
+ * the character is picked from the loaded sector with three bit-selects on the same masks. ---- */
+struct __align__(16) BsTab {
+    uint32_t xlo, xhi;      /* all-ones when bit 0 / bit 1 of the character code is clear */
+    uint32_t C;             /* dna_fmi.c[c] (low half; the 64-bit path adds Chi) */
+    uint32_t plim;          /* c == A: rows [primary, primary + plim) share primary's block ('$' is coded A); else 0 */
+};
+__device__ __forceinline__ void as_bs_tab_init(const DevIndex &ix, BsTab *tab, uint32_t *tabChi, uint32_t tid) {
+    if (tid < 4) {
+        const uint64_t C = tid == 0 ? ix.C[0] : tid == 1 ? ix.C[1] : tid == 2 ? ix.C[2] : ix.C[3];
+        BsTab b;
+        b.xlo = (tid & 1u) ? 0u : 0xFFFFFFFFu;
+        b.xhi = (tid & 2u) ? 0u : 0xFFFFFFFFu;
+        b.C = (uint32_t)C;
+        b.plim = tid == 0 ? 64u - ((uint32_t)ix.primary & 63u) : 0u;
+        tab[tid] = b;
+        tabChi[tid] = (uint32_t)(C >> 32);
+    }
+}
+__device__ __forceinline__ uint32_t as_bitsel(uint32_t a, uint32_t b, uint32_t m) { return (a & m) | (b & ~m); }
+/* both FM blocks of a backward-search step in one asm statement, so the two 256-bit requests are issued back to back
+ * (left to itself ptxas sank the second load below the first one's consumers and serialised the two round trips) */
+__device__ __forceinline__ void as_ld_block256x2(const FmBlock *pa, const FmBlock *pb, uint32_t (&a)[8], uint32_t (&b)[8]) {
+    asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%16];\n\t"
+                 "ld.global.nc.v8.b32 {%8,%9,%10,%11,%12,%13,%14,%15}, [%17];"
+                 : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3]), "=r"(a[4]), "=r"(a[5]), "=r"(a[6]), "=r"(a[7]),
+                   "=r"(b[0]), "=r"(b[1]), "=r"(b[2]), "=r"(b[3]), "=r"(b[4]), "=r"(b[5]), "=r"(b[6]), "=r"(b[7])
+                 : "l"(pa), "l"(pb));
+}
+/* count of the character in the loaded block up to row r, plus the block's own count: ~14 instructions */
+__device__ __forceinline__ uint32_t as_occ_blk(const uint32_t (&v8)[8], const uint4 ct, uint32_t r) {
+    const uint32_t base = as_bitsel(as_bitsel(v8[0], v8[1], ct.x), as_bitsel(v8[2], v8[3], ct.x), ct.y);
+    const uint32_t k0 = ~as_shl_clamp(0xFFFFFFFEu, r);                       /* rows 0..r of the low half */
+    const uint32_t k1 = as_shr_clamp(0xFFFFFFFFu, 63u - r);                  /* rows 32..r of the high half */
+    const uint32_t m0 = ((v8[4] ^ ct.x) & k0) & (v8[6] ^ ct.y), m1 = ((v8[5] ^ ct.x) & k1) & (v8[7] ^ ct.y);
+    return base + __popc(m0) + __popc(m1);
+}
+__device__ __forceinline__ void as_bs_step32t(const DevIndex &ix, const uint4 ct, uint32_t &k, uint32_t &l) {
+    const uint32_t a = k - 1, b = l, p = (uint32_t)ix.primary;
+    uint32_t va[8], vb[8];
+    as_ld_block256x2(ix.fm + (a >> 6), ix.fm + (b >> 6), va, vb);
+    uint32_t ok = as_occ_blk(va, ct, a & 63u);
+    uint32_t ol = as_occ_blk(vb, ct, b & 63u);
+    ok -= (a - p) < ct.w ? 1u : 0u;                                          /* the '$' row is stored as code 0 */
+    ol -= (b - p) < ct.w ? 1u : 0u;
+    k = ct.z + ok + 1;
+    l = ct.z + ol;
+}
+__device__ __forceinline__ void as_bs_step64t(const DevIndex &ix, const uint4 ct, uint32_t Chi, uint32_t c,
+                                              uint64_t &k, uint64_t &l) {
+    const uint64_t a = k - 1, b = l;
+    const uint64_t C = ((uint64_t)Chi << 32) | ct.z;
+    uint32_t va[8], vb[8];
+    as_ld_block256x2(ix.fm + (a >> 6), ix.fm + (b >> 6), va, vb);
+    uint64_t ok = __ldg(ix.super + 4 * (a >> AS_SB_SHIFT) + c) + as_occ_blk(va, ct, (uint32_t)a & 63u);
+    uint64_t ol = __ldg(ix.super + 4 * (b >> AS_SB_SHIFT) + c) + as_occ_blk(vb, ct, (uint32_t)b & 63u);
+    ok -= (a - ix.primary) < (uint64_t)ct.w ? 1u : 0u;
+    ol -= (b - ix.primary) < (uint64_t)ct.w ? 1u : 0u;
+    k = C + ok + 1;
+    l = C + ol;
+}
+
 __device__ __forceinline__ uint64_t as_sa(const DevIndex &ix, uint64_t row) {
     uint64_t v = __ldg(ix.sa_lo + row);
     if (ix.sa_hi) v |= (uint64_t)__ldg(ix.sa_hi + row) << 32;

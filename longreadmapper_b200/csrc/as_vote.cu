@@ -19,6 +19,9 @@
 #ifndef VOTE_CLAIM
 #define VOTE_CLAIM 1
 #endif
+#ifndef VOTE_MIN_BLOCKS
+#define VOTE_MIN_BLOCKS 6
+#endif
 #define MAXP 34                      /* seed_len <= 32 -> at most 33 phases */
 #define EMPTY_BUCKET 0xFFFFFFFFFFFFFFFFULL
 
@@ -83,9 +86,7 @@ __device__ __forceinline__ void top2_push(uint64_t &a0, uint64_t &a1, uint64_t c
 
 /* warp-wide max of a small unsigned value (all 32 lanes take part) */
 __device__ __forceinline__ uint32_t warp_max_u32(uint32_t v) {
-#pragma unroll
-    for (int d = 16; d >= 1; d >>= 1) v = max(v, __shfl_xor_sync(0xFFFFFFFFu, v, d));
-    return v;
+    return __reduce_max_sync(0xFFFFFFFFu, v);                       /* REDUX.MAX: one instruction */
 }
 
 /*
@@ -95,7 +96,7 @@ __device__ __forceinline__ uint32_t warp_max_u32(uint32_t v) {
  * sub-warps: reads that need 1 phase and reads that need 21 share full-width instructions.
  */
 template <int G, bool BIG, bool SMALL>
-__global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, VoteArgs a) {
+__global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? VOTE_MIN_BLOCKS + 1 : VOTE_MIN_BLOCKS)) k_vote(DevIndex ix, VoteArgs a) {
     constexpr int CAP = 8 * G;
     constexpr int GROUPS = VOTE_THREADS / G;
     constexpr uint32_t FULL = 0xFFFFFFFFu;
@@ -106,6 +107,8 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
     __shared__ uint32_t s_val[BIG ? 1 : GROUPS * CAP], s_ord[BIG ? 1 : GROUPS * CAP], s_low[BIG ? 1 : GROUPS * CAP];
     __shared__ unsigned long long s_okey[(BIG ? 1 : GROUPS) * MAXP];
     __shared__ uint32_t s_oval[(BIG ? 1 : GROUPS) * MAXP];
+    __shared__ BsTab s_tab[4];                 /* per-character constants of a backward-search step */
+    __shared__ uint32_t s_tabChi[4];
 
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t g = lane & (G - 1);
@@ -143,7 +146,8 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
         t.low[s] = 0xFFFFFFFFu;
     }
     if (g == 0) *t.n_used = 0;
-    __syncwarp();
+    as_bs_tab_init(ix, s_tab, s_tabChi, threadIdx.x);
+    __syncthreads();
 
     const int sl = a.sl, P = sl + 1;
     const int left0 = sl - ix.hlen;
@@ -153,7 +157,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
     /* state of the read this group owns */
     bool have = false, drained = false;
     uint32_t claim_next = 0, claim_end = 0;
-    uint32_t read = 0, len = 0, num_seeds = 0, span = 0, n_outer = 0;
+    uint32_t read = 0, len = 0, num_seeds = 0, span = 0, n_outer = 0, span_q = 0, span_r = 0;
     const uint32_t *pr = a.pack;
     int iter = 0;
 
@@ -175,6 +179,8 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
                 pr = a.pack + (size_t)read * a.wstride;
                 num_seeds = len / (uint32_t)P;                                   /* alnmain.c:371 */
                 span = len > (uint32_t)sl ? len - (uint32_t)sl : 0;               /* seeds start at j < len - sl (:353) */
+                span_q = span / (uint32_t)P;                                      /* one division per read, not per phase */
+                span_r = span - span_q * (uint32_t)P;
                 n_outer = 0;
                 iter = 0;
                 have = true;
@@ -185,10 +191,12 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
         if (!__any_sync(FULL, have)) break;
 
         /* ---- one phase: seeds iter, iter+P, ... of the read (alnmain.c:353) ---- */
-        const uint32_t m_count =
-            (have && (uint32_t)iter < span) ? (span - (uint32_t)iter + (uint32_t)P - 1) / (uint32_t)P : 0;
+        /* seeds of the phase = ceil((span - iter) / P) = span/P + (iter < span%P), because 0 <= iter < P */
+        const uint32_t m_count = have ? span_q + ((uint32_t)iter < span_r ? 1u : 0u) : 0u;
         const uint32_t m_max = warp_max_u32(m_count);
-        bool ok = true;
+        bool ok = true, reg_vote = false;
+        uint32_t v0val = 0, v1val = 0;
+        uint64_t c0key = 0;
         for (uint32_t c0 = 0; c0 < m_max; c0 += G) {
             const uint32_t m = c0 + g;
             const uint32_t j = (uint32_t)iter + m * (uint32_t)P;
@@ -206,8 +214,12 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
                 if (!absent) {
                     if (SMALL) {
                         uint32_t k32 = (uint32_t)kk, l32 = (uint32_t)ll;
+                        /* the constants of step tt-1 are fetched while step tt's sectors are in flight */
+                        uint4 ct = *reinterpret_cast<const uint4 *>(s_tab + ((uint32_t)(seed >> (2 * (left0 - 1))) & 3u));
                         for (int tt = left0 - 1; tt >= 0; tt--) {                /* fmidx.c:300-310 */
-                            as_bs_step32(ix, (uint32_t)(seed >> (2 * tt)) & 3u, k32, l32);
+                            const uint4 cur = ct;
+                            ct = *reinterpret_cast<const uint4 *>(s_tab + ((uint32_t)(seed >> (2 * (tt > 0 ? tt - 1 : 0))) & 3u));
+                            as_bs_step32t(ix, cur, k32, l32);
                             st_steps++;
                             if (k32 > l32) break;
                         }
@@ -215,7 +227,8 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
                         ll = l32;
                     } else {
                         for (int tt = left0 - 1; tt >= 0; tt--) {                /* fmidx.c:300-310 */
-                            as_bs_step(ix, (uint32_t)(seed >> (2 * tt)) & 3u, kk, ll);
+                            const uint32_t c = (uint32_t)(seed >> (2 * tt)) & 3u;
+                            as_bs_step64t(ix, *reinterpret_cast<const uint4 *>(s_tab + c), s_tabChi[c], c, kk, ll);
                             st_steps++;
                             if (kk > ll) break;
                         }
@@ -225,8 +238,46 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
             }
             __syncwarp();
             const uint32_t rr_eff = (rr > 0 && rr < a.thres) ? (uint32_t)rr : 0u;   /* alnmain.c:360 */
-            if (!__any_sync(FULL, rr_eff > 1)) {
-                /* common case: every surviving seed of the warp has exactly one SA row */
+            if (m_max <= (uint32_t)G && !__any_sync(FULL, rr_eff > 1)) {
+                /* the whole phase is this one round and every surviving seed has exactly one SA row: at most one
+                 * vote per lane, so the vote list is built in registers.  Lanes voting for the same bucket of the
+                 * same read find each other with MATCH.ANY; the entry's val is their number, its list position the
+                 * lowest such lane (votes are cast in seed order = lane order, histo.c:42-56), its key the smallest
+                 * key among them.  TOP2 (histo.c:84-96) is then a 3..5-round butterfly on 32-bit words. */
+                const bool valid = rr_eff != 0;
+                uint64_t key = 0;
+                if (valid) {
+                    key = as_sa(ix, kk) - (uint64_t)j;                          /* alnmain.c:363-365, u64 wrap kept */
+                    st_hits++;
+                }
+                const uint64_t tag = valid ? ((key >> 4) | ((uint64_t)(lane / G) << 60)) : (0xF000000000000000ULL | lane);
+                const uint32_t peers = __match_any_sync(FULL, tag);
+                const uint32_t low = (uint32_t)key & 15u;
+                const uint32_t b3 = __ballot_sync(FULL, low & 8u), b2 = __ballot_sync(FULL, low & 4u),
+                               b1 = __ballot_sync(FULL, low & 2u), b0 = __ballot_sync(FULL, low & 1u);
+                uint32_t cand = peers, minlow = 0, z;                           /* min of `low` over the peers */
+                z = cand & ~b3; if (z) cand = z; else minlow |= 8u;
+                z = cand & ~b2; if (z) cand = z; else minlow |= 4u;
+                z = cand & ~b1; if (z) cand = z; else minlow |= 2u;
+                z = cand & ~b0; if (z) cand = z; else minlow |= 1u;
+                const bool leader = valid && ((uint32_t)__ffs((int)peers) - 1u) == lane;
+                uint32_t a0 = leader ? (((uint32_t)__popc(peers) << 5) | (31u - lane)) : 0u, a1 = 0u;
+#pragma unroll
+                for (int d = G >> 1; d >= 1; d >>= 1) {
+                    const uint32_t o0 = __shfl_xor_sync(FULL, a0, d), o1 = __shfl_xor_sync(FULL, a1, d);
+                    const uint32_t mn = min(a0, o0), mx1 = max(a1, o1);
+                    a0 = max(a0, o0);
+                    a1 = max(mn, mx1);
+                }
+                v0val = a0 >> 5;
+                v1val = a1 >> 5;
+                const uint32_t wl = 31u - (a0 & 31u);
+                const uint64_t wkey = __shfl_sync(FULL, key, wl);
+                const uint32_t wlow = __shfl_sync(FULL, minlow, wl);
+                c0key = v0val ? ((wkey & ~15ULL) | wlow) : 0ULL;
+                reg_vote = true;
+            } else if (!__any_sync(FULL, rr_eff > 1)) {
+                /* every surviving seed of the warp has exactly one SA row */
                 if (rr_eff) {
                     uint64_t key = as_sa(ix, kk) - (uint64_t)j;                 /* alnmain.c:363-365, u64 wrap kept */
                     st_hits++;
@@ -270,6 +321,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
         __syncwarp();
         const bool overflow = have && (__ballot_sync(gmask, !ok) & gmask) != 0;
 
+        if (!reg_vote) {                     /* warp-uniform: reg_vote follows from m_max and a warp vote */
         /* ---- TOP2 of the phase (histo.c:84-96) over the slots the phase claimed ---- */
         uint64_t a0 = 0, a1 = 0;
         uint32_t slot0 = 0;
@@ -297,8 +349,8 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
             }
             a1 = mn > mx1 ? mn : mx1;
         }
-        const uint32_t v0val = (uint32_t)(a0 >> 32), v1val = (uint32_t)(a1 >> 32);
-        uint64_t c0key = 0;
+        v0val = (uint32_t)(a0 >> 32);
+        v1val = (uint32_t)(a1 >> 32);
         if (v0val) c0key = ((uint64_t)t.bucket[slot0] << 4) | t.low[slot0];
         __syncwarp();
         /* ---- reset: the claimed slots, or the whole table when the phase overflowed it ---- */
@@ -325,15 +377,18 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS) k_vote(DevIndex ix, V
         __syncwarp();
         if (g == 0) *t.n_used = 0;
         __syncwarp();
+        }
 
         /* ---- phase control (alnmain.c:371-404) ---- */
         bool finished = false, broke = false;
         uint64_t best_key = 0, best_val = 0;
         uint32_t vote_outer = 0;             /* this group adds c0key to its outer list */
         if (have && !overflow && num_seeds > 0) {                               /* alnmain.c:373 */
+            /* score = (double)v / num_seeds > 0.6 (alnmain.c:371-378) decided in integers: 5v > 3n makes the quotient
+             * exceed 0.6 by >= 1/(5n), far more than an ulp; 5v == 3n makes the correctly rounded quotient the double
+             * nearest 0.6, i.e. the literal itself (not greater); 5v < 3n puts it below.  Same verdict, no fp64 divide. */
             const uint64_t v = (uint64_t)v0val + v1val;
-            const double score = (double)v / (double)(int)num_seeds;
-            if (score > 0.6) {                                                  /* :378-384 */
+            if (5ull * v > 3ull * (uint64_t)num_seeds) {                        /* :378-384 */
                 best_key = c0key;
                 best_val = v0val;
                 broke = true;
@@ -478,19 +533,30 @@ int as_launch_vote(as_gpu *h, const as_params *p, const uint32_t *d_pack, size_t
     uint64_t groups_needed = n;
     uint64_t groups_per_block = VOTE_THREADS / G;
     uint64_t blocks = (groups_needed + groups_per_block - 1) / groups_per_block;
-    uint64_t cap = (uint64_t)h->sm_count * 8;          /* 8 blocks of <= 27 KB shared memory per SM */
-    unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
+    unsigned grid = 0;
     /* indexes of one super block (<= 2^30 rows) take the 32-bit backward-search path */
     const bool small = h->ix.N <= (1ULL << AS_SB_SHIFT) && !(p->flags & AS_F_WIDE_INDEX);
-#define VOTE_LAUNCH(GG)                                                                      \
-    do {                                                                                     \
-        if (small) k_vote<GG, false, true><<<grid, VOTE_THREADS, 0, h->stream>>>(h->ix, a);  \
-        else k_vote<GG, false, false><<<grid, VOTE_THREADS, 0, h->stream>>>(h->ix, a);       \
+    /* reads are claimed from a work counter, so the grid is exactly the resident blocks (registers / shared memory) */
+#define VOTE_LAUNCH1(GG, SM)                                                                                     \
+    do {                                                                                                         \
+        int occ = 0;                                                                                             \
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_vote<GG, false, SM>, VOTE_THREADS, 0) != cudaSuccess || \
+            occ < 1)                                                                                             \
+            occ = VOTE_MIN_BLOCKS;                                                                               \
+        const uint64_t cap = (uint64_t)h->sm_count * (uint64_t)occ;                                              \
+        grid = (unsigned)(blocks < cap ? blocks : cap);                                                          \
+        k_vote<GG, false, SM><<<grid, VOTE_THREADS, 0, h->stream>>>(h->ix, a);                                   \
+    } while (0)
+#define VOTE_LAUNCH(GG)                 \
+    do {                                \
+        if (small) VOTE_LAUNCH1(GG, true); \
+        else VOTE_LAUNCH1(GG, false);   \
     } while (0)
     if (G == 8) VOTE_LAUNCH(8);
     else if (G == 16) VOTE_LAUNCH(16);
     else VOTE_LAUNCH(32);
 #undef VOTE_LAUNCH
+#undef VOTE_LAUNCH1
     h->launches++;
     AS_CUDA(cudaGetLastError());
     /* overflow pass: exits at once when the queue is empty */

@@ -1,5 +1,8 @@
-for v in "-DAS_OCC_256=0 -DVOTE_CLAIM=1" "-DAS_OCC_256=1 -DVOTE_CLAIM=1" "-DAS_OCC_256=0 -DVOTE_CLAIM=4" "-DAS_OCC_256=0 -DVOTE_CLAIM=16"; do
+# A/B builds of k_vote on the GPU box: rebuild as_vote.cu with each flag set, print step and PART 1 times (c2, c3)
+for v in "$@"; do
   touch longreadmapper_b200/csrc/as_vote.cu
   make -s -C longreadmapper_b200/csrc cuda EXTRA_NVFLAGS="$v" > /dev/null 2>&1
-  python bench.py --no-cpu --no-e2e --steps 3 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('$v', d['ms_per_step'], d['roofline']['stages']['part1_seed_vote']['ms'])"
+  for w in "c2" "c3 --reads 20000"; do
+    python bench.py --no-cpu --no-e2e --steps 3 --workload $w | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('$v', '$w', round(d['ms_per_step'],3), round(d['roofline']['stages']['part1_seed_vote']['ms'],3))"
+  done
 done
