@@ -95,6 +95,9 @@ typedef struct as_params {
     int32_t  gact_T;     /* GACT tile size (DESIGN.md GACT spec), default 320 */
     int32_t  gact_O;     /* GACT overlap, default 120 */
     uint32_t flags;      /* AS_F_* */
+    int32_t  gact_band;  /* bit-parallel GACT: half-width of the banded first attempt at a tile; 0 = adaptive (default),
+                          * < 0 = full matrix only.  Results never depend on it (a tile the band cannot prove exact is
+                          * filled again with the whole matrix). */
 } as_params;
 #define AS_F_MYERS        1u   /* also run the edlib-equivalent NW distance with k=(int)(0.05*len*2) per read */
 #define AS_F_NO_ALIGN     2u   /* stop after PART 1+2 (no GACT): results carry loc/off/strand/flag only */
@@ -149,6 +152,9 @@ uint64_t as_gpu_launch_count(as_gpu *h);
 /* Per-shard counters for the end-of-run statistics (alnmain.c:541 "Sensitivity: valid/total"). */
 typedef struct as_stats {
     uint64_t total, valid, n_flag4, n_flag16, sum_ed, dp_cells, seeds, sa_hits, bs_steps, overflow_reads;
+    uint64_t dp_cells_eval;   /* DP cells the GACT kernels actually filled (banded pass + redone reads); dp_cells is
+                               * the tile area Tq x Tt of the spec */
+    uint64_t gact_redone;     /* warp-tiles (one tile of 32 reads) filled a second time with the whole matrix */
 } as_stats;
 int as_gpu_stats(as_gpu *h, as_stats *out);          /* accumulated since open / last reset */
 int as_gpu_stats_reset(as_gpu *h);

@@ -45,12 +45,12 @@ class AsIndexOut(C.Structure):
 
 class Params(C.Structure):
     _fields_ = [("seed_len", C.c_uint32), ("thres", C.c_uint32), ("gact_T", C.c_int32), ("gact_O", C.c_int32),
-                ("flags", C.c_uint32)]
+                ("flags", C.c_uint32), ("gact_band", C.c_int32)]
 
 
 class AsStats(C.Structure):
     _fields_ = [(k, C.c_uint64) for k in ("total", "valid", "n_flag4", "n_flag16", "sum_ed", "dp_cells", "seeds",
-                                           "sa_hits", "bs_steps", "overflow_reads")]
+                                           "sa_hits", "bs_steps", "overflow_reads", "dp_cells_eval", "gact_redone")]
 
 
 class AsHostIndex(C.Structure):
@@ -303,10 +303,12 @@ class GpuMapper:
         except Exception:
             pass
 
-    def params(self, seed_len=20, thres=300, T=None, O=None, flags=0):
+    def params(self, seed_len=20, thres=300, T=None, O=None, flags=0, band=None):
         p = Params()
         self.L.as_params_default(C.byref(p))
         p.seed_len, p.thres, p.flags = seed_len, thres, flags
+        if band is not None:
+            p.gact_band = band
         if T is not None:
             p.gact_T = T
         if O is not None:

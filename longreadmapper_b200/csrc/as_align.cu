@@ -297,6 +297,8 @@ int as_launch_gact(as_gpu *h, const as_params *p, const uint32_t *d_qpack, size_
     AS_CUDA(cudaMemsetAsync(h->misc[5].p, 0, 64, h->stream));
     a.work_counter = (unsigned int *)h->misc[5].p;
     a.stats = h->d_stats;
+    a.band = p->gact_band;
+    a.fail_count = nullptr;
     /* two implementations of the same tile DP: bit-parallel, one read per lane (as_gact_bp.cu) for batches that fill
      * the GPU with lanes; anti-diagonal, one read per warp (below) for small batches */
     const bool force_warp = (p->flags & AS_F_GACT_WARP) != 0, force_bp = (p->flags & AS_F_GACT_BITPAR) != 0;

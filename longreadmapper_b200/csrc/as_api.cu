@@ -12,6 +12,7 @@ extern "C" void as_params_default(as_params *p) {
     p->gact_T = 320;       /* Darwin GACT operating point (README.md:5; DESIGN.md "GACT spec") */
     p->gact_O = 120;
     p->flags = 0;
+    p->gact_band = 0;      /* adaptive banded first pass */
 }
 
 static size_t pack_wstride(uint32_t max_len) { return ((size_t)max_len + 15) / 16 + 3; }
@@ -308,10 +309,11 @@ extern "C" int as_gpu_stats(as_gpu *h, as_stats *out) {
     if (!h || !out) return AS_EINVAL;
     AS_CUDA(cudaSetDevice(h->device));
     AS_CUDA(cudaStreamSynchronize(h->stream));
-    unsigned long long v[10];
+    unsigned long long v[12];
     AS_CUDA(cudaMemcpy(v, h->d_stats, sizeof v, cudaMemcpyDeviceToHost));
     out->total = v[0]; out->valid = v[1]; out->n_flag4 = v[2]; out->n_flag16 = v[3]; out->sum_ed = v[4];
     out->dp_cells = v[5]; out->seeds = v[6]; out->sa_hits = v[7]; out->bs_steps = v[8]; out->overflow_reads = v[9];
+    out->dp_cells_eval = v[10]; out->gact_redone = v[11];
     return AS_OK;
 }
 

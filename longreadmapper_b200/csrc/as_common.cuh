@@ -75,6 +75,7 @@ struct as_gpu {
     bool timing_pending = false;           /* as_map_batch_device enqueued a call whose events were not read yet */
     int *d_chunk_max = nullptr;            /* per chunk: max n_cigar_op (trims the CIGAR-column D2H) */
     int *h_chunk_max = nullptr;            /* pinned mirror */
+    unsigned int *h_band = nullptr, *d_band = nullptr;   /* adaptive GACT band: mapped pinned word + its device alias */
     int sm_count = 148;
     uint64_t launches = 0;      /* kernels launched by this handle since open */
 };
@@ -133,7 +134,12 @@ struct GactArgs {
     as_result *res;              /* map mode output (may be NULL) */
     unsigned int *work_counter;
     unsigned long long *stats;
+    /* bit-parallel kernel with a banded first attempt per tile (as_gact_bp.cu) */
+    int band;                    /* < 0: full matrix only; 0: adaptive; > 0: fixed half-width (rounded up to a level) */
+    unsigned int *fail_count;    /* policy counters of the launch: warp-tiles refilled, warp-tiles, lane-tiles served by
+                                  * half the band, lane-tiles */
 };
+#define AS_GACT_BAND0 16
 
 /* bit-parallel GACT (as_gact_bp.cu): one read per lane; `a` is filled by as_launch_gact */
 int as_launch_gact_bp(as_gpu *h, GactArgs &a, size_t n, uint32_t max_qlen, uint32_t max_tlen);

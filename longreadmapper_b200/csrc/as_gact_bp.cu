@@ -4,7 +4,7 @@
  *
  * Same tiles, same DP matrix, same traceback priority (diag, up, left) as the warp-per-read kernel in
  * as_align.cu -- but the tile is filled with the Myers/Hyyro bit-vector recurrence (the one edlib's
- * calculateBlock uses, edlib.cpp:373-408): 32 DP rows per 32-bit word, ~25 integer instructions per word instead of
+ * calculateBlock uses, edlib.cpp:373-408): 32 DP rows per 32-bit word, ~24 integer instructions per word instead of
  * ~10 per CELL.  One read per LANE; a warp walks the tiles of its 32 reads in lock step.
  *
  * What makes the traceback exact: with dv = D[i][j]-D[i-1][j] (+1 <=> bit of Pv'), D0 <=> D[i][j]==D[i-1][j-1],
@@ -15,12 +15,28 @@
  *   lo = ~Eq & (Pv' | ~D0)      hi = ~Eq & (~Pv' | ~D0)
  * The two planes of every (column, word) go to a per-warp slab in HBM laid out [column][word][lane] as uint2, so a
  * warp's store is one 256-byte line and the traceback of lanes that sit on the same column reads one line.
+ *
+ * Sliding band (first attempt at a tile).  A cell of value v has every optimal path inside |i-j| <= v, so a tile
+ * whose traceback costs at most KB is fully determined by the cells with |i-j| <= KB.  The first attempt therefore
+ * keeps only NB words per column in registers -- the words that meet rows [j-KB, j+KB], KB = 16(NB-1) -- and slides
+ * them down one word every 32 columns (the range is the same for all 32 lanes of the warp, because they sit on the
+ * same column).  A word entering the band starts from Pv = ~0, Mv = 0 and the top word takes hin = +1, which is what
+ * edlib's block band does (edlib.cpp:694-895): values computed that way are never below the true ones and are exact
+ * wherever the true value is <= KB.  Hence: if the walk from the end cell stays in |i-j| <= KB and costs <= KB, every
+ * value and every tie-break on it equals the full matrix's, and the ops are bit-identical; otherwise the warp fills
+ * the same tile again with the whole matrix (lanes that had passed recompute what they had).  For 150-bp reads at
+ * NB = 2 that is 2 of 5 words per column filled and stored.
+ *
+ * Traceback reads the planes through a per-lane window in shared memory: BP_WIN columns down the diagonal are fetched
+ * with independent loads in one go, then walked from shared memory, so the chain of dependent global loads is one
+ * round trip per window instead of one per op.  The committed ops leave as whole 32-bit words: four 2-bit codes of
+ * the walk are turned into four op bytes, in forward order, by one lookup.
  */
 #include "as_common.cuh"
 #include <stdlib.h>
 
 #define BP_THREADS 128
-#define BP_PREFETCH 12
+#define BP_WIN 16                     /* columns of traceback planes staged in shared memory per refill */
 
 /* even bits of x (bit 2r) -> bit r of the low word; odd bits -> high word */
 __device__ __forceinline__ uint32_t compress_even(uint64_t x) {
@@ -41,15 +57,239 @@ __device__ __forceinline__ void put_bytes(uint8_t *ops, long pos, uint32_t acc, 
     }
 }
 
-template <int W>
+/* bit planes of query rows [32w, 32w+32) of the tile that starts at base i0 (rows at and past Tq read as 'A') */
+__device__ __forceinline__ void load_qword(const uint32_t *qp, int i0, int w, int Tq, uint32_t &lo, uint32_t &hi) {
+    uint64_t x = 0;
+    if (32 * w < Tq) x = as_bases16(qp, (uint64_t)(i0 + 32 * w));
+    if (32 * w + 16 < Tq) x |= (uint64_t)as_bases16(qp, (uint64_t)(i0 + 32 * w + 16)) << 32;
+    lo = compress_even(x);
+    hi = compress_even(x >> 1);
+}
+
+struct TileGeom {
+    const uint32_t *qp;
+    const uint32_t *tbase;
+    uint64_t toff;
+    int i0, j0, Tq, Tt, maxTt, T, inner, KB;
+    bool done, q_done, t_done, last, track_row, track_col;
+};
+struct TileOut {
+    int m, ai, aj, tscore, walkcost;
+    bool bad;
+};
+
+/*
+ * One attempt at one tile: fill (NBW words per column; SLIDE: the words slide down the diagonal, else they are the
+ * whole tile), end cell, traceback into the warp's slab `tb` (16 ops per word, walk order).
+ */
+template <int NBW, bool SLIDE>
+__device__ __forceinline__ void tile_pass(const TileGeom &g, uint2 *__restrict__ planes, uint32_t *__restrict__ tb,
+                                          uint2 (*win)[32], uint32_t lane, unsigned long long &st_eval, TileOut &out) {
+    const int Tq = g.Tq, Tt = g.Tt, KB = SLIDE ? g.KB : 0x3FFFFFFF;
+    uint32_t qlo[NBW], qhi[NBW], Pv[NBW], Mv[NBW];
+#pragma unroll
+    for (int s = 0; s < NBW; s++) {
+        load_qword(g.qp, g.i0, s, Tq, qlo[s], qhi[s]);
+        Pv[s] = 0xFFFFFFFFu;                    /* D[i][0] = i */
+        Mv[s] = 0u;
+    }
+    const int wlast = Tq > 0 ? (Tq - 1) >> 5 : 0;
+    const uint32_t blast = Tq > 0 ? (uint32_t)(Tq - 1) & 31u : 0u;
+    int sc = Tq;                                            /* D[Tq][j], valid while the bottom row is in the band */
+    int rowkey = (Tq << 12) | (Tt << 1);                    /* bottom-row candidates (edge 0), column 0 first */
+    /* sliding band: sb = value at the bottom row of the band's lowest word, in the column just filled */
+    const bool track_sb = SLIDE && (g.track_row || g.track_col);
+    int sb = 32 * NBW, wlo = 0;
+
+    /* ---- fill: one column per iteration ---- */
+    uint32_t tw = 0;
+    uint2 *pcol = planes;
+    for (int j = 1; j <= g.maxTt; j++, pcol += NBW * 32) {
+        if (SLIDE) {
+            const int nwlo = j - KB > 1 ? (j - KB - 1) >> 5 : 0;
+            if (nwlo != wlo) {                               /* warp-uniform: the band moves down one word */
+                wlo = nwlo;
+#pragma unroll
+                for (int s = 0; s + 1 < NBW; s++) {
+                    Pv[s] = Pv[s + 1]; Mv[s] = Mv[s + 1]; qlo[s] = qlo[s + 1]; qhi[s] = qhi[s + 1];
+                }
+                Pv[NBW - 1] = 0xFFFFFFFFu;                   /* the entering word's column j-1 is +1 per row */
+                Mv[NBW - 1] = 0u;
+                load_qword(g.qp, g.i0, wlo + NBW - 1, Tq, qlo[NBW - 1], qhi[NBW - 1]);
+                if (track_sb && j <= Tt) {
+                    sb += 32;
+                    if (wlo + NBW - 1 == wlast) sc = sb - 31 + (int)blast;
+                }
+            }
+        }
+        if (j <= Tt) {
+            if (((j - 1) & 15) == 0) tw = as_bases16(g.tbase, g.toff + (uint64_t)(g.j0 + j - 1));
+            const uint32_t tl = 0u - (tw & 1u), th = 0u - ((tw >> 1) & 1u);
+            tw >>= 2;
+            uint32_t hpos = 1u, hneg = 0u;                   /* D[0][j] - D[0][j-1] = +1 (also above a band) */
+#pragma unroll
+            for (int s = 0; s < NBW; s++) {
+                const uint32_t eq = ~((qlo[s] ^ tl) | (qhi[s] ^ th));
+                const uint32_t pv = Pv[s], mv = Mv[s];
+                const uint32_t xv = eq | mv;
+                const uint32_t eq2 = eq | hneg;
+                const uint32_t xh = (((eq2 & pv) + pv) ^ pv) | eq2;
+                uint32_t ph = mv | ~(xh | pv);
+                uint32_t mh = pv & xh;
+                if (g.track_row) {
+                    if (wlo + s == wlast && Tq > 0) sc += (int)((ph >> blast) & 1u) - (int)((mh >> blast) & 1u);
+                }
+                const uint32_t hp_out = ph >> 31, hn_out = mh >> 31;
+                ph = (ph << 1) | hpos;
+                mh = (mh << 1) | hneg;
+                const uint32_t npv = mh | ~(xv | ph);
+                Pv[s] = npv;
+                Mv[s] = ph & xv;
+                const uint32_t nd0 = ~(xh | mv);            /* ~D0 */
+                uint2 o;
+                o.x = ~eq & (npv | nd0);
+                o.y = ~eq & (~npv | nd0);
+                pcol[s * 32] = o;
+                hpos = hp_out;
+                hneg = hn_out;
+            }
+            if (track_sb) sb += (int)hpos - (int)hneg;
+            if (g.track_row && wlast >= wlo && wlast < wlo + NBW) rowkey = min(rowkey, (sc << 12) | ((Tt - j) << 1));
+        }
+    }
+    __syncwarp();
+    if (!g.done) st_eval += (unsigned long long)(32 * NBW) * (unsigned long long)Tt;
+
+    /* ---- end cell (non-last tiles): min (D, distance from the corner, edge) over the interior edges ---- */
+    int ei = Tq, ej = Tt;
+    if (!g.done && !g.last) {
+        int best = 0x7FFFFFFF;
+        if (!g.q_done) best = rowkey;
+        if (!g.t_done) {                                     /* Tt == maxTt here, so wlo is this lane's last band */
+            int v = Tt;                                      /* D[0][Tt] */
+            if (SLIDE) {                                     /* value just above the band of the last column */
+                v = sb;
+#pragma unroll
+                for (int s = 0; s < NBW; s++) v -= __popc(Pv[s]) - __popc(Mv[s]);
+            }
+            int ck = wlo == 0 ? ((v << 12) | (Tq << 1) | 1) : 0x7FFFFFFF;
+#pragma unroll
+            for (int s = 0; s < NBW; s++) {
+                const int r0 = 32 * (wlo + s);
+                if (r0 < Tq) {
+                    const uint32_t pv = Pv[s], mv = Mv[s];
+                    const int lim = Tq - r0 < 32 ? Tq - r0 : 32;
+                    for (int b = 0; b < lim; b++) {
+                        v += (int)((pv >> b) & 1u) - (int)((mv >> b) & 1u);
+                        ck = min(ck, (v << 12) | ((Tq - (r0 + b + 1)) << 1) | 1);
+                    }
+                }
+            }
+            best = min(best, ck);
+        }
+        const int dist = (best >> 1) & 0x7FF;
+        if (best & 1) { ei = Tq - dist; ej = Tt; } else { ei = Tq; ej = Tt - dist; }
+    }
+
+    /* ---- traceback: ops of the walk, packed 16 per word, into the warp's slab ---- */
+    int ci = g.done ? 0 : ei, cj = g.done ? 0 : ej;
+    bool anchored = false, oob = false;
+    if (SLIDE && (ci < 0 || cj < 0)) {                      /* no edge cell inside the band */
+        oob = true;
+        ci = cj = 0;
+    }
+    uint32_t acc = 0;
+    int m = 0, ai = ei, aj = ej, tscore = 0, walkcost = 0;
+    int wc0 = -1, wi0 = 0;               /* window: entry k holds column wc0-k at the word of row wi0-1-k */
+    while (__any_sync(0xFFFFFFFFu, (ci | cj) != 0)) {
+        if (SLIDE && (ci | cj) != 0 && abs(ci - cj) > KB) {  /* left the band: planes there were never written */
+            oob = true;
+            ci = cj = 0;
+        }
+        const bool interior = ci > 0 && cj > 0;
+        int k = wc0 - (cj - 1);
+        const bool hit = interior && (unsigned)k < (unsigned)BP_WIN && ((wi0 - 1 - k) >> 5) == ((ci - 1) >> 5);
+        if (__any_sync(0xFFFFFFFFu, interior && !hit)) {
+            /* refill: BP_WIN independent loads down the diagonal from the current cell; the lines of the window
+             * after this one are pulled into L2 meanwhile (lanes of a warp mostly share them) */
+            if (interior) {
+                wc0 = cj - 1;
+                wi0 = ci;
+#pragma unroll
+                for (int kk = 0; kk < BP_WIN; kk++) {
+                    const int col = wc0 - kk, row = wi0 - 1 - kk;
+                    if (col >= 0 && row >= 0) {
+                        const int cwlo = SLIDE ? (col - KB > 0 ? (col - KB) >> 5 : 0) : 0;    /* band of column j = col+1 */
+                        int s = (row >> 5) - cwlo;
+                        if (SLIDE) s = min(max(s, 0), NBW - 1);                               /* only off-band entries clamp */
+                        win[kk][lane] = planes[((size_t)col * NBW + s) * 32];
+                    }
+                }
+                if (wc0 >= 2 * BP_WIN && wi0 > 2 * BP_WIN) {
+                    const int col = wc0 - BP_WIN - BP_WIN / 2, row = wi0 - 1 - BP_WIN - BP_WIN / 2;
+                    const int cwlo = SLIDE ? (col - KB > 0 ? (col - KB) >> 5 : 0) : 0;
+                    const int s = SLIDE ? min(max((row >> 5) - cwlo, 0), NBW - 1) : (row >> 5);
+                    const uint2 *pf = planes + ((size_t)col * NBW + s) * 32;
+#pragma unroll
+                    for (int kk = -BP_WIN / 2; kk < BP_WIN / 2; kk += 2)
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(pf + (ptrdiff_t)kk * NBW * 32));
+                }
+                k = 0;
+            }
+        }
+        if ((ci | cj) != 0) {
+            uint32_t op;
+            if (ci == 0) op = 2;
+            else if (cj == 0) op = 1;
+            else {
+                const int b = (ci - 1) & 31;
+                const uint2 v = win[k][lane];
+                op = ((v.x >> b) & 1u) | (((v.y >> b) & 1u) << 1);
+            }
+            const int si = ci - (op != 2u), sj = cj - (op != 1u);
+            walkcost += (op != 0u);
+            if (g.last || (si < g.inner && sj < g.inner)) {
+                if (!anchored) { ai = ci; aj = cj; anchored = true; }
+                acc |= op << (2 * (m & 15));
+                m++;
+                if ((m & 15) == 0) { tb[(size_t)((m >> 4) - 1) * 32] = acc; acc = 0; }
+                tscore += (op != 0u);
+            }
+            ci = si;
+            cj = sj;
+        }
+    }
+    if (m & 15) tb[(size_t)(m >> 4) * 32] = acc;
+    __syncwarp();
+    out.m = m; out.ai = ai; out.aj = aj; out.tscore = tscore; out.walkcost = walkcost;
+    out.bad = SLIDE && !g.done && (oob || walkcost > KB);
+}
+
+/*
+ * W = words of a whole tile column (full-matrix attempt); NB = words of the sliding band of the first attempt
+ * (NB == W: no band, every tile is filled once with the whole matrix).
+ */
+template <int W, int NB>
 __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__restrict__ planes_all, size_t planes_per_warp,
                                                         uint32_t *__restrict__ tb_all, size_t tb_per_warp) {
+    constexpr bool BANDED = NB < W;
+    __shared__ uint2 s_win[BP_THREADS / 32][BP_WIN][32];
+    __shared__ uint32_t s_lut[256];      /* 4 walk-order op codes (one byte of the slab) -> 4 op bytes in forward order */
+    for (uint32_t e = threadIdx.x; e < 256; e += BP_THREADS)
+        s_lut[e] = ((e >> 6) & 3u) | (((e >> 4) & 3u) << 8) | (((e >> 2) & 3u) << 16) | ((e & 3u) << 24);
+    __syncthreads();
     const uint32_t lane = threadIdx.x & 31u;
     const size_t gwarp = ((size_t)blockIdx.x * BP_THREADS + threadIdx.x) >> 5;
-    uint2 *planes = planes_all + gwarp * planes_per_warp + lane;          /* [(col*W + w)*32] */
+    uint2 *planes = planes_all + gwarp * planes_per_warp + lane;          /* [(col*words + slot)*32] */
     uint32_t *tb = tb_all + gwarp * tb_per_warp + lane;                    /* [word*32]: 16 ops per word, walk order */
-    const int T = a.T, inner = a.T - a.O;
-    unsigned long long st_cells = 0;
+    uint2 (*win)[32] = s_win[threadIdx.x >> 5];
+    unsigned long long st_cells = 0, st_eval = 0;
+    unsigned int st_retry = 0, st_tiles = 0, st_wtiles = 0, st_half = 0;
+    TileGeom g;
+    g.T = a.T;
+    g.inner = a.T - a.O;
+    g.KB = BANDED ? 16 * (NB - 1) : 256;
+    g.tbase = a.tbase;
 
     for (;;) {
         uint32_t base = 0;
@@ -59,18 +299,20 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
         const size_t read = (size_t)base + lane;
         bool done = read >= a.n;
         int qlen = 0, tlen = 0;
-        uint64_t toff = 0;
+        g.toff = 0;
         if (!done) {
             qlen = (int)a.qlens[read];
             tlen = a.tlens ? (int)a.tlens[read] : qlen;
-            toff = a.toff ? a.toff[read] : 0;
+            g.toff = a.toff ? a.toff[read] : 0;
             /* seq_lookup failed: flag 4 was set by PART 2; reference behaviour is undefined (alnmain.c:409,430-446) */
-            if (toff == AS_TOFF_NONE) done = true;
+            if (g.toff == AS_TOFF_NONE) done = true;
         }
         const bool skipped = done;
-        const uint32_t *qp = a.qpack + (done ? 0 : read * a.q_wstride);
+        g.qp = a.qpack + (done ? 0 : read * a.q_wstride);
         uint8_t *ops = (a.ops && !done) ? a.ops + read * a.ops_stride : nullptr;
-        int i0 = 0, j0 = 0, n = 0, score = 0;
+        int n = 0, score = 0;
+        g.i0 = 0;
+        g.j0 = 0;
         /* column ops leave as aligned 32-bit words: omis = misalignment of the row, oacc = the word being filled */
         const uint32_t omis = (uint32_t)(reinterpret_cast<uintptr_t>(ops) & 3u);
         uint32_t oacc = 0;
@@ -78,170 +320,91 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
 
         while (__any_sync(0xFFFFFFFFu, !done)) {
             /* ---- tile geometry of this lane ---- */
-            int Tq = 0, Tt = 0;
-            bool q_done = true, t_done = true;
+            g.Tq = 0;
+            g.Tt = 0;
+            g.q_done = g.t_done = true;
             if (!done) {
-                Tq = qlen - i0 < T ? qlen - i0 : T;
-                Tt = tlen - j0 < T ? tlen - j0 : T;
-                q_done = (i0 + Tq == qlen);
-                t_done = (j0 + Tt == tlen);
+                g.Tq = qlen - g.i0 < g.T ? qlen - g.i0 : g.T;
+                g.Tt = tlen - g.j0 < g.T ? tlen - g.j0 : g.T;
+                g.q_done = (g.i0 + g.Tq == qlen);
+                g.t_done = (g.j0 + g.Tt == tlen);
             }
-            const bool last = q_done && t_done;
-            /* ---- query bit planes of the tile rows ---- */
-            uint32_t qlo[W], qhi[W], Pv[W], Mv[W];
-#pragma unroll
-            for (int w = 0; w < W; w++) {
-                uint64_t x = 0;
-                if (32 * w < Tq) x = as_bases16(qp, (uint64_t)(i0 + 32 * w));
-                if (32 * w + 16 < Tq) x |= (uint64_t)as_bases16(qp, (uint64_t)(i0 + 32 * w + 16)) << 32;
-                qlo[w] = compress_even(x);
-                qhi[w] = compress_even(x >> 1);
-                Pv[w] = 0xFFFFFFFFu;                    /* D[i][0] = i */
-                Mv[w] = 0u;
-            }
-            const int wlast = Tq > 0 ? (Tq - 1) >> 5 : 0;
-            const uint32_t blast = Tq > 0 ? (uint32_t)(Tq - 1) & 31u : 0u;
-            int sc = Tq;                                            /* D[Tq][j] */
-            int rowkey = (Tq << 12) | (Tt << 1);                    /* bottom-row candidates (edge 0), column 0 first */
-            int maxTt = Tt;
-#pragma unroll
-            for (int d = 16; d >= 1; d >>= 1) maxTt = max(maxTt, __shfl_xor_sync(0xFFFFFFFFu, maxTt, d));
+            g.done = done;
+            g.last = g.q_done && g.t_done;
+            g.maxTt = __reduce_max_sync(0xFFFFFFFFu, g.Tt);
             /* the bottom row only matters to tiles that leave query rows behind (never for reads of one tile) */
-            const bool track_row = __any_sync(0xFFFFFFFFu, !done && !q_done);
+            g.track_row = __any_sync(0xFFFFFFFFu, !done && !g.q_done);
+            g.track_col = __any_sync(0xFFFFFFFFu, !done && !g.t_done);
 
-            /* ---- fill: one column per iteration, W words per column ---- */
-            uint32_t tw = 0;
-            uint2 *pcol = planes;
-            for (int j = 1; j <= maxTt; j++, pcol += W * 32) {
-                if (j <= Tt) {
-                    if (((j - 1) & 15) == 0) tw = as_bases16(a.tbase, toff + (uint64_t)(j0 + j - 1));
-                    const uint32_t tl = 0u - (tw & 1u), th = 0u - ((tw >> 1) & 1u);
-                    tw >>= 2;
-                    uint32_t hpos = 1u, hneg = 0u;                   /* D[0][j] - D[0][j-1] = +1 */
-#pragma unroll
-                    for (int w = 0; w < W; w++) {
-                        const uint32_t eq = ~((qlo[w] ^ tl) | (qhi[w] ^ th));
-                        const uint32_t pv = Pv[w], mv = Mv[w];
-                        const uint32_t xv = eq | mv;
-                        const uint32_t eq2 = eq | hneg;
-                        const uint32_t xh = (((eq2 & pv) + pv) ^ pv) | eq2;
-                        uint32_t ph = mv | ~(xh | pv);
-                        uint32_t mh = pv & xh;
-                        if (track_row) {
-                            if (w == wlast && Tq > 0) sc += (int)((ph >> blast) & 1u) - (int)((mh >> blast) & 1u);
-                        }
-                        const uint32_t hp_out = ph >> 31, hn_out = mh >> 31;
-                        ph = (ph << 1) | hpos;
-                        mh = (mh << 1) | hneg;
-                        const uint32_t npv = mh | ~(xv | ph);
-                        Pv[w] = npv;
-                        Mv[w] = ph & xv;
-                        const uint32_t nd0 = ~(xh | mv);            /* ~D0 */
-                        uint2 o;
-                        o.x = ~eq & (npv | nd0);
-                        o.y = ~eq & (~npv | nd0);
-                        pcol[w * 32] = o;
-                        hpos = hp_out;
-                        hneg = hn_out;
-                    }
-                    if (track_row) rowkey = min(rowkey, (sc << 12) | ((Tt - j) << 1));
-                }
+            TileOut o;
+            bool full = !BANDED;
+            if (BANDED) {
+                tile_pass<NB, true>(g, planes, tb, win, lane, st_eval, o);
+                /* some lane's walk cannot be proven exact: the warp fills the tile again with the whole matrix */
+                full = __any_sync(0xFFFFFFFFu, o.bad);
+                st_retry += (full && lane == 0);
             }
-            __syncwarp();
-            if (!done) st_cells += (unsigned long long)Tq * (unsigned long long)Tt;
-
-            /* ---- end cell (non-last tiles): min (D, distance from the corner, edge) over the interior edges ---- */
-            int ei = Tq, ej = Tt;
-            if (!done && !last) {
-                int best = 0x7FFFFFFF;
-                if (!q_done) best = rowkey;
-                if (!t_done) {
-                    int v = Tt;                                      /* D[0][Tt] */
-                    int ck = (v << 12) | (Tq << 1) | 1;
-#pragma unroll
-                    for (int w = 0; w < W; w++) {
-                        if (32 * w < Tq) {
-                            const uint32_t pv = Pv[w], mv = Mv[w];
-                            const int lim = Tq - 32 * w < 32 ? Tq - 32 * w : 32;
-                            for (int b = 0; b < lim; b++) {
-                                v += (int)((pv >> b) & 1u) - (int)((mv >> b) & 1u);
-                                const int i = 32 * w + b + 1;
-                                ck = min(ck, (v << 12) | ((Tq - i) << 1) | 1);
-                            }
-                        }
-                    }
-                    best = min(best, ck);
-                }
-                const int dist = (best >> 1) & 0x7FF;
-                if (best & 1) { ei = Tq - dist; ej = Tt; } else { ei = Tq; ej = Tt - dist; }
+            if (full) tile_pass<W, false>(g, planes, tb, win, lane, st_eval, o);
+            if (!done) {
+                st_cells += (unsigned long long)g.Tq * (unsigned long long)g.Tt;
+                st_tiles++;
+                st_half += (2 * o.walkcost <= g.KB);
             }
-
-            /* ---- traceback: ops of the walk, packed 16 per word, into the warp's slab ---- */
-            int ci = done ? 0 : ei, cj = done ? 0 : ej, m = 0, ai = ei, aj = ej;
-            bool anchored = false;
-            uint32_t acc = 0;
-            while (__any_sync(0xFFFFFFFFu, (ci | cj) != 0)) {
-                if ((ci | cj) != 0) {
-                    uint32_t op;
-                    if (ci == 0) op = 2;
-                    else if (cj == 0) op = 1;
-                    else {
-                        const int w = (ci - 1) >> 5, b = (ci - 1) & 31;
-                        const uint2 v = planes[((size_t)(cj - 1) * W + w) * 32];
-                        op = ((v.x >> b) & 1u) | (((v.y >> b) & 1u) << 1);
-                    }
-                    const int si = ci - (op != 2u), sj = cj - (op != 1u);
-                    /* the walk is a chain of dependent loads of planes written long ago: pull the line it will need
-                     * BP_PREFETCH columns further down the diagonal into L2 (lanes of a warp share that line) */
-                    if (sj > BP_PREFETCH && si > BP_PREFETCH) {
-                        const uint2 *pf = planes + ((size_t)(sj - 1 - BP_PREFETCH) * W + ((si - 1 - BP_PREFETCH) >> 5)) * 32;
-                        asm volatile("prefetch.global.L2 [%0];" ::"l"(pf));
-                    }
-                    if (last || (si < inner && sj < inner)) {
-                        if (!anchored) { ai = ci; aj = cj; anchored = true; }
-                        acc |= op << (2 * (m & 15));
-                        m++;
-                        if ((m & 15) == 0) { tb[(size_t)((m >> 4) - 1) * 32] = acc; acc = 0; }
-                        score += (op != 0u);
-                    }
-                    ci = si;
-                    cj = sj;
-                }
-            }
-            if (m & 15) tb[(size_t)(m >> 4) * 32] = acc;
-            __syncwarp();
+            st_wtiles += (lane == 0);
+            score += o.tscore;
             /* ---- emit the committed ops in forward order ---- */
             int mym = 0;
             if (!done) {
-                if (m == 0 && !last) { score = -1; done = true; }
-                else mym = m;
+                if (o.m == 0 && !g.last) { score = -1; done = true; }
+                else mym = o.m;
             }
-            int maxm = mym;
-#pragma unroll
-            for (int d = 16; d >= 1; d >>= 1) maxm = max(maxm, __shfl_xor_sync(0xFFFFFFFFu, maxm, d));
             if (a.ops) {
-                uint32_t word = 0;
-                int have = -1;
-                for (int x = 0; x < maxm; x++) {
-                    if (x < mym) {
-                        const int p = mym - 1 - x;
-                        if ((p >> 4) != have) { have = p >> 4; word = tb[(size_t)have * 32]; }
-                        const uint32_t vp = (uint32_t)(n + x) + omis;             /* byte slot counted from the aligned base */
-                        oacc |= ((word >> (2 * (p & 15))) & 3u) << (8 * (vp & 3u));
-                        if ((vp & 3u) == 3u) {
-                            const long pos = (long)(vp & ~3u) - (long)omis;     /* offset of the word inside the row */
-                            if (pos >= 0 && (size_t)pos + 4 <= a.ops_stride) *reinterpret_cast<uint32_t *>(ops + pos) = oacc;
-                            else put_bytes(ops, pos, oacc, 0, 4, a.ops_stride);
-                            oacc = 0;
+                /* one op: walk index p = mym-1-x of the slab -> byte slot n+x of the row */
+                auto put_one = [&](int x) {
+                    const int p = mym - 1 - x;
+                    const uint32_t wd = tb[(size_t)(p >> 4) * 32];
+                    const uint32_t vp = (uint32_t)(n + x) + omis;              /* byte slot counted from the aligned base */
+                    oacc |= ((wd >> (2 * (p & 15))) & 3u) << (8 * (vp & 3u));
+                    if ((vp & 3u) == 3u) {
+                        const long pos = (long)(vp & ~3u) - (long)omis;       /* offset of the word inside the row */
+                        if (pos >= 0 && (size_t)pos + 4 <= a.ops_stride) *reinterpret_cast<uint32_t *>(ops + pos) = oacc;
+                        else put_bytes(ops, pos, oacc, 0, 4, a.ops_stride);
+                        oacc = 0;
+                    }
+                };
+                int x = 0;
+                while (x < mym && ((((uint32_t)(n + x) + omis) & 3u) != 0u)) { put_one(x); x++; }     /* up to 3 ops */
+                /* whole words: 4 ops = 8 bits of the slab (walk order) -> 4 bytes (forward order) by one lookup */
+                const int nb4 = (mym - x) >> 2;
+                const int maxnb = __reduce_max_sync(0xFFFFFFFFu, nb4);
+                const int wtop = mym > 0 ? (mym - 1) >> 4 : 0;
+                uint32_t lo = 0, hi = 0;
+                int have = -2;
+                for (int it = 0; it < maxnb; it++) {
+                    if (it < nb4) {
+                        const int x0 = x + 4 * it;
+                        const int q = mym - 4 - x0;                             /* lowest walk index of the four */
+                        const int wq = q >> 4;
+                        if (wq != have) {
+                            hi = (have == wq + 1) ? lo : (wq + 1 <= wtop ? tb[(size_t)(wq + 1) * 32] : 0u);
+                            lo = tb[(size_t)wq * 32];
+                            have = wq;
                         }
+                        const uint32_t e = __funnelshift_r(lo, hi, 2u * ((uint32_t)q & 15u)) & 0xFFu;
+                        const uint32_t word = s_lut[e];
+                        const long pos = (long)((uint32_t)(n + x0) + omis) - (long)omis;
+                        if ((size_t)pos + 4 <= a.ops_stride) *reinterpret_cast<uint32_t *>(ops + pos) = word;
+                        else put_bytes(ops, pos, word, 0, 4, a.ops_stride);
                     }
                 }
+                x += 4 * nb4;
+                while (x < mym) { put_one(x); x++; }                            /* up to 3 ops, left in oacc */
             }
             if (!done) {
-                n += m;
-                i0 += ai;
-                j0 += aj;
-                if (last) done = true;
+                n += o.m;
+                g.i0 += o.ai;
+                g.j0 += o.aj;
+                if (g.last) done = true;
             }
             __syncwarp();
         }
@@ -251,29 +414,55 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
         }
         if (!skipped && read < a.n) {
             if (a.res) {                                        /* PART 3, alnmain.c:458-477 */
-                as_result *o = a.res + read;
-                o->ed = score;
-                o->n_cigar_op = n;
-                if (score == -1) { o->valid = 0; o->flag = 4; o->mapq = 0; }
+                as_result *r = a.res + read;
+                r->ed = score;
+                r->n_cigar_op = n;
+                if (score == -1) { r->valid = 0; r->flag = 4; r->mapq = 0; }
             }
             if (a.n_ops) a.n_ops[read] = n;
             if (a.score) a.score[read] = score;
         }
     }
 #pragma unroll
-    for (int d = 16; d >= 1; d >>= 1) st_cells += __shfl_xor_sync(0xFFFFFFFFu, st_cells, d);
-    if (lane == 0 && st_cells) atomicAdd(a.stats + 5, st_cells);
+    for (int d = 16; d >= 1; d >>= 1) {
+        st_cells += __shfl_xor_sync(0xFFFFFFFFu, st_cells, d);
+        st_eval += __shfl_xor_sync(0xFFFFFFFFu, st_eval, d);
+        st_tiles += __shfl_xor_sync(0xFFFFFFFFu, st_tiles, d);
+        st_half += __shfl_xor_sync(0xFFFFFFFFu, st_half, d);
+    }
+    if (lane == 0) {
+        if (st_cells) atomicAdd(a.stats + 5, st_cells);
+        if (st_eval) atomicAdd(a.stats + 10, st_eval);
+        if (st_retry) atomicAdd(a.stats + 11, (unsigned long long)st_retry);
+        atomicAdd(a.fail_count + 0, st_retry);                  /* policy counters of this launch */
+        atomicAdd(a.fail_count + 1, st_wtiles);
+        atomicAdd(a.fail_count + 2, st_half);
+        atomicAdd(a.fail_count + 3, st_tiles);
+    }
 }
 
-template <int W>
-static int launch_bp(as_gpu *h, const GactArgs &a, size_t n, int blocks_per_sm) {
-    const size_t planes_per_warp = (size_t)a.TS * W * 32;                 /* uint2 */
-    const size_t tb_per_warp = (size_t)((a.TS + a.TQ + 15) / 16 + 1) * 32;  /* u32 */
+/* Adaptive band.  cnt: warp-tiles filled twice, warp-tiles, lane-tiles half the band would serve, lane-tiles.
+ * Widen when more than a quarter of the warp-tiles were filled twice; narrow when at most one lane-tile in 256 would
+ * fail at half the band (about one warp-tile in eight refilled).  The verdict goes to pinned host memory, which the
+ * launcher reads when it picks the next launch's instantiation; results never depend on it. */
+__global__ void k_gact_policy(volatile unsigned int *host_band, const unsigned int *cnt, unsigned int cur) {
+    const unsigned long long retry = cnt[0], wtiles = cnt[1], half = cnt[2], tiles = cnt[3];
+    if (wtiles == 0) return;
+    unsigned int kb = cur;
+    if (4ull * retry > wtiles) kb = cur >= 128 ? 256 : cur * 2;
+    else if (cur > 16 && 256ull * (tiles - half) <= tiles) kb = cur / 2;
+    *host_band = kb;
+}
+
+template <int W, int NB>
+static int launch_bp(as_gpu *h, GactArgs &a, size_t n, int blocks_per_sm, unsigned int cur_band) {
+    const size_t planes_per_warp = (size_t)a.TS * W * 32;                 /* uint2; the band's slab is the smaller one */
+    const size_t tb_per_warp = (size_t)((a.TS + a.TQ + 15) / 16 + 2) * 32;  /* u32 */
     size_t warps_needed = (n + 31) / 32;
     size_t blocks = (warps_needed + BP_THREADS / 32 - 1) / (BP_THREADS / 32);
-    if (blocks_per_sm <= 0) {        /* as many resident blocks as the register file allows: the traceback is latency bound */
+    if (blocks_per_sm <= 0) {        /* reads are claimed from a work counter: the grid is the resident blocks */
         int occ = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_gact_bp<W>, BP_THREADS, 0) != cudaSuccess || occ < 1) occ = 4;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_gact_bp<W, NB>, BP_THREADS, 0) != cudaSuccess || occ < 1) occ = 4;
         blocks_per_sm = occ;
     }
     size_t cap = (size_t)h->sm_count * blocks_per_sm;
@@ -281,11 +470,29 @@ static int launch_bp(as_gpu *h, const GactArgs &a, size_t n, int blocks_per_sm) 
     const size_t warps = blocks * (BP_THREADS / 32);
     AS_TRY(as_scratch(h, &h->gact_planes, warps * planes_per_warp * sizeof(uint2)));
     AS_TRY(as_scratch(h, &h->gact_tb, warps * tb_per_warp * sizeof(uint32_t)));
-    k_gact_bp<W><<<(unsigned)blocks, BP_THREADS, 0, h->stream>>>(a, (uint2 *)h->gact_planes.p, planes_per_warp,
-                                                                  (uint32_t *)h->gact_tb.p, tb_per_warp);
+    /* counters (zeroed by as_launch_gact): [0] work counter, [1..4] policy counters of this launch */
+    unsigned int *cnt = a.work_counter;
+    a.fail_count = cnt + 1;
+    k_gact_bp<W, NB><<<(unsigned)blocks, BP_THREADS, 0, h->stream>>>(a, (uint2 *)h->gact_planes.p, planes_per_warp,
+                                                                      (uint32_t *)h->gact_tb.p, tb_per_warp);
     h->launches++;
     AS_CUDA(cudaGetLastError());
+    if (a.band == 0) {
+        k_gact_policy<<<1, 1, 0, h->stream>>>(h->d_band, cnt + 1, cur_band);
+        h->launches++;
+        AS_CUDA(cudaGetLastError());
+    }
     return AS_OK;
+}
+
+template <int W>
+static int launch_bp_w(as_gpu *h, GactArgs &a, size_t n, int bps, unsigned int kb) {
+    /* band half-width -> words of the sliding band, KB = 16 (NB - 1); a band as tall as the tile is no band */
+    if (kb <= 16 && 2 < W) return launch_bp<W, 2>(h, a, n, bps, 16);
+    if (kb <= 32 && 3 < W) return launch_bp<W, 3>(h, a, n, bps, 32);
+    if (kb <= 64 && 5 < W) return launch_bp<W, 5>(h, a, n, bps, 64);
+    if (kb <= 128 && 9 < W) return launch_bp<W, 9>(h, a, n, bps, 128);
+    return launch_bp<W, W>(h, a, n, bps, 256);
 }
 
 int as_launch_gact_bp(as_gpu *h, GactArgs &a, size_t n, uint32_t max_qlen, uint32_t max_tlen) {
@@ -298,11 +505,14 @@ int as_launch_gact_bp(as_gpu *h, GactArgs &a, size_t n, uint32_t max_qlen, uint3
         int v = atoi(e);
         if (v >= 1 && v <= 16) bps = v;
     }
-    if (words <= 2) return launch_bp<2>(h, a, n, bps);
-    if (words <= 4) return launch_bp<4>(h, a, n, bps);
-    if (words <= 5) return launch_bp<5>(h, a, n, bps);
-    if (words <= 8) return launch_bp<8>(h, a, n, bps);
-    if (words <= 10) return launch_bp<10>(h, a, n, bps);
-    if (words <= 12) return launch_bp<12>(h, a, n, bps);
-    return launch_bp<16>(h, a, n, bps);
+    if (!h->h_band) {          /* adaptive band: written by k_gact_policy, read here (mapped pinned memory) */
+        AS_CUDA(cudaHostAlloc((void **)&h->h_band, sizeof(unsigned int), cudaHostAllocMapped));
+        *h->h_band = AS_GACT_BAND0;
+        AS_CUDA(cudaHostGetDevicePointer((void **)&h->d_band, (void *)h->h_band, 0));
+    }
+    unsigned int kb = a.band < 0 ? 0xFFFFu : a.band > 0 ? (unsigned int)a.band : *(volatile unsigned int *)h->h_band;
+    if (kb == 0) kb = AS_GACT_BAND0;
+    if (words <= 5) return launch_bp_w<5>(h, a, n, bps, kb);
+    if (words <= 10) return launch_bp_w<10>(h, a, n, bps, kb);
+    return launch_bp_w<16>(h, a, n, bps, kb);
 }

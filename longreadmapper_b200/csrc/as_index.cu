@@ -175,6 +175,7 @@ extern "C" void as_gpu_close(as_gpu *h) {
     if (h->ev_d2h0) cudaEventDestroy(h->ev_d2h0);
     if (h->d_chunk_max) cudaFree(h->d_chunk_max);
     if (h->h_chunk_max) cudaFreeHost(h->h_chunk_max);
+    if (h->h_band) cudaFreeHost(h->h_band);
     if (h->s_h2d) cudaStreamDestroy(h->s_h2d);
     if (h->s_d2h) cudaStreamDestroy(h->s_d2h);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);

@@ -299,6 +299,48 @@ def test_gact_pairs(orc, gpu_uniform, T, O, lmax, gact):
             assert int(np.isin(ops[i], (0, 1, 3)).sum()) == len(q) and int(np.isin(ops[i], (0, 2, 3)).sum()) == len(t)
 
 
+def tie_rich_pairs(seed, n, lmax):
+    """low-complexity pairs (homopolymer runs, short tandem repeats, shifted copies): many equal-cost paths, so the
+    diag > up > left priority and the banded pass's exactness argument are both exercised"""
+    rng = np.random.default_rng(seed)
+    qs, ts = [], []
+    for _ in range(n):
+        L = int(rng.integers(8, lmax + 1))
+        unit = bytes(np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, int(rng.integers(1, 5)))])
+        t = (unit * (L // len(unit) + 1))[:L]
+        kind = rng.integers(0, 3)
+        if kind == 0:
+            q = mutate(rng, t, 0.05)
+        elif kind == 1:                       # the window starts a few bases off, as a voted locus does (alnmain.c:427)
+            sh = int(rng.integers(1, 14))
+            q = mutate(rng, t[sh:] + t[:sh][::-1], 0.03)
+        else:
+            q = t[: L // 2] + mutate(rng, t[L // 2:], 0.3)
+        qs.append(q)
+        ts.append(t)
+    return qs, ts
+
+
+@pytest.mark.parametrize("band", [0, 3, 16, 48, 128, -1])
+@pytest.mark.parametrize("T,O,lmax", [(320, 120, 300), (320, 120, 2500), (64, 20, 700), (32, 8, 300), (512, 200, 3000)])
+def test_gact_banded_pass_is_exact(orc, gpu_uniform, T, O, lmax, band):
+    """bit-parallel kernel: banded first pass + full-matrix second pass give the oracle's ops for every half-width"""
+    qs, ts = random_pairs(7 * T + lmax, 90, 1, lmax, 0.25)
+    q2, t2 = tie_rich_pairs(T + lmax, 60, min(lmax, 900))
+    qs, ts = qs + q2 + [b"", b"ACG", b"A" * 40], ts + t2 + [b"ACGTA", b"", b"A" * 90]
+    gpu_uniform.stats_reset()
+    score, ops = gpu_uniform.cigar_align_batch(qs, ts, gpu_uniform.params(T=T, O=O, flags=GACT_IMPL["bitpar"], band=band))
+    st = gpu_uniform.stats()
+    for i, (q, t) in enumerate(zip(qs, ts)):
+        es, eops, _ = orc.gact(np.frombuffer(q, np.uint8), np.frombuffer(t, np.uint8), T, O)
+        assert es == score[i], (i, len(q), len(t))
+        assert np.array_equal(eops, ops[i]), i
+    if band == 3:
+        assert st["gact_redone"] > 0          # the narrow band cannot prove most of these: the second pass ran
+    if band == -1:
+        assert st["gact_redone"] == 0
+
+
 @pytest.mark.parametrize("gact", ["warp", "bitpar"])
 def test_gact_single_tile_is_exact_nw(orc, gpu_uniform, gact):
     qs, ts = random_pairs(3, 200, 20, 320, 0.25)
