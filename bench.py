@@ -460,8 +460,8 @@ def run_b200(args):
             "gcups": stages["gact"]["gcups"],
             "quality": {"mapped_frac": float(ok.mean()), "exact_pos_strand_frac": exact, "within_50bp_strand_frac": near,
                         "valid_total": [st["valid"], st["total"]]},
-            "stats_per_step_per_gpu": {k: per_step[k] for k in ("seeds", "bs_steps", "sa_hits", "dp_cells", "dp_cells_eval", "gact_redone",
-                                                                   "overflow_reads")}}
+            "stats_per_step_per_gpu": {k: per_step[k] for k in ("seeds", "bs_steps", "fm_steps_exec", "text_verified", "sa_hits", "dp_cells",
+                                                                   "dp_cells_eval", "gact_redone", "overflow_reads")}}
 
     if rank == 0 and world == 1 and not args.no_cpu:
         cores = host_cores()

@@ -155,6 +155,9 @@ typedef struct as_stats {
     uint64_t dp_cells_eval;   /* DP cells the GACT kernels actually filled (banded pass + redone reads); dp_cells is
                                * the tile area Tq x Tt of the spec */
     uint64_t gact_redone;     /* warp-tiles (one tile of 32 reads) filled a second time with the whole matrix */
+    uint64_t fm_steps_exec;   /* backward-search steps the GPU really walked through the FM index; bs_steps counts the
+                               * steps of the reference's loop (fmidx.c:300-310), the rest were decided by the text */
+    uint64_t text_verified;   /* seeds whose one-row interval was finished by one SA + one text gather */
 } as_stats;
 int as_gpu_stats(as_gpu *h, as_stats *out);          /* accumulated since open / last reset */
 int as_gpu_stats_reset(as_gpu *h);

@@ -50,7 +50,7 @@ class Params(C.Structure):
 
 class AsStats(C.Structure):
     _fields_ = [(k, C.c_uint64) for k in ("total", "valid", "n_flag4", "n_flag16", "sum_ed", "dp_cells", "seeds",
-                                           "sa_hits", "bs_steps", "overflow_reads", "dp_cells_eval", "gact_redone")]
+                                           "sa_hits", "bs_steps", "overflow_reads", "dp_cells_eval", "gact_redone", "fm_steps_exec", "text_verified")]
 
 
 class AsHostIndex(C.Structure):

@@ -153,6 +153,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
     const int left0 = sl - ix.hlen;
     const uint64_t hmask = (1ULL << (2 * ix.hlen)) - 1ULL;
     unsigned long long st_seeds = 0, st_steps = 0, st_hits = 0, st_ovf = 0;
+    unsigned int st_fm = 0, st_txt = 0;          /* FM steps done here / tails decided by the text */
 
     /* state of the read this group owns */
     bool have = false, drained = false;
@@ -201,6 +202,8 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
             const uint32_t m = c0 + g;
             const uint32_t j = (uint32_t)iter + m * (uint32_t)P;
             uint64_t kk = 1, ll = ix.N - 1, rr = 0;                             /* alnmain.c:354 */
+            bool have_pos = false;                                               /* hit_pos = SA of the seed's one row */
+            uint64_t hit_pos = 0;
             if (m < m_count) {
                 const uint64_t seed = as_bases32(pr, j);
                 bool absent = false;
@@ -212,27 +215,73 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                 }
                 st_seeds++;
                 if (!absent) {
+                    /* Backward search (fmidx.c:300-310) until the interval is empty, the seed is used up, or ONE row is
+                     * left.  A one-row interval [r,r] can only shrink to empty or map to one row, and which of the two
+                     * is decided by the text: the remaining bases [0,tt] of the seed must equal the tt+1 bases in front
+                     * of SA[r], and then the final row's SA value is SA[r]-(tt+1).  So the tail of the walk is one SA
+                     * gather and one text gather instead of 2(tt+1) dependent sector gathers, and the vote needs no
+                     * further SA access.  st_steps still counts the steps the reference's loop executes (up to and
+                     * including the failing one); st_fm counts the FM steps actually done here. */
+                    int tt = left0 - 1;
+                    bool fail = false;
                     if (SMALL) {
                         uint32_t k32 = (uint32_t)kk, l32 = (uint32_t)ll;
-                        /* the constants of step tt-1 are fetched while step tt's sectors are in flight */
-                        uint4 ct = *reinterpret_cast<const uint4 *>(s_tab + ((uint32_t)(seed >> (2 * (left0 - 1))) & 3u));
-                        for (int tt = left0 - 1; tt >= 0; tt--) {                /* fmidx.c:300-310 */
-                            const uint4 cur = ct;
-                            ct = *reinterpret_cast<const uint4 *>(s_tab + ((uint32_t)(seed >> (2 * (tt > 0 ? tt - 1 : 0))) & 3u));
-                            as_bs_step32t(ix, cur, k32, l32);
+                        while (tt >= 0 && k32 != l32) {
+                            const uint32_t c = (uint32_t)(seed >> (2 * tt)) & 3u;
+                            as_bs_step32t(ix, *reinterpret_cast<const uint4 *>(s_tab + c), k32, l32);
                             st_steps++;
-                            if (k32 > l32) break;
+                            st_fm++;
+                            tt--;
+                            if (k32 > l32) { fail = true; break; }
                         }
                         kk = k32;
                         ll = l32;
                     } else {
-                        for (int tt = left0 - 1; tt >= 0; tt--) {                /* fmidx.c:300-310 */
+                        while (tt >= 0 && kk != ll) {
                             const uint32_t c = (uint32_t)(seed >> (2 * tt)) & 3u;
                             as_bs_step64t(ix, *reinterpret_cast<const uint4 *>(s_tab + c), s_tabChi[c], c, kk, ll);
                             st_steps++;
-                            if (kk > ll) break;
+                            st_fm++;
+                            tt--;
+                            if (kk > ll) { fail = true; break; }
                         }
                     }
+                    if (!fail && tt >= 0) {                                     /* one row left, tt+1 bases to go */
+                        const uint64_t p = as_sa(ix, kk);
+                        const int nrem = tt + 1;
+                        if (p >= (uint64_t)nrem) {
+                            int steps;
+                            bool match;
+                            if (nrem <= 16) {
+                                const uint32_t x = ((uint32_t)seed ^ as_bases16(ix.text2, p - (uint64_t)nrem)) &
+                                                   (nrem == 16 ? 0xFFFFFFFFu : ((1u << (2 * nrem)) - 1u));
+                                match = x == 0;
+                                steps = match ? nrem : nrem - ((31 - __clz(x)) >> 1);
+                            } else {
+                                const uint64_t x = (seed ^ as_bases32(ix.text2, p - (uint64_t)nrem)) & ((1ULL << (2 * nrem)) - 1ULL);
+                                match = x == 0;
+                                steps = match ? nrem : nrem - ((63 - __clzll((long long)x)) >> 1);
+                            }
+                            st_steps += steps;
+                            st_txt++;
+                            if (match) {
+                                have_pos = true;
+                                hit_pos = p - (uint64_t)nrem;
+                            } else {
+                                fail = true;
+                            }
+                        } else {                                                /* the text starts inside the seed: walk it */
+                            while (tt >= 0) {
+                                const uint32_t c = (uint32_t)(seed >> (2 * tt)) & 3u;
+                                as_bs_step64t(ix, *reinterpret_cast<const uint4 *>(s_tab + c), s_tabChi[c], c, kk, ll);
+                                st_steps++;
+                                st_fm++;
+                                tt--;
+                                if (kk > ll) { fail = true; break; }
+                            }
+                        }
+                    }
+                    if (fail) { kk = 1; ll = 0; }
                     rr = kk > ll ? 0 : ll - kk + 1;
                 }
             }
@@ -247,7 +296,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                 const bool valid = rr_eff != 0;
                 uint64_t key = 0;
                 if (valid) {
-                    key = as_sa(ix, kk) - (uint64_t)j;                          /* alnmain.c:363-365, u64 wrap kept */
+                    key = (have_pos ? hit_pos : as_sa(ix, kk)) - (uint64_t)j;   /* alnmain.c:363-365, u64 wrap kept */
                     st_hits++;
                 }
                 const uint64_t tag = valid ? ((key >> 4) | ((uint64_t)(lane / G) << 60)) : (0xF000000000000000ULL | lane);
@@ -279,7 +328,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
             } else if (!__any_sync(FULL, rr_eff > 1)) {
                 /* every surviving seed of the warp has exactly one SA row */
                 if (rr_eff) {
-                    uint64_t key = as_sa(ix, kk) - (uint64_t)j;                 /* alnmain.c:363-365, u64 wrap kept */
+                    uint64_t key = (have_pos ? hit_pos : as_sa(ix, kk)) - (uint64_t)j;   /* alnmain.c:363-365, u64 wrap kept */
                     st_hits++;
                     if (!table_insert<USED_T>(t, key >> 4, (uint32_t)key & 15u, m * a.thres)) ok = false;
                 }
@@ -306,12 +355,15 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                     const uint32_t ob = __shfl_sync(gmask, base, lo, G);
                     const uint32_t okl = __shfl_sync(gmask, (uint32_t)kk, lo, G);
                     const uint32_t okh = __shfl_sync(gmask, (uint32_t)(kk >> 32), lo, G);
+                    const uint32_t opl = __shfl_sync(gmask, (uint32_t)hit_pos, lo, G);
+                    const uint32_t oph = __shfl_sync(gmask, (uint32_t)(hit_pos >> 32), lo, G);
+                    const bool opk = __shfl_sync(gmask, (int)have_pos, lo, G) != 0;
                     if (v < V) {
                         const uint32_t om = c0 + lo;
                         const uint32_t oj = (uint32_t)iter + om * (uint32_t)P;
                         const uint32_t off = v - ob;
                         uint64_t row = (((uint64_t)okh << 32) | okl) + off;
-                        uint64_t key = as_sa(ix, row) - (uint64_t)oj;
+                        uint64_t key = (opk ? (((uint64_t)oph << 32) | opl) : as_sa(ix, row)) - (uint64_t)oj;
                         st_hits++;
                         if (!table_insert<USED_T>(t, key >> 4, (uint32_t)key & 15u, om * a.thres + off)) ok = false;
                     }
@@ -471,12 +523,16 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
         st_steps += __shfl_xor_sync(0xFFFFFFFFu, st_steps, d);
         st_hits += __shfl_xor_sync(0xFFFFFFFFu, st_hits, d);
         st_ovf += __shfl_xor_sync(0xFFFFFFFFu, st_ovf, d);
+        st_fm += __shfl_xor_sync(0xFFFFFFFFu, st_fm, d);
+        st_txt += __shfl_xor_sync(0xFFFFFFFFu, st_txt, d);
     }
     if (lane == 0) {
         if (st_seeds) atomicAdd(a.stats + 6, st_seeds);
         if (st_hits) atomicAdd(a.stats + 7, st_hits);
         if (st_steps) atomicAdd(a.stats + 8, st_steps);
         if (st_ovf) atomicAdd(a.stats + 9, st_ovf);
+        if (st_fm) atomicAdd(a.stats + 12, (unsigned long long)st_fm);
+        if (st_txt) atomicAdd(a.stats + 13, (unsigned long long)st_txt);
     }
 }
 
