@@ -64,7 +64,7 @@ void as_gpu_close(as_gpu *h);
 /* Build the index ON the GPU from the .cat text (asindex.c:97-110: forward + reverse complement per sequence,
  * one final '$') -- replaces fmi_build (fmidx.c:166-199: pSAscan suffix sort psascan/sa_use.cc:8-18, BWT
  * :76-98, C table :101-125, O table :128-150) and lc_build (lchash.c:52-73) of the reference's `accidx`.
- * Requires con_len < 2^32-1.  The handle is ready for as_map_batch; as_gpu_export returns the same index in
+ * Texts of 2^32-1 rows and more (3.1 Gbp genomes) are sorted in partitions with 40-bit rows.  The handle is ready for as_map_batch; as_gpu_export returns the same index in
  * the reference's layouts, byte-identical to the files accidx writes. */
 int  as_gpu_build(as_gpu **h, int device, const char *content, uint64_t con_len, const as_mta *mta, int mta_len,
                   int hlen);

@@ -11,8 +11,8 @@
  *                                                                   hlen-mer that starts every suffix
  * The suffix array of a text is unique, so every exported file is byte-identical to what accidx writes
  * (tests/test_index_build.py diffs them against the oracle and the compiled reference).
- * Limit: N < 2^32 - 1 rows (rank pairs are sorted as one 64-bit key); configs 1-3 of BASELINE.json.  Larger
- * texts must be indexed by the reference tool chain and loaded through as_gpu_open.
+ * This file's sort takes N < 2^32 - 1 rows (rank pairs are sorted as one 64-bit key): configs 1-3 of BASELINE.json.
+ * Larger texts (configs 4-5) go through the partitioned builder in as_build_big.cu.
  */
 #include "as_common.cuh"
 
@@ -349,12 +349,6 @@ extern "C" int as_gpu_build(as_gpu **out, int device, const char *content, uint6
         as_set_error("as_gpu_build: the text must be a .cat image ending in '$' (asindex.c:108-110)");
         return AS_EINVAL;
     }
-    if (con_len >= 0xFFFFFFFFull - 1) {
-        as_set_error("as_gpu_build: %llu rows; the GPU builder sorts rank pairs as 64-bit keys and takes N < 2^32-1. "
-                     "Index larger genomes with the reference tools and load them with as_gpu_open",
-                     (unsigned long long)con_len);
-        return AS_ERANGE;
-    }
     if (hlen < 1 || hlen > 14) {
         as_set_error("as_gpu_build: hlen %d out of range [1,14]", hlen);
         return AS_EINVAL;
@@ -362,7 +356,12 @@ extern "C" int as_gpu_build(as_gpu **out, int device, const char *content, uint6
     as_gpu *h = as_handle_new(device);
     if (!h) return AS_ENODEV;
     cudaGetLastError();
-    int rc = build_on_device(h, content, con_len, mta, mta_len, hlen);
+    /* texts the single prefix-doubling sort cannot hold go through the partitioned builder (as_build_big.cu);
+     * AS_BUILD_PART_MAX=<suffixes per partition> forces that path on small texts (tests) */
+    uint64_t part_max = 0;
+    if (const char *e = getenv("AS_BUILD_PART_MAX")) part_max = strtoull(e, nullptr, 10);
+    int rc = (con_len >= 0xFFFFFFFFull - 1 || part_max > 0) ? as_build_big(h, content, con_len, mta, mta_len, hlen, part_max)
+                                                            : build_on_device(h, content, con_len, mta, mta_len, hlen);
     if (rc != AS_OK) {
         as_gpu_close(h);
         return rc;

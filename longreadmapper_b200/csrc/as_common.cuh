@@ -97,6 +97,8 @@ void as_set_error(const char *fmt, ...);
     } while (0)
 
 as_gpu *as_handle_new(int device);                        /* as_index.cu: device checks + stream/events/stats */
+int as_build_big(as_gpu *h, const char *content, uint64_t N, const as_mta *mta, int mta_len, int hlen,
+                 uint64_t part_max);                      /* as_build_big.cu: partitioned suffix sort, 40-bit rows */
 int as_launch_pack_text(as_gpu *h, const uint8_t *d_in, uint64_t n, uint32_t *d_out);   /* ASCII text -> 2-bit words */
 int as_scratch(as_gpu *h, ScratchBuf *b, size_t bytes);   /* ensure capacity (device memory) */
 int as_pinned(as_gpu *h, size_t bytes);                   /* ensure h->h_pin capacity */

@@ -84,3 +84,32 @@ def test_known_suffix_array(native):
 def test_build_rejects_bad_text(native):
     with pytest.raises(native.AccSeqError):
         native.GpuMapper.build([b"ACGTNNACGT" * 5], 0)     # cat_image maps N -> N: not ACGT
+
+
+# ---------------------------------------------------------------------------------------------------
+# partitioned builder (as_build_big.cu): the path 3.1 Gbp genomes take, forced onto small texts
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("part_max", [1, 5000, 200000])
+def test_partitioned_build_matches_oracle(native, idx_repeat, monkeypatch, part_max):
+    """AS_BUILD_PART_MAX caps the suffixes sorted at once: 1 = one partition per 4-character bin; the planted repeats
+    need many 21-character refinement rounds inside their partitions"""
+    ix, gs = idx_repeat
+    monkeypatch.setenv("AS_BUILD_PART_MAX", str(part_max))
+    built = native.GpuMapper.build(gs, 0)
+    monkeypatch.delenv("AS_BUILD_PART_MAX")
+    assert built.N == ix.n
+    check_export(ix, built)
+    built.close()
+
+
+@pytest.mark.parametrize("text", [b"A", b"ACGT", b"A" * 300, b"ACGTACGT" * 40, b"GATTACA" * 19])
+def test_partitioned_build_degenerate_texts(native, orc, monkeypatch, text):
+    ix = orc.OracleIndex.build(["t"], [text], hlen=4)
+    monkeypatch.setenv("AS_BUILD_PART_MAX", "7")
+    built = native.GpuMapper.build([text], 0, hlen=4)
+    monkeypatch.delenv("AS_BUILD_PART_MAX")
+    ex = built.export(hlen=4)
+    assert np.array_equal(ex["sa"], ix.sa) and np.array_equal(ex["bwt"], ix.bwt) and np.array_equal(ex["lc"], ix.lc)
+    assert np.array_equal(ex["C"], ix.Ctab)
+    built.close()
+    ix.close()
