@@ -35,6 +35,9 @@ WORKLOADS = {
     "c1": dict(genome=1_000_000, reads=10_000, len=(150, 150), err=(0.01, 0.01), sub=0.9),
     "c2": dict(genome=4_600_000, reads=1_000_000, len=(150, 150), err=(0.02, 0.02), sub=0.8),
     "c3": dict(genome=100_000_000, reads=100_000, len=(10_000, 10_000), err=(0.10, 0.10), sub=1 / 3),
+    # human scale: a 6.2 G-row .cat, 40-bit SA rows, 64-bit backward search; the index (~45 GB) is replicated per GPU
+    "c4": dict(genome=3_100_000_000, reads=10_000_000, len=(150, 150), err=(0.02, 0.02), sub=0.8),
+    "c5": dict(genome=3_100_000_000, reads=125_000, len=(1_000, 50_000), err=(0.05, 0.15), sub=1 / 3),
 }
 GENOME_SEED = 20240
 READS_SEED = 777

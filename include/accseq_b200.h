@@ -104,6 +104,7 @@ typedef struct as_params {
 #define AS_F_GACT_WARP    4u   /* force the one-read-per-warp anti-diagonal GACT kernel (default for n < 2048) */
 #define AS_F_GACT_BITPAR  8u   /* force the bit-parallel one-read-per-lane GACT kernel (default for n >= 2048) */
 #define AS_F_WIDE_INDEX  16u   /* force the 64-bit backward-search path (default only for indexes of > 2^30 rows) */
+#define AS_F_NO_LC2      32u   /* PART 1 starts every seed from the reference's 12-mer table, not the deep table */
 void as_params_default(as_params *p);
 
 /* ---- per-read output: the fields of `result` (accaln.h:95-103) that the path computes ---- */

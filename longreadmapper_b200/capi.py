@@ -15,6 +15,7 @@ AS_F_NO_ALIGN = 2
 AS_F_GACT_WARP = 4
 AS_F_GACT_BITPAR = 8
 AS_F_WIDE_INDEX = 16
+AS_F_NO_LC2 = 32
 
 # as_result (include/accseq_b200.h)
 RESULT_DTYPE = np.dtype([("loc", "<u8"), ("off", "<u8"), ("seq_id", "<i4"), ("strand", "<i4"), ("flag", "<i4"),
@@ -187,7 +188,8 @@ def cat_image(seqs):
     parts, mta, off = [], [], 0
     for s in seqs:
         s = np.frombuffer(bytes(s), np.uint8) if not isinstance(s, np.ndarray) else s
-        s = np.where(s > 0x60, s - 0x20, s).astype(np.uint8)
+        if s.size and int(s.max()) > 0x60:            # lower case -> upper case (asindex.c:63-67)
+            s = np.where(s > 0x60, s - 0x20, s).astype(np.uint8)
         parts += [s, comp[s][::-1]]
         mta.append((off, int(s.size)))
         off += 2 * int(s.size)

@@ -362,6 +362,7 @@ extern "C" int as_gpu_build(as_gpu **out, int device, const char *content, uint6
     if (const char *e = getenv("AS_BUILD_PART_MAX")) part_max = strtoull(e, nullptr, 10);
     int rc = (con_len >= 0xFFFFFFFFull - 1 || part_max > 0) ? as_build_big(h, content, con_len, mta, mta_len, hlen, part_max)
                                                             : build_on_device(h, content, con_len, mta, mta_len, hlen);
+    if (rc == AS_OK) rc = as_build_lc2(h);
     if (rc != AS_OK) {
         as_gpu_close(h);
         return rc;

@@ -35,6 +35,8 @@ struct DevIndex {
     const uint64_t *super;      /* [n_super][4] */
     const ulonglong2 *lc;       /* (k,l) per 12-mer, indexed by the LSB-first code of the k-mer */
     int hlen;
+    const unsigned long long *lc2;   /* deep table (as_lc2.cu): row | rows << 40 per hlen2-mer, LSB-first code; may be NULL */
+    int hlen2;
     const uint32_t *sa_lo;      /* low 32 bits of SA[row] */
     const uint8_t *sa_hi;       /* bits 32..39, NULL when N <= 2^32 */
     const uint32_t *text2;      /* .cat text, 2 bits per base, 16 bases per word, LSB first */
@@ -53,6 +55,7 @@ struct as_gpu {
     cudaStream_t stream = nullptr;
     DevIndex ix{};
     /* owned device allocations of the index */
+    void *d_lc2 = nullptr;
     void *d_fm = nullptr, *d_super = nullptr, *d_lc = nullptr, *d_sa_lo = nullptr, *d_sa_hi = nullptr,
          *d_text2 = nullptr, *d_mta = nullptr;
     /* device scratch, grown on demand */
@@ -99,6 +102,7 @@ void as_set_error(const char *fmt, ...);
 as_gpu *as_handle_new(int device);                        /* as_index.cu: device checks + stream/events/stats */
 int as_build_big(as_gpu *h, const char *content, uint64_t N, const as_mta *mta, int mta_len, int hlen,
                  uint64_t part_max);                      /* as_build_big.cu: partitioned suffix sort, 40-bit rows */
+int as_build_lc2(as_gpu *h);                              /* as_lc2.cu: deep k-mer table from the device index */
 int as_launch_pack_text(as_gpu *h, const uint8_t *d_in, uint64_t n, uint32_t *d_out);   /* ASCII text -> 2-bit words */
 int as_scratch(as_gpu *h, ScratchBuf *b, size_t bytes);   /* ensure capacity (device memory) */
 int as_pinned(as_gpu *h, size_t bytes);                   /* ensure h->h_pin capacity */

@@ -143,7 +143,7 @@ static int upload_chunk(void *d_dst, const void *h_src, size_t bytes, cudaStream
 }
 
 static void free_index(as_gpu *h) {
-    void **ptrs[] = {&h->d_fm, &h->d_super, &h->d_lc, &h->d_sa_lo, &h->d_sa_hi, &h->d_text2, &h->d_mta};
+    void **ptrs[] = {&h->d_lc2, &h->d_fm, &h->d_super, &h->d_lc, &h->d_sa_lo, &h->d_sa_hi, &h->d_text2, &h->d_mta};
     for (void **p : ptrs) {
         if (*p) cudaFree(*p);
         *p = nullptr;
@@ -394,6 +394,7 @@ extern "C" int as_gpu_open(as_gpu **out, int device, const as_index_view *v) {
     as_gpu *h = as_handle_new(device);
     if (!h) return AS_ENODEV;
     int rc = build_index(h, v);
+    if (rc == AS_OK) rc = as_build_lc2(h);
     if (rc != AS_OK) {
         as_gpu_close(h);
         return rc;

@@ -1,0 +1,95 @@
+/*
+ * as_lc2.cu -- the deep k-mer table: the SA interval of every h2-mer, h2 chosen so that 4^h2 is about 4x the rows
+ * (13 for the 4.6 Mbp genome, 16 for 3.1 Gbp), 8 bytes per entry.
+ *
+ * The reference's lchash (lchash.c:52-104) answers the last hlen = 12 bases of a seed from a 256 MiB table and walks
+ * the other 8 through the FM index -- 16 dependent sector gathers on a genome where a 12-mer still has hundreds of
+ * rows.  With 180 GB of HBM the same question can be asked for the last h2 bases at once: most h2-mers of a genome
+ * have one row, and a one-row interval is finished against the text (as_vote.cu), so a seed costs one table sector,
+ * one SA sector and one text sector.  The 12-mer table stays (it is what `.lch` holds and what as_lc_aln_batch
+ * answers from); PART 1 uses this one when seed_len >= h2.  Results are identical: the interval of the seed's last h2
+ * bases is what lc_access + (h2 - hlen) steps of fmi_aln (fmidx.c:295-313) would have reached, including the
+ * reference's k = 1 start, which drops the occurrence that ends on the text's last base (see k_lc_codes, as_build.cu).
+ *
+ * Entry: bits 0..39 = first row k, bits 40..63 = rows in the interval, 0xFFFFFF = "2^24-1 or more" (PART 1 then takes
+ * the 12-mer table and walks); 0 = absent.  Built from the device index alone (SA + 2-bit text), so handles opened
+ * from the reference's files get it too.
+ */
+#include "as_common.cuh"
+#include <stdlib.h>
+
+#define LC2_NONE 0xFFFFFFFFFFFFFFFFULL
+
+/* LSB-first code of the h-mer starting suffix SA[r], or LC2_NONE (row 0, or the h-mer would touch the last base / '$') */
+__device__ __forceinline__ uint64_t lc2_code(const DevIndex &ix, int h, uint64_t r) {
+    const uint64_t p = as_sa(ix, r);
+    if (r < 1 || p + (uint64_t)h >= ix.N - 1) return LC2_NONE;
+    const uint64_t x = h <= 16 ? (uint64_t)as_bases16(ix.text2, p) : as_bases32(ix.text2, p);
+    return h >= 32 ? x : (x & ((1ULL << (2 * h)) - 1ULL));
+}
+
+__global__ void __launch_bounds__(256) k_lc2_fill(DevIndex ix, int h, unsigned long long *__restrict__ lc2) {
+    const uint64_t RUN = 16, N = ix.N;
+    const uint64_t nruns = (N + RUN - 1) / RUN;
+    for (uint64_t q = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; q < nruns; q += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t r0 = q * RUN, r1 = r0 + RUN < N ? r0 + RUN : N;
+        uint64_t cur = lc2_code(ix, h, r0);
+        uint64_t start = r0;                 /* first row of cur's run, as far as this thread has seen */
+        bool open_left = r0 > 0 && cur != LC2_NONE && lc2_code(ix, h, r0 - 1) == cur;
+        for (uint64_t r = r0; r < r1; r++) {
+            const uint64_t next = r + 1 < N ? lc2_code(ix, h, r + 1) : LC2_NONE;
+            if (next != cur) {
+                if (cur != LC2_NONE) {       /* r closes cur's run: the thread that sees the end writes the entry */
+                    uint64_t k = start;
+                    if (open_left) {         /* the run began before r0: gallop back, then bisect */
+                        uint64_t lo = 0, hi = r0 - 1, step = 1;      /* code(hi) == cur; find the smallest such row */
+                        while (hi >= step && lc2_code(ix, h, hi - step) == cur) {
+                            hi -= step;
+                            step <<= 1;
+                        }
+                        lo = hi >= step ? hi - step + 1 : 0;          /* code(lo-1) != cur (or lo == 0), code(hi) == cur */
+                        while (lo < hi) {
+                            const uint64_t mid = lo + ((hi - lo) >> 1);
+                            if (lc2_code(ix, h, mid) == cur) hi = mid; else lo = mid + 1;
+                        }
+                        k = lo;
+                    }
+                    const uint64_t cnt = r - k + 1;
+                    lc2[cur] = k | ((cnt >= 0xFFFFFFULL ? 0xFFFFFFULL : cnt) << 40);
+                }
+                start = r + 1;
+                open_left = false;
+            }
+            cur = next;
+        }
+    }
+}
+
+int as_build_lc2(as_gpu *h) {
+    DevIndex &ix = h->ix;
+    ix.lc2 = nullptr;
+    ix.hlen2 = 0;
+    if (!ix.text2 || !ix.sa_lo || ix.N < 2) return AS_OK;
+    int h2 = 1;
+    while (h2 < 16 && (1ULL << (2 * h2)) < ix.N) h2++;           /* ceil(log4 N) */
+    h2 += 1;
+    if (h2 > 16) h2 = 16;
+    if (const char *e = getenv("AS_LC2_HLEN")) h2 = atoi(e);
+    if (h2 <= ix.hlen || h2 > 16) return AS_OK;                   /* nothing deeper than the reference's table to offer */
+    size_t free_b = 0, total_b = 0;
+    AS_CUDA(cudaMemGetInfo(&free_b, &total_b));
+    while (h2 > ix.hlen && (8ULL << (2 * h2)) > free_b / 3) h2--;  /* leave room for the batches */
+    if (h2 <= ix.hlen) return AS_OK;
+    const uint64_t entries = 1ULL << (2 * h2);
+    AS_CUDA(cudaMalloc(&h->d_lc2, entries * sizeof(unsigned long long)));
+    AS_CUDA(cudaMemsetAsync(h->d_lc2, 0, entries * sizeof(unsigned long long), h->stream));
+    const uint64_t nruns = (ix.N + 15) / 16;
+    uint64_t blocks = (nruns + 255) / 256, cap = (uint64_t)h->sm_count * 16;
+    k_lc2_fill<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(ix, h2, (unsigned long long *)h->d_lc2);
+    h->launches++;
+    AS_CUDA(cudaGetLastError());
+    AS_CUDA(cudaStreamSynchronize(h->stream));
+    ix.lc2 = (const unsigned long long *)h->d_lc2;
+    ix.hlen2 = h2;
+    return AS_OK;
+}

@@ -51,6 +51,7 @@ struct VoteArgs {
     size_t big_stride;
     uint32_t big_cap;
     unsigned long long *stats;   /* as_stats layout */
+    int use2;                    /* seeds start from the deep table (DevIndex.lc2) instead of the 12-mer table */
 };
 
 __device__ __forceinline__ uint32_t hash_bucket(uint64_t b, uint32_t shift) {
@@ -150,8 +151,9 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
     __syncthreads();
 
     const int sl = a.sl, P = sl + 1;
-    const int left0 = sl - ix.hlen;
-    const uint64_t hmask = (1ULL << (2 * ix.hlen)) - 1ULL;
+    const int hl = a.use2 ? ix.hlen2 : ix.hlen;          /* bases answered by the table */
+    const int left0 = sl - hl;
+    const uint64_t hmask = (1ULL << (2 * hl)) - 1ULL;
     unsigned long long st_seeds = 0, st_steps = 0, st_hits = 0, st_ovf = 0;
     unsigned int st_fm = 0, st_txt = 0;          /* FM steps done here / tails decided by the text */
 
@@ -207,7 +209,24 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
             if (m < m_count) {
                 const uint64_t seed = as_bases32(pr, j);
                 bool absent = false;
-                if (left0 >= 0) {                                               /* lchash.c:93-101 */
+                int tt = left0 - 1;                                             /* next seed base to walk */
+                if (a.use2) {
+                    /* deep table: the interval lc_access + (hlen2 - hlen) steps of fmi_aln would have reached */
+                    const unsigned long long e = __ldg(ix.lc2 + ((seed >> (2 * left0)) & hmask));
+                    const uint32_t cnt = (uint32_t)(e >> 40);
+                    kk = e & 0xFFFFFFFFFFULL;
+                    ll = kk + cnt - 1;
+                    absent = e == 0;
+                    if (cnt == 0xFFFFFFu) {                                     /* too many rows for the entry: 12-mer table */
+                        tt = sl - ix.hlen - 1;
+                        const ulonglong2 kl = __ldg(ix.lc + ((seed >> (2 * (tt + 1))) & ((1ULL << (2 * ix.hlen)) - 1ULL)));
+                        kk = kl.x;
+                        ll = kl.y;
+                        absent = (kk == 0 && ll == 0);
+                    } else if (!absent) {
+                        st_steps += (unsigned)(ix.hlen2 - ix.hlen);            /* steps of the reference's loop it stands for */
+                    }
+                } else if (left0 >= 0) {                                        /* lchash.c:93-101 */
                     ulonglong2 kl = __ldg(ix.lc + ((seed >> (2 * left0)) & hmask));
                     kk = kl.x;
                     ll = kl.y;
@@ -222,7 +241,6 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                      * gather and one text gather instead of 2(tt+1) dependent sector gathers, and the vote needs no
                      * further SA access.  st_steps still counts the steps the reference's loop executes (up to and
                      * including the failing one); st_fm counts the FM steps actually done here. */
-                    int tt = left0 - 1;
                     bool fail = false;
                     if (SMALL) {
                         uint32_t k32 = (uint32_t)kk, l32 = (uint32_t)ll;
@@ -583,6 +601,7 @@ int as_launch_vote(as_gpu *h, const as_params *p, const uint32_t *d_pack, size_t
     a.big_stride = big_stride;
     a.big_cap = big_cap;
     a.stats = h->d_stats;
+    a.use2 = (h->ix.lc2 && sl >= h->ix.hlen2 && !(p->flags & AS_F_NO_LC2)) ? 1 : 0;
 
     /* lanes per read from the seeds of one phase of the longest read */
     int G = seeds_per_phase <= 8 ? 8 : seeds_per_phase <= 16 ? 16 : 32;

@@ -139,6 +139,41 @@ def test_vote_long_reads(native, gpu_repeat, idx_repeat, wide):
     check_vote(gpu_repeat, ix, reads, lens, flags=wide)
 
 
+# deep k-mer table (as_lc2.cu): PART 1 must give the reference's votes whether a seed starts from the 12-mer table
+# or from the h2-mer table, for every h2 (AS_LC2_HLEN forces a depth the small test genomes would not get)
+@pytest.mark.parametrize("h2", [13, 14, 16])
+@pytest.mark.parametrize("wide", [0, 16])
+def test_vote_deep_table(native, idx_repeat, monkeypatch, h2, wide):
+    ix, gs = idx_repeat
+    monkeypatch.setenv("AS_LC2_HLEN", str(h2))
+    m = native.GpuMapper.from_oracle_index(ix, 0)
+    monkeypatch.delenv("AS_LC2_HLEN")
+    try:
+        for k, (lmin, lmax, e, sl, th) in enumerate([(100, 100, 0.0, 20, 300), (150, 150, 0.02, 20, 300), (100, 250, 0.08, 20, 300),
+                                                    (60, 260, 0.05, h2, 50), (60, 260, 0.05, 24, 2), (80, 200, 0.03, 32, 1000),
+                                                    (80, 200, 0.03, 12, 300)]):
+            reads, lens, _ = reads_from(native, 900 + k, gs, 300, lmin, lmax, e, e, 0.7)
+            check_vote(m, ix, reads, lens, sl, th, flags=wide)                          # deep table when sl >= h2
+            check_vote(m, ix, reads, lens, sl, th, flags=wide | native.AS_F_NO_LC2)     # the reference's 12-mer table
+        reads, lens, _ = reads_from(native, 950, gs, 30, 1000, 5000, 0.05, 0.15, 0.34)
+        check_vote(m, ix, reads, lens, flags=wide)
+    finally:
+        m.close()
+
+
+def test_map_deep_table_built_index(native, idx_repeat, monkeypatch):
+    """the same through as_gpu_build and the whole path"""
+    ix, gs = idx_repeat
+    monkeypatch.setenv("AS_LC2_HLEN", "15")
+    m = native.GpuMapper.build(gs, 0)
+    monkeypatch.delenv("AS_LC2_HLEN")
+    try:
+        reads, lens, stride = reads_from(native, 960, gs, 1200, 100, 250, 0.0, 0.08, 0.6)
+        compare_map(native, m, ix, reads, lens, stride)
+    finally:
+        m.close()
+
+
 # ---------------------------------------------------------------------------------------------------
 # whole path (alnmain.c:330-479)
 # ---------------------------------------------------------------------------------------------------
