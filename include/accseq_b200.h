@@ -105,6 +105,11 @@ typedef struct as_params {
 #define AS_F_GACT_BITPAR  8u   /* force the bit-parallel one-read-per-lane GACT kernel (default for n >= 2048) */
 #define AS_F_WIDE_INDEX  16u   /* force the 64-bit backward-search path (default only for indexes of > 2^30 rows) */
 #define AS_F_NO_LC2      32u   /* PART 1 starts every seed from the reference's 12-mer table, not the deep table */
+#define AS_F_RLE_CIGAR   64u   /* store_mem rows hold run bytes ((len << 2) | class; class 0 M, 1 I, 2 D; len 1..63, longer
+                                * runs continue in the next byte) and n_cigar_op counts them: what parse_cigar prints
+                                * (alnmain.c:497-498), ~10 bytes instead of ~150 per short read across PCIe */
+#define AS_F_KEEP_READS 128u   /* as_map_batch leaves the host reads untouched: strand-1 reads are NOT copied back reverse-
+                                * complemented (alnmain.c:433-438); the SAM emitter reverse-complements them as it prints */
 void as_params_default(as_params *p);
 
 /* ---- per-read output: the fields of `result` (accaln.h:95-103) that the path computes ---- */

@@ -53,6 +53,10 @@ int  as_cigar_text(const uint8_t *ops, int n_ops, char *buf, size_t buflen);
 int  as_sam_record(FILE *out, const as_host_index *ix, const char *qname, size_t qname_len,
                    const char *seq, const char *qual, uint32_t len, const as_result *r,
                    const uint8_t *ops);
+/* the same for batches mapped with AS_F_RLE_CIGAR / AS_F_KEEP_READS (map_flags = the as_params.flags of the batch) */
+int  as_cigar_text_rle(const uint8_t *runs, int n_runs, char *buf, size_t buflen);
+int  as_sam_record2(FILE *out, const as_host_index *ix, const char *qname, size_t qname_len, const char *seq,
+                    const char *qual, uint32_t len, const as_result *r, const uint8_t *ops, unsigned map_flags);
 
 /* ---- FASTQ ingest (accaln.c:45-58 reads_load + alnmain.c:87-103 refactor_reads_seq) ---- */
 typedef struct as_read_batch {

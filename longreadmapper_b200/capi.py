@@ -16,6 +16,8 @@ AS_F_GACT_WARP = 4
 AS_F_GACT_BITPAR = 8
 AS_F_WIDE_INDEX = 16
 AS_F_NO_LC2 = 32
+AS_F_RLE_CIGAR = 64
+AS_F_KEEP_READS = 128
 
 # as_result (include/accseq_b200.h)
 RESULT_DTYPE = np.dtype([("loc", "<u8"), ("off", "<u8"), ("seq_id", "<i4"), ("strand", "<i4"), ("flag", "<i4"),
@@ -141,6 +143,7 @@ def host_lib():
     L.as_index_out_of.restype = None
     L.as_index_write.argtypes = [C.c_char_p, C.POINTER(AsHostIndex)]
     L.as_cigar_text.argtypes = [vp, C.c_int, C.c_char_p, sz]
+    L.as_cigar_text_rle.argtypes = [vp, C.c_int, C.c_char_p, sz]
     _host = L
     return L
 
@@ -195,6 +198,16 @@ def cat_image(seqs):
         off += 2 * int(s.size)
     parts.append(np.frombuffer(b"$", np.uint8))
     return np.ascontiguousarray(np.concatenate(parts)), mta
+
+
+def cigar_text_rle(runs):
+    """CIGAR text of AS_F_RLE_CIGAR run bytes ((len << 2) | class)."""
+    runs = np.ascontiguousarray(runs, dtype=np.uint8)
+    buf = C.create_string_buffer(24 * runs.size + 16)
+    n = host_lib().as_cigar_text_rle(runs.ctypes.data, runs.size, buf, len(buf))
+    if n < 0:
+        raise AccSeqError("bad run bytes")
+    return buf.value.decode()
 
 
 def cigar_text(ops):

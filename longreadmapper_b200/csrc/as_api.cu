@@ -15,6 +15,8 @@ extern "C" void as_params_default(as_params *p) {
     p->gact_band = 0;      /* adaptive banded first pass */
 }
 
+__global__ void k_rle_ops(uint8_t *__restrict__ ops, size_t stride, as_result *__restrict__ res, size_t n);
+
 static size_t pack_wstride(uint32_t max_len) { return ((size_t)max_len + 15) / 16 + 3; }
 
 /* all device-side stages of n reads, asynchronous on h->stream; ev[0..4] bracket the stages.  `slot0` is the index
@@ -43,11 +45,70 @@ static int run_stages(as_gpu *h, const as_params *p, char *d_reads, size_t strid
     if (!(p->flags & AS_F_NO_ALIGN))
         AS_TRY(as_launch_gact(h, p, d_pack, ws, d_lens, h->ix.text2, d_toff, nullptr, n, max_len, max_len, d_store,
                               store_stride, nullptr, nullptr, d_res));
+    if ((p->flags & AS_F_RLE_CIGAR) && !(p->flags & AS_F_NO_ALIGN) && d_store) {
+        uint64_t blocks = (n + 7) / 8, cap = (uint64_t)h->sm_count * 8;
+        k_rle_ops<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(d_store, store_stride, d_res, n);
+        h->launches++;
+        AS_CUDA(cudaGetLastError());
+    }
     AS_CUDA(cudaEventRecord(ev[3], h->stream));
     if ((p->flags & AS_F_MYERS) && !(p->flags & AS_F_NO_ALIGN))
         AS_TRY(as_launch_myers(h, d_pack, ws, d_lens, h->ix.text2, d_toff, nullptr, n, max_len, nullptr, nullptr, d_res));
     AS_CUDA(cudaEventRecord(ev[4], h->stream));
     return AS_OK;
+}
+
+/*
+ * AS_F_RLE_CIGAR: the column ops of every read become run bytes in place -- (len << 2) | class, class 0 M ('=' and 'X',
+ * the STANDARD alphabet of edlibAlignmentToCigar, edlib.cpp:262-311), 1 I, 2 D, len 1..63 (longer runs continue in the
+ * next byte) -- and n_cigar_op becomes the number of run bytes.  It is what parse_cigar (alnmain.c:497-498) prints, one
+ * pass earlier: a 150-bp read at 2 % error needs about ten bytes instead of 150, so the D2H copy shrinks by as much.
+ * One warp per read; runs never outnumber columns, so writing in place never overtakes the columns still to be read.
+ */
+__global__ void __launch_bounds__(256) k_rle_ops(uint8_t *__restrict__ ops, size_t stride, as_result *__restrict__ res, size_t n) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const size_t warp0 = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((size_t)gridDim.x * blockDim.x) >> 5;
+    for (size_t r = warp0; r < n; r += nwarps) {
+        const int nops = res[r].n_cigar_op;
+        if (nops <= 0) continue;
+        uint8_t *row = ops + r * stride;
+        int out = 0, open_cls = -1, open_len = 0;
+        for (int base = 0; base < nops; base += 32) {
+            const bool valid = base + (int)lane < nops;
+            const uint32_t c = valid ? row[base + lane] : 0u;
+            const int cls = !valid ? 3 : (c == 1u ? 1 : (c == 2u ? 2 : 0));
+            int prev = __shfl_up_sync(0xFFFFFFFFu, cls, 1);
+            if (lane == 0) prev = open_cls;
+            uint32_t heads = __ballot_sync(0xFFFFFFFFu, valid && cls != prev);
+            const int nvalid = nops - base < 32 ? nops - base : 32;
+            __syncwarp();
+            int pos = 0;                                   /* columns of the strip already attributed to a run */
+            while (pos < nvalid) {
+                /* the run that covers column `pos` reaches to the next head after pos (or the strip's end) */
+                const uint32_t later = heads & ~((2u << pos) - 1u);          /* heads at columns > pos */
+                const int end = later ? __ffs((int)later) - 1 : nvalid;
+                const int c0 = __shfl_sync(0xFFFFFFFFu, cls, pos);
+                if ((heads >> pos) & 1u) {                 /* a new run opens here: close the one that was open */
+                    while (open_len > 0) {
+                        const int l = open_len > 63 ? 63 : open_len;
+                        if (lane == 0) row[out] = (uint8_t)((l << 2) | open_cls);
+                        out++;
+                        open_len -= l;
+                    }
+                    open_cls = c0;
+                }
+                open_len += end - pos;
+                pos = end;
+            }
+        }
+        while (open_len > 0) {
+            const int l = open_len > 63 ? 63 : open_len;
+            if (lane == 0) row[out] = (uint8_t)((l << 2) | open_cls);
+            out++;
+            open_len -= l;
+        }
+        if (lane == 0) res[r].n_cigar_op = out;
+    }
 }
 
 /* per-batch counters that are cheap to take from the results on the device */
@@ -140,7 +201,7 @@ static int ensure_pipeline(as_gpu *h) {
 /* Chunk schedule of one as_map_batch call.  The D2H stream is the longest of the three (results + CIGAR columns + the
  * reverse-complemented reads), so the first chunk is small -- it reaches the D2H stream early -- and the following
  * ones grow to the size at which the kernels run at full efficiency; AS_CHUNK_READS forces a fixed size. */
-static int plan_chunks(size_t n, size_t stride, size_t *begin /* AS_MAX_CHUNKS + 1 */) {
+static int plan_chunks(size_t n, size_t stride, size_t *begin /* AS_MAX_CHUNKS + 1 */, bool light_d2h) {
     size_t fixed = 0;
     if (const char *e = getenv("AS_CHUNK_READS")) {
         long v = atol(e);
@@ -155,10 +216,12 @@ static int plan_chunks(size_t n, size_t stride, size_t *begin /* AS_MAX_CHUNKS +
     }
     const size_t min_reads = 32768;
     /* long reads: cap a chunk at ~256 MB of sequence */
-    size_t big = n / 4, by_bytes = ((size_t)256 << 20) / (stride ? stride : 1);
+    /* with run-byte CIGARs and no read copy-back the D2H stream is short: fewer, larger chunks keep the kernels efficient */
+    size_t big = light_d2h ? n / 3 : n / 4, by_bytes = ((size_t)256 << 20) / (stride ? stride : 1);
     if (big > by_bytes) big = by_bytes;
     if (big < min_reads) big = min_reads;
-    size_t c = big / 4 > min_reads ? big / 4 : min_reads;      /* ramp: big/4, big/2, big, big, ... */
+    size_t c = light_d2h ? big / 3 : big / 4;                  /* ramp: big/4, big/2, big, big, ... */
+    if (c < min_reads) c = min_reads;
     size_t r = 0;
     while (r < n) {
         size_t take = c;
@@ -199,7 +262,7 @@ extern "C" int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t s
     uint8_t *d_store = want_ops ? (uint8_t *)h->store.p : nullptr;
 
     size_t cb[AS_MAX_CHUNKS + 1];
-    const int nc = plan_chunks(n, stride, cb);
+    const int nc = plan_chunks(n, stride, cb, (p->flags & AS_F_KEEP_READS) && (p->flags & AS_F_RLE_CIGAR));
     h->n_chunks_last = nc;
     /* per-read scratch of every chunk is carved out of one allocation made before anything is enqueued */
     {
@@ -211,7 +274,8 @@ extern "C" int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t s
         AS_TRY(as_scratch(h, &h->toff, n * sizeof(uint64_t)));
     }
     h->last_h2d_bytes = n * stride + n * sizeof(uint32_t);
-    h->last_d2h_bytes = n * sizeof(as_result) + n * stride + (size_t)nc * sizeof(int);
+    const bool copy_reads_back = !(p->flags & AS_F_KEEP_READS);
+    h->last_d2h_bytes = n * sizeof(as_result) + (copy_reads_back ? n * stride : 0) + (size_t)nc * sizeof(int);
     AS_CUDA(cudaEventRecord(h->ev[0], h->stream));
     AS_CUDA(cudaStreamWaitEvent(h->s_h2d, h->ev[0], 0));
     AS_CUDA(cudaStreamWaitEvent(h->s_d2h, h->ev[0], 0));
@@ -251,7 +315,8 @@ extern "C" int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t s
         AS_CUDA(cudaEventRecord(h->cev[c][7], h->s_d2h));
         AS_CUDA(cudaMemcpyAsync(results + r0, d_res + r0, cn * sizeof(as_result), cudaMemcpyDeviceToHost, h->s_d2h));
         /* strand-1 reads were reverse-complemented in place (alnmain.c:433-438; the OpenACC copy(reads_mem) :421) */
-        AS_CUDA(cudaMemcpyAsync(reads + r0 * stride, d_reads + r0 * stride, cn * stride, cudaMemcpyDeviceToHost, h->s_d2h));
+        if (copy_reads_back)
+            AS_CUDA(cudaMemcpyAsync(reads + r0 * stride, d_reads + r0 * stride, cn * stride, cudaMemcpyDeviceToHost, h->s_d2h));
     }
     if (want_ops) AS_TRY(finish_chunk(nc - 1));
     AS_CUDA(cudaEventRecord(h->ev[7], h->s_d2h));

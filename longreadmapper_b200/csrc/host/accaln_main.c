@@ -36,6 +36,9 @@ int main(int argc, const char **argv) {
     t_start = now_s();
     as_params p;
     as_params_default(&p);
+    /* compact D2H: run-length CIGAR bytes, reads not copied back (the emitter reverse-complements strand-1 records);
+     * ACCALN_FULL_COPY=1 keeps the reference's layout (one op byte per column, reads reverse-complemented in place) */
+    if (!getenv("ACCALN_FULL_COPY")) p.flags |= AS_F_RLE_CIGAR | AS_F_KEEP_READS;
     unsigned long batch = 1000000ul;
     if (argc == 6) {
         batch = strtoul(argv[3], NULL, 10);
@@ -112,8 +115,8 @@ int main(int argc, const char **argv) {
         }
         for (size_t i = 0; i < b.n; i++) {                              /* alnmain.c:488-526 */
             valid += res[i].valid != 0;
-            as_sam_record(stdout, ix, b.names[i], strlen(b.names[i]), b.seqs + i * b.stride, b.quals[i], b.lens[i],
-                          &res[i], store + i * store_stride);
+            as_sam_record2(stdout, ix, b.names[i], strlen(b.names[i]), b.seqs + i * b.stride, b.quals[i], b.lens[i],
+                           &res[i], store + i * store_stride, p.flags);
         }
         fflush(stdout);
         total += b.n;

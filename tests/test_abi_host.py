@@ -190,3 +190,23 @@ def test_sim_reads_are_seeded_and_truthful(native):
         ref = g[int(p1[i]):int(p1[i]) + int(l1[i])]
         rd = r1[i, :l1[i]]
         assert np.array_equal(rd, ref if s1[i] == 0 else comp[ref][::-1])
+
+
+def test_cigar_text_rle_host():
+    """run bytes of AS_F_RLE_CIGAR print like the column ops they stand for (alnmain.c:497-498 parse_cigar)"""
+    import longreadmapper_b200 as lm
+    rng = np.random.default_rng(5)
+    for _ in range(50):
+        cls = rng.integers(0, 3, rng.integers(1, 40))
+        lens = rng.integers(1, 200, cls.size)
+        ops = np.concatenate([np.full(l, (0, 1, 2)[c], np.uint8) for c, l in zip(cls, lens)])
+        ops[(ops == 0) & (rng.random(ops.size) < 0.1)] = 3                 # X prints as M
+        runs = []
+        for c, l in zip(cls, lens):
+            while l > 0:
+                t = min(63, int(l))
+                runs.append((t << 2) | int(c))
+                l -= t
+        assert lm.cigar_text_rle(np.array(runs, np.uint8)) == lm.cigar_text(ops)
+    with pytest.raises(lm.AccSeqError):
+        lm.cigar_text_rle(np.array([3], np.uint8))

@@ -233,6 +233,29 @@ def test_map_edge_cases(native, gpu_repeat, idx_repeat, gact):
     compare_map(native, gpu_repeat, ix, reads, lens, stride, gact=gact)
 
 
+@pytest.mark.parametrize("gact", ["warp", "bitpar"])
+def test_map_compact_output(native, gpu_repeat, idx_repeat, gact):
+    """AS_F_RLE_CIGAR | AS_F_KEEP_READS: same results, the CIGAR as run bytes that print the same text, host reads
+    left as sequenced (the emitter reverse-complements strand-1 records, alnmain.c:433-438)"""
+    ix, gs = idx_repeat
+    reads, lens, stride = reads_from(native, 640, gs, 900, 30, 700, 0.0, 0.12, 0.5)
+    full, fops = gpu_repeat.map_batch(reads.copy(), lens, params=gpu_repeat.params(flags=GACT_IMPL[gact]))
+    host = reads.copy()
+    comp, runs = gpu_repeat.map_batch(host, lens, params=gpu_repeat.params(
+        flags=GACT_IMPL[gact] | native.AS_F_RLE_CIGAR | native.AS_F_KEEP_READS))
+    assert np.array_equal(host, reads)                                   # nothing copied back over the reads
+    for f in full.dtype.names:
+        if f != "n_cigar_op":
+            assert np.array_equal(full[f], comp[f]), f
+    assert (full["strand"] == 1).sum() > 100
+    for i in range(len(lens)):
+        n, m = int(full["n_cigar_op"][i]), int(comp["n_cigar_op"][i])
+        assert (n > 0) == (m > 0)
+        if n > 0:
+            assert m <= n and native.cigar_text_rle(runs[i, :m]) == native.cigar_text(fops[i, :n]), i
+            assert int((runs[i, :m] >> 2).sum()) == n
+
+
 def test_map_empty_and_single(native, gpu_uniform, idx_uniform):
     ix, (g,) = idx_uniform
     res, ops = gpu_uniform.map_batch(np.zeros((0, 151), np.uint8), np.zeros(0, np.uint32))
