@@ -432,7 +432,9 @@ def run_b200(args):
     # algorithmic bytes of seeding+voting per SURVEY 8(d): 16 B lc pair per seed + 49 B per backward step + 5 B per SA hit
     vote_bytes = per_step["seeds"] * 16 + per_step["bs_steps"] * 49 + per_step["sa_hits"] * 5 + n * max_len / 4
     sm_clock = (clocks.get("sm_mhz") or 1965.0) * 1e6
-    int_peak = 148 * 128 * 1965.0e6 / 1e12          # lanes x max clock, Tops/s
+    # LOP3/SHF/IADD3 go to the alu pipe, which takes one warp instruction per 2 cycles per SMSP (B300_MICROARCH.md "Pipe
+    # rates"; ncu's sm__inst_executed_pipe_alu agrees): 148 SMs x 4 SMSPs x 16 lanes x max clock, in Tops/s
+    int_peak = 148 * 64 * 1965.0e6 / 1e12
     stages = {
         "part1_seed_vote": {"ms": tm["part1"], "bound": "hbm", "achieved": vote_bytes / (tm["part1"] / 1e3) / 1e9 if tm["part1"] else None,
                             "peak": hbm_peak, "unit": "GB/s"},
@@ -450,6 +452,12 @@ def run_b200(args):
     for s in stages.values():
         if s.get("achieved") is not None:
             s["frac"] = s["achieved"] / s["peak"]
+    try:        # pipe utilisation ncu measured for the committed capture of this command (profiles/ncu_traffic.json)
+        tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(args.workload, {})
+        if "k_gact_bp_alu_pipe_pct" in tj:
+            stages["gact"]["alu_pipe_pct_ncu"] = tj["k_gact_bp_alu_pipe_pct"]
+    except (OSError, ValueError):
+        pass
     # DRAM bytes per launch of the dominant kernels, from the committed `ncu --set full` capture of this same command
     # (profiles/ncu_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum); null for workloads it was not taken on
     traffic = {}
@@ -463,7 +471,7 @@ def run_b200(args):
                 "peak": d["peak"], "unit": d["unit"], "frac": d.get("frac"),
                 "traffic": traffic.get("k_gact_bp" if dom == "gact" else "k_vote") if n == wl["reads"] else None,
                 "algorithmic": vote_bytes if dom != "gact" else per_step["dp_cells_eval"] * INT_OPS_PER_CELL,
-                "peak_source": peak_src if d["bound"] == "hbm" else "148 SMs x 128 INT32 lanes x clocks.max.sm 1965 MHz",
+                "peak_source": peak_src if d["bound"] == "hbm" else "alu pipe: 148 SMs x 64 INT32 lanes x clocks.max.sm 1965 MHz",
                 "ms_per_launch": d["ms"], "share_of_step": d["ms"] / tm["total"] if tm["total"] else None,
                 "stages": stages, "sm_clock_mhz_under_load": sm_clock / 1e6}
 
