@@ -27,35 +27,50 @@ __device__ __forceinline__ uint32_t comp_ascii(uint32_t c) {             /* alnm
 }
 
 
+/* reverse the sixteen 2-bit groups of a word */
+__device__ __forceinline__ uint32_t rev2(uint32_t x) {
+    const uint32_t r = __brev(x);
+    return ((r >> 1) & 0x55555555u) | ((r & 0x55555555u) << 1);
+}
+
+/*
+ * Thread per read for the lookup (vote -> mta binary search -> result), then the warp turns to the strand-1 reads among
+ * its 32, one at a time: ASCII reverse complement by mirrored pairs (both halves coalesced), and the packed copy straight
+ * from the packed words (reverse the 2-bit groups, complement) unless the read holds a byte outside ACGT, whose code the
+ * packed form cannot complement -- those re-pack from the ASCII, as do reads of more than 512 bases.
+ */
 __global__ void __launch_bounds__(256) k_locus(DevIndex ix, char *__restrict__ ascii, size_t stride,
                                                const uint32_t *__restrict__ lens, size_t n, uint32_t *__restrict__ pack,
                                                size_t wstride, const VoteOut *__restrict__ vote,
                                                as_result *__restrict__ res, uint64_t *__restrict__ toff) {
     const uint32_t lane = threadIdx.x & 31u;
-    const uint64_t warp0 = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
-    const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
-    for (uint64_t r = warp0; r < n; r += nwarps) {
-        const VoteOut v = vote[r];
-        const uint32_t len = lens[r];
-        const uint64_t loc = v.best_key;
-        /* seq_lookup: the entries tile .cat, so only the last one starting at or before loc can match */
-        int lo = 0, hi = ix.mta_len;     /* first entry with offset > loc */
-        while (lo < hi) {
-            int mid = (lo + hi) >> 1;
-            if (ix.mta[mid].offset <= loc) lo = mid + 1; else hi = mid;
-        }
-        int seq_id = -1, strand = 0;
-        uint64_t off = 0, fwd = 0;
-        if (lo > 0 && v.phases >= 0 && loc + len >= loc) {               /* u64 wrap of loc+len: reference UB, unmapped here */
-            const int i = lo - 1;
-            const uint64_t start = ix.mta[i].offset, sl = ix.mta[i].seq_len, end = start + 2 * sl;
-            if (loc >= start && loc + len <= start + sl) {               /* alnmain.c:158-164 */
-                seq_id = i; strand = 0; fwd = loc; off = loc - start;
-            } else if (loc >= start + sl && loc + len <= end) {          /* alnmain.c:165-172 */
-                seq_id = i; strand = 1; off = end - loc - len; fwd = off + start;
+    const size_t warp0 = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const size_t nwarps = ((size_t)gridDim.x * blockDim.x) >> 5;
+    for (size_t base = warp0 * 32; base < n; base += nwarps * 32) {
+        const size_t r = base + lane;
+        uint32_t len = 0;
+        int strand = 0;
+        if (r < n) {
+            const VoteOut v = vote[r];
+            len = lens[r];
+            const uint64_t loc = v.best_key;
+            /* seq_lookup: the entries tile .cat, so only the last one starting at or before loc can match */
+            int lo = 0, hi = ix.mta_len;     /* first entry with offset > loc */
+            while (lo < hi) {
+                int mid = (lo + hi) >> 1;
+                if (ix.mta[mid].offset <= loc) lo = mid + 1; else hi = mid;
             }
-        }
-        if (lane == 0) {
+            int seq_id = -1;
+            uint64_t off = 0, fwd = 0;
+            if (lo > 0 && v.phases >= 0 && loc + len >= loc) {           /* u64 wrap of loc+len: reference UB, unmapped here */
+                const int i = lo - 1;
+                const uint64_t start = ix.mta[i].offset, sl = ix.mta[i].seq_len, end = start + 2 * sl;
+                if (loc >= start && loc + len <= start + sl) {           /* alnmain.c:158-164 */
+                    seq_id = i; strand = 0; fwd = loc; off = loc - start;
+                } else if (loc >= start + sl && loc + len <= end) {      /* alnmain.c:165-172 */
+                    seq_id = i; strand = 1; off = end - loc - len; fwd = off + start;
+                }
+            }
             as_result o;
             o.loc = loc;
             o.off = off;
@@ -72,23 +87,50 @@ __global__ void __launch_bounds__(256) k_locus(DevIndex ix, char *__restrict__ a
             res[r] = o;
             toff[r] = seq_id < 0 ? AS_TOFF_NONE : fwd;
         }
-        if (strand == 1) {                                               /* alnmain.c:433-438 */
-            uint8_t *s = (uint8_t *)ascii + r * stride;
-            const uint32_t half = len >> 1;
+        /* ---- strand-1 reads of this warp's 32, one after the other (alnmain.c:433-438) ---- */
+        uint32_t todo = __ballot_sync(0xFFFFFFFFu, strand == 1);
+        while (todo) {
+            const int src = __ffs((int)todo) - 1;
+            todo &= todo - 1;
+            const uint32_t rl = __shfl_sync(0xFFFFFFFFu, len, src);
+            const size_t rr = base + (size_t)src;
+            uint8_t *s = (uint8_t *)ascii + rr * stride;
+            uint32_t *pw = pack + rr * wstride;
+            const uint32_t half = rl >> 1;
+            bool other = false;                                          /* a byte outside ACGT/acgt */
             for (uint32_t i = lane; i < half; i += 32) {
-                uint32_t a = s[i], b = s[len - 1 - i];
-                s[i] = (uint8_t)comp_ascii(b);
-                s[len - 1 - i] = (uint8_t)comp_ascii(a);
+                const uint32_t ca = comp_ascii(s[i]), cb = comp_ascii(s[rl - 1 - i]);
+                other |= (ca == 'N') | (cb == 'N');
+                s[i] = (uint8_t)cb;
+                s[rl - 1 - i] = (uint8_t)ca;
             }
-            if ((len & 1u) && lane == 0) s[half] = (uint8_t)comp_ascii(s[half]);
+            if ((rl & 1u) && lane == 0) {
+                const uint32_t cm = comp_ascii(s[half]);
+                other |= cm == 'N';
+                s[half] = (uint8_t)cm;
+            }
+            const uint32_t nw = (rl + 15) >> 4;
+            if (!__any_sync(0xFFFFFFFFu, other) && nw <= 32) {
+                /* out word w = complement of input bases [rl-16w-16, rl-16w), last first */
+                uint32_t y = 0;
+                if (lane < nw) {
+                    const int st = (int)rl - 16 * (int)lane - 16;
+                    const uint32_t cnt = st >= 0 ? 16u : (uint32_t)(16 + st);
+                    const uint32_t x = as_bases16(pw, (uint64_t)(st > 0 ? st : 0));
+                    y = ~rev2(x) >> (2u * (16u - cnt));
+                    if (cnt < 16u) y &= (1u << (2u * cnt)) - 1u;
+                }
+                __syncwarp();
+                if (lane < nw) pw[lane] = y;
+            } else {
+                __syncwarp();
+                for (uint32_t w = lane; w < nw; w += 32) {
+                    uint32_t b0 = w << 4, lim = rl - b0 < 16 ? rl - b0 : 16, val = 0;
+                    for (uint32_t t = 0; t < lim; t++) val |= as_base_code(s[b0 + t]) << (2 * t);
+                    pw[w] = val;
+                }
+            }
             __syncwarp();
-            uint32_t *pw = pack + r * wstride;
-            const uint32_t nw = (len + 15) >> 4;
-            for (uint32_t w = lane; w < nw; w += 32) {
-                uint32_t b0 = w << 4, lim = len - b0 < 16 ? len - b0 : 16, val = 0;
-                for (uint32_t t = 0; t < lim; t++) val |= as_base_code(s[b0 + t]) << (2 * t);
-                pw[w] = val;
-            }
         }
     }
 }
@@ -96,7 +138,7 @@ __global__ void __launch_bounds__(256) k_locus(DevIndex ix, char *__restrict__ a
 int as_launch_locus(as_gpu *h, char *d_ascii, size_t stride, const uint32_t *d_lens, size_t n,
                     uint32_t *d_pack, size_t wstride, const VoteOut *d_vote, as_result *d_res, uint64_t *d_toff) {
     if (n == 0) return AS_OK;
-    uint64_t blocks = (n + 7) / 8, cap = (uint64_t)h->sm_count * 8;
+    uint64_t blocks = (n + 255) / 256, cap = (uint64_t)h->sm_count * 8;
     k_locus<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(h->ix, d_ascii, stride, d_lens, n, d_pack, wstride,
                                                                           d_vote, d_res, d_toff);
     h->launches++;
