@@ -125,9 +125,8 @@ __global__ void __launch_bounds__(256) k_locus(DevIndex ix, char *__restrict__ a
             } else {
                 __syncwarp();
                 for (uint32_t w = lane; w < nw; w += 32) {
-                    uint32_t b0 = w << 4, lim = rl - b0 < 16 ? rl - b0 : 16, val = 0;
-                    for (uint32_t t = 0; t < lim; t++) val |= as_base_code(s[b0 + t]) << (2 * t);
-                    pw[w] = val;
+                    const uint32_t b0 = w << 4, lim = rl - b0 < 16 ? rl - b0 : 16;
+                    pw[w] = as_pack16(s + b0, lim);
                 }
             }
             __syncwarp();
@@ -135,9 +134,83 @@ __global__ void __launch_bounds__(256) k_locus(DevIndex ix, char *__restrict__ a
     }
 }
 
+/* long reads: one warp per read, so that the byte work of a 10-kbp reverse complement spreads over all warps */
+__global__ void __launch_bounds__(256) k_locus_long(DevIndex ix, char *__restrict__ ascii, size_t stride,
+                                               const uint32_t *__restrict__ lens, size_t n, uint32_t *__restrict__ pack,
+                                               size_t wstride, const VoteOut *__restrict__ vote,
+                                               as_result *__restrict__ res, uint64_t *__restrict__ toff) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint64_t warp0 = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
+    const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+    for (uint64_t r = warp0; r < n; r += nwarps) {
+        const VoteOut v = vote[r];
+        const uint32_t len = lens[r];
+        const uint64_t loc = v.best_key;
+        /* seq_lookup: the entries tile .cat, so only the last one starting at or before loc can match */
+        int lo = 0, hi = ix.mta_len;     /* first entry with offset > loc */
+        while (lo < hi) {
+            int mid = (lo + hi) >> 1;
+            if (ix.mta[mid].offset <= loc) lo = mid + 1; else hi = mid;
+        }
+        int seq_id = -1, strand = 0;
+        uint64_t off = 0, fwd = 0;
+        if (lo > 0 && v.phases >= 0 && loc + len >= loc) {               /* u64 wrap of loc+len: reference UB, unmapped here */
+            const int i = lo - 1;
+            const uint64_t start = ix.mta[i].offset, sl = ix.mta[i].seq_len, end = start + 2 * sl;
+            if (loc >= start && loc + len <= start + sl) {               /* alnmain.c:158-164 */
+                seq_id = i; strand = 0; fwd = loc; off = loc - start;
+            } else if (loc >= start + sl && loc + len <= end) {          /* alnmain.c:165-172 */
+                seq_id = i; strand = 1; off = end - loc - len; fwd = off + start;
+            }
+        }
+        if (lane == 0) {
+            as_result o;
+            o.loc = loc;
+            o.off = off;
+            o.seq_id = seq_id;
+            o.strand = strand;
+            o.flag = seq_id < 0 ? 4 : (strand ? 16 : 0);                 /* alnmain.c:466-474; GACT may still fail it */
+            o.mapq = seq_id < 0 ? 0 : 255;
+            o.ed = -1;
+            o.valid = seq_id >= 0;
+            o.n_cigar_op = 0;
+            o.myers = -2;
+            o.phases = v.phases;
+            o.from_outer = v.from_outer;
+            res[r] = o;
+            toff[r] = seq_id < 0 ? AS_TOFF_NONE : fwd;
+        }
+        if (strand == 1) {                                               /* alnmain.c:433-438 */
+            uint8_t *s = (uint8_t *)ascii + r * stride;
+            const uint32_t half = len >> 1;
+            for (uint32_t i = lane; i < half; i += 32) {
+                uint32_t a = s[i], b = s[len - 1 - i];
+                s[i] = (uint8_t)comp_ascii(b);
+                s[len - 1 - i] = (uint8_t)comp_ascii(a);
+            }
+            if ((len & 1u) && lane == 0) s[half] = (uint8_t)comp_ascii(s[half]);
+            __syncwarp();
+            uint32_t *pw = pack + r * wstride;
+            const uint32_t nw = (len + 15) >> 4;
+            for (uint32_t w = lane; w < nw; w += 32) {
+                const uint32_t b0 = w << 4, lim = len - b0 < 16 ? len - b0 : 16;
+                pw[w] = as_pack16(s + b0, lim);
+            }
+        }
+    }
+}
+
 int as_launch_locus(as_gpu *h, char *d_ascii, size_t stride, const uint32_t *d_lens, size_t n,
                     uint32_t *d_pack, size_t wstride, const VoteOut *d_vote, as_result *d_res, uint64_t *d_toff) {
     if (n == 0) return AS_OK;
+    if (wstride > 32 + 3) {                              /* reads of more than 512 bases in the batch */
+        uint64_t blocks = (n + 7) / 8, cap = (uint64_t)h->sm_count * 8;
+        k_locus_long<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(h->ix, d_ascii, stride, d_lens, n, d_pack,
+                                                                                   wstride, d_vote, d_res, d_toff);
+        h->launches++;
+        AS_CUDA(cudaGetLastError());
+        return AS_OK;
+    }
     uint64_t blocks = (n + 255) / 256, cap = (uint64_t)h->sm_count * 8;
     k_locus<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(h->ix, d_ascii, stride, d_lens, n, d_pack, wstride,
                                                                           d_vote, d_res, d_toff);

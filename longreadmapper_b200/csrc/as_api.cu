@@ -16,6 +16,7 @@ extern "C" void as_params_default(as_params *p) {
 }
 
 __global__ void k_rle_ops(uint8_t *__restrict__ ops, size_t stride, as_result *__restrict__ res, size_t n);
+__global__ void k_rle_ops_warp(uint8_t *__restrict__ ops, size_t stride, as_result *__restrict__ res, size_t n);
 
 static size_t pack_wstride(uint32_t max_len) { return ((size_t)max_len + 15) / 16 + 3; }
 
@@ -46,8 +47,13 @@ static int run_stages(as_gpu *h, const as_params *p, char *d_reads, size_t strid
         AS_TRY(as_launch_gact(h, p, d_pack, ws, d_lens, h->ix.text2, d_toff, nullptr, n, max_len, max_len, d_store,
                               store_stride, nullptr, nullptr, d_res));
     if ((p->flags & AS_F_RLE_CIGAR) && !(p->flags & AS_F_NO_ALIGN) && d_store) {
-        uint64_t blocks = (n + 7) / 8, cap = (uint64_t)h->sm_count * 8;
-        k_rle_ops<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(d_store, store_stride, d_res, n);
+        if (store_stride > 1024) {
+            uint64_t blocks = (n + 7) / 8, cap = (uint64_t)h->sm_count * 8;
+            k_rle_ops_warp<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(d_store, store_stride, d_res, n);
+        } else {
+            uint64_t blocks = (n + 255) / 256, cap = (uint64_t)h->sm_count * 8;
+            k_rle_ops<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(d_store, store_stride, d_res, n);
+        }
         h->launches++;
         AS_CUDA(cudaGetLastError());
     }
@@ -63,9 +69,53 @@ static int run_stages(as_gpu *h, const as_params *p, char *d_reads, size_t strid
  * the STANDARD alphabet of edlibAlignmentToCigar, edlib.cpp:262-311), 1 I, 2 D, len 1..63 (longer runs continue in the
  * next byte) -- and n_cigar_op becomes the number of run bytes.  It is what parse_cigar (alnmain.c:497-498) prints, one
  * pass earlier: a 150-bp read at 2 % error needs about ten bytes instead of 150, so the D2H copy shrinks by as much.
- * One warp per read; runs never outnumber columns, so writing in place never overtakes the columns still to be read.
  */
 __global__ void __launch_bounds__(256) k_rle_ops(uint8_t *__restrict__ ops, size_t stride, as_result *__restrict__ res, size_t n) {
+    /* one thread per read: a sequential scan of its columns, four per 32-bit load; the run bytes go back into the same
+     * row, always behind the read position (runs never outnumber columns) */
+    const bool words = (stride & 3) == 0 && (reinterpret_cast<uintptr_t>(ops) & 3) == 0;
+    for (size_t r = (size_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (size_t)gridDim.x * blockDim.x) {
+        const int nops = res[r].n_cigar_op;
+        if (nops <= 0) continue;
+        uint8_t *row = ops + r * stride;
+        int out = 0, open_cls = -1, open_len = 0;
+        for (int base = 0; base < nops; base += 4) {
+            uint32_t x;
+            if (words) x = *reinterpret_cast<const uint32_t *>(row + base);
+            else {
+                x = 0;
+                for (int t = 0; t < 4 && base + t < nops; t++) x |= (uint32_t)row[base + t] << (8 * t);
+            }
+            const int lim = nops - base < 4 ? nops - base : 4;
+#pragma unroll
+            for (int t = 0; t < 4; t++) {
+                if (t < lim) {
+                    const uint32_t c = (x >> (8 * t)) & 0xFFu;
+                    const int cls = c == 1u ? 1 : (c == 2u ? 2 : 0);       /* '=' and 'X' are M */
+                    if (cls != open_cls) {
+                        while (open_len > 0) {
+                            const int l = open_len > 63 ? 63 : open_len;
+                            row[out++] = (uint8_t)((l << 2) | open_cls);
+                            open_len -= l;
+                        }
+                        open_cls = cls;
+                    }
+                    open_len++;
+                }
+            }
+        }
+        while (open_len > 0) {
+            const int l = open_len > 63 ? 63 : open_len;
+            row[out++] = (uint8_t)((l << 2) | open_cls);
+            open_len -= l;
+        }
+        res[r].n_cigar_op = out;
+    }
+}
+
+/* the same with one warp per read (ballot of class changes per 32 columns): long reads, where a thread per read would
+ * leave most of the GPU idle */
+__global__ void __launch_bounds__(256) k_rle_ops_warp(uint8_t *__restrict__ ops, size_t stride, as_result *__restrict__ res, size_t n) {
     const uint32_t lane = threadIdx.x & 31u;
     const size_t warp0 = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((size_t)gridDim.x * blockDim.x) >> 5;
     for (size_t r = warp0; r < n; r += nwarps) {

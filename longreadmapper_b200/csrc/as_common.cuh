@@ -346,4 +346,25 @@ __device__ __forceinline__ uint64_t as_bases32(const uint32_t *w, uint64_t i) {
     return ((uint64_t)__funnelshift_r(b, c, s) << 32) | __funnelshift_r(a, b, s);
 }
 
+/* four ASCII bases in a word -> their four 2-bit codes in the low byte (A0 C1 G2 T3, as_base_code per byte lane) */
+__device__ __forceinline__ uint32_t as_pack4(uint32_t x) {
+    const uint32_t c = ((x >> 1) & 0x03030303u) ^ ((x >> 2) & 0x01010101u);     /* one code per byte */
+    return (c * 0x01041040u) >> 24;                                               /* b0 | b1<<2 | b2<<4 | b3<<6, no carries */
+}
+/* lim <= 16 ASCII bases at src (any alignment) -> one packed word: aligned 32-bit loads shifted into place.  Reads whole
+ * words, so up to 3 bytes either side of the bases are touched (inside the 256-byte aligned batch buffer). */
+__device__ __forceinline__ uint32_t as_pack16(const uint8_t *src, uint32_t lim) {
+    const uint32_t mis = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 3u);
+    const uint32_t *p = reinterpret_cast<const uint32_t *>(src - mis);
+    const uint32_t nload = (mis + lim + 3) >> 2;                                  /* <= 5 words */
+    uint32_t q[5], v = 0;
+#pragma unroll
+    for (int t = 0; t < 5; t++) q[t] = (uint32_t)t < nload ? p[t] : 0u;
+    const uint32_t sh = 8u * mis;
+#pragma unroll
+    for (int t = 0; t < 4; t++) v |= as_pack4(__funnelshift_r(q[t], q[t + 1], sh)) << (8 * t);
+    if (lim < 16) v &= (1u << (2 * lim)) - 1u;
+    return v;
+}
+
 #endif /* __CUDACC__ */

@@ -14,7 +14,8 @@
 __global__ void __launch_bounds__(256) k_pack_reads(const char *__restrict__ ascii, size_t stride,
                                                     const uint32_t *__restrict__ lens, size_t n,
                                                     uint32_t *__restrict__ pack, size_t wstride) {
-    /* one thread per output word; consecutive threads write consecutive words of a read */
+    /* one thread per output word; consecutive threads write consecutive words of a read.  The 16 bytes of a word are
+     * fetched as aligned 32-bit loads (rows start at any byte: stride = max_len+1) and shifted into place. */
     uint64_t total = (uint64_t)n * wstride;
     for (uint64_t g = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; g < total; g += (uint64_t)gridDim.x * blockDim.x) {
         uint64_t r = g / wstride;
@@ -23,9 +24,8 @@ __global__ void __launch_bounds__(256) k_pack_reads(const char *__restrict__ asc
         uint32_t b0 = w << 4;
         uint32_t v = 0;
         if (b0 < len) {
-            const uint8_t *src = (const uint8_t *)ascii + r * stride + b0;
-            uint32_t lim = len - b0 < 16 ? len - b0 : 16;
-            for (uint32_t t = 0; t < lim; t++) v |= as_base_code(src[t]) << (2 * t);
+            const uint32_t lim = len - b0 < 16 ? len - b0 : 16;
+            v = as_pack16((const uint8_t *)ascii + r * stride + b0, lim);
         }
         pack[g] = v;
     }

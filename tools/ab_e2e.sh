@@ -1,7 +1,8 @@
-# e2e (compact mode) under different chunk plans: AS_CHUNK_READS=<fixed size>, or the built-in ramp
+# e2e (compact mode) under different settings: each argument is an env assignment list ("-" = defaults),
+# e.g.  bash tools/ab_e2e.sh - AS_ONE_STREAM=1 AS_CHUNK_READS=125000
 for c in "$@"; do
-  if [ "$c" = "auto" ]; then unset AS_CHUNK_READS; else export AS_CHUNK_READS=$c; fi
-  python bench.py --no-cpu --steps 5 | python -c "
+  ( [ "$c" = "-" ] || export $c
+    python bench.py --no-cpu --steps 5 | python -c "
 import sys,json; d=json.loads(sys.stdin.read()); e=d['e2e']; f=d['e2e_full_copy']
-print('chunk $c', 'compact', round(e['ms_per_step'],3), e['stage_ms_last_step'], 'full', round(f['ms_per_step'],3))"
+print('$c', 'compact', round(e['ms_per_step'],3), e['same_results_as_device_path'], e['stage_ms_last_step'], 'full', round(f['ms_per_step'],3), f['same_results_as_device_path'])" )
 done
