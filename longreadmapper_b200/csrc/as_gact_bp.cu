@@ -82,7 +82,7 @@ struct TileOut {
  * One attempt at one tile: fill (NBW words per column; SLIDE: the words slide down the diagonal, else they are the
  * whole tile), end cell, traceback into the warp's slab `tb` (16 ops per word, walk order).
  */
-template <int NBW, bool SLIDE>
+template <int NBW, bool SLIDE, bool TRACK>
 __device__ __forceinline__ void tile_pass(const TileGeom &g, uint2 *__restrict__ planes, uint32_t *__restrict__ tb,
                                           uint2 (*win)[32], uint32_t lane, unsigned long long &st_eval, TileOut &out) {
     const int Tq = g.Tq, Tt = g.Tt, KB = SLIDE ? g.KB : 0x3FFFFFFF;
@@ -98,7 +98,10 @@ __device__ __forceinline__ void tile_pass(const TileGeom &g, uint2 *__restrict__
     int sc = Tq;                                            /* D[Tq][j], valid while the bottom row is in the band */
     int rowkey = (Tq << 12) | (Tt << 1);                    /* bottom-row candidates (edge 0), column 0 first */
     /* sliding band: sb = value at the bottom row of the band's lowest word, in the column just filled */
-    const bool track_sb = SLIDE && (g.track_row || g.track_col);
+    /* TRACK = some lane of the warp needs edge values (a tile that is not its read's last); reads of one tile never do,
+     * and their instantiation carries none of the bookkeeping */
+    const bool track_row = TRACK && g.track_row;
+    const bool track_sb = TRACK && SLIDE && (g.track_row || g.track_col);
     int sb = 32 * NBW, wlo = 0;
 
     /* ---- fill: one column per iteration ---- */
@@ -136,7 +139,7 @@ __device__ __forceinline__ void tile_pass(const TileGeom &g, uint2 *__restrict__
                 const uint32_t xh = (((eq2 & pv) + pv) ^ pv) | eq2;
                 uint32_t ph = mv | ~(xh | pv);
                 uint32_t mh = pv & xh;
-                if (g.track_row) {
+                if (track_row) {
                     if (wlo + s == wlast && Tq > 0) sc += (int)((ph >> blast) & 1u) - (int)((mh >> blast) & 1u);
                 }
                 const uint32_t hp_out = ph >> 31, hn_out = mh >> 31;
@@ -154,7 +157,7 @@ __device__ __forceinline__ void tile_pass(const TileGeom &g, uint2 *__restrict__
                 hneg = hn_out;
             }
             if (track_sb) sb += (int)hpos - (int)hneg;
-            if (g.track_row && wlast >= wlo && wlast < wlo + NBW) rowkey = min(rowkey, (sc << 12) | ((Tt - j) << 1));
+            if (track_row && wlast >= wlo && wlast < wlo + NBW) rowkey = min(rowkey, (sc << 12) | ((Tt - j) << 1));
         }
     }
     __syncwarp();
@@ -339,12 +342,15 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
             TileOut o;
             bool full = !BANDED;
             if (BANDED) {
-                tile_pass<NB, true>(g, planes, tb, win, lane, st_eval, o);
+                /* the lean instantiation pays off for short reads only: in the wide kernels a third copy of the tile code
+                 * costs more registers (occupancy) than the bookkeeping it saves */
+                if (W > 5 || g.track_row || g.track_col) tile_pass<NB, true, true>(g, planes, tb, win, lane, st_eval, o);
+                else tile_pass<NB, true, (W > 5)>(g, planes, tb, win, lane, st_eval, o);
                 /* some lane's walk cannot be proven exact: the warp fills the tile again with the whole matrix */
                 full = __any_sync(0xFFFFFFFFu, o.bad);
                 st_retry += (full && lane == 0);
             }
-            if (full) tile_pass<W, false>(g, planes, tb, win, lane, st_eval, o);
+            if (full) tile_pass<W, false, true>(g, planes, tb, win, lane, st_eval, o);
             if (!done) {
                 st_cells += (unsigned long long)g.Tq * (unsigned long long)g.Tt;
                 st_tiles++;
