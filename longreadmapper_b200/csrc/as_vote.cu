@@ -19,6 +19,10 @@
 #ifndef VOTE_CLAIM
 #define VOTE_CLAIM 1
 #endif
+/* intervals of at most this many rows are finished against the text: 2 where the index sits in L2 for good part and the
+ * kernel waits on latency (the rows' gathers overlap); 1 at human scale, where every gather is a DRAM sector and the
+ * kernel is bound by their number (measured: c2 2.54 -> 2.39 ms with 2, c4 39 -> 44 ms) */
+#define VOTE_VW (SMALL ? 2 : 1)
 #ifndef VOTE_MIN_BLOCKS
 #define VOTE_MIN_BLOCKS 6
 #endif
@@ -234,17 +238,17 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                 }
                 st_seeds++;
                 if (!absent) {
-                    /* Backward search (fmidx.c:300-310) until the interval is empty, the seed is used up, or ONE row is
-                     * left.  A one-row interval [r,r] can only shrink to empty or map to one row, and which of the two
-                     * is decided by the text: the remaining bases [0,tt] of the seed must equal the tt+1 bases in front
-                     * of SA[r], and then the final row's SA value is SA[r]-(tt+1).  So the tail of the walk is one SA
+                    /* Backward search (fmidx.c:300-310) until the interval is empty, the seed is used up, or at most
+                     * VOTE_VW rows are left.  A row r of the interval survives the rest of the walk iff the remaining bases
+                     * [0,tt] of the seed equal the tt+1 bases in front of SA[r] -- the text decides -- and the row it
+                     * maps to has SA value SA[r]-(tt+1).  So the tail of the walk is one SA
                      * gather and one text gather instead of 2(tt+1) dependent sector gathers, and the vote needs no
                      * further SA access.  st_steps still counts the steps the reference's loop executes (up to and
                      * including the failing one); st_fm counts the FM steps actually done here. */
                     bool fail = false;
                     if (SMALL) {
                         uint32_t k32 = (uint32_t)kk, l32 = (uint32_t)ll;
-                        while (tt >= 0 && k32 != l32) {
+                        while (tt >= 0 && l32 - k32 >= (uint32_t)VOTE_VW) {
                             const uint32_t c = (uint32_t)(seed >> (2 * tt)) & 3u;
                             as_bs_step32t(ix, *reinterpret_cast<const uint4 *>(s_tab + c), k32, l32);
                             st_steps++;
@@ -255,7 +259,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                         kk = k32;
                         ll = l32;
                     } else {
-                        while (tt >= 0 && kk != ll) {
+                        while (tt >= 0 && ll - kk >= (uint64_t)VOTE_VW) {
                             const uint32_t c = (uint32_t)(seed >> (2 * tt)) & 3u;
                             as_bs_step64t(ix, *reinterpret_cast<const uint4 *>(s_tab + c), s_tabChi[c], c, kk, ll);
                             st_steps++;
@@ -264,31 +268,53 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                             if (kk > ll) { fail = true; break; }
                         }
                     }
-                    if (!fail && tt >= 0) {                                     /* one row left, tt+1 bases to go */
-                        const uint64_t p = as_sa(ix, kk);
+                    if (!fail && tt >= 0) {
+                        /* 1..VOTE_VW rows left, tt+1 bases to go: every row's tail is read off the text -- the SA gathers
+                         * of the rows are independent, so are the text gathers, where the FM walk is a chain */
                         const int nrem = tt + 1;
-                        if (p >= (uint64_t)nrem) {
-                            int steps;
-                            bool match;
-                            if (nrem <= 16) {
-                                const uint32_t x = ((uint32_t)seed ^ as_bases16(ix.text2, p - (uint64_t)nrem)) &
-                                                   (nrem == 16 ? 0xFFFFFFFFu : ((1u << (2 * nrem)) - 1u));
-                                match = x == 0;
-                                steps = match ? nrem : nrem - ((31 - __clz(x)) >> 1);
-                            } else {
-                                const uint64_t x = (seed ^ as_bases32(ix.text2, p - (uint64_t)nrem)) & ((1ULL << (2 * nrem)) - 1ULL);
-                                match = x == 0;
-                                steps = match ? nrem : nrem - ((63 - __clzll((long long)x)) >> 1);
+                        const uint32_t wdt = (uint32_t)(ll - kk) + 1u;
+                        uint64_t pr[VOTE_VW];
+                        bool in_text = true;
+#pragma unroll
+                        for (int r = 0; r < VOTE_VW; r++) {
+                            pr[r] = (uint32_t)r < wdt ? as_sa(ix, kk + (uint64_t)r) : ~0ULL;
+                            in_text &= pr[r] >= (uint64_t)nrem;
+                        }
+                        bool resolved = false;
+                        if (in_text) {
+                            int nsurv = 0, steps = 0;
+                            uint64_t pos1 = 0;
+#pragma unroll
+                            for (int r = 0; r < VOTE_VW; r++) {
+                                if ((uint32_t)r < wdt) {
+                                    int sr;
+                                    if (nrem <= 16) {
+                                        const uint32_t x = ((uint32_t)seed ^ as_bases16(ix.text2, pr[r] - (uint64_t)nrem)) &
+                                                           (nrem == 16 ? 0xFFFFFFFFu : ((1u << (2 * nrem)) - 1u));
+                                        sr = x == 0 ? nrem : nrem - ((31 - __clz(x)) >> 1);
+                                        if (x == 0) { nsurv++; pos1 = pr[r] - (uint64_t)nrem; }
+                                    } else {
+                                        const uint64_t x = (seed ^ as_bases32(ix.text2, pr[r] - (uint64_t)nrem)) & ((1ULL << (2 * nrem)) - 1ULL);
+                                        sr = x == 0 ? nrem : nrem - ((63 - __clzll((long long)x)) >> 1);
+                                        if (x == 0) { nsurv++; pos1 = pr[r] - (uint64_t)nrem; }
+                                    }
+                                    steps = max(steps, sr);      /* the reference's loop stops when the last row drops out */
+                                }
                             }
-                            st_steps += steps;
-                            st_txt++;
-                            if (match) {
-                                have_pos = true;
-                                hit_pos = p - (uint64_t)nrem;
-                            } else {
-                                fail = true;
+                            if (nsurv <= 1) {
+                                st_steps += steps;
+                                st_txt++;
+                                resolved = true;
+                                if (nsurv == 1) {
+                                    have_pos = true;
+                                    hit_pos = pos1;
+                                    ll = kk;                                    /* one row survives: rr = 1 */
+                                } else {
+                                    fail = true;
+                                }
                             }
-                        } else {                                                /* the text starts inside the seed: walk it */
+                        }
+                        if (!resolved) {       /* two or more rows survive, or the text starts inside the seed: walk it */
                             while (tt >= 0) {
                                 const uint32_t c = (uint32_t)(seed >> (2 * tt)) & 3u;
                                 as_bs_step64t(ix, *reinterpret_cast<const uint4 *>(s_tab + c), s_tabChi[c], c, kk, ll);
