@@ -37,6 +37,7 @@ struct DevIndex {
     int hlen;
     const unsigned long long *lc2;   /* deep table (as_lc2.cu): row | rows << 40 per hlen2-mer, LSB-first code; may be NULL */
     int hlen2;
+    const unsigned long long *sax;   /* SA[row] | 12 preceding text bases << 40 (as_lc2.cu); may be NULL */
     const uint32_t *sa_lo;      /* low 32 bits of SA[row] */
     const uint8_t *sa_hi;       /* bits 32..39, NULL when N <= 2^32 */
     const uint32_t *text2;      /* .cat text, 2 bits per base, 16 bases per word, LSB first */
@@ -55,7 +56,7 @@ struct as_gpu {
     cudaStream_t stream = nullptr;
     DevIndex ix{};
     /* owned device allocations of the index */
-    void *d_lc2 = nullptr;
+    void *d_lc2 = nullptr, *d_sax = nullptr;
     void *d_fm = nullptr, *d_super = nullptr, *d_lc = nullptr, *d_sa_lo = nullptr, *d_sa_hi = nullptr,
          *d_text2 = nullptr, *d_mta = nullptr;
     /* device scratch, grown on demand */

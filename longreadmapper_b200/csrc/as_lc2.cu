@@ -65,11 +65,44 @@ __global__ void __launch_bounds__(256) k_lc2_fill(DevIndex ix, int h, unsigned l
     }
 }
 
-int as_build_lc2(as_gpu *h) {
+/*
+ * sax[row] = SA[row] (40 bits) | the 12 text bases in front of that position (24 bits, base SA-12 lowest).  A one-row
+ * interval is finished by comparing the seed's remaining bases with the text in front of SA[row] (as_vote.cu); with the
+ * bases stored next to the SA value that is ONE gather instead of two (SA, then text) -- on the long-read and human-scale
+ * workloads PART 1 moves 5 TB/s of DRAM sectors, so a third fewer gathers is a third less time there.  8 bytes per row on
+ * top of the split SA (which stays: export and the sa_access primitive read it); skipped when memory is short.
+ */
+__global__ void __launch_bounds__(256) k_sax_fill(DevIndex ix, unsigned long long *__restrict__ sax) {
+    for (uint64_t r = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; r < ix.N; r += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t p = as_sa(ix, r);
+        uint32_t prev;
+        if (p >= 12) prev = as_bases16(ix.text2, p - 12) & 0xFFFFFFu;
+        else prev = (as_bases16(ix.text2, 0) << (2u * (12u - (uint32_t)p))) & 0xFFFFFFu;   /* bases [0,p) at the top */
+        sax[r] = p | ((unsigned long long)prev << 40);
+    }
+}
+
+static int build_sax(as_gpu *h) {
     DevIndex &ix = h->ix;
-    ix.lc2 = nullptr;
-    ix.hlen2 = 0;
-    if (!ix.text2 || !ix.sa_lo || ix.N < 2) return AS_OK;
+    ix.sax = nullptr;
+    if (const char *e = getenv("AS_NO_SAX")) {
+        if (atoi(e)) return AS_OK;
+    }
+    size_t free_b = 0, total_b = 0;
+    AS_CUDA(cudaMemGetInfo(&free_b, &total_b));
+    if (ix.N * 8ULL > free_b / 2) return AS_OK;                   /* leave room for the batches */
+    AS_CUDA(cudaMalloc(&h->d_sax, ix.N * sizeof(unsigned long long)));
+    uint64_t blocks = (ix.N + 255) / 256, cap = (uint64_t)h->sm_count * 16;
+    k_sax_fill<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(ix, (unsigned long long *)h->d_sax);
+    h->launches++;
+    AS_CUDA(cudaGetLastError());
+    AS_CUDA(cudaStreamSynchronize(h->stream));
+    ix.sax = (const unsigned long long *)h->d_sax;
+    return AS_OK;
+}
+
+static int build_lc2_table(as_gpu *h) {
+    DevIndex &ix = h->ix;
     int h2 = 1;
     while (h2 < 16 && (1ULL << (2 * h2)) < ix.N) h2++;           /* ceil(log4 N) */
     h2 += 1;
@@ -92,4 +125,15 @@ int as_build_lc2(as_gpu *h) {
     ix.lc2 = (const unsigned long long *)h->d_lc2;
     ix.hlen2 = h2;
     return AS_OK;
+}
+
+/* the derived tables of a device index: the deep k-mer table first (it buys more per byte), then SA+context */
+int as_build_lc2(as_gpu *h) {
+    DevIndex &ix = h->ix;
+    ix.lc2 = nullptr;
+    ix.hlen2 = 0;
+    ix.sax = nullptr;
+    if (!ix.text2 || !ix.sa_lo || ix.N < 2) return AS_OK;
+    AS_TRY(build_lc2_table(h));
+    return build_sax(h);
 }

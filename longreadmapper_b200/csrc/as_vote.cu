@@ -274,10 +274,21 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                         const int nrem = tt + 1;
                         const uint32_t wdt = (uint32_t)(ll - kk) + 1u;
                         uint64_t pr[VOTE_VW];
+                        uint32_t pv[VOTE_VW];                  /* with sax: the nrem bases in front of SA[r], no text gather */
+                        const bool ctx = ix.sax != nullptr && nrem <= 12;
                         bool in_text = true;
 #pragma unroll
                         for (int r = 0; r < VOTE_VW; r++) {
-                            pr[r] = (uint32_t)r < wdt ? as_sa(ix, kk + (uint64_t)r) : ~0ULL;
+                            pv[r] = 0;
+                            if ((uint32_t)r >= wdt) {
+                                pr[r] = ~0ULL;
+                            } else if (ctx) {
+                                const unsigned long long e = __ldg(ix.sax + kk + (uint64_t)r);
+                                pr[r] = e & 0xFFFFFFFFFFULL;
+                                pv[r] = (uint32_t)(e >> 40) >> (2 * (12 - nrem));
+                            } else {
+                                pr[r] = as_sa(ix, kk + (uint64_t)r);
+                            }
                             in_text &= pr[r] >= (uint64_t)nrem;
                         }
                         bool resolved = false;
@@ -289,8 +300,8 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                                 if ((uint32_t)r < wdt) {
                                     int sr;
                                     if (nrem <= 16) {
-                                        const uint32_t x = ((uint32_t)seed ^ as_bases16(ix.text2, pr[r] - (uint64_t)nrem)) &
-                                                           (nrem == 16 ? 0xFFFFFFFFu : ((1u << (2 * nrem)) - 1u));
+                                        const uint32_t tb = ctx ? pv[r] : as_bases16(ix.text2, pr[r] - (uint64_t)nrem);
+                                        const uint32_t x = ((uint32_t)seed ^ tb) & (nrem == 16 ? 0xFFFFFFFFu : ((1u << (2 * nrem)) - 1u));
                                         sr = x == 0 ? nrem : nrem - ((31 - __clz(x)) >> 1);
                                         if (x == 0) { nsurv++; pos1 = pr[r] - (uint64_t)nrem; }
                                     } else {
