@@ -280,6 +280,15 @@ static int plan_chunks(size_t n, size_t stride, size_t *begin /* AS_MAX_CHUNKS +
         begin[++nc] = r;
         if (c < big) c = (2 * c < big) ? 2 * c : big;
     }
+    /* ramp down as well: nothing overlaps the last chunk's D2H, so the last chunk is the smaller part of a split */
+    int tail = 1;
+    if (const char *e = getenv("AS_CHUNK_TAIL")) tail = atoi(e);
+    for (int t = 0; t < tail && nc < AS_MAX_CHUNKS; t++) {
+        const size_t b0 = begin[nc - 1], sz = begin[nc] - b0;
+        if (sz < 4 * min_reads) break;
+        begin[nc] = b0 + (sz * 2 / 3 + 31) / 32 * 32;
+        begin[++nc] = n;
+    }
     return nc;
 }
 

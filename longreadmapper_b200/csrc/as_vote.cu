@@ -19,10 +19,14 @@
 #ifndef VOTE_CLAIM
 #define VOTE_CLAIM 1
 #endif
-/* intervals of at most this many rows are finished against the text: 2 where the index sits in L2 for good part and the
- * kernel waits on latency (the rows' gathers overlap); 1 at human scale, where every gather is a DRAM sector and the
- * kernel is bound by their number (measured: c2 2.54 -> 2.39 ms with 2, c4 39 -> 44 ms) */
-#define VOTE_VW (SMALL ? 2 : 1)
+/* intervals of at most this many rows are finished against the text.  With the sax table the rows' SA values and
+ * contexts are neighbours in one or two sectors, so two rows cost what one does and save the FM steps that would
+ * have split them (c4: 369M -> 153M steps, PART 1 35.9 -> 33.5 ms; 3 and 4 rows bring nothing more).  Without the
+ * table a second row is two more gathers: worth it when the index sits in L2 for good part (one super block),
+ * not at human scale (measured 39 -> 44 ms), see vw below */
+#ifndef VOTE_VW
+#define VOTE_VW 2
+#endif
 #ifndef VOTE_MIN_BLOCKS
 #define VOTE_MIN_BLOCKS 6
 #endif
@@ -246,9 +250,10 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                      * further SA access.  st_steps still counts the steps the reference's loop executes (up to and
                      * including the failing one); st_fm counts the FM steps actually done here. */
                     bool fail = false;
+                    const uint32_t vw = (SMALL || ix.sax != nullptr) ? (uint32_t)VOTE_VW : 1u;
                     if (SMALL) {
                         uint32_t k32 = (uint32_t)kk, l32 = (uint32_t)ll;
-                        while (tt >= 0 && l32 - k32 >= (uint32_t)VOTE_VW) {
+                        while (tt >= 0 && l32 - k32 >= vw) {
                             const uint32_t c = (uint32_t)(seed >> (2 * tt)) & 3u;
                             as_bs_step32t(ix, *reinterpret_cast<const uint4 *>(s_tab + c), k32, l32);
                             st_steps++;
@@ -259,7 +264,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                         kk = k32;
                         ll = l32;
                     } else {
-                        while (tt >= 0 && ll - kk >= (uint64_t)VOTE_VW) {
+                        while (tt >= 0 && ll - kk >= (uint64_t)vw) {
                             const uint32_t c = (uint32_t)(seed >> (2 * tt)) & 3u;
                             as_bs_step64t(ix, *reinterpret_cast<const uint4 *>(s_tab + c), s_tabChi[c], c, kk, ll);
                             st_steps++;

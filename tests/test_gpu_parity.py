@@ -161,6 +161,35 @@ def test_vote_deep_table(native, idx_repeat, monkeypatch, h2, wide):
         m.close()
 
 
+@pytest.mark.parametrize("wide", [0, 16])
+@pytest.mark.parametrize("no_sax", ["0", "1"])
+def test_vote_sa_context_table(native, idx_repeat, monkeypatch, no_sax, wide):
+    """sax (SA value + the 12 bases in front of it, as_lc2.cu) against the plain SA + text gathers: same votes, also for
+    hits within 12 bases of the text start (context shorter than the entry), seeds whose tail is longer than the entry
+    holds (seed_len - h2 > 12: the text gather stays) and exact repeats (two-row intervals)."""
+    ix, gs = idx_repeat
+    monkeypatch.setenv("AS_LC2_HLEN", "13")
+    monkeypatch.setenv("AS_NO_SAX", no_sax)
+    m = native.GpuMapper.from_oracle_index(ix, 0)
+    monkeypatch.delenv("AS_LC2_HLEN")
+    monkeypatch.delenv("AS_NO_SAX")
+    try:
+        a = gs[0]
+        L = 120
+        starts = list(range(0, 40)) + [len(a) - L - k for k in range(0, 20)]
+        reads = np.zeros((len(starts), L + 1), dtype=np.uint8)
+        for i, p0 in enumerate(starts):
+            reads[i, :L] = a[p0:p0 + L]
+        lens = np.full(len(starts), L, dtype=np.uint32)
+        for sl, th in [(20, 300), (14, 300), (24, 300), (28, 50), (32, 1000)]:
+            check_vote(m, ix, reads, lens, sl, th, flags=wide)
+        for k, (lmin, lmax, e, sl, th) in enumerate([(100, 250, 0.05, 20, 300), (80, 200, 0.03, 32, 1000), (60, 260, 0.05, 27, 2)]):
+            r2, l2, _ = reads_from(native, 970 + k, gs, 300, lmin, lmax, e, e, 0.7)
+            check_vote(m, ix, r2, l2, sl, th, flags=wide)
+    finally:
+        m.close()
+
+
 def test_map_deep_table_built_index(native, idx_repeat, monkeypatch):
     """the same through as_gpu_build and the whole path"""
     ix, gs = idx_repeat
