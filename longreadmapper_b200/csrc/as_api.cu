@@ -331,6 +331,7 @@ extern "C" int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t s
         AS_TRY(as_scratch(h, &h->qpack, n * ws * sizeof(uint32_t)));
         AS_TRY(as_scratch(h, &h->vote, n * sizeof(VoteOut)));
         AS_TRY(as_scratch(h, &h->toff, n * sizeof(uint64_t)));
+        if (!(p->flags & AS_F_NO_ALIGN) && max_len > (uint32_t)p->gact_T) AS_TRY(as_gact_order_reserve(h, n));
     }
     h->last_h2d_bytes = n * stride + n * sizeof(uint32_t);
     const bool copy_reads_back = !(p->flags & AS_F_KEEP_READS);

@@ -62,6 +62,7 @@ struct as_gpu {
     /* device scratch, grown on demand */
     ScratchBuf reads, lens, results, store, qpack, tpack, toff, vote, counters, ovf_list, ovf_table, misc[6];
     ScratchBuf gact_planes, gact_tb;     /* bit-parallel GACT: traceback planes / packed tile ops, per resident warp */
+    ScratchBuf gact_order;               /* bit-parallel GACT: reads by decreasing length (multi-tile batches) */
     /* pinned staging for small D2H/H2D */
     void *h_pin = nullptr;
     size_t h_pin_cap = 0;
@@ -143,6 +144,7 @@ struct GactArgs {
     unsigned long long *stats;
     /* bit-parallel kernel with a banded first attempt per tile (as_gact_bp.cu) */
     int band;                    /* < 0: full matrix only; 0: adaptive; > 0: fixed half-width (rounded up to a level) */
+    const uint32_t *order;       /* slot -> read, longest first (NULL: identity); lanes of a warp then finish together */
     unsigned int *fail_count;    /* policy counters of the launch: warp-tiles refilled, warp-tiles, lane-tiles served by
                                   * half the band, lane-tiles */
 };
@@ -150,6 +152,7 @@ struct GactArgs {
 
 /* bit-parallel GACT (as_gact_bp.cu): one read per lane; `a` is filled by as_launch_gact */
 int as_launch_gact_bp(as_gpu *h, GactArgs &a, size_t n, uint32_t max_qlen, uint32_t max_tlen);
+int as_gact_order_reserve(as_gpu *h, size_t n);
 int as_launch_myers(as_gpu *h, const uint32_t *d_qpack, size_t q_wstride, const uint32_t *d_qlens,
                     const uint32_t *d_tbase, const uint64_t *d_toff, const uint32_t *d_tlens, size_t n,
                     uint32_t max_qlen, const int32_t *d_ks, int32_t *d_dist, as_result *d_res);

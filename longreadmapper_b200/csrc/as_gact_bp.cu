@@ -34,6 +34,7 @@
  */
 #include "as_common.cuh"
 #include <stdlib.h>
+#include <cub/cub.cuh>
 
 #define BP_THREADS 128
 #define BP_WIN 16                     /* columns of traceback planes staged in shared memory per refill */
@@ -299,8 +300,9 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
         if (lane == 0) base = atomicAdd(a.work_counter, 32u);
         base = __shfl_sync(0xFFFFFFFFu, base, 0);
         if (base >= a.n) break;
-        const size_t read = (size_t)base + lane;
-        bool done = read >= a.n;
+        const size_t slot = (size_t)base + lane;
+        bool done = slot >= a.n;
+        const size_t read = done ? 0 : (a.order ? (size_t)a.order[slot] : slot);
         int qlen = 0, tlen = 0;
         g.toff = 0;
         if (!done) {
@@ -501,9 +503,54 @@ static int launch_bp_w(as_gpu *h, GactArgs &a, size_t n, int bps, unsigned int k
     return launch_bp<W, W>(h, a, n, bps, 256);
 }
 
+/*
+ * Reads of several tiles: a warp walks its 32 reads tile by tile until the longest is through, so lanes with short
+ * reads idle (1-50 kbp reads: the mean is half the maximum).  Handing out the reads by decreasing work (query + target
+ * bases; unmapped reads last) gives a warp 32 reads of nearly one length and puts the longest at the front of the
+ * work queue.  One radix sort of n (key, index) pairs per launch; results do not depend on the order.
+ */
+__global__ void __launch_bounds__(256) k_gact_order_keys(GactArgs a, uint32_t maxw, uint32_t *__restrict__ keys,
+                                                         uint32_t *__restrict__ idx) {
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= a.n) return;
+    const uint32_t q = a.qlens[i], t = a.tlens ? a.tlens[i] : q;
+    const bool skip = a.toff && a.toff[i] == AS_TOFF_NONE;
+    const uint32_t w = q + t < maxw ? q + t : maxw;
+    keys[i] = skip ? maxw + 1u : maxw - w;
+    idx[i] = (uint32_t)i;
+}
+
+static int gact_order(as_gpu *h, GactArgs &a, size_t n, uint32_t max_qlen, uint32_t max_tlen) {
+    const uint32_t maxw = max_qlen + max_tlen;
+    int bits = 1;
+    while (bits < 32 && ((maxw + 1u) >> bits)) bits++;
+    size_t temp = 0;
+    const size_t n4 = (n + 63) & ~(size_t)63;
+    AS_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, temp, (const uint32_t *)nullptr, (uint32_t *)nullptr,
+                                            (const uint32_t *)nullptr, (uint32_t *)nullptr, (int)n, 0, bits, h->stream));
+    AS_TRY(as_scratch(h, &h->gact_order, 4 * n4 * sizeof(uint32_t) + temp + 256));
+    uint32_t *k0 = (uint32_t *)h->gact_order.p, *i0 = k0 + n4, *k1 = i0 + n4, *i1 = k1 + n4;
+    k_gact_order_keys<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(a, maxw, k0, i0);
+    AS_CUDA(cudaGetLastError());
+    AS_CUDA(cub::DeviceRadixSort::SortPairs((void *)(i1 + n4), temp, (const uint32_t *)k0, k1, (const uint32_t *)i0, i1, (int)n, 0,
+                                            bits, h->stream));
+    h->launches += 4;
+    a.order = i1;
+    return AS_OK;
+}
+
+/* as_map_batch sizes the order buffer for the whole batch before it enqueues chunks (growing a scratch buffer waits) */
+int as_gact_order_reserve(as_gpu *h, size_t n) {
+    return as_scratch(h, &h->gact_order, 4 * ((n + 63) & ~(size_t)63) * sizeof(uint32_t) + (n * 16 + (1u << 20)));
+}
+
 int as_launch_gact_bp(as_gpu *h, GactArgs &a, size_t n, uint32_t max_qlen, uint32_t max_tlen) {
-    (void)max_tlen;
-    if (n >= 0xFFFFFFE0ull) return AS_ERANGE;
+    if (n >= 0x7FFFFFE0ull) return AS_ERANGE;
+    {
+        bool order = max_qlen > (uint32_t)a.T || max_tlen > (uint32_t)a.T;
+        if (const char *e = getenv("AS_GACT_ORDER")) order = atoi(e) != 0;
+        if (order) AS_TRY(gact_order(h, a, n, max_qlen, max_tlen));
+    }
     const int rows = (int)(max_qlen < (uint32_t)a.T ? max_qlen : (uint32_t)a.T);
     const int words = rows > 0 ? (rows + 31) / 32 : 1;
     int bps = 0;

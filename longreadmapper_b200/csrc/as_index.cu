@@ -162,7 +162,7 @@ extern "C" void as_gpu_close(as_gpu *h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     free_index(h);
     ScratchBuf *bufs[] = {&h->reads, &h->lens, &h->results, &h->store, &h->qpack, &h->tpack, &h->toff,
-                          &h->vote, &h->counters, &h->ovf_list, &h->ovf_table, &h->gact_planes, &h->gact_tb};
+                          &h->vote, &h->counters, &h->ovf_list, &h->ovf_table, &h->gact_planes, &h->gact_tb, &h->gact_order};
     for (ScratchBuf *b : bufs) free_scratch(b);
     for (ScratchBuf &b : h->misc) free_scratch(&b);
     if (h->h_pin) cudaFreeHost(h->h_pin);
