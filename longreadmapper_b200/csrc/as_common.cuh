@@ -82,6 +82,7 @@ struct as_gpu {
     int *h_chunk_max = nullptr;            /* pinned mirror */
     unsigned int *h_band = nullptr, *d_band = nullptr;   /* adaptive GACT band: mapped pinned word + its device alias */
     int sm_count = 148;
+    size_t l2_bytes = 126u << 20;
     uint64_t launches = 0;      /* kernels launched by this handle since open */
 };
 

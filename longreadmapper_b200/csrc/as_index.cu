@@ -341,6 +341,7 @@ as_gpu *as_handle_new(int device) {
     if (!h) return nullptr;
     h->device = device;
     h->sm_count = prop.multiProcessorCount;
+    h->l2_bytes = prop.l2CacheSize > 0 ? (size_t)prop.l2CacheSize : h->l2_bytes;
     cudaError_t e = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) {
         as_set_error("cudaStreamCreate: %s", cudaGetErrorString(e));

@@ -11,14 +11,21 @@
  * bases is what lc_access + (h2 - hlen) steps of fmi_aln (fmidx.c:295-313) would have reached, including the
  * reference's k = 1 start, which drops the occurrence that ends on the text's last base (see k_lc_codes, as_build.cu).
  *
- * Entry: bits 0..39 = first row k, bits 40..63 = rows in the interval, 0xFFFFFF = "2^24-1 or more" (PART 1 then takes
- * the 12-mer table and walks); 0 = absent.  Built from the device index alone (SA + 2-bit text), so handles opened
- * from the reference's files get it too.
+ * Entry: bits 0..39 = first row k, bits 40..63 = info, 0 = absent.  info >> 22 is a tag:
+ *   0: info = rows in the interval, 0x3FFFFF = "2^22-1 or more" (PART 1 then takes the 12-mer table and walks);
+ *   1: ONE row, and info & 0x3FFFFF = the 11 text bases in front of SA[k] (base SA-11 lowest);
+ *   2: TWO rows, bits 0..9 / 10..19 = the 5 text bases in front of SA[k] / SA[k+1].
+ * Tags 1 and 2 let PART 1 decide the rest of the walk from the entry itself (a row survives iff the seed's remaining
+ * bases equal the text in front of it): a seed that dies there -- most seeds of a noisy long read, whose h2-mer
+ * exists in a human-size genome by chance -- costs ONE gather; only survivors fetch their position.  Rows closer to the
+ * text start than the context is long keep tag 0.  Built from the device index alone (SA + 2-bit text), so handles
+ * opened from the reference's files get it too.
  */
 #include "as_common.cuh"
 #include <stdlib.h>
 
 #define LC2_NONE 0xFFFFFFFFFFFFFFFFULL
+#define LC2_SAT 0x3FFFFFULL
 
 /* LSB-first code of the h-mer starting suffix SA[r], or LC2_NONE (row 0, or the h-mer would touch the last base / '$') */
 __device__ __forceinline__ uint64_t lc2_code(const DevIndex &ix, int h, uint64_t r) {
@@ -55,7 +62,16 @@ __global__ void __launch_bounds__(256) k_lc2_fill(DevIndex ix, int h, unsigned l
                         k = lo;
                     }
                     const uint64_t cnt = r - k + 1;
-                    lc2[cur] = k | ((cnt >= 0xFFFFFFULL ? 0xFFFFFFULL : cnt) << 40);
+                    uint64_t info = cnt >= LC2_SAT ? LC2_SAT : cnt;
+                    if (cnt == 1) {
+                        const uint64_t p = as_sa(ix, k);
+                        if (p >= 11) info = (1ULL << 22) | (as_bases16(ix.text2, p - 11) & 0x3FFFFFu);
+                    } else if (cnt == 2) {
+                        const uint64_t p0 = as_sa(ix, k), p1 = as_sa(ix, k + 1);
+                        if (p0 >= 5 && p1 >= 5)
+                            info = (2ULL << 22) | (as_bases16(ix.text2, p0 - 5) & 0x3FFu) | ((uint64_t)(as_bases16(ix.text2, p1 - 5) & 0x3FFu) << 10);
+                    }
+                    lc2[cur] = k | (info << 40);
                 }
                 start = r + 1;
                 open_left = false;

@@ -60,6 +60,7 @@ struct VoteArgs {
     uint32_t big_cap;
     unsigned long long *stats;   /* as_stats layout */
     int use2;                    /* seeds start from the deep table (DevIndex.lc2) instead of the 12-mer table */
+    int use_ectx;                /* decide one- and two-row entries from the context bases they carry (as_lc2.cu) */
 };
 
 __device__ __forceinline__ uint32_t hash_bucket(uint64_t b, uint32_t shift) {
@@ -217,15 +218,19 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
             if (m < m_count) {
                 const uint64_t seed = as_bases32(pr, j);
                 bool absent = false;
+                uint32_t etag = 0, ectx = 0;
                 int tt = left0 - 1;                                             /* next seed base to walk */
                 if (a.use2) {
                     /* deep table: the interval lc_access + (hlen2 - hlen) steps of fmi_aln would have reached */
                     const unsigned long long e = __ldg(ix.lc2 + ((seed >> (2 * left0)) & hmask));
-                    const uint32_t cnt = (uint32_t)(e >> 40);
+                    const uint32_t info = (uint32_t)(e >> 40);
+                    etag = info >> 22;                                          /* as_lc2.cu: 0 count, 1 / 2 rows + context */
+                    ectx = info & 0x3FFFFFu;
+                    const uint32_t cnt = etag ? etag : ectx;
                     kk = e & 0xFFFFFFFFFFULL;
                     ll = kk + cnt - 1;
                     absent = e == 0;
-                    if (cnt == 0xFFFFFFu) {                                     /* too many rows for the entry: 12-mer table */
+                    if (info == 0x3FFFFFu) {                                     /* too many rows for the entry: 12-mer table */
                         tt = sl - ix.hlen - 1;
                         const ulonglong2 kl = __ldg(ix.lc + ((seed >> (2 * (tt + 1))) & ((1ULL << (2 * ix.hlen)) - 1ULL)));
                         kk = kl.x;
@@ -250,7 +255,9 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                      * further SA access.  st_steps still counts the steps the reference's loop executes (up to and
                      * including the failing one); st_fm counts the FM steps actually done here. */
                     bool fail = false;
-                    const uint32_t vw = (SMALL || ix.sax != nullptr) ? (uint32_t)VOTE_VW : 1u;
+                    /* entry with context that covers the rest of the seed: no FM step is taken (the interval has <= 2 rows) */
+                    const bool e_ok = a.use_ectx && etag != 0 && tt >= 0 && tt < (etag == 1 ? 11 : 5);
+                    const uint32_t vw = (SMALL || ix.sax != nullptr || e_ok) ? (uint32_t)VOTE_VW : 1u;
                     if (SMALL) {
                         uint32_t k32 = (uint32_t)kk, l32 = (uint32_t)ll;
                         while (tt >= 0 && l32 - k32 >= vw) {
@@ -280,13 +287,19 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                         const uint32_t wdt = (uint32_t)(ll - kk) + 1u;
                         uint64_t pr[VOTE_VW];
                         uint32_t pv[VOTE_VW];                  /* with sax: the nrem bases in front of SA[r], no text gather */
-                        const bool ctx = ix.sax != nullptr && nrem <= 12;
+                        /* the table entry itself carries the context of its one or two rows (as_lc2.cu, tags 1 and 2):
+                         * nothing is fetched to decide, and only a surviving row's position is */
+                        const bool from_e = e_ok;
+                        const bool ctx = from_e || (ix.sax != nullptr && nrem <= 12);
                         bool in_text = true;
 #pragma unroll
                         for (int r = 0; r < VOTE_VW; r++) {
                             pv[r] = 0;
                             if ((uint32_t)r >= wdt) {
                                 pr[r] = ~0ULL;
+                            } else if (from_e) {
+                                pr[r] = 1ULL << 62;                             /* not known yet; the builder checked SA >= context */
+                                pv[r] = (etag == 1 ? ectx : ((ectx >> (10 * r)) & 0x3FFu)) >> (2 * ((etag == 1 ? 11 : 5) - nrem));
                             } else if (ctx) {
                                 const unsigned long long e = __ldg(ix.sax + kk + (uint64_t)r);
                                 pr[r] = e & 0xFFFFFFFFFFULL;
@@ -300,6 +313,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                         if (in_text) {
                             int nsurv = 0, steps = 0;
                             uint64_t pos1 = 0;
+                            uint32_t rsurv = 0;
 #pragma unroll
                             for (int r = 0; r < VOTE_VW; r++) {
                                 if ((uint32_t)r < wdt) {
@@ -308,11 +322,11 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                                         const uint32_t tb = ctx ? pv[r] : as_bases16(ix.text2, pr[r] - (uint64_t)nrem);
                                         const uint32_t x = ((uint32_t)seed ^ tb) & (nrem == 16 ? 0xFFFFFFFFu : ((1u << (2 * nrem)) - 1u));
                                         sr = x == 0 ? nrem : nrem - ((31 - __clz(x)) >> 1);
-                                        if (x == 0) { nsurv++; pos1 = pr[r] - (uint64_t)nrem; }
+                                        if (x == 0) { nsurv++; pos1 = pr[r] - (uint64_t)nrem; rsurv = (uint32_t)r; }
                                     } else {
                                         const uint64_t x = (seed ^ as_bases32(ix.text2, pr[r] - (uint64_t)nrem)) & ((1ULL << (2 * nrem)) - 1ULL);
                                         sr = x == 0 ? nrem : nrem - ((63 - __clzll((long long)x)) >> 1);
-                                        if (x == 0) { nsurv++; pos1 = pr[r] - (uint64_t)nrem; }
+                                        if (x == 0) { nsurv++; pos1 = pr[r] - (uint64_t)nrem; rsurv = (uint32_t)r; }
                                     }
                                     steps = max(steps, sr);      /* the reference's loop stops when the last row drops out */
                                 }
@@ -322,6 +336,10 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                                 st_txt++;
                                 resolved = true;
                                 if (nsurv == 1) {
+                                    if (from_e) {
+                                        const uint64_t row = kk + rsurv;
+                                        pos1 = (ix.sax ? (__ldg(ix.sax + row) & 0xFFFFFFFFFFULL) : as_sa(ix, row)) - (uint64_t)nrem;
+                                    }
                                     have_pos = true;
                                     hit_pos = pos1;
                                     ll = kk;                                    /* one row survives: rr = 1 */
@@ -644,6 +662,11 @@ int as_launch_vote(as_gpu *h, const as_params *p, const uint32_t *d_pack, size_t
     a.big_cap = big_cap;
     a.stats = h->d_stats;
     a.use2 = (h->ix.lc2 && sl >= h->ix.hlen2 && !(p->flags & AS_F_NO_LC2)) ? 1 : 0;
+    /* Deciding a seed from its table entry saves the SA/context gather of every seed that dies there, at the price of
+     * fetching a survivor's position after the compare instead of along with the context.  It pays when that gather is
+     * a DRAM sector (c3: PART 1 7.4 -> 6.5 ms, c4: 33.2 -> 31.7), not when the SA table sits in L2 (c2: 2.35 -> 2.55) */
+    a.use_ectx = h->ix.N * 8ULL > 2ULL * (unsigned long long)h->l2_bytes ? 1 : 0;
+    if (const char *e = getenv("AS_VOTE_ECTX")) a.use_ectx = atoi(e) != 0;
 
     /* lanes per read from the seeds of one phase of the longest read */
     int G = seeds_per_phase <= 8 ? 8 : seeds_per_phase <= 16 ? 16 : 32;

@@ -148,6 +148,7 @@ def test_vote_deep_table(native, idx_repeat, monkeypatch, h2, wide):
     monkeypatch.setenv("AS_LC2_HLEN", str(h2))
     m = native.GpuMapper.from_oracle_index(ix, 0)
     monkeypatch.delenv("AS_LC2_HLEN")
+    monkeypatch.setenv("AS_VOTE_ECTX", "1")      # entries decide from their context bases (default only for large indexes)
     try:
         for k, (lmin, lmax, e, sl, th) in enumerate([(100, 100, 0.0, 20, 300), (150, 150, 0.02, 20, 300), (100, 250, 0.08, 20, 300),
                                                     (60, 260, 0.05, h2, 50), (60, 260, 0.05, 24, 2), (80, 200, 0.03, 32, 1000),
@@ -162,17 +163,21 @@ def test_vote_deep_table(native, idx_repeat, monkeypatch, h2, wide):
 
 
 @pytest.mark.parametrize("wide", [0, 16])
+@pytest.mark.parametrize("ectx", ["0", "1"])
 @pytest.mark.parametrize("no_sax", ["0", "1"])
-def test_vote_sa_context_table(native, idx_repeat, monkeypatch, no_sax, wide):
+def test_vote_sa_context_table(native, idx_repeat, monkeypatch, no_sax, wide, ectx):
     """sax (SA value + the 12 bases in front of it, as_lc2.cu) against the plain SA + text gathers: same votes, also for
     hits within 12 bases of the text start (context shorter than the entry), seeds whose tail is longer than the entry
-    holds (seed_len - h2 > 12: the text gather stays) and exact repeats (two-row intervals)."""
+    holds (seed_len - h2 > 12: the text gather stays) and exact repeats (two-row intervals).  AS_VOTE_ECTX=1 forces the
+    path that decides one- and two-row deep-table entries from the context bases they carry (on by itself only for
+    indexes larger than L2)."""
     ix, gs = idx_repeat
     monkeypatch.setenv("AS_LC2_HLEN", "13")
     monkeypatch.setenv("AS_NO_SAX", no_sax)
     m = native.GpuMapper.from_oracle_index(ix, 0)
     monkeypatch.delenv("AS_LC2_HLEN")
     monkeypatch.delenv("AS_NO_SAX")
+    monkeypatch.setenv("AS_VOTE_ECTX", ectx)
     try:
         a = gs[0]
         L = 120
@@ -196,6 +201,7 @@ def test_map_deep_table_built_index(native, idx_repeat, monkeypatch):
     monkeypatch.setenv("AS_LC2_HLEN", "15")
     m = native.GpuMapper.build(gs, 0)
     monkeypatch.delenv("AS_LC2_HLEN")
+    monkeypatch.setenv("AS_VOTE_ECTX", "1")
     try:
         reads, lens, stride = reads_from(native, 960, gs, 1200, 100, 250, 0.0, 0.08, 0.6)
         compare_map(native, m, ix, reads, lens, stride)
