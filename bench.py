@@ -274,6 +274,10 @@ def run_b200(args):
     if lm.device_count() < 1 or not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the hot path has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
+    numa = None
+    if world > 1 and not os.environ.get("AS_NO_NUMA_BIND"):
+        from longreadmapper_b200.shard import bind_to_gpu_numa
+        numa = bind_to_gpu_numa(local)      # before any pinned buffer exists: first touch puts them on the GPU's node
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     wl = WORKLOADS[args.workload]
@@ -482,7 +486,8 @@ def run_b200(args):
                        "thres": 300, "gact_T": int(params.gact_T), "gact_O": int(params.gact_O),
                        "l2": f"inputs exceed L2: reads {n * stride / 1e6:.0f} MB + lc table 268 MB + SA {4 * (2 * wl['genome'] + 1) / 1e6:.0f} MB "
                              f"+ GACT planes per pass > 126 MB, no flush needed",
-                       "index": "built on the GPU (as_gpu_build), replicated per rank", "index_build_s": round(t_index, 2)},
+                       "index": "built on the GPU (as_gpu_build), replicated per rank", "index_build_s": round(t_index, 2),
+                       "host_numa_node_rank0": numa},
             "clocks": clocks, "e2e": e2e, "e2e_full_copy": e2e_full, "gpu_launches": int(launches),
             "roofline": roofline,
             "gcups": stages["gact"]["gcups"],

@@ -57,3 +57,41 @@ def gather_in_rank_order(local, dst=0, group=None):
     if rank != dst:
         return None
     return np.concatenate(parts) if isinstance(local, np.ndarray) else b"".join(parts)
+
+
+def bind_to_gpu_numa(device_index):
+    """Pin this process (and so the pinned host buffers it allocates afterwards) to the NUMA node of its GPU.
+
+    One process per GPU streams its read shard over that GPU's PCIe link; with eight processes the copies of
+    the GPUs on the other socket otherwise cross the inter-socket link both ways.  Returns the node, or None when
+    the box does not say (one node, no sysfs entry) -- then nothing is changed."""
+    import os
+    try:
+        import torch
+        p = torch.cuda.get_device_properties(device_index)
+        bdf = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        with open("/sys/bus/pci/devices/%s/numa_node" % bdf) as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return None
+        with open("/sys/devices/system/node/node%d/cpulist" % node) as f:
+            cpus = parse_cpulist(f.read())
+        allowed = os.sched_getaffinity(0)
+        cpus = cpus & allowed if cpus & allowed else cpus
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return node
+    except (OSError, ValueError, AttributeError, RuntimeError):
+        return None
+
+
+def parse_cpulist(text):
+    """'0-3,8,10-11' -> {0,1,2,3,8,10,11} (the kernel's cpulist format)."""
+    out = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        out.update(range(int(lo), int(hi or lo) + 1))
+    return out

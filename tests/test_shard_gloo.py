@@ -77,3 +77,10 @@ def test_two_rank_sharding_equals_single_process(native, orc, tmp_path):
     assert int(got["st_dp_cells"]) == cells and int(got["st_n_flag16"]) == int((res["flag"] == 16).sum())
     assert float(got["tmax"]) == 11.0
     ix.close()
+
+
+def test_parse_cpulist():
+    from longreadmapper_b200.shard import parse_cpulist
+    assert parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert parse_cpulist("5") == {5}
+    assert parse_cpulist("") == set()
