@@ -292,27 +292,66 @@ static int plan_chunks(size_t n, size_t stride, size_t *begin /* AS_MAX_CHUNKS +
     return nc;
 }
 
+static int map_batch_impl(as_gpu *h, const as_params *p, char *reads, size_t stride, const uint32_t *lens, size_t n,
+                          as_result *results, uint8_t *store_mem, size_t store_stride);
+
 extern "C" int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t stride, const uint32_t *lens, size_t n,
                             as_result *results, uint8_t *store_mem, size_t store_stride) {
     AS_TRY(check_map_args(h, p, reads, stride, lens, results));
     if (n == 0) return AS_OK;
     AS_CUDA(cudaSetDevice(h->device));
     AS_TRY(ensure_pipeline(h));
-    uint32_t max_len = 0;
-    for (size_t i = 0; i < n; i++) {
-        if (lens[i] > max_len) max_len = lens[i];
+    const int rc = map_batch_impl(h, p, reads, stride, lens, n, results, store_mem, store_stride);
+    if (rc != AS_OK) {           /* copies may be in flight on the caller's buffers: let them end before the caller sees the error */
+        cudaStreamSynchronize(h->s_h2d);
+        cudaStreamSynchronize(h->stream);
+        cudaStreamSynchronize(h->s_d2h);
+        cudaGetLastError();
     }
-    if ((size_t)max_len + 1 > stride) {
-        as_set_error("as_map_batch: a read of %u bases does not fit stride %zu", max_len, stride);
-        return AS_EINVAL;
-    }
-    const bool want_ops = store_mem != nullptr && !(p->flags & AS_F_NO_ALIGN);
-    if (want_ops && store_stride < 2 * (size_t)max_len) {
-        as_set_error("as_map_batch: store_stride %zu < 2*max_read_len (alnmain.c:316-320)", store_stride);
-        return AS_EINVAL;
-    }
+    return rc;
+}
+
+static int map_batch_impl(as_gpu *h, const as_params *p, char *reads, size_t stride, const uint32_t *lens, size_t n,
+                          as_result *results, uint8_t *store_mem, size_t store_stride) {
     AS_TRY(as_scratch(h, &h->reads, n * stride));
     AS_TRY(as_scratch(h, &h->lens, n * sizeof(uint32_t)));
+    size_t cb[AS_MAX_CHUNKS + 1];
+    const int nc = plan_chunks(n, stride, cb, (p->flags & AS_F_KEEP_READS) && (p->flags & AS_F_RLE_CIGAR));
+    h->n_chunks_last = nc;
+    AS_CUDA(cudaEventRecord(h->ev[0], h->stream));
+    AS_CUDA(cudaStreamWaitEvent(h->s_h2d, h->ev[0], 0));
+    AS_CUDA(cudaStreamWaitEvent(h->s_d2h, h->ev[0], 0));
+    /* every H2D copy is queued up front: they stream in order while the kernels of earlier chunks run -- and while the
+     * host looks at the lengths below */
+    for (int c = 0; c < nc; c++) {
+        const size_t r0 = cb[c], cn = cb[c + 1] - cb[c];
+        AS_CUDA(cudaMemcpyAsync((char *)h->reads.p + r0 * stride, reads + r0 * stride, cn * stride, cudaMemcpyHostToDevice, h->s_h2d));
+        AS_CUDA(cudaMemcpyAsync((uint32_t *)h->lens.p + r0, lens + r0, cn * sizeof(uint32_t), cudaMemcpyHostToDevice, h->s_h2d));
+        AS_CUDA(cudaEventRecord(h->cev[c][5], h->s_h2d));
+    }
+    uint32_t max_len = 0;
+    {
+        uint32_t m0 = 0, m1 = 0, m2 = 0, m3 = 0;
+        size_t i = 0;
+        for (; i + 4 <= n; i += 4) {
+            m0 = lens[i] > m0 ? lens[i] : m0;
+            m1 = lens[i + 1] > m1 ? lens[i + 1] : m1;
+            m2 = lens[i + 2] > m2 ? lens[i + 2] : m2;
+            m3 = lens[i + 3] > m3 ? lens[i + 3] : m3;
+        }
+        for (; i < n; i++) m0 = lens[i] > m0 ? lens[i] : m0;
+        m0 = m0 > m1 ? m0 : m1;
+        m2 = m2 > m3 ? m2 : m3;
+        max_len = m0 > m2 ? m0 : m2;
+    }
+    const bool want_ops = store_mem != nullptr && !(p->flags & AS_F_NO_ALIGN);
+    if ((size_t)max_len + 1 > stride || (want_ops && store_stride < 2 * (size_t)max_len)) {
+        if ((size_t)max_len + 1 > stride)
+            as_set_error("as_map_batch: a read of %u bases does not fit stride %zu", max_len, stride);
+        else
+            as_set_error("as_map_batch: store_stride %zu < 2*max_read_len (alnmain.c:316-320)", store_stride);
+        return AS_EINVAL;
+    }
     AS_TRY(as_scratch(h, &h->results, n * sizeof(as_result)));
     if (want_ops) AS_TRY(as_scratch(h, &h->store, n * store_stride));
     char *d_reads = (char *)h->reads.p;
@@ -320,9 +359,6 @@ extern "C" int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t s
     as_result *d_res = (as_result *)h->results.p;
     uint8_t *d_store = want_ops ? (uint8_t *)h->store.p : nullptr;
 
-    size_t cb[AS_MAX_CHUNKS + 1];
-    const int nc = plan_chunks(n, stride, cb, (p->flags & AS_F_KEEP_READS) && (p->flags & AS_F_RLE_CIGAR));
-    h->n_chunks_last = nc;
     /* per-read scratch of every chunk is carved out of one allocation made before anything is enqueued */
     {
         VoteOut *unused;
@@ -336,17 +372,7 @@ extern "C" int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t s
     h->last_h2d_bytes = n * stride + n * sizeof(uint32_t);
     const bool copy_reads_back = !(p->flags & AS_F_KEEP_READS);
     h->last_d2h_bytes = n * sizeof(as_result) + (copy_reads_back ? n * stride : 0) + (size_t)nc * sizeof(int);
-    AS_CUDA(cudaEventRecord(h->ev[0], h->stream));
-    AS_CUDA(cudaStreamWaitEvent(h->s_h2d, h->ev[0], 0));
-    AS_CUDA(cudaStreamWaitEvent(h->s_d2h, h->ev[0], 0));
     AS_CUDA(cudaMemsetAsync(h->d_chunk_max, 0, AS_MAX_CHUNKS * sizeof(int), h->stream));
-    /* every H2D copy is queued up front: they stream in order while the kernels of earlier chunks run */
-    for (int c = 0; c < nc; c++) {
-        const size_t r0 = cb[c], cn = cb[c + 1] - cb[c];
-        AS_CUDA(cudaMemcpyAsync(d_reads + r0 * stride, reads + r0 * stride, cn * stride, cudaMemcpyHostToDevice, h->s_h2d));
-        AS_CUDA(cudaMemcpyAsync(d_lens + r0, lens + r0, cn * sizeof(uint32_t), cudaMemcpyHostToDevice, h->s_h2d));
-        AS_CUDA(cudaEventRecord(h->cev[c][5], h->s_h2d));
-    }
     /* the CIGAR columns of chunk c are copied once the chunk's widest row is known: only that many columns of
      * every row cross PCIe (the reference leaves columns >= n_cigar_op uninitialised, alnmain.c:316-320) */
     auto finish_chunk = [&](int c) -> int {

@@ -126,6 +126,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
     const int grp = threadIdx.x / G;
 
     VoteTableT<USED_T> t;
+    if (BIG && *(volatile unsigned int *)a.ovf_count == 0) return;      /* nothing overflowed: do not even clear the table */
     if (BIG) {
         unsigned char *m = a.big_mem + (size_t)blockIdx.x * a.big_stride;
         t.cap = a.big_cap;
