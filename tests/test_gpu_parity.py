@@ -468,3 +468,78 @@ def test_myers_pairs(orc, gpu_uniform, lmax, emax):
     ks = np.maximum(0, exp + rng.integers(-5, 6, len(qs))).astype(np.int32)
     d = gpu_uniform.edit_distance_batch(qs, ts, ks)
     assert np.array_equal(d, np.where(exp > ks, -1, exp))
+
+
+# ---------------------------------------------------------------------------------------------------
+# BASELINE config 2 at its full size (4.6 Mbp genome, 1 M reads of 150 bp at 2 %): size-independent properties, plus the
+# oracle on a random sample of the same batch
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.gpu
+def test_c2_full_size_properties(native, orc):
+    g = native.sim_genome(11, 4_600_000)
+    n = 1_000_000
+    reads, lens, pos, strand = native.sim_reads(5, g, n, 150, 150, 0.02, 0.02, 0.8)     # bench.py's c2 mix
+    stride = reads.shape[1]
+    m = native.GpuMapper.build([g], 0)
+    try:
+        p = m.params(flags=native.AS_F_MYERS)
+        r_all = reads.copy()
+        res, ops = m.map_batch(r_all, lens, params=p)
+        ok = res["valid"] == 1
+        # (1) the simulated position and strand come back
+        assert ok.mean() > 0.99
+        near = np.abs(res["off"][ok].astype(np.int64) - pos[ok].astype(np.int64)) <= 50   # indels move the voted start
+        assert near.mean() > 0.999
+        assert ((res["strand"][ok] == 1) == (strand[ok] == 1)).mean() > 0.999
+        # (2) CIGAR consistency of every valid read: query-consuming ops (=, I, X) add up to the read, ED = non-'=' ops,
+        #     and one tile is exact NW (reads are shorter than T): ED equals the Myers distance
+        nops = res["n_cigar_op"].astype(np.int64)
+        live = np.arange(ops.shape[1])[None, :] < np.maximum(nops, 0)[:, None]
+        qcons = (((ops == 0) | (ops == 1) | (ops == 3)) & live).sum(axis=1)
+        nonmatch = ((ops != 0) & live).sum(axis=1)
+        assert np.array_equal(qcons[ok], lens[ok].astype(np.int64))
+        assert np.array_equal(nonmatch[ok], res["ed"][ok].astype(np.int64))
+        both = ok & (res["myers"] >= 0)
+        assert both.sum() > 0.8 * n and np.array_equal(res["ed"][both], res["myers"][both])
+        # (3) strand-1 reads were reverse-complemented in place, the others left alone (alnmain.c:433-438)
+        s1 = ok & (res["strand"] == 1)
+        assert np.array_equal(r_all[~s1], reads[~s1])
+        comp = np.zeros(256, np.uint8)
+        comp[list(b"ACGT")] = list(b"TGCA")
+        k = np.nonzero(s1)[0][:20000]
+        assert np.array_equal(r_all[k, :150], comp[reads[k, :150]][:, ::-1])
+        # (4) batch-split invariance: two unequal halves give the rows of the whole batch
+        cut = 400_003
+        for lo, hi in ((0, cut), (cut, n)):
+            r_part = reads[lo:hi].copy()
+            res_p, ops_p = m.map_batch(r_part, lens[lo:hi], params=p)
+            assert np.array_equal(res_p, res[lo:hi])
+            assert np.array_equal(ops_p * live[lo:hi], ops[lo:hi] * live[lo:hi])
+            assert np.array_equal(r_part, r_all[lo:hi])
+        # (5) compact output: same records, run lengths add up to the columns
+        r_c = reads.copy()
+        res_c, runs = m.map_batch(r_c, lens, params=m.params(flags=native.AS_F_MYERS | native.AS_F_RLE_CIGAR | native.AS_F_KEEP_READS))
+        assert np.array_equal(r_c, reads)
+        for f in res.dtype.names:
+            if f != "n_cigar_op":
+                assert np.array_equal(res_c[f], res[f]), f
+        nr = res_c["n_cigar_op"].astype(np.int64)
+        lr = np.arange(runs.shape[1])[None, :] < np.maximum(nr, 0)[:, None]
+        assert np.array_equal(((runs >> 2).astype(np.int64) * lr).sum(axis=1)[ok], nops[ok])
+        # (6) the oracle on a random sample of the batch: bit-identical records and CIGAR columns
+        ix = orc.OracleIndex.build(["chr1"], [g.tobytes()])
+        try:
+            pick = np.sort(np.random.default_rng(3).choice(n, 3000, replace=False))
+            r_cpu = reads[pick].copy()
+            exp, exp_ops, _ = ix.map_batch(r_cpu, stride, lens[pick], seed_len=20, thres=300, T=320, O=120, myers=True)
+            for f in FIELDS:
+                assert np.array_equal(exp[f], res[f][pick]), f
+            assert np.array_equal(exp["n_ops"], res["n_cigar_op"][pick])
+            for i, r in enumerate(pick):
+                k = int(exp["n_ops"][i])
+                assert np.array_equal(exp_ops[i, :k], ops[r, :k])
+            assert np.array_equal(r_cpu, r_all[pick])
+        finally:
+            ix.close()
+    finally:
+        m.close()
