@@ -543,3 +543,48 @@ def test_c2_full_size_properties(native, orc):
             ix.close()
     finally:
         m.close()
+
+
+def test_c3_scale_properties(native, monkeypatch):
+    """BASELINE config 3's genome size (100 Mbp: deep table of 4^15 entries, SA + context table larger than L2, so PART 1
+    decides one- and two-row entries from their context bases BY DEFAULT) with 10 kbp reads at 10 % error.  The oracle
+    cannot build this index in test time; the checks are the size-independent ones, and that every alternative PART 1
+    path (plain 12-mer table, no entry contexts, no SA + context table rows) returns the same records and CIGARs."""
+    g = native.sim_genome(11, 100_000_000)
+    n = 3000
+    reads, lens, pos, strand = native.sim_reads(9, g, n, 10_000, 10_000, 0.10, 0.10, 1 / 3)
+    m = native.GpuMapper.build([g], 0)
+    try:
+        p = m.params()
+        r0 = reads.copy()
+        res, ops = m.map_batch(r0, lens, params=p)
+        ok = res["valid"] == 1
+        assert ok.mean() > 0.99
+        near = np.abs(res["off"][ok].astype(np.int64) - pos[ok].astype(np.int64)) <= 200
+        assert near.mean() > 0.99
+        assert ((res["strand"][ok] == 1) == (strand[ok] == 1)).mean() > 0.99
+        nops = res["n_cigar_op"].astype(np.int64)
+        live = np.arange(ops.shape[1])[None, :] < np.maximum(nops, 0)[:, None]
+        qcons = (((ops == 0) | (ops == 1) | (ops == 3)) & live).sum(axis=1)
+        nonmatch = ((ops != 0) & live).sum(axis=1)
+        assert np.array_equal(qcons[ok], lens[ok].astype(np.int64))
+        assert np.array_equal(nonmatch[ok], res["ed"][ok].astype(np.int64))
+        # the other ways through PART 1 / GACT: same answers
+        for env, flags in ((("AS_VOTE_ECTX", "0"), 0), (None, native.AS_F_NO_LC2), (("AS_GACT_ORDER", "0"), 0)):
+            if env:
+                monkeypatch.setenv(*env)
+            r1 = reads.copy()
+            res1, ops1 = m.map_batch(r1, lens, params=m.params(flags=flags))
+            if env:
+                monkeypatch.delenv(env[0])
+            assert np.array_equal(res1, res), (env, flags)
+            assert np.array_equal(ops1 * live, ops * live), (env, flags)
+            assert np.array_equal(r1, r0)
+        # batch-split invariance
+        cut = 1234
+        res_a, ops_a = m.map_batch(reads[:cut].copy(), lens[:cut], params=p)
+        res_b, ops_b = m.map_batch(reads[cut:].copy(), lens[cut:], params=p)
+        assert np.array_equal(np.concatenate([res_a, res_b]), res)
+        assert np.array_equal(np.concatenate([ops_a, ops_b]) * live, ops * live)
+    finally:
+        m.close()
