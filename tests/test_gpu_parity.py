@@ -588,3 +588,51 @@ def test_c3_scale_properties(native, monkeypatch):
         assert np.array_equal(np.concatenate([ops_a, ops_b]) * live, ops * live)
     finally:
         m.close()
+
+
+def test_c4_human_scale_properties(native, monkeypatch):
+    """BASELINE config 4's genome size (3.1 Gbp: 6.2 G rows, partitioned suffix sort, 40-bit SA, super blocks, 64-bit
+    backward search, deep table of 4^16 entries) with 150 bp reads at 2 %.  Needs a whole B200 and ~20 GB of host
+    memory; skipped on anything smaller.  Checks: truth recovery, CIGAR consistency, and that the 12-mer-table walk and
+    the no-entry-context path return the same records and CIGARs as the default path."""
+    import torch
+    free_b, total_b = torch.cuda.mem_get_info(0)
+    try:
+        host_kb = int(next(l for l in open("/proc/meminfo") if l.startswith("MemAvailable")).split()[1])
+    except (OSError, StopIteration, ValueError):
+        host_kb = 0
+    if free_b < 150 * 2**30 or host_kb < 48 * 2**20:
+        pytest.skip("needs 150 GB of free HBM and 48 GB of free host memory")
+    g = native.sim_genome(11, 3_100_000_000)
+    n = 200_000
+    reads, lens, pos, strand = native.sim_reads(13, g, n, 150, 150, 0.02, 0.02, 0.8)
+    m = native.GpuMapper.build([g], 0)
+    try:
+        p = m.params(flags=native.AS_F_MYERS)
+        r0 = reads.copy()
+        res, ops = m.map_batch(r0, lens, params=p)
+        ok = res["valid"] == 1
+        assert ok.mean() > 0.99
+        near = np.abs(res["off"][ok].astype(np.int64) - pos[ok].astype(np.int64)) <= 50
+        assert near.mean() > 0.995
+        assert ((res["strand"][ok] == 1) == (strand[ok] == 1)).mean() > 0.995
+        nops = res["n_cigar_op"].astype(np.int64)
+        live = np.arange(ops.shape[1])[None, :] < np.maximum(nops, 0)[:, None]
+        qcons = (((ops == 0) | (ops == 1) | (ops == 3)) & live).sum(axis=1)
+        nonmatch = ((ops != 0) & live).sum(axis=1)
+        assert np.array_equal(qcons[ok], lens[ok].astype(np.int64))
+        assert np.array_equal(nonmatch[ok], res["ed"][ok].astype(np.int64))
+        both = ok & (res["myers"] >= 0)
+        assert both.sum() > 0.8 * n and np.array_equal(res["ed"][both], res["myers"][both])
+        for env, flags in ((("AS_VOTE_ECTX", "0"), 0), (None, native.AS_F_NO_LC2)):
+            if env:
+                monkeypatch.setenv(*env)
+            r1 = reads.copy()
+            res1, ops1 = m.map_batch(r1, lens, params=m.params(flags=native.AS_F_MYERS | flags))
+            if env:
+                monkeypatch.delenv(env[0])
+            assert np.array_equal(res1, res), (env, flags)
+            assert np.array_equal(ops1 * live, ops * live), (env, flags)
+            assert np.array_equal(r1, r0)
+    finally:
+        m.close()
