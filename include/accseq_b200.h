@@ -184,6 +184,12 @@ int as_lc_aln_batch(as_gpu *h, const char *seeds, int qlen, size_t n, uint64_t *
 int as_fmi_aln_batch(as_gpu *h, const char *qry, int qlen, size_t n, uint64_t *k, uint64_t *l, uint64_t *r);
 /* sa_access (fmidx.c:18-33) */
 int as_sa_access_batch(as_gpu *h, const uint64_t *rows, size_t n, uint64_t *pos);
+/* csa_access (fmidx.c:315-331): SA[row] from the sampled suffix array csa[i] = SA[csa_ratio*i] (_build_csa,
+ * fmidx.c:152-163; the reference builds ratio 4, fmidx.c:194) by walking LF to a sampled row.  The sample is taken
+ * on the device at the first call with a given ratio and kept in the handle.  literal = 0: LF(row) =
+ * c[ch] + occ(ch,row), the walk the reference's test expects (csa_access(i) == sa[i], test/test-fmidx.cc:104-106);
+ * literal = 1: the statement as the reference wrote it (`- 1`, and 0 after more than 5*ratio steps). */
+int as_csa_access_batch(as_gpu *h, int csa_ratio, int literal, const uint64_t *rows, size_t n, uint64_t *pos);
 /* PART 1 only (alnmain.c:333-405): best.key / best.val / phases / from_outer per read. */
 int as_vote_batch(as_gpu *h, const as_params *p, const char *reads, size_t stride, const uint32_t *lens,
                   size_t n, uint64_t *best_key, uint64_t *best_val, int32_t *phases, int32_t *from_outer);

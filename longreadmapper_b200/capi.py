@@ -106,6 +106,7 @@ def cuda_lib():
     L.as_lc_aln_batch.argtypes = [vp, vp, i32, sz, vp, vp, vp]
     L.as_fmi_aln_batch.argtypes = [vp, vp, i32, sz, vp, vp, vp]
     L.as_sa_access_batch.argtypes = [vp, vp, sz, vp]
+    L.as_csa_access_batch.argtypes = [vp, i32, i32, vp, sz, vp]
     L.as_vote_batch.argtypes = [vp, C.POINTER(Params), vp, sz, vp, sz, vp, vp, vp, vp]
     L.as_cigar_align_batch.argtypes = [vp, C.POINTER(Params), vp, sz, vp, vp, sz, vp, sz, vp, sz, vp, vp]
     L.as_edit_distance_batch.argtypes = [vp, vp, sz, vp, vp, sz, vp, sz, vp, vp]
@@ -400,6 +401,14 @@ class GpuMapper:
         rows = np.ascontiguousarray(rows, dtype=np.uint64)
         pos = np.zeros(rows.size, np.uint64)
         self._check(self.L.as_sa_access_batch(self.h, rows.ctypes.data, rows.size, pos.ctypes.data), "as_sa_access_batch")
+        return pos
+
+    def csa_access_batch(self, rows, ratio=4, literal=False):
+        """csa_access (fmidx.c:315-331) on a batch of rows."""
+        rows = np.ascontiguousarray(rows, dtype=np.uint64)
+        pos = np.zeros(rows.size, np.uint64)
+        self._check(self.L.as_csa_access_batch(self.h, ratio, int(literal), rows.ctypes.data, rows.size, pos.ctypes.data),
+                    "as_csa_access_batch")
         return pos
 
     def vote_batch(self, reads, lens, params=None):

@@ -57,6 +57,8 @@ struct as_gpu {
     DevIndex ix{};
     /* owned device allocations of the index */
     void *d_lc2 = nullptr, *d_sax = nullptr;
+    void *d_csa_lo = nullptr, *d_csa_hi = nullptr;   /* sampled SA of as_csa_access_batch: SA[csa_ratio * i], 32 + 8 bits */
+    int csa_ratio = 0;
     void *d_fm = nullptr, *d_super = nullptr, *d_lc = nullptr, *d_sa_lo = nullptr, *d_sa_hi = nullptr,
          *d_text2 = nullptr, *d_mta = nullptr;
     /* device scratch, grown on demand */

@@ -143,7 +143,9 @@ static int upload_chunk(void *d_dst, const void *h_src, size_t bytes, cudaStream
 }
 
 static void free_index(as_gpu *h) {
-    void **ptrs[] = {&h->d_lc2, &h->d_sax, &h->d_fm, &h->d_super, &h->d_lc, &h->d_sa_lo, &h->d_sa_hi, &h->d_text2, &h->d_mta};
+    void **ptrs[] = {&h->d_lc2, &h->d_sax, &h->d_fm, &h->d_super, &h->d_lc, &h->d_sa_lo, &h->d_sa_hi, &h->d_text2, &h->d_mta,
+                     &h->d_csa_lo, &h->d_csa_hi};
+    h->csa_ratio = 0;
     for (void **p : ptrs) {
         if (*p) cudaFree(*p);
         *p = nullptr;

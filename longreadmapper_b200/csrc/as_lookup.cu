@@ -3,6 +3,7 @@
  *   lc_aln   lchash.c:89-104  (+ lc_access :12-16, _num_from_seq :36-49)
  *   fmi_aln  fmidx.c:295-313  (+ _occ_access :277-293)
  *   sa_access fmidx.c:18-33
+ *   csa_access fmidx.c:315-331 (+ _build_csa :152-163)
  * One thread per query; every lookup is a chain of dependent 32-byte sector gathers, so the kernels are
  * sized for memory-level parallelism (many resident warps), not arithmetic.
  */
@@ -126,6 +127,98 @@ extern "C" int as_sa_access_batch(as_gpu *h, const uint64_t *rows, size_t n, uin
     uint64_t blocks = (n + 255) / 256, cap = (uint64_t)h->sm_count * 16;
     k_sa_access<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(h->ix, (const uint64_t *)h->misc[0].p, n,
                                                                               (uint64_t *)h->misc[1].p);
+    h->launches++;
+    AS_CUDA(cudaGetLastError());
+    AS_CUDA(cudaMemcpyAsync(pos, h->misc[1].p, n * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));
+    AS_CUDA(cudaStreamSynchronize(h->stream));
+    return AS_OK;
+}
+
+/* ---------------------------------------------------------------------------------------------- */
+/* csa_access (fmidx.c:315-331): locate through the sampled suffix array                           */
+/* ---------------------------------------------------------------------------------------------- */
+/* _build_csa (fmidx.c:152-163): csa[i] = SA[ratio * i], i < N / ratio + 1 (the last entry lies past the SA when
+ * ratio divides N: the reference reads sa_access' out-of-scope 0 there, fmidx.c:20-23). */
+__global__ void __launch_bounds__(256) k_csa_sample(DevIndex ix, uint64_t ratio, uint64_t len, uint32_t *__restrict__ lo,
+                                                    uint8_t *__restrict__ hi) {
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < len; i += (uint64_t)gridDim.x * blockDim.x) {
+        uint64_t row = i * ratio;
+        uint64_t v = row < ix.N ? as_sa(ix, row) : 0;
+        lo[i] = (uint32_t)v;
+        if (hi) hi[i] = (uint8_t)(v >> 32);
+    }
+}
+
+/* One thread per row.  A step reads ONE FM sector: the row's BWT code comes out of the two planes of the block whose
+ * counts give occ(code, row), so the walk is `ratio/2` dependent 32-byte gathers on average plus one sampled-SA
+ * gather.  literal: the reference's statement as written (LF - 1, give up after 5*ratio steps). */
+__global__ void __launch_bounds__(256) k_csa_access(DevIndex ix, const uint32_t *__restrict__ csa_lo,
+                                                    const uint8_t *__restrict__ csa_hi, uint64_t ratio, int literal,
+                                                    const uint64_t *__restrict__ rows, size_t n, uint64_t *__restrict__ pos) {
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        uint64_t loc = rows[i], counter = 0, out = 0;
+        bool done = loc >= ix.N;                                        /* out of scope -> 0, as sa_access */
+        while (!done && loc % ratio != 0) {
+            if (loc == ix.primary) {                                    /* bwt[loc] == '$' (fmidx.c:320-322) */
+                out = counter;
+                done = true;
+                break;
+            }
+            uint4 cnt;
+            uint64_t lo, hi;
+            as_ld_block(ix.fm + (loc >> 6), cnt, lo, hi);
+            const uint32_t r = (uint32_t)loc & 63u;
+            const uint32_t c = (uint32_t)((lo >> r) & 1u) | ((uint32_t)((hi >> r) & 1u) << 1);
+            uint64_t m = ((c & 1u) ? lo : ~lo) & ((c & 2u) ? hi : ~hi);
+            m &= (r == 63u) ? ~0ULL : ((1ULL << (r + 1)) - 1ULL);
+            const uint32_t base = c == 0 ? cnt.x : c == 1 ? cnt.y : c == 2 ? cnt.z : cnt.w;
+            uint64_t occ = __ldg(ix.super + 4 * (loc >> AS_SB_SHIFT) + c) + base + (uint64_t)__popcll(m);
+            if (c == 0 && (ix.primary >> 6) == (loc >> 6) && ((uint32_t)ix.primary & 63u) <= r) occ -= 1;   /* '$' is stored as A */
+            const uint64_t cc = c == 0 ? ix.C[0] : c == 1 ? ix.C[1] : c == 2 ? ix.C[2] : ix.C[3];
+            loc = cc + occ - (literal ? 1u : 0u);                       /* fmidx.c:323 */
+            counter++;
+            if (literal && counter > 5 * ratio) done = true;            /* fmidx.c:325-327: returns 0 */
+        }
+        if (!done) {
+            uint64_t j = loc / ratio;
+            uint64_t v = __ldg(csa_lo + j);
+            if (csa_hi) v |= (uint64_t)__ldg(csa_hi + j) << 32;
+            out = v + counter;                                          /* fmidx.c:330 */
+        }
+        pos[i] = out;
+    }
+}
+
+extern "C" int as_csa_access_batch(as_gpu *h, int csa_ratio, int literal, const uint64_t *rows, size_t n, uint64_t *pos) {
+    if (!h || !rows || !pos || csa_ratio <= 0) return AS_EINVAL;
+    if (n == 0) return AS_OK;
+    AS_CUDA(cudaSetDevice(h->device));
+    if (!h->ix.sa_lo) {
+        as_set_error("as_csa_access_batch: the handle has no suffix array to sample");
+        return AS_EINVAL;
+    }
+    if (h->csa_ratio != csa_ratio) {                                    /* (re)sample: _build_csa */
+        if (h->d_csa_lo) cudaFree(h->d_csa_lo);
+        if (h->d_csa_hi) cudaFree(h->d_csa_hi);
+        h->d_csa_lo = h->d_csa_hi = nullptr;
+        h->csa_ratio = 0;
+        const uint64_t len = h->ix.N / (uint64_t)csa_ratio + 1;
+        AS_CUDA(cudaMalloc(&h->d_csa_lo, len * sizeof(uint32_t)));
+        if (h->ix.sa_hi) AS_CUDA(cudaMalloc(&h->d_csa_hi, len));
+        uint64_t blocks = (len + 255) / 256, cap = (uint64_t)h->sm_count * 16;
+        k_csa_sample<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(h->ix, (uint64_t)csa_ratio, len,
+                                                                                    (uint32_t *)h->d_csa_lo, (uint8_t *)h->d_csa_hi);
+        h->launches++;
+        AS_CUDA(cudaGetLastError());
+        h->csa_ratio = csa_ratio;
+    }
+    AS_TRY(as_scratch(h, &h->misc[0], n * sizeof(uint64_t)));
+    AS_TRY(as_scratch(h, &h->misc[1], n * sizeof(uint64_t)));
+    AS_CUDA(cudaMemcpyAsync(h->misc[0].p, rows, n * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
+    uint64_t blocks = (n + 255) / 256, cap = (uint64_t)h->sm_count * 16;
+    k_csa_access<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(
+        h->ix, (const uint32_t *)h->d_csa_lo, (const uint8_t *)h->d_csa_hi, (uint64_t)csa_ratio, literal,
+        (const uint64_t *)h->misc[0].p, n, (uint64_t *)h->misc[1].p);
     h->launches++;
     AS_CUDA(cudaGetLastError());
     AS_CUDA(cudaMemcpyAsync(pos, h->misc[1].p, n * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->stream));

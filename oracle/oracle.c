@@ -427,6 +427,29 @@ uint64_t orc_lc_aln(const orc_index *ix, const char *qry, int qlen, uint64_t *k,
 
 uint64_t orc_sa_access(const orc_index *ix, uint64_t row) { return ix->sa[row]; }  /* fmidx.c:18-33 */
 
+/* csa_access, fmidx.c:315-331: locate through the sampled suffix array csa[i] = SA[ratio*i] (_build_csa,
+ * fmidx.c:152-163) by walking LF until a sampled row.  literal != 0 follows the reference's statement as written,
+ * `loc = c[ch] + occ(ch, loc) - 1` with its `counter > 5*ratio -> 0` cut-off; with this index's C table (text
+ * characters before '$' only, fmidx.c:110) that lands one row below LF(loc), so the literal walk does not return
+ * SA[loc] in general.  literal == 0 is the walk the reference's own test expects (`csa_access(i) == sa[i]`,
+ * test/test-fmidx.cc:104-106): LF(loc) = c[ch] + occ(ch, loc), no cut-off. */
+uint64_t orc_csa_access(const orc_index *ix, int ratio, uint64_t loc, int literal) {
+    uint64_t r = (uint64_t)ratio, counter = 0;
+    if (ratio <= 0 || loc >= ix->n) return 0;
+    while (loc % r != 0) {
+        char c = (char)ix->bwt[loc];
+        if (c == '$') return counter;                                  /* fmidx.c:320-322: SA of that row is 0 */
+        loc = ix->C[(uint8_t)c] + orc_occ(ix, c, loc) - (literal ? 1 : 0);
+        counter++;
+        if (literal && counter > 5 * r) return 0;                      /* fmidx.c:325-327 */
+    }
+    return ix->sa[loc] + counter;                                      /* csa[loc / ratio], fmidx.c:330 */
+}
+
+void orc_csa_access_batch(const orc_index *ix, int ratio, const uint64_t *rows, size_t n, int literal, uint64_t *pos) {
+    for (size_t i = 0; i < n; i++) pos[i] = orc_csa_access(ix, ratio, rows[i], literal);
+}
+
 void orc_lc_aln_batch(const orc_index *ix, const char *seeds, int qlen, size_t n,
                       uint64_t *k, uint64_t *l, uint64_t *r) {
     for (size_t i = 0; i < n; i++) {

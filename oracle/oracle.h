@@ -78,6 +78,8 @@ uint64_t orc_occ(const orc_index *ix, char c, uint64_t loc);
 uint64_t orc_fmi_aln(const orc_index *ix, const char *qry, int len, uint64_t *k, uint64_t *l);
 uint64_t orc_lc_aln(const orc_index *ix, const char *qry, int qlen, uint64_t *k, uint64_t *l);
 uint64_t orc_sa_access(const orc_index *ix, uint64_t row);
+uint64_t orc_csa_access(const orc_index *ix, int ratio, uint64_t loc, int literal);   /* fmidx.c:315-331 */
+void orc_csa_access_batch(const orc_index *ix, int ratio, const uint64_t *rows, size_t n, int literal, uint64_t *pos);
 void  orc_lc_aln_batch(const orc_index *ix, const char *seeds, int qlen, size_t n,
                        uint64_t *k, uint64_t *l, uint64_t *r);
 

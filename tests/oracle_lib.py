@@ -58,6 +58,8 @@ def lib():
     L.orc_lc_aln_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]
     L.orc_sa_access.restype = C.c_uint64
     L.orc_sa_access.argtypes = [C.c_void_p, C.c_uint64]
+    L.orc_csa_access_batch.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]
+    L.orc_csa_access_batch.restype = None
     L.orc_vote_read.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(OrcVote)]
     L.orc_seq_lookup.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.POINTER(C.c_int), C.POINTER(C.c_int), u64p, u64p]
     L.orc_gact.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
@@ -141,6 +143,12 @@ class OracleIndex:
         k = np.zeros(n, np.uint64); l = np.zeros(n, np.uint64); r = np.zeros(n, np.uint64)
         lib().orc_lc_aln_batch(self.h, seeds.ctypes.data, qlen, n, k.ctypes.data, l.ctypes.data, r.ctypes.data)
         return k, l, r
+
+    def csa_access_batch(self, rows, ratio=4, literal=False):
+        rows = np.ascontiguousarray(rows, dtype=np.uint64)
+        pos = np.zeros(rows.size, np.uint64)
+        lib().orc_csa_access_batch(self.h, ratio, rows.ctypes.data, rows.size, int(literal), pos.ctypes.data)
+        return pos
 
     def fmi_aln(self, q):
         k = C.c_uint64(1); l = C.c_uint64(self.n - 1)
@@ -232,6 +240,8 @@ def ref():
         R.fmi_aln.argtypes = [C.POINTER(RefFmi), C.c_char_p, C.c_int, u64p, u64p]
         R.lc_aln.restype = C.c_uint64
         R.lc_aln.argtypes = [C.c_char_p, C.c_int, u64p, u64p, C.POINTER(RefFmi), C.POINTER(RefLch)]
+        R.csa_access.restype = C.c_uint64
+        R.csa_access.argtypes = [C.POINTER(RefFmi), C.c_uint64]
         R.histo_init.restype = C.c_void_p
         R.histo_init.argtypes = [C.c_uint32]
         R.histo_add.argtypes = [C.c_void_p, C.c_uint64]

@@ -277,6 +277,36 @@ def test_live_lookups_against_libref(gold_index, tmp_path):
 
 
 @needs_ref
+def test_live_csa_access_against_libref(gold_index, tmp_path):
+    """csa_access (fmidx.c:315-331) of the reference's object code on the .mfi it reads (csa_ratio 4, fmidx.c:194)
+    against the oracle's literal restatement, at every row."""
+    ix, _, _ = gold_index
+    fa = str(tmp_path / "r.fa")
+    ix.write(fa)
+    R = oracle_lib.ref()
+    fmi = oracle_lib.RefFmi()
+    R.fmi_read(C.byref(fmi), (fa + ".cat").encode())
+    assert fmi.csa_ratio == 4
+    rows = np.arange(ix.n, dtype=np.uint64)
+    lit = ix.csa_access_batch(rows, 4, literal=True)
+    step = max(1, ix.n // 20000)
+    for r in range(0, ix.n, step):
+        assert R.csa_access(C.byref(fmi), r) == int(lit[r]), r
+
+
+def test_csa_access_walk_returns_the_suffix_array(gold_index):
+    """The property the reference's test states (csa_access(i) == sa[i], test/test-fmidx.cc:104-106) holds for the
+    LF walk at every ratio; sampled rows are exact in the literal form too."""
+    ix, _, _ = gold_index
+    rows = np.arange(ix.n, dtype=np.uint64)
+    for ratio in (1, 4, 7, 32):
+        assert np.array_equal(ix.csa_access_batch(rows, ratio), ix.sa)
+        lit = ix.csa_access_batch(rows, ratio, literal=True)
+        assert np.array_equal(lit[::ratio], ix.sa[::ratio])
+    assert ix.csa_access_batch(np.array([ix.n, ix.n + 5], np.uint64), 4).tolist() == [0, 0]
+
+
+@needs_ref
 def test_live_edit_distance_against_edlib():
     rng = np.random.default_rng(8)
     acgt = np.frombuffer(b"ACGT", np.uint8)
