@@ -659,5 +659,13 @@ def test_c4_human_scale_properties(native, monkeypatch):
             assert np.array_equal(res1, res), (env, flags)
             assert np.array_equal(ops1 * live, ops * live), (env, flags)
             assert np.array_equal(r1, r0)
+        # csa_access (fmidx.c:315-331) on 40-bit rows: the 32 + 8-bit sample and the super-block counts of the walk
+        N = 2 * g.size + 1
+        rows = np.random.default_rng(17).integers(0, N, 2_000_000).astype(np.uint64)
+        rows[:4] = (0, N - 1, (1 << 32) - 1, 1 << 32)
+        sa = m.sa_access_batch(rows)
+        assert sa.max() >= 1 << 32
+        assert np.array_equal(m.csa_access_batch(rows, 4), sa)
+        assert np.array_equal(m.csa_access_batch(rows, 32), sa)
     finally:
         m.close()
