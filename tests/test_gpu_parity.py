@@ -101,31 +101,6 @@ def test_sa_access(gpu_uniform, idx_uniform):
     assert np.array_equal(gpu_uniform.sa_access_batch(np.arange(ix.n, dtype=np.uint64)), ix.sa)
 
 
-@pytest.mark.parametrize("ratio", [1, 4, 5, 32, 64])
-def test_csa_access(gpu_uniform, idx_uniform, gpu_repeat, idx_repeat, ratio):
-    """csa_access (fmidx.c:315-331): the LF walk to the sampled SA returns SA[row] at every row, and the walk as the
-    reference wrote it equals the oracle's literal restatement (pinned on the reference's object code in
-    tests/test_oracle_vs_ref.py).  Rows past the index give 0; ratios alternate on one handle (resampling)."""
-    for mapper, (ix, _) in ((gpu_uniform, idx_uniform), (gpu_repeat, idx_repeat)):
-        rows = np.arange(ix.n, dtype=np.uint64) if ix.n <= 400000 else \
-            np.random.default_rng(ratio).integers(0, ix.n, 300000).astype(np.uint64)
-        rows = np.concatenate([rows, np.array([0, ix.n - 1, ix.n, ix.n + 7, 2**40], np.uint64)])
-        want = ix.csa_access_batch(rows, ratio)
-        got = mapper.csa_access_batch(rows, ratio)
-        assert np.array_equal(got, want)
-        inside = rows < ix.n
-        assert np.array_equal(got[inside], ix.sa[rows[inside]]) and not got[~inside].any()
-        assert np.array_equal(mapper.csa_access_batch(rows, ratio, literal=True),
-                              ix.csa_access_batch(rows, ratio, literal=True))
-        assert np.array_equal(got[inside], mapper.sa_access_batch(rows[inside]))
-
-
-def test_csa_access_errors(gpu_uniform):
-    with pytest.raises(Exception):
-        gpu_uniform.csa_access_batch(np.zeros(4, np.uint64), 0)
-    assert gpu_uniform.csa_access_batch(np.zeros(0, np.uint64), 4).size == 0
-
-
 # ---------------------------------------------------------------------------------------------------
 # PART 1 (alnmain.c:333-405)
 # ---------------------------------------------------------------------------------------------------
@@ -659,13 +634,5 @@ def test_c4_human_scale_properties(native, monkeypatch):
             assert np.array_equal(res1, res), (env, flags)
             assert np.array_equal(ops1 * live, ops * live), (env, flags)
             assert np.array_equal(r1, r0)
-        # csa_access (fmidx.c:315-331) on 40-bit rows: the 32 + 8-bit sample and the super-block counts of the walk
-        N = 2 * g.size + 1
-        rows = np.random.default_rng(17).integers(0, N, 2_000_000).astype(np.uint64)
-        rows[:4] = (0, N - 1, (1 << 32) - 1, 1 << 32)
-        sa = m.sa_access_batch(rows)
-        assert sa.max() >= 1 << 32
-        assert np.array_equal(m.csa_access_batch(rows, 4), sa)
-        assert np.array_equal(m.csa_access_batch(rows, 32), sa)
     finally:
         m.close()
