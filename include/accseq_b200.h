@@ -61,6 +61,20 @@ typedef struct as_index_view {
 int  as_gpu_open(as_gpu **h, int device, const as_index_view *ix);
 void as_gpu_close(as_gpu *h);
 
+/* Open-time options (what used to be environment variables: a drop-in library must not read its host's environment).
+ * Zero-initialised = the defaults; as_gpu_open / as_gpu_build use the defaults. */
+typedef struct as_open_opts {
+    int32_t  lc2_hlen;        /* depth of the deep k-mer table: 0 = min(16, ceil(log4 N)+1); <= hlen disables it; 13..16 forces */
+    int32_t  no_sax;          /* 1: do not build the SA + context table (PART 1 then gathers SA and text separately) */
+    uint64_t build_part_max;  /* as_gpu_build only: > 0 forces the partitioned suffix sort with at most this many suffixes
+                               * per partition (the path texts of >= 2^32-1 rows take) */
+    int32_t  sampled_sa;      /* 0: the full suffix array stays in HBM (5 bytes/row, + 8 for the SA + context table);
+                               * r > 0: keep only SA[r*i] (csa, fmidx.c:152-163) and resolve vote positions by the LF walk of
+                               * csa_access (fmidx.c:315-331): no SA, no SA + context table -- ~1/r of the SA bytes per GPU */
+    int32_t  reserved[5];
+} as_open_opts;
+int  as_gpu_open_opts(as_gpu **h, int device, const as_index_view *ix, const as_open_opts *opts);
+
 /* Build the index ON the GPU from the .cat text (asindex.c:97-110: forward + reverse complement per sequence,
  * one final '$') -- replaces fmi_build (fmidx.c:166-199: pSAscan suffix sort psascan/sa_use.cc:8-18, BWT
  * :76-98, C table :101-125, O table :128-150) and lc_build (lchash.c:52-73) of the reference's `accidx`.
@@ -68,6 +82,8 @@ void as_gpu_close(as_gpu *h);
  * the reference's layouts, byte-identical to the files accidx writes. */
 int  as_gpu_build(as_gpu **h, int device, const char *content, uint64_t con_len, const as_mta *mta, int mta_len,
                   int hlen);
+int  as_gpu_build_opts(as_gpu **h, int device, const char *content, uint64_t con_len, const as_mta *mta, int mta_len,
+                       int hlen, const as_open_opts *opts);
 typedef struct as_index_out {       /* caller-owned buffers; a NULL member is skipped */
     uint64_t *C;                    /* 256 entries */
     uint64_t *O;                    /* 4*(N/o_ratio+1) entries (fmidx.c:128-150) */
@@ -98,6 +114,13 @@ typedef struct as_params {
     int32_t  gact_band;  /* bit-parallel GACT: half-width of the banded first attempt at a tile; 0 = adaptive (default),
                           * < 0 = full matrix only.  Results never depend on it (a tile the band cannot prove exact is
                           * filled again with the whole matrix). */
+    /* scheduling knobs (A/B runs and tests; results never depend on them).  as_params_default sets the "auto" values. */
+    int32_t  vote_ectx;  /* PART 1 decides one- and two-row deep-table entries from their context bases: -1 = only when the
+                          * index is larger than L2 (default), 0 = never, 1 = always */
+    int32_t  gact_order; /* hand reads to GACT by decreasing length: -1 = only for reads of several tiles (default), 0, 1 */
+    int32_t  gact_blocks_per_sm;  /* resident GACT blocks per SM; 0 = occupancy query (default) */
+    uint32_t chunk_reads;         /* as_map_batch: fixed chunk size; 0 = the ramp-up / ramp-down plan (default) */
+    int32_t  chunk_tail;          /* as_map_batch: how many times the last chunk is split 2:1; -1 = default (1) */
 } as_params;
 #define AS_F_MYERS        1u   /* also run the edlib-equivalent NW distance with k=(int)(0.05*len*2) per read */
 #define AS_F_NO_ALIGN     2u   /* stop after PART 1+2 (no GACT): results carry loc/off/strand/flag only */

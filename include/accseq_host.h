@@ -74,6 +74,8 @@ as_fastq *as_fastq_open(const char *path);       /* plain or gzip */
 int  as_fastq_next_batch(as_fastq *fq, size_t max_reads, as_read_batch *b, void *(*alloc)(size_t));
 void as_read_batch_free(as_read_batch *b, void (*dealloc)(void *));
 void as_fastq_close(as_fastq *fq);
+/* all records of a FASTA file (plain or gzip) as heap strings the caller frees: the input of accidx (asindex.c:78-117) */
+int  as_fasta_load(const char *path, int *nseq, char ***names, char ***seqs, uint64_t **lens);
 
 #ifdef __cplusplus
 }

@@ -48,7 +48,19 @@ class AsIndexOut(C.Structure):
 
 class Params(C.Structure):
     _fields_ = [("seed_len", C.c_uint32), ("thres", C.c_uint32), ("gact_T", C.c_int32), ("gact_O", C.c_int32),
-                ("flags", C.c_uint32), ("gact_band", C.c_int32)]
+                ("flags", C.c_uint32), ("gact_band", C.c_int32), ("vote_ectx", C.c_int32), ("gact_order", C.c_int32),
+                ("gact_blocks_per_sm", C.c_int32), ("chunk_reads", C.c_uint32), ("chunk_tail", C.c_int32)]
+
+
+class OpenOpts(C.Structure):
+    _fields_ = [("lc2_hlen", C.c_int32), ("no_sax", C.c_int32), ("build_part_max", C.c_uint64), ("sampled_sa", C.c_int32),
+                ("reserved", C.c_int32 * 5)]
+
+
+def open_opts(lc2_hlen=0, no_sax=0, build_part_max=0, sampled_sa=0):
+    o = OpenOpts()
+    o.lc2_hlen, o.no_sax, o.build_part_max, o.sampled_sa = int(lc2_hlen), int(no_sax), int(build_part_max), int(sampled_sa)
+    return o
 
 
 class AsStats(C.Structure):
@@ -86,6 +98,8 @@ def cuda_lib():
     L.as_device_count.restype = i32
     L.as_gpu_open.argtypes = [C.POINTER(vp), i32, C.POINTER(AsIndexView)]
     L.as_gpu_build.argtypes = [C.POINTER(vp), i32, vp, u64, vp, i32, i32]
+    L.as_gpu_open_opts.argtypes = [C.POINTER(vp), i32, C.POINTER(AsIndexView), C.POINTER(OpenOpts)]
+    L.as_gpu_build_opts.argtypes = [C.POINTER(vp), i32, vp, u64, vp, i32, i32, C.POINTER(OpenOpts)]
     L.as_gpu_export.argtypes = [vp, C.POINTER(AsIndexOut)]
     L.as_gpu_index_length.argtypes = [vp]
     L.as_gpu_index_length.restype = u64
@@ -228,7 +242,7 @@ def _ptr(a):
 class GpuMapper:
     """One as_gpu handle: the index resident on one B200, mirrors the calls alnmain.c makes per batch."""
 
-    def __init__(self, device, *, length, C_table, O, o_ratio, bwt, lc, hlen, sa, sa_entry_bytes, content, mta):
+    def __init__(self, device, *, length, C_table, O, o_ratio, bwt, lc, hlen, sa, sa_entry_bytes, content, mta, opts=None):
         L = cuda_lib()
         self._keep = [np.ascontiguousarray(x) for x in (C_table, O, bwt, lc, sa, content)]
         Ct, Ot, bw, lcv, sav, con = self._keep
@@ -237,7 +251,7 @@ class GpuMapper:
                         lcv.ctypes.data, lcv.size, int(hlen), sav.ctypes.data, int(sa_entry_bytes), con.ctypes.data,
                         con.size, C.cast(mta_arr, C.c_void_p), len(mta))
         h = C.c_void_p()
-        rc = L.as_gpu_open(C.byref(h), device, C.byref(v))
+        rc = L.as_gpu_open_opts(C.byref(h), device, C.byref(v), C.byref(opts) if opts is not None else None)
         if rc != 0:
             raise AccSeqError(f"as_gpu_open failed ({rc}): {L.as_last_error().decode()}")
         self.h = h
@@ -247,20 +261,21 @@ class GpuMapper:
         self._keep = None          # the device copy is complete; host arrays are no longer referenced
 
     @classmethod
-    def from_oracle_index(cls, ox, device=0):
-        """ox: tests/oracle_lib.OracleIndex (the reference's in-memory layout)."""
-        return cls(device, length=ox.n, C_table=ox.Ctab, O=ox.O, o_ratio=ox.s.o_ratio, bwt=ox.bwt, lc=ox.lc,
-                   hlen=ox.s.hlen, sa=ox.sa, sa_entry_bytes=8, content=ox.cat,
-                   mta=[(o, s) for (_, o, s) in ox.mta])
+    def build(cls, seqs, device=0, hlen=12, names=None, opts=None):
+        """Index construction on the GPU from raw sequences (the accidx path: asindex.c:129-153)."""
+        cat, mta = cat_image(seqs)
+        return cls.build_cat(cat, mta, device, hlen, names, opts)
 
     @classmethod
-    def build(cls, seqs, device=0, hlen=12, names=None):
-        """Index construction on the GPU from raw sequences (the accidx path: asindex.c:129-153)."""
+    def build_cat(cls, cat, mta, device=0, hlen=12, names=None, opts=None):
+        """The same from a ready .cat image (uint8[N], forward + reverse complement per sequence, final '$') and its
+        [(offset, seq_len)] table."""
         L = cuda_lib()
-        cat, mta = cat_image(seqs)
+        cat = np.ascontiguousarray(cat, dtype=np.uint8)
         mta_arr = (AsMta * max(1, len(mta)))(*[AsMta(o, s) for (o, s) in mta])
         h = C.c_void_p()
-        rc = L.as_gpu_build(C.byref(h), device, cat.ctypes.data, cat.size, C.cast(mta_arr, C.c_void_p), len(mta), hlen)
+        rc = L.as_gpu_build_opts(C.byref(h), device, cat.ctypes.data, cat.size, C.cast(mta_arr, C.c_void_p), len(mta), hlen,
+                                 C.byref(opts) if opts is not None else None)
         if rc != 0:
             raise AccSeqError(f"as_gpu_build failed ({rc}): {L.as_last_error().decode()}")
         self = cls.__new__(cls)
@@ -269,21 +284,20 @@ class GpuMapper:
         self.mta, self.hlen = mta, hlen
         return self
 
-    def export(self, o_ratio=32, csa_ratio=4, hlen=None, sa_entry_bytes=8):
-        """The index in the reference's in-memory layouts: dict of numpy arrays C, O, bwt, lc, sa, csa."""
+    def export(self, o_ratio=32, csa_ratio=4, hlen=None, sa_entry_bytes=8, want=("C", "O", "bwt", "lc", "sa", "csa")):
+        """The index in the reference's in-memory layouts: dict of numpy arrays C, O, bwt, lc, sa, csa (those in `want`)."""
         hlen = hlen if hlen is not None else getattr(self, "hlen", 12)
         N = self.N
-        out = dict(C=np.zeros(256, np.uint64), O=np.zeros(4 * (N // o_ratio + 1), np.uint64), bwt=np.zeros(N, np.uint8),
-                   lc=np.zeros(2 * 4 ** hlen, np.uint64),
-                   sa=np.zeros(N, np.uint64) if sa_entry_bytes == 8 else np.zeros(N * 5, np.uint8),
-                   csa=np.zeros(N // csa_ratio + 1, np.uint64))
-        o = AsIndexOut(out["C"].ctypes.data, out["O"].ctypes.data, o_ratio, out["bwt"].ctypes.data, out["lc"].ctypes.data,
-                       out["sa"].ctypes.data, sa_entry_bytes, out["csa"].ctypes.data, csa_ratio)
+        shapes = dict(C=(256, np.uint64), O=(4 * (N // o_ratio + 1), np.uint64), bwt=(N, np.uint8), lc=(2 * 4 ** hlen, np.uint64),
+                      sa=(N, np.uint64) if sa_entry_bytes == 8 else (N * 5, np.uint8), csa=(N // csa_ratio + 1, np.uint64))
+        out = {k: np.zeros(shapes[k][0], shapes[k][1]) for k in want}
+        ptr = lambda k: out[k].ctypes.data if k in out else None
+        o = AsIndexOut(ptr("C"), ptr("O"), o_ratio, ptr("bwt"), ptr("lc"), ptr("sa"), sa_entry_bytes, ptr("csa"), csa_ratio)
         self._check(self.L.as_gpu_export(self.h, C.byref(o)), "as_gpu_export")
         return out
 
     @classmethod
-    def from_index_files(cls, fasta_path, device=0):
+    def from_index_files(cls, fasta_path, device=0, opts=None):
         """Loads <fa>.mta/.cat/.cat.mfi/.cat.lch/.cat.sa5 with the C loader (libaccseq_host.so) and uploads."""
         H = host_lib()
         L = cuda_lib()
@@ -293,7 +307,7 @@ class GpuMapper:
             raise AccSeqError(f"as_index_load({fasta_path}) failed: {rc}")
         try:
             h = C.c_void_p()
-            rc = L.as_gpu_open(C.byref(h), device, C.byref(p.contents.view))
+            rc = L.as_gpu_open_opts(C.byref(h), device, C.byref(p.contents.view), C.byref(opts) if opts is not None else None)
             if rc != 0:
                 raise AccSeqError(f"as_gpu_open failed ({rc}): {L.as_last_error().decode()}")
             names = [p.contents.names[i].decode() for i in range(p.contents.view.mta_len)]
@@ -319,10 +333,15 @@ class GpuMapper:
         except Exception:
             pass
 
-    def params(self, seed_len=20, thres=300, T=None, O=None, flags=0, band=None):
+    def params(self, seed_len=20, thres=300, T=None, O=None, flags=0, band=None, **knobs):
+        """as_params; knobs = vote_ectx, gact_order, gact_blocks_per_sm, chunk_reads, chunk_tail (scheduling only)."""
         p = Params()
         self.L.as_params_default(C.byref(p))
         p.seed_len, p.thres, p.flags = seed_len, thres, flags
+        for k, v in knobs.items():
+            if k not in ("vote_ectx", "gact_order", "gact_blocks_per_sm", "chunk_reads", "chunk_tail"):
+                raise TypeError(f"unknown as_params field {k}")
+            setattr(p, k, int(v))
         if band is not None:
             p.gact_band = band
         if T is not None:

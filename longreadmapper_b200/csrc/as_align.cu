@@ -413,6 +413,8 @@ int as_launch_gact(as_gpu *h, const as_params *p, const uint32_t *d_qpack, size_
     a.work_counter = (unsigned int *)h->misc[5].p;
     a.stats = h->d_stats;
     a.band = p->gact_band;
+    a.order_mode = p->gact_order;
+    a.blocks_per_sm = p->gact_blocks_per_sm;
     a.fail_count = nullptr;
     a.order = nullptr;
     /* two implementations of the same tile DP: bit-parallel, one read per lane (as_gact_bp.cu) for batches that fill

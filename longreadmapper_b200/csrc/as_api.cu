@@ -13,6 +13,11 @@ extern "C" void as_params_default(as_params *p) {
     p->gact_O = 120;
     p->flags = 0;
     p->gact_band = 0;      /* adaptive banded first pass */
+    p->vote_ectx = -1;
+    p->gact_order = -1;
+    p->gact_blocks_per_sm = 0;
+    p->chunk_reads = 0;
+    p->chunk_tail = -1;
 }
 
 __global__ void k_rle_ops(uint8_t *__restrict__ ops, size_t stride, as_result *__restrict__ res, size_t n);
@@ -250,13 +255,9 @@ static int ensure_pipeline(as_gpu *h) {
 
 /* Chunk schedule of one as_map_batch call.  The D2H stream is the longest of the three (results + CIGAR columns + the
  * reverse-complemented reads), so the first chunk is small -- it reaches the D2H stream early -- and the following
- * ones grow to the size at which the kernels run at full efficiency; AS_CHUNK_READS forces a fixed size. */
-static int plan_chunks(size_t n, size_t stride, size_t *begin /* AS_MAX_CHUNKS + 1 */, bool light_d2h) {
-    size_t fixed = 0;
-    if (const char *e = getenv("AS_CHUNK_READS")) {
-        long v = atol(e);
-        if (v > 0) fixed = (size_t)v;
-    }
+ * ones grow to the size at which the kernels run at full efficiency; as_params.chunk_reads forces a fixed size. */
+static int plan_chunks(const as_params *p, size_t n, size_t stride, size_t *begin /* AS_MAX_CHUNKS + 1 */, bool light_d2h) {
+    size_t fixed = p->chunk_reads;
     int nc = 0;
     begin[0] = 0;
     if (fixed) {
@@ -281,8 +282,7 @@ static int plan_chunks(size_t n, size_t stride, size_t *begin /* AS_MAX_CHUNKS +
         if (c < big) c = (2 * c < big) ? 2 * c : big;
     }
     /* ramp down as well: nothing overlaps the last chunk's D2H, so the last chunk is the smaller part of a split */
-    int tail = 1;
-    if (const char *e = getenv("AS_CHUNK_TAIL")) tail = atoi(e);
+    const int tail = p->chunk_tail >= 0 ? p->chunk_tail : 1;
     for (int t = 0; t < tail && nc < AS_MAX_CHUNKS; t++) {
         const size_t b0 = begin[nc - 1], sz = begin[nc] - b0;
         if (sz < 4 * min_reads) break;
@@ -316,7 +316,7 @@ static int map_batch_impl(as_gpu *h, const as_params *p, char *reads, size_t str
     AS_TRY(as_scratch(h, &h->reads, n * stride));
     AS_TRY(as_scratch(h, &h->lens, n * sizeof(uint32_t)));
     size_t cb[AS_MAX_CHUNKS + 1];
-    const int nc = plan_chunks(n, stride, cb, (p->flags & AS_F_KEEP_READS) && (p->flags & AS_F_RLE_CIGAR));
+    const int nc = plan_chunks(p, n, stride, cb, (p->flags & AS_F_KEEP_READS) && (p->flags & AS_F_RLE_CIGAR));
     h->n_chunks_last = nc;
     AS_CUDA(cudaEventRecord(h->ev[0], h->stream));
     AS_CUDA(cudaStreamWaitEvent(h->s_h2d, h->ev[0], 0));

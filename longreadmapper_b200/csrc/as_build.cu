@@ -343,6 +343,11 @@ out:
 
 extern "C" int as_gpu_build(as_gpu **out, int device, const char *content, uint64_t con_len, const as_mta *mta,
                             int mta_len, int hlen) {
+    return as_gpu_build_opts(out, device, content, con_len, mta, mta_len, hlen, nullptr);
+}
+
+extern "C" int as_gpu_build_opts(as_gpu **out, int device, const char *content, uint64_t con_len, const as_mta *mta,
+                                 int mta_len, int hlen, const as_open_opts *opts) {
     if (!out || !content || mta_len < 0 || (mta_len > 0 && !mta)) return AS_EINVAL;
     *out = nullptr;
     if (con_len < 2 || content[con_len - 1] != '$') {
@@ -356,10 +361,10 @@ extern "C" int as_gpu_build(as_gpu **out, int device, const char *content, uint6
     as_gpu *h = as_handle_new(device);
     if (!h) return AS_ENODEV;
     cudaGetLastError();
+    if (opts) h->opts = *opts;
     /* texts the single prefix-doubling sort cannot hold go through the partitioned builder (as_build_big.cu);
-     * AS_BUILD_PART_MAX=<suffixes per partition> forces that path on small texts (tests) */
-    uint64_t part_max = 0;
-    if (const char *e = getenv("AS_BUILD_PART_MAX")) part_max = strtoull(e, nullptr, 10);
+     * as_open_opts.build_part_max = <suffixes per partition> forces that path on small texts (tests) */
+    const uint64_t part_max = h->opts.build_part_max;
     int rc = (con_len >= 0xFFFFFFFFull - 1 || part_max > 0) ? as_build_big(h, content, con_len, mta, mta_len, hlen, part_max)
                                                             : build_on_device(h, content, con_len, mta, mta_len, hlen);
     if (rc == AS_OK) rc = as_build_lc2(h);

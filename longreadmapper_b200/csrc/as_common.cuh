@@ -55,6 +55,7 @@ struct as_gpu {
     cudaStream_t own_stream = nullptr;
     cudaStream_t stream = nullptr;
     DevIndex ix{};
+    as_open_opts opts{};        /* as_gpu_open_opts / as_gpu_build_opts */
     /* owned device allocations of the index */
     void *d_lc2 = nullptr, *d_sax = nullptr;
     void *d_csa_lo = nullptr, *d_csa_hi = nullptr;   /* sampled SA of as_csa_access_batch: SA[csa_ratio * i], 32 + 8 bits */
@@ -148,6 +149,8 @@ struct GactArgs {
     /* bit-parallel kernel with a banded first attempt per tile (as_gact_bp.cu) */
     int band;                    /* < 0: full matrix only; 0: adaptive; > 0: fixed half-width (rounded up to a level) */
     const uint32_t *order;       /* slot -> read, longest first (NULL: identity); lanes of a warp then finish together */
+    int order_mode;              /* as_params.gact_order: -1 auto, 0 off, 1 on */
+    int blocks_per_sm;           /* as_params.gact_blocks_per_sm: 0 = occupancy query */
     unsigned int *fail_count;    /* policy counters of the launch: warp-tiles refilled, warp-tiles, lane-tiles served by
                                   * half the band, lane-tiles */
 };

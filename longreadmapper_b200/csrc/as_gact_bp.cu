@@ -548,16 +548,12 @@ int as_launch_gact_bp(as_gpu *h, GactArgs &a, size_t n, uint32_t max_qlen, uint3
     if (n >= 0x7FFFFFE0ull) return AS_ERANGE;
     {
         bool order = max_qlen > (uint32_t)a.T || max_tlen > (uint32_t)a.T;
-        if (const char *e = getenv("AS_GACT_ORDER")) order = atoi(e) != 0;
+        if (a.order_mode >= 0) order = a.order_mode != 0;
         if (order) AS_TRY(gact_order(h, a, n, max_qlen, max_tlen));
     }
     const int rows = (int)(max_qlen < (uint32_t)a.T ? max_qlen : (uint32_t)a.T);
     const int words = rows > 0 ? (rows + 31) / 32 : 1;
-    int bps = 0;
-    if (const char *e = getenv("AS_GACT_BLOCKS_PER_SM")) {
-        int v = atoi(e);
-        if (v >= 1 && v <= 16) bps = v;
-    }
+    const int bps = a.blocks_per_sm >= 1 && a.blocks_per_sm <= 16 ? a.blocks_per_sm : 0;
     if (!h->h_band) {          /* adaptive band: written by k_gact_policy, read here (mapped pinned memory) */
         AS_CUDA(cudaHostAlloc((void **)&h->h_band, sizeof(unsigned int), cudaHostAllocMapped));
         *h->h_band = AS_GACT_BAND0;

@@ -371,6 +371,10 @@ int as_launch_pack_text(as_gpu *h, const uint8_t *d_in, uint64_t n, uint32_t *d_
 }
 
 extern "C" int as_gpu_open(as_gpu **out, int device, const as_index_view *v) {
+    return as_gpu_open_opts(out, device, v, nullptr);
+}
+
+extern "C" int as_gpu_open_opts(as_gpu **out, int device, const as_index_view *v, const as_open_opts *opts) {
     if (!out || !v) return AS_EINVAL;
     *out = nullptr;
     if (!v->C || !v->O || !v->bwt || !v->lc || !v->sa || !v->content || v->length < 2 || v->mta_len < 0 ||
@@ -396,6 +400,7 @@ extern "C" int as_gpu_open(as_gpu **out, int device, const as_index_view *v) {
     }
     as_gpu *h = as_handle_new(device);
     if (!h) return AS_ENODEV;
+    if (opts) h->opts = *opts;
     int rc = build_index(h, v);
     if (rc == AS_OK) rc = as_build_lc2(h);
     if (rc != AS_OK) {

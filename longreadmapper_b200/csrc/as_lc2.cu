@@ -101,9 +101,7 @@ __global__ void __launch_bounds__(256) k_sax_fill(DevIndex ix, unsigned long lon
 static int build_sax(as_gpu *h) {
     DevIndex &ix = h->ix;
     ix.sax = nullptr;
-    if (const char *e = getenv("AS_NO_SAX")) {
-        if (atoi(e)) return AS_OK;
-    }
+    if (h->opts.no_sax || h->opts.sampled_sa > 0) return AS_OK;
     size_t free_b = 0, total_b = 0;
     AS_CUDA(cudaMemGetInfo(&free_b, &total_b));
     if (ix.N * 8ULL > free_b / 2) return AS_OK;                   /* leave room for the batches */
@@ -123,7 +121,7 @@ static int build_lc2_table(as_gpu *h) {
     while (h2 < 16 && (1ULL << (2 * h2)) < ix.N) h2++;           /* ceil(log4 N) */
     h2 += 1;
     if (h2 > 16) h2 = 16;
-    if (const char *e = getenv("AS_LC2_HLEN")) h2 = atoi(e);
+    if (h->opts.lc2_hlen > 0) h2 = h->opts.lc2_hlen;
     if (h2 <= ix.hlen || h2 > 16) return AS_OK;                   /* nothing deeper than the reference's table to offer */
     size_t free_b = 0, total_b = 0;
     AS_CUDA(cudaMemGetInfo(&free_b, &total_b));

@@ -667,7 +667,7 @@ int as_launch_vote(as_gpu *h, const as_params *p, const uint32_t *d_pack, size_t
      * fetching a survivor's position after the compare instead of along with the context.  It pays when that gather is
      * a DRAM sector (c3: PART 1 7.4 -> 6.5 ms, c4: 33.2 -> 31.7), not when the SA table sits in L2 (c2: 2.35 -> 2.55) */
     a.use_ectx = h->ix.N * 8ULL > 2ULL * (unsigned long long)h->l2_bytes ? 1 : 0;
-    if (const char *e = getenv("AS_VOTE_ECTX")) a.use_ectx = atoi(e) != 0;
+    if (p->vote_ectx >= 0) a.use_ectx = p->vote_ectx != 0;
 
     /* lanes per read from the seeds of one phase of the longest read */
     int G = seeds_per_phase <= 8 ? 8 : seeds_per_phase <= 16 ? 16 : 32;

@@ -210,3 +210,44 @@ done:
     }
     return AS_OK;
 }
+
+/* every record of a FASTA (or FASTQ) file as separate heap strings: what create_meta (asindex.c:78-117) iterates over */
+int as_fasta_load(const char *path, int *nseq, char ***names, char ***seqs, uint64_t **lens) {
+    if (!path || !nseq || !names || !seqs || !lens) return AS_EINVAL;
+    as_fastq *fq = as_fastq_open(path);
+    if (!fq) return AS_EIO;
+    dstr name = {0}, seq = {0}, qual = {0};
+    int n = 0, cap = 0, rc = AS_OK;
+    char **nm = NULL, **sq = NULL;
+    uint64_t *ln = NULL;
+    for (;;) {
+        int r = fq_record(fq, &name, &seq, &qual);
+        if (r == 0) break;
+        if (r < 0) { rc = r; break; }
+        if (n == cap) {
+            cap = cap ? 2 * cap : 16;
+            nm = realloc(nm, sizeof(char *) * (size_t)cap);
+            sq = realloc(sq, sizeof(char *) * (size_t)cap);
+            ln = realloc(ln, sizeof(uint64_t) * (size_t)cap);
+            if (!nm || !sq || !ln) { rc = AS_ENOMEM; break; }
+        }
+        nm[n] = malloc(name.l + 1);
+        if (!nm[n]) { rc = AS_ENOMEM; break; }
+        memcpy(nm[n], name.s ? name.s : "", name.l);
+        nm[n][name.l] = 0;
+        sq[n] = seq.s;                    /* hand the buffer over instead of copying a chromosome */
+        ln[n] = seq.l;
+        seq.s = NULL;
+        seq.l = seq.cap = 0;
+        n++;
+    }
+    free(name.s); free(seq.s); free(qual.s);
+    as_fastq_close(fq);
+    if (rc != AS_OK) {
+        for (int i = 0; i < n; i++) { free(nm[i]); free(sq[i]); }
+        free(nm); free(sq); free(ln);
+        return rc;
+    }
+    *nseq = n; *names = nm; *seqs = sq; *lens = ln;
+    return AS_OK;
+}

@@ -425,7 +425,13 @@ uint64_t orc_lc_aln(const orc_index *ix, const char *qry, int qlen, uint64_t *k,
     return lc_aln_count(ix, qry, qlen, k, l, NULL);
 }
 
-uint64_t orc_sa_access(const orc_index *ix, uint64_t row) { return ix->sa[row]; }  /* fmidx.c:18-33 */
+/* SA[row]: the expanded array, or -- for borrowed human-scale indexes (tests) -- the raw .sa5 bytes (sa_use.h:17-46) */
+static inline uint64_t sa_at(const orc_index *ix, uint64_t row) {
+    if (ix->sa) return ix->sa[row];
+    const uint8_t *e = ix->sa5 + 5 * row;
+    return (uint64_t)e[0] | (uint64_t)e[1] << 8 | (uint64_t)e[2] << 16 | (uint64_t)e[3] << 24 | (uint64_t)e[4] << 32;
+}
+uint64_t orc_sa_access(const orc_index *ix, uint64_t row) { return sa_at(ix, row); }  /* fmidx.c:18-33 */
 
 /* csa_access, fmidx.c:315-331: locate through the sampled suffix array csa[i] = SA[ratio*i] (_build_csa,
  * fmidx.c:152-163) by walking LF until a sampled row.  literal != 0 follows the reference's statement as written,
@@ -443,7 +449,7 @@ uint64_t orc_csa_access(const orc_index *ix, int ratio, uint64_t loc, int litera
         counter++;
         if (literal && counter > 5 * r) return 0;                      /* fmidx.c:325-327 */
     }
-    return ix->sa[loc] + counter;                                      /* csa[loc / ratio], fmidx.c:330 */
+    return sa_at(ix, loc) + counter;                                      /* csa[loc / ratio], fmidx.c:330 */
 }
 
 void orc_csa_access_batch(const orc_index *ix, int ratio, const uint64_t *rows, size_t n, int literal, uint64_t *pos) {
@@ -526,7 +532,7 @@ void orc_vote_read(const orc_index *ix, const char *seq, uint32_t len,
                 out->n_seeds++;
                 if (rr > 0 && rr < thres) {
                     for (uint64_t k = kk; k <= ll; ++k) {
-                        orc_histo_add(&inner, ix->sa[k] - j);          /* u64 wrap-around kept */
+                        orc_histo_add(&inner, sa_at(ix, k) - j);          /* u64 wrap-around kept */
                         out->n_hits++;
                     }
                 }

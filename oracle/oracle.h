@@ -63,6 +63,8 @@ typedef struct {
     /* .mta */
     int       n_mta;
     orc_mta  *mta;
+    /* raw .sa5 bytes, read when `sa` is NULL: lets a test borrow a human-scale index without 8 bytes per row */
+    const uint8_t *sa5;
 } orc_index;
 
 /* ---- index construction / IO (asindex.c:78-153, fmidx.c:76-199, lchash.c:52-73) ---- */

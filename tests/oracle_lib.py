@@ -76,7 +76,8 @@ class OrcIndexStruct(C.Structure):
     _fields_ = [("n", C.c_uint64), ("cat", C.c_void_p), ("C", C.c_uint64 * 256), ("o_ratio", C.c_int),
                 ("o_len", C.c_uint64), ("O", C.c_void_p), ("bwt", C.c_void_p), ("csa_ratio", C.c_int),
                 ("csa_len", C.c_uint64), ("csa", C.c_void_p), ("hlen", C.c_int), ("lc_len", C.c_uint64),
-                ("lc", C.c_void_p), ("sa", C.c_void_p), ("n_mta", C.c_int), ("mta", C.c_void_p)]
+                ("lc", C.c_void_p), ("sa", C.c_void_p), ("n_mta", C.c_int), ("mta", C.c_void_p),
+                ("sa5", C.c_void_p)]
 
 
 class OrcMta(C.Structure):
@@ -95,6 +96,48 @@ class OracleIndex:
         self.h = handle
         self.s = OrcIndexStruct.from_address(handle)
         self.n = int(self.s.n)
+        self._borrowed = None
+
+    @classmethod
+    def from_arrays(cls, *, cat, C_table, O, o_ratio, bwt, lc, hlen, sa, mta, names=None):
+        """An orc_index over numpy arrays the caller already holds in the reference's layouts -- e.g. what
+        as_gpu_export returned for an index built on the GPU at a BASELINE config's full size, where the oracle's own
+        builder would take too long.  `sa` is uint64[N] or the raw .sa5 bytes uint8[5N]; mta = [(offset, seq_len)].
+        Nothing is copied; the arrays stay referenced by the object."""
+        lib()
+        cat, C_table, O, bwt, lc, sa = (np.ascontiguousarray(x) for x in (cat, C_table, O, bwt, lc, sa))
+        assert cat.dtype == np.uint8 and bwt.dtype == np.uint8 and C_table.dtype == np.uint64 and C_table.size == 256
+        assert O.dtype == np.uint64 and lc.dtype == np.uint64 and lc.size == 2 * 4 ** hlen
+        n = int(cat.size)
+        s = OrcIndexStruct()
+        s.n, s.cat, s.o_ratio, s.o_len, s.O, s.bwt = n, cat.ctypes.data, int(o_ratio), int(O.size), O.ctypes.data, bwt.ctypes.data
+        C.memmove(s.C, C_table.ctypes.data, 256 * 8)
+        s.csa_ratio, s.csa_len, s.csa = 0, 0, None
+        s.hlen, s.lc_len, s.lc = int(hlen), int(lc.size), lc.ctypes.data
+        if sa.dtype == np.uint64:
+            assert sa.size == n
+            s.sa, s.sa5 = sa.ctypes.data, None
+        else:
+            assert sa.dtype == np.uint8 and sa.size == 5 * n
+            s.sa, s.sa5 = None, sa.ctypes.data
+        names = list(names) if names else [f"seq{i}" for i in range(len(mta))]
+        name_bufs = [C.create_string_buffer(x.encode()) for x in names]
+        marr = (OrcMta * max(1, len(mta)))()
+        for i, (o, l) in enumerate(mta):
+            marr[i].name = C.cast(name_bufs[i], C.c_char_p)
+            marr[i].name_len, marr[i].offset, marr[i].seq_len = len(names[i]), int(o), int(l)
+        s.n_mta, s.mta = len(mta), C.cast(marr, C.c_void_p)
+        self = cls.__new__(cls)
+        self.s, self.h, self.n = s, C.addressof(s), n
+        self._borrowed = (cat, C_table, O, bwt, lc, sa, marr, name_bufs)
+        return self
+
+    @classmethod
+    def from_gpu_export(cls, mapper, cat, mta, names=None, sa_entry_bytes=8):
+        """The index a GpuMapper holds, exported in the reference's layouts (as_gpu_export) and wrapped for the oracle."""
+        ex = mapper.export(sa_entry_bytes=sa_entry_bytes, want=("C", "O", "bwt", "lc", "sa"))
+        return cls.from_arrays(cat=cat, C_table=ex["C"], O=ex["O"], o_ratio=32, bwt=ex["bwt"], lc=ex["lc"], hlen=12,
+                               sa=ex["sa"], mta=mta, names=names)
 
     @classmethod
     def build(cls, names, seqs, o_ratio=32, hlen=12):
@@ -175,9 +218,18 @@ class OracleIndex:
         return res, ops.reshape(n, ops_stride) if n else ops, int(cells.value)
 
     def close(self):
-        if self.h:
+        if self.h and self._borrowed is None:
             lib().orc_index_free(self.h)
-            self.h = None
+        self.h = None
+        self._borrowed = None
+
+
+def gpu_mapper(lm, ox, device=0, opts=None):
+    """A GpuMapper over an OracleIndex (the reference's in-memory layout) -- test convenience, so that the package itself
+    never names the oracle."""
+    return lm.GpuMapper(device, length=ox.n, C_table=ox.Ctab, O=ox.O, o_ratio=ox.s.o_ratio, bwt=ox.bwt, lc=ox.lc,
+                        hlen=ox.s.hlen, sa=ox.sa, sa_entry_bytes=8, content=ox.cat, mta=[(o, s) for (_, o, s) in ox.mta],
+                        opts=opts)
 
 
 def gact(q, t, T=320, O=120):

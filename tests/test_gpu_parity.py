@@ -4,6 +4,8 @@ Myers distance.  The oracle itself is pinned against the compiled reference in t
 import numpy as np
 import pytest
 
+import oracle_lib
+
 from conftest import reads_from
 
 pytestmark = pytest.mark.gpu
@@ -15,7 +17,7 @@ FIELDS = ("loc", "off", "seq_id", "strand", "flag", "mapq", "ed", "valid", "myer
 @pytest.fixture(scope="module")
 def gpu_uniform(native, idx_uniform):
     ix, _ = idx_uniform
-    m = native.GpuMapper.from_oracle_index(ix, 0)
+    m = oracle_lib.gpu_mapper(native, ix, 0)
     yield m
     m.close()
 
@@ -23,7 +25,7 @@ def gpu_uniform(native, idx_uniform):
 @pytest.fixture(scope="module")
 def gpu_repeat(native, idx_repeat):
     ix, _ = idx_repeat
-    m = native.GpuMapper.from_oracle_index(ix, 0)
+    m = oracle_lib.gpu_mapper(native, ix, 0)
     yield m
     m.close()
 
@@ -36,7 +38,8 @@ def compare_map(native, mapper, ix, reads, lens, stride, **kw):
     r_cpu = reads.copy()
     r_gpu = reads.copy()
     exp, exp_ops, cells = ix.map_batch(r_cpu, stride, lens, seed_len=seed_len, thres=thres, T=T, O=O, myers=True)
-    p = mapper.params(seed_len=seed_len, thres=thres, T=T, O=O, flags=native.AS_F_MYERS | GACT_IMPL.get(kw.get("gact"), 0))
+    p = mapper.params(seed_len=seed_len, thres=thres, T=T, O=O, flags=native.AS_F_MYERS | GACT_IMPL.get(kw.get("gact"), 0),
+                      **kw.get("knobs", {}))
     mapper.stats_reset()
     got, got_ops = mapper.map_batch(r_gpu, lens, params=p)
     for f in FIELDS:
@@ -104,8 +107,8 @@ def test_sa_access(gpu_uniform, idx_uniform):
 # ---------------------------------------------------------------------------------------------------
 # PART 1 (alnmain.c:333-405)
 # ---------------------------------------------------------------------------------------------------
-def check_vote(mapper, ix, reads, lens, seed_len=20, thres=300, flags=0):
-    key, val, ph, fo = mapper.vote_batch(reads, lens, mapper.params(seed_len=seed_len, thres=thres, flags=flags))
+def check_vote(mapper, ix, reads, lens, seed_len=20, thres=300, flags=0, **knobs):
+    key, val, ph, fo = mapper.vote_batch(reads, lens, mapper.params(seed_len=seed_len, thres=thres, flags=flags, **knobs))
     for i in range(len(lens)):
         v = ix.vote(reads[i, : lens[i]], seed_len, thres)
         assert (int(key[i]), int(val[i]), int(ph[i]), int(fo[i])) == (v.best_key, v.best_val, v.phases, v.from_outer), i
@@ -140,24 +143,22 @@ def test_vote_long_reads(native, gpu_repeat, idx_repeat, wide):
 
 
 # deep k-mer table (as_lc2.cu): PART 1 must give the reference's votes whether a seed starts from the 12-mer table
-# or from the h2-mer table, for every h2 (AS_LC2_HLEN forces a depth the small test genomes would not get)
+# or from the h2-mer table, for every h2 (as_open_opts.lc2_hlen forces a depth the small test genomes would not get)
 @pytest.mark.parametrize("h2", [13, 14, 16])
 @pytest.mark.parametrize("wide", [0, 16])
-def test_vote_deep_table(native, idx_repeat, monkeypatch, h2, wide):
+def test_vote_deep_table(native, idx_repeat, h2, wide):
     ix, gs = idx_repeat
-    monkeypatch.setenv("AS_LC2_HLEN", str(h2))
-    m = native.GpuMapper.from_oracle_index(ix, 0)
-    monkeypatch.delenv("AS_LC2_HLEN")
-    monkeypatch.setenv("AS_VOTE_ECTX", "1")      # entries decide from their context bases (default only for large indexes)
+    m = oracle_lib.gpu_mapper(native, ix, 0, native.open_opts(lc2_hlen=h2))
+    ectx = dict(vote_ectx=1)      # entries decide from their context bases (default only for large indexes)
     try:
         for k, (lmin, lmax, e, sl, th) in enumerate([(100, 100, 0.0, 20, 300), (150, 150, 0.02, 20, 300), (100, 250, 0.08, 20, 300),
                                                     (60, 260, 0.05, h2, 50), (60, 260, 0.05, 24, 2), (80, 200, 0.03, 32, 1000),
                                                     (80, 200, 0.03, 12, 300)]):
             reads, lens, _ = reads_from(native, 900 + k, gs, 300, lmin, lmax, e, e, 0.7)
-            check_vote(m, ix, reads, lens, sl, th, flags=wide)                          # deep table when sl >= h2
-            check_vote(m, ix, reads, lens, sl, th, flags=wide | native.AS_F_NO_LC2)     # the reference's 12-mer table
+            check_vote(m, ix, reads, lens, sl, th, flags=wide, **ectx)                          # deep table when sl >= h2
+            check_vote(m, ix, reads, lens, sl, th, flags=wide | native.AS_F_NO_LC2, **ectx)     # the reference's 12-mer table
         reads, lens, _ = reads_from(native, 950, gs, 30, 1000, 5000, 0.05, 0.15, 0.34)
-        check_vote(m, ix, reads, lens, flags=wide)
+        check_vote(m, ix, reads, lens, flags=wide, **ectx)
     finally:
         m.close()
 
@@ -165,19 +166,15 @@ def test_vote_deep_table(native, idx_repeat, monkeypatch, h2, wide):
 @pytest.mark.parametrize("wide", [0, 16])
 @pytest.mark.parametrize("ectx", ["0", "1"])
 @pytest.mark.parametrize("no_sax", ["0", "1"])
-def test_vote_sa_context_table(native, idx_repeat, monkeypatch, no_sax, wide, ectx):
+def test_vote_sa_context_table(native, idx_repeat, no_sax, wide, ectx):
     """sax (SA value + the 12 bases in front of it, as_lc2.cu) against the plain SA + text gathers: same votes, also for
     hits within 12 bases of the text start (context shorter than the entry), seeds whose tail is longer than the entry
-    holds (seed_len - h2 > 12: the text gather stays) and exact repeats (two-row intervals).  AS_VOTE_ECTX=1 forces the
+    holds (seed_len - h2 > 12: the text gather stays) and exact repeats (two-row intervals).  vote_ectx=1 forces the
     path that decides one- and two-row deep-table entries from the context bases they carry (on by itself only for
     indexes larger than L2)."""
     ix, gs = idx_repeat
-    monkeypatch.setenv("AS_LC2_HLEN", "13")
-    monkeypatch.setenv("AS_NO_SAX", no_sax)
-    m = native.GpuMapper.from_oracle_index(ix, 0)
-    monkeypatch.delenv("AS_LC2_HLEN")
-    monkeypatch.delenv("AS_NO_SAX")
-    monkeypatch.setenv("AS_VOTE_ECTX", ectx)
+    m = oracle_lib.gpu_mapper(native, ix, 0, native.open_opts(lc2_hlen=13, no_sax=int(no_sax)))
+    ectx = dict(vote_ectx=int(ectx))
     try:
         a = gs[0]
         L = 120
@@ -187,24 +184,21 @@ def test_vote_sa_context_table(native, idx_repeat, monkeypatch, no_sax, wide, ec
             reads[i, :L] = a[p0:p0 + L]
         lens = np.full(len(starts), L, dtype=np.uint32)
         for sl, th in [(20, 300), (14, 300), (24, 300), (28, 50), (32, 1000)]:
-            check_vote(m, ix, reads, lens, sl, th, flags=wide)
+            check_vote(m, ix, reads, lens, sl, th, flags=wide, **ectx)
         for k, (lmin, lmax, e, sl, th) in enumerate([(100, 250, 0.05, 20, 300), (80, 200, 0.03, 32, 1000), (60, 260, 0.05, 27, 2)]):
             r2, l2, _ = reads_from(native, 970 + k, gs, 300, lmin, lmax, e, e, 0.7)
-            check_vote(m, ix, r2, l2, sl, th, flags=wide)
+            check_vote(m, ix, r2, l2, sl, th, flags=wide, **ectx)
     finally:
         m.close()
 
 
-def test_map_deep_table_built_index(native, idx_repeat, monkeypatch):
+def test_map_deep_table_built_index(native, idx_repeat):
     """the same through as_gpu_build and the whole path"""
     ix, gs = idx_repeat
-    monkeypatch.setenv("AS_LC2_HLEN", "15")
-    m = native.GpuMapper.build(gs, 0)
-    monkeypatch.delenv("AS_LC2_HLEN")
-    monkeypatch.setenv("AS_VOTE_ECTX", "1")
+    m = native.GpuMapper.build(gs, 0, opts=native.open_opts(lc2_hlen=15))
     try:
         reads, lens, stride = reads_from(native, 960, gs, 1200, 100, 250, 0.0, 0.08, 0.6)
-        compare_map(native, m, ix, reads, lens, stride)
+        compare_map(native, m, ix, reads, lens, stride, knobs=dict(vote_ectx=1))
     finally:
         m.close()
 
@@ -312,19 +306,17 @@ def test_map_batch_split_invariance(native, gpu_uniform, idx_uniform):
     assert np.array_equal(wops, np.concatenate([x[1] for x in parts]))
 
 
-def test_map_chunked_pipeline(native, gpu_uniform, idx_uniform, monkeypatch):
+def test_map_chunked_pipeline(native, gpu_uniform, idx_uniform):
     """as_map_batch pipelines chunks over three streams and trims the CIGAR-column copy per chunk: a ragged last
     chunk, chunk-local scratch and the trimmed 2D copy must leave results identical to the oracle's."""
     ix, gs = idx_uniform
     reads, lens, stride = reads_from(native, 950, gs, 4099, 100, 180, 0.0, 0.05, 0.6)
-    monkeypatch.setenv("AS_CHUNK_READS", "1000")
-    compare_map(native, gpu_uniform, ix, reads, lens, stride)
+    compare_map(native, gpu_uniform, ix, reads, lens, stride, knobs=dict(chunk_reads=1000))
     h2d, d2h = gpu_uniform.last_transfer()
     assert h2d == 4099 * (stride + 4) and d2h < 4099 * (56 + stride + 2 * 180)
     tm = gpu_uniform.last_timing()
     assert tm["total"] > 0 and tm["part1"] > 0 and tm["gact"] > 0
-    monkeypatch.setenv("AS_CHUNK_READS", "5")
-    compare_map(native, gpu_uniform, ix, reads[:100], lens[:100], stride)   # 20 chunks of 5 reads
+    compare_map(native, gpu_uniform, ix, reads[:100], lens[:100], stride, knobs=dict(chunk_reads=5))   # 20 chunks of 5 reads
 
 
 def test_truth_recovered(native, gpu_uniform, idx_uniform):
@@ -541,98 +533,5 @@ def test_c2_full_size_properties(native, orc):
             assert np.array_equal(r_cpu, r_all[pick])
         finally:
             ix.close()
-    finally:
-        m.close()
-
-
-def test_c3_scale_properties(native, monkeypatch):
-    """BASELINE config 3's genome size (100 Mbp: deep table of 4^15 entries, SA + context table larger than L2, so PART 1
-    decides one- and two-row entries from their context bases BY DEFAULT) with 10 kbp reads at 10 % error.  The oracle
-    cannot build this index in test time; the checks are the size-independent ones, and that every alternative PART 1
-    path (plain 12-mer table, no entry contexts, no SA + context table rows) returns the same records and CIGARs."""
-    g = native.sim_genome(11, 100_000_000)
-    n = 3000
-    reads, lens, pos, strand = native.sim_reads(9, g, n, 10_000, 10_000, 0.10, 0.10, 1 / 3)
-    m = native.GpuMapper.build([g], 0)
-    try:
-        p = m.params()
-        r0 = reads.copy()
-        res, ops = m.map_batch(r0, lens, params=p)
-        ok = res["valid"] == 1
-        assert ok.mean() > 0.99
-        near = np.abs(res["off"][ok].astype(np.int64) - pos[ok].astype(np.int64)) <= 200
-        assert near.mean() > 0.99
-        assert ((res["strand"][ok] == 1) == (strand[ok] == 1)).mean() > 0.99
-        nops = res["n_cigar_op"].astype(np.int64)
-        live = np.arange(ops.shape[1])[None, :] < np.maximum(nops, 0)[:, None]
-        qcons = (((ops == 0) | (ops == 1) | (ops == 3)) & live).sum(axis=1)
-        nonmatch = ((ops != 0) & live).sum(axis=1)
-        assert np.array_equal(qcons[ok], lens[ok].astype(np.int64))
-        assert np.array_equal(nonmatch[ok], res["ed"][ok].astype(np.int64))
-        # the other ways through PART 1 / GACT: same answers
-        for env, flags in ((("AS_VOTE_ECTX", "0"), 0), (None, native.AS_F_NO_LC2), (("AS_GACT_ORDER", "0"), 0)):
-            if env:
-                monkeypatch.setenv(*env)
-            r1 = reads.copy()
-            res1, ops1 = m.map_batch(r1, lens, params=m.params(flags=flags))
-            if env:
-                monkeypatch.delenv(env[0])
-            assert np.array_equal(res1, res), (env, flags)
-            assert np.array_equal(ops1 * live, ops * live), (env, flags)
-            assert np.array_equal(r1, r0)
-        # batch-split invariance
-        cut = 1234
-        res_a, ops_a = m.map_batch(reads[:cut].copy(), lens[:cut], params=p)
-        res_b, ops_b = m.map_batch(reads[cut:].copy(), lens[cut:], params=p)
-        assert np.array_equal(np.concatenate([res_a, res_b]), res)
-        assert np.array_equal(np.concatenate([ops_a, ops_b]) * live, ops * live)
-    finally:
-        m.close()
-
-
-def test_c4_human_scale_properties(native, monkeypatch):
-    """BASELINE config 4's genome size (3.1 Gbp: 6.2 G rows, partitioned suffix sort, 40-bit SA, super blocks, 64-bit
-    backward search, deep table of 4^16 entries) with 150 bp reads at 2 %.  Needs a whole B200 and ~20 GB of host
-    memory; skipped on anything smaller.  Checks: truth recovery, CIGAR consistency, and that the 12-mer-table walk and
-    the no-entry-context path return the same records and CIGARs as the default path."""
-    import torch
-    free_b, total_b = torch.cuda.mem_get_info(0)
-    try:
-        host_kb = int(next(l for l in open("/proc/meminfo") if l.startswith("MemAvailable")).split()[1])
-    except (OSError, StopIteration, ValueError):
-        host_kb = 0
-    if free_b < 150 * 2**30 or host_kb < 48 * 2**20:
-        pytest.skip("needs 150 GB of free HBM and 48 GB of free host memory")
-    g = native.sim_genome(11, 3_100_000_000)
-    n = 200_000
-    reads, lens, pos, strand = native.sim_reads(13, g, n, 150, 150, 0.02, 0.02, 0.8)
-    m = native.GpuMapper.build([g], 0)
-    try:
-        p = m.params(flags=native.AS_F_MYERS)
-        r0 = reads.copy()
-        res, ops = m.map_batch(r0, lens, params=p)
-        ok = res["valid"] == 1
-        assert ok.mean() > 0.99
-        near = np.abs(res["off"][ok].astype(np.int64) - pos[ok].astype(np.int64)) <= 50
-        assert near.mean() > 0.995
-        assert ((res["strand"][ok] == 1) == (strand[ok] == 1)).mean() > 0.995
-        nops = res["n_cigar_op"].astype(np.int64)
-        live = np.arange(ops.shape[1])[None, :] < np.maximum(nops, 0)[:, None]
-        qcons = (((ops == 0) | (ops == 1) | (ops == 3)) & live).sum(axis=1)
-        nonmatch = ((ops != 0) & live).sum(axis=1)
-        assert np.array_equal(qcons[ok], lens[ok].astype(np.int64))
-        assert np.array_equal(nonmatch[ok], res["ed"][ok].astype(np.int64))
-        both = ok & (res["myers"] >= 0)
-        assert both.sum() > 0.8 * n and np.array_equal(res["ed"][both], res["myers"][both])
-        for env, flags in ((("AS_VOTE_ECTX", "0"), 0), (None, native.AS_F_NO_LC2)):
-            if env:
-                monkeypatch.setenv(*env)
-            r1 = reads.copy()
-            res1, ops1 = m.map_batch(r1, lens, params=m.params(flags=native.AS_F_MYERS | flags))
-            if env:
-                monkeypatch.delenv(env[0])
-            assert np.array_equal(res1, res), (env, flags)
-            assert np.array_equal(ops1 * live, ops * live), (env, flags)
-            assert np.array_equal(r1, r0)
     finally:
         m.close()

@@ -4,6 +4,8 @@ array of a text is unique, so the files are byte-identical to the reference's.""
 import numpy as np
 import pytest
 
+import oracle_lib
+
 from conftest import reads_from
 
 pytestmark = pytest.mark.gpu
@@ -41,7 +43,7 @@ def test_build_repeat_rich_two_sequences(native, idx_repeat):
     built = native.GpuMapper.build(gs, 0)
     check_export(ix, built)
     # and the handle maps exactly like one opened from the reference layout
-    opened = native.GpuMapper.from_oracle_index(ix, 0)
+    opened = oracle_lib.gpu_mapper(native, ix, 0)
     reads, lens, stride = reads_from(native, 31, gs, 500, 100, 400, 0.0, 0.1, 0.5)
     p = built.params(flags=native.AS_F_MYERS)
     a, aops = built.map_batch(reads.copy(), lens, params=p)
@@ -90,24 +92,20 @@ def test_build_rejects_bad_text(native):
 # partitioned builder (as_build_big.cu): the path 3.1 Gbp genomes take, forced onto small texts
 # ---------------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("part_max", [1, 5000, 200000])
-def test_partitioned_build_matches_oracle(native, idx_repeat, monkeypatch, part_max):
-    """AS_BUILD_PART_MAX caps the suffixes sorted at once: 1 = one partition per 4-character bin; the planted repeats
+def test_partitioned_build_matches_oracle(native, idx_repeat, part_max):
+    """as_open_opts.build_part_max caps the suffixes sorted at once: 1 = one partition per 4-character bin; the planted repeats
     need many 21-character refinement rounds inside their partitions"""
     ix, gs = idx_repeat
-    monkeypatch.setenv("AS_BUILD_PART_MAX", str(part_max))
-    built = native.GpuMapper.build(gs, 0)
-    monkeypatch.delenv("AS_BUILD_PART_MAX")
+    built = native.GpuMapper.build(gs, 0, opts=native.open_opts(build_part_max=part_max))
     assert built.N == ix.n
     check_export(ix, built)
     built.close()
 
 
 @pytest.mark.parametrize("text", [b"A", b"ACGT", b"A" * 300, b"ACGTACGT" * 40, b"GATTACA" * 19])
-def test_partitioned_build_degenerate_texts(native, orc, monkeypatch, text):
+def test_partitioned_build_degenerate_texts(native, orc, text):
     ix = orc.OracleIndex.build(["t"], [text], hlen=4)
-    monkeypatch.setenv("AS_BUILD_PART_MAX", "7")
-    built = native.GpuMapper.build([text], 0, hlen=4)
-    monkeypatch.delenv("AS_BUILD_PART_MAX")
+    built = native.GpuMapper.build([text], 0, hlen=4, opts=native.open_opts(build_part_max=7))
     ex = built.export(hlen=4)
     assert np.array_equal(ex["sa"], ix.sa) and np.array_equal(ex["bwt"], ix.bwt) and np.array_equal(ex["lc"], ix.lc)
     assert np.array_equal(ex["C"], ix.Ctab)

@@ -3,13 +3,15 @@ oracle's restatement (pinned on the reference's object code in test_oracle_vs_re
 import numpy as np
 import pytest
 
+import oracle_lib
+
 pytestmark = pytest.mark.gpu
 
 
 @pytest.fixture(scope="module")
 def gpu_uniform(native, idx_uniform):
     ix, _ = idx_uniform
-    m = native.GpuMapper.from_oracle_index(ix, 0)
+    m = oracle_lib.gpu_mapper(native, ix, 0)
     yield m
     m.close()
 
@@ -17,7 +19,7 @@ def gpu_uniform(native, idx_uniform):
 @pytest.fixture(scope="module")
 def gpu_repeat(native, idx_repeat):
     ix, _ = idx_repeat
-    m = native.GpuMapper.from_oracle_index(ix, 0)
+    m = oracle_lib.gpu_mapper(native, ix, 0)
     yield m
     m.close()
 
