@@ -45,7 +45,8 @@ typedef struct as_index_view {
     uint64_t        o_len;
     int             o_ratio;
     const char     *bwt;            /* dna_fmi.bwt, one byte per row: A C G T $ */
-    const uint64_t *lc;             /* lc_hash.lc (lchash.h:12-16): (k,l) pairs, 2*4^hlen entries */
+    const uint64_t *lc;             /* lc_hash.lc (lchash.h:12-16): (k,l) pairs, 2*4^hlen entries.  lc, sa and content may be
+                                     * NULL: a lookup-only handle (fmi_aln / csa walks), which as_map_batch refuses */
     uint64_t        lc_len;
     int             hlen;
     const void     *sa;             /* suffix array, N entries */
@@ -87,7 +88,7 @@ int  as_gpu_build_opts(as_gpu **h, int device, const char *content, uint64_t con
 typedef struct as_index_out {       /* caller-owned buffers; a NULL member is skipped */
     uint64_t *C;                    /* 256 entries */
     uint64_t *O;                    /* 4*(N/o_ratio+1) entries (fmidx.c:128-150) */
-    int       o_ratio;              /* must divide 64; the reference uses 32 (asindex.c:138) */
+    int       o_ratio;              /* any positive ratio; the reference uses 32 (asindex.c:138) */
     char     *bwt;                  /* N bytes */
     uint64_t *lc;                   /* 2*4^hlen entries, MSB-first code order (lchash.c:36-49) */
     void     *sa;                   /* N entries of sa_entry_bytes (5 = .sa5 bytes, 8 = u64 / ui40_t structs) */
@@ -205,6 +206,12 @@ int as_gpu_last_transfer(as_gpu *h, uint64_t *h2d_bytes, uint64_t *d2h_bytes);
 int as_lc_aln_batch(as_gpu *h, const char *seeds, int qlen, size_t n, uint64_t *k, uint64_t *l, uint64_t *r);
 /* fmi_aln (fmidx.c:295-313) from the full range. */
 int as_fmi_aln_batch(as_gpu *h, const char *qry, int qlen, size_t n, uint64_t *k, uint64_t *l, uint64_t *r);
+/* fmi_aln continuing from the caller's intervals: k[i], l[i] are read and overwritten (fmidx.c:303; lc_aln calls it
+ * that way after the table lookup, lchash.c:103) */
+int as_fmi_aln_from_batch(as_gpu *h, const char *qry, int qlen, size_t n, uint64_t *k, uint64_t *l, uint64_t *r);
+/* lc_build (lchash.c:52-73): the 4^hlen backward searches of the reference, one thread each; lc receives 2*4^hlen
+ * values in the reference's (MSB-first) order.  Needs only the FM index of the handle. */
+int as_lc_build(as_gpu *h, int hlen, uint64_t *lc);
 /* sa_access (fmidx.c:18-33) */
 int as_sa_access_batch(as_gpu *h, const uint64_t *rows, size_t n, uint64_t *pos);
 /* csa_access (fmidx.c:315-331): SA[row] from the sampled suffix array csa[i] = SA[csa_ratio*i] (_build_csa,

@@ -211,6 +211,10 @@ static int check_map_args(as_gpu *h, const as_params *p, const void *reads, size
         as_set_error("as_map_batch: NULL argument");
         return AS_EINVAL;
     }
+    if (!h->ix.lc || !h->ix.text2 || !(h->ix.sa_lo || h->d_csa_lo)) {
+        as_set_error("as_map_batch: lookup-only handle (opened without lc table, suffix array or text)");
+        return AS_EINVAL;
+    }
     return AS_OK;
 }
 

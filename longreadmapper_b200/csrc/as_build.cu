@@ -389,7 +389,7 @@ __global__ void __launch_bounds__(256) k_export_bwt(DevIndex ix, uint64_t row0, 
     }
 }
 
-/* O[4*j + c] = # of c in bwt[0, o_ratio*j)  (fmidx.c:128-150); o_ratio divides 64 */
+/* O[4*j + c] = # of c in bwt[0, o_ratio*j)  (fmidx.c:128-150) */
 __global__ void __launch_bounds__(256) k_export_o(DevIndex ix, int o_ratio, uint64_t j0, uint64_t n, uint64_t *__restrict__ out) {
     for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
         const uint64_t row = (j0 + i) * (uint64_t)o_ratio;       /* counts over rows < row */
@@ -444,8 +444,8 @@ extern "C" int as_gpu_export(as_gpu *h, as_index_out *o) {
             }
         }
         if (o->O) {
-            if (o->o_ratio <= 0 || 64 % o->o_ratio != 0) {
-                as_set_error("as_gpu_export: o_ratio %d must divide 64", o->o_ratio);
+            if (o->o_ratio <= 0) {
+                as_set_error("as_gpu_export: o_ratio %d must be positive", o->o_ratio);
                 rc = AS_EINVAL;
                 goto out;
             }

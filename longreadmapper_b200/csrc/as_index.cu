@@ -85,11 +85,18 @@ __global__ void k_build_fm_blocks(const uint8_t *__restrict__ bwt, uint64_t row0
         uint64_t row = row0 + r0;
         const uint64_t *o = Oc + 4 * (r0 / (uint64_t)o_ratio);
         const uint64_t *sb = super + 4 * (row >> AS_SB_SHIFT);
+        /* o_ratio > 64 (the reference's tests build with 128): the checkpoint lies up to o_ratio - 64 rows before the
+         * block; count the rows in between (chunks start at multiples of o_ratio, so they are in `bwt`) */
+        uint32_t extra[4] = {0, 0, 0, 0};
+        for (uint64_t r = r0 & ~((uint64_t)o_ratio - 1); r < r0; r++) {
+            const uint32_t ch = bwt[r];
+            if (ch != '$') extra[as_base_code(ch)]++;
+        }
         FmBlock blk;
-        blk.cnt[0] = (uint32_t)(o[0] - sb[0]);
-        blk.cnt[1] = (uint32_t)(o[1] - sb[1]);
-        blk.cnt[2] = (uint32_t)(o[2] - sb[2]);
-        blk.cnt[3] = (uint32_t)(o[3] - sb[3]);
+        blk.cnt[0] = (uint32_t)(o[0] - sb[0]) + extra[0];
+        blk.cnt[1] = (uint32_t)(o[1] - sb[1]) + extra[1];
+        blk.cnt[2] = (uint32_t)(o[2] - sb[2]) + extra[2];
+        blk.cnt[3] = (uint32_t)(o[3] - sb[3]) + extra[3];
         blk.lo = lo;
         blk.hi = hi;
         out[row >> 6] = blk;
@@ -258,9 +265,9 @@ static int build_index(as_gpu *h, const as_index_view *v) {
         ix.fm = (const FmBlock *)h->d_fm;
         ix.super = (const uint64_t *)h->d_super;
 
-        /* ---- lc table ---- */
-        uint64_t ncodes = 1ULL << (2 * v->hlen);
-        CU(cudaMalloc(&h->d_lc, ncodes * sizeof(ulonglong2)));
+        /* ---- lc table (absent in a lookup-only view: fmi_aln / csa_access still work) ---- */
+        uint64_t ncodes = v->lc ? 1ULL << (2 * v->hlen) : 0;
+        if (v->lc) CU(cudaMalloc(&h->d_lc, ncodes * sizeof(ulonglong2)));
         uint64_t per = (CH * 8) / sizeof(ulonglong2);
         for (uint64_t c0 = 0; c0 < ncodes; c0 += per) {
             uint64_t nc = (ncodes - c0 < per) ? ncodes - c0 : per;
@@ -271,11 +278,12 @@ static int build_index(as_gpu *h, const as_index_view *v) {
             CU(cudaStreamSynchronize(s));
         }
         ix.lc = (const ulonglong2 *)h->d_lc;
+        if (!v->lc) ix.hlen = 0;
 
-        /* ---- suffix array ---- */
-        CU(cudaMalloc(&h->d_sa_lo, N * sizeof(uint32_t)));
-        if (N > (1ULL << 32)) CU(cudaMalloc(&h->d_sa_hi, N));
-        for (uint64_t r0 = 0; r0 < N; r0 += CH) {
+        /* ---- suffix array (may be absent) ---- */
+        if (v->sa) CU(cudaMalloc(&h->d_sa_lo, N * sizeof(uint32_t)));
+        if (v->sa && N > (1ULL << 32)) CU(cudaMalloc(&h->d_sa_hi, N));
+        for (uint64_t r0 = 0; v->sa && r0 < N; r0 += CH) {
             uint64_t nr = (N - r0 < CH) ? N - r0 : CH;
             STEP(upload_chunk(d_stage, (const uint8_t *)v->sa + r0 * (uint64_t)v->sa_entry_bytes,
                               nr * (size_t)v->sa_entry_bytes, s));
@@ -288,11 +296,13 @@ static int build_index(as_gpu *h, const as_index_view *v) {
         ix.sa_lo = (const uint32_t *)h->d_sa_lo;
         ix.sa_hi = (const uint8_t *)h->d_sa_hi;
 
-        /* ---- text ---- */
+        /* ---- text (may be absent) ---- */
         uint64_t nwords = ((v->con_len + 15) >> 4) + 4;          /* slack for the funnel-shift readers */
-        CU(cudaMalloc(&h->d_text2, nwords * sizeof(uint32_t)));
-        CU(cudaMemset(h->d_text2, 0, nwords * sizeof(uint32_t)));
-        for (uint64_t b0 = 0; b0 < v->con_len; b0 += CH) {
+        if (v->content) {
+            CU(cudaMalloc(&h->d_text2, nwords * sizeof(uint32_t)));
+            CU(cudaMemset(h->d_text2, 0, nwords * sizeof(uint32_t)));
+        }
+        for (uint64_t b0 = 0; v->content && b0 < v->con_len; b0 += CH) {
             uint64_t nb = (v->con_len - b0 < CH) ? v->con_len - b0 : CH;
             STEP(upload_chunk(d_stage, v->content + b0, nb, s));
             uint64_t nw = (nb + 15) >> 4;
@@ -377,26 +387,37 @@ extern "C" int as_gpu_open(as_gpu **out, int device, const as_index_view *v) {
 extern "C" int as_gpu_open_opts(as_gpu **out, int device, const as_index_view *v, const as_open_opts *opts) {
     if (!out || !v) return AS_EINVAL;
     *out = nullptr;
-    if (!v->C || !v->O || !v->bwt || !v->lc || !v->sa || !v->content || v->length < 2 || v->mta_len < 0 ||
-        (v->mta_len > 0 && !v->mta)) {
+    /* C, O and the BWT are the index; lc / sa / content may be NULL (a lookup-only handle: the scalar wrappers of
+     * libaccseq_compat open one from a bare dna_fmi) -- the entries that need a missing table refuse to run */
+    if (!v->C || !v->O || !v->bwt || v->length < 2 || v->mta_len < 0 || (v->mta_len > 0 && !v->mta)) {
         as_set_error("as_gpu_open: incomplete index view");
         return AS_EINVAL;
     }
-    if (v->o_ratio <= 0 || 64 % v->o_ratio != 0) {
-        as_set_error("as_gpu_open: o_ratio %d must divide 64 (the reference builds with 32, asindex.c:138)", v->o_ratio);
+    if (v->o_ratio <= 0 || (v->o_ratio & (v->o_ratio - 1)) != 0 || v->o_ratio > (1 << 20)) {
+        as_set_error("as_gpu_open: o_ratio %d must be a power of two <= 2^20 (the reference builds with 32, asindex.c:138)", v->o_ratio);
         return AS_EINVAL;
     }
-    if (v->hlen < 1 || v->hlen > 14 || v->lc_len != (2ULL << (2 * v->hlen))) {
+    if (v->lc && (v->hlen < 1 || v->hlen > 14 || v->lc_len != (2ULL << (2 * v->hlen)))) {
         as_set_error("as_gpu_open: hlen %d / lc_len %llu inconsistent", v->hlen, (unsigned long long)v->lc_len);
         return AS_EINVAL;
     }
-    if (v->sa_entry_bytes != 4 && v->sa_entry_bytes != 5 && v->sa_entry_bytes != 8) {
+    if (v->sa && v->sa_entry_bytes != 4 && v->sa_entry_bytes != 5 && v->sa_entry_bytes != 8) {
         as_set_error("as_gpu_open: sa_entry_bytes must be 4, 5 or 8");
         return AS_EINVAL;
     }
-    if (v->length >= (1ULL << 40) || v->con_len < v->length - 1) {
+    if (v->length >= (1ULL << 40) || (v->content && v->con_len < v->length - 1)) {
         as_set_error("as_gpu_open: bad length/con_len");
         return AS_EINVAL;
+    }
+    /* seq_lookup here is a binary search (the reference scans linearly and takes the first match, alnmain.c:151-176):
+     * the entries must be sorted by offset and tile the text the way create_meta lays them out (asindex.c:89-93) */
+    for (int i = 0; i < v->mta_len; i++) {
+        const uint64_t want = i == 0 ? 0 : v->mta[i - 1].offset + 2 * v->mta[i - 1].seq_len;
+        if (v->mta[i].offset != want || v->mta[i].offset + 2 * v->mta[i].seq_len > v->length) {
+            as_set_error("as_gpu_open: mta entry %d (offset %llu, seq_len %llu) does not tile the .cat text", i,
+                         (unsigned long long)v->mta[i].offset, (unsigned long long)v->mta[i].seq_len);
+            return AS_EINVAL;
+        }
     }
     as_gpu *h = as_handle_new(device);
     if (!h) return AS_ENODEV;

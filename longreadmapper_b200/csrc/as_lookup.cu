@@ -53,9 +53,13 @@ __global__ void __launch_bounds__(128) k_lc_aln_ascii(DevIndex ix, const char *_
     for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
         const uint8_t *s = (const uint8_t *)q + i * (uint64_t)qlen;
         uint64_t k = 1, l = ix.N - 1;                                   /* alnmain.c:354 */
+        if (use_table == 2) {                                           /* fmi_aln from the caller's interval (fmidx.c:303) */
+            k = ko[i];
+            l = lo[i];
+        }
         int left = qlen;
         bool absent = false;
-        if (use_table && qlen >= ix.hlen) {                             /* lchash.c:93-96 */
+        if (use_table == 1 && qlen >= ix.hlen) {                        /* lchash.c:93-96 */
             left = qlen - ix.hlen;
             uint64_t code = 0;
             for (int t = 0; t < ix.hlen; t++) code |= (uint64_t)as_base_code(s[left + t]) << (2 * t);
@@ -63,7 +67,7 @@ __global__ void __launch_bounds__(128) k_lc_aln_ascii(DevIndex ix, const char *_
             k = kl.x;
             l = kl.y;
             absent = (k == 0 && l == 0);                                /* lchash.c:101 */
-        } else if (use_table) {
+        } else if (use_table == 1) {
             left = qlen - ix.hlen;                                      /* negative: no steps (lchash.c:90,103) */
         }
         uint64_t r = 0;
@@ -91,12 +95,20 @@ __global__ void __launch_bounds__(256) k_sa_access(DevIndex ix, const uint64_t *
 static int aln_batch(as_gpu *h, const char *q, int qlen, size_t n, int use_table, uint64_t *k, uint64_t *l, uint64_t *r) {
     if (!h || !q || !k || !l || !r || qlen < 0) return AS_EINVAL;
     if (n == 0) return AS_OK;
+    if (use_table == 1 && !h->ix.lc) {
+        as_set_error("as_lc_aln_batch: the handle was opened without an lc table");
+        return AS_EINVAL;
+    }
     AS_CUDA(cudaSetDevice(h->device));
     size_t qb = n * (size_t)qlen;
     AS_TRY(as_scratch(h, &h->misc[0], qb + 16));
     AS_TRY(as_scratch(h, &h->misc[1], n * 3 * sizeof(uint64_t)));
     uint64_t *d_out = (uint64_t *)h->misc[1].p;
     AS_CUDA(cudaMemcpyAsync(h->misc[0].p, q, qb, cudaMemcpyHostToDevice, h->stream));
+    if (use_table == 2) {
+        AS_CUDA(cudaMemcpyAsync(d_out, k, n * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
+        AS_CUDA(cudaMemcpyAsync(d_out + n, l, n * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
+    }
     uint64_t blocks = (n + 127) / 128, cap = (uint64_t)h->sm_count * 16;
     k_lc_aln_ascii<<<(unsigned)(blocks < cap ? blocks : cap), 128, 0, h->stream>>>(h->ix, (const char *)h->misc[0].p, qlen, n,
                                                                                  use_table, d_out, d_out + n, d_out + 2 * n);
@@ -117,9 +129,49 @@ extern "C" int as_fmi_aln_batch(as_gpu *h, const char *qry, int qlen, size_t n, 
     return aln_batch(h, qry, qlen, n, 0, k, l, r);
 }
 
+extern "C" int as_fmi_aln_from_batch(as_gpu *h, const char *qry, int qlen, size_t n, uint64_t *k, uint64_t *l, uint64_t *r) {
+    return aln_batch(h, qry, qlen, n, 2, k, l, r);
+}
+
+/* lc_build (lchash.c:52-73) as the reference does it -- one backward search of hlen steps per k-mer from (1, N-1),
+ * (0,0) when the k-mer is absent -- but 4^hlen searches at once, a thread each; needs nothing but the FM index.
+ * Entry i of the output is the k-mer whose MSB-first code is i (_seq_from_num, lchash.c:19-33). */
+__global__ void __launch_bounds__(256) k_lc_build_bs(DevIndex ix, int hlen, uint64_t code0, uint64_t n, ulonglong2 *__restrict__ out) {
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t code = code0 + i;
+        uint64_t k = 1, l = ix.N - 1;
+        for (int t = 0; t < hlen; t++) {                                /* last base of the k-mer first: the low bits */
+            as_bs_step(ix, (uint32_t)(code >> (2 * t)) & 3u, k, l);
+            if (k > l) break;
+        }
+        out[i] = k > l ? make_ulonglong2(0, 0) : make_ulonglong2(k, l);
+    }
+}
+
+extern "C" int as_lc_build(as_gpu *h, int hlen, uint64_t *lc) {
+    if (!h || !lc || hlen < 1 || hlen > 14) return AS_EINVAL;
+    AS_CUDA(cudaSetDevice(h->device));
+    const uint64_t ncodes = 1ULL << (2 * hlen), CH = 1ULL << 22;
+    AS_TRY(as_scratch(h, &h->misc[1], CH * sizeof(ulonglong2)));
+    for (uint64_t c0 = 0; c0 < ncodes; c0 += CH) {
+        const uint64_t n = ncodes - c0 < CH ? ncodes - c0 : CH;
+        uint64_t blocks = (n + 255) / 256, cap = (uint64_t)h->sm_count * 16;
+        k_lc_build_bs<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(h->ix, hlen, c0, n, (ulonglong2 *)h->misc[1].p);
+        h->launches++;
+        AS_CUDA(cudaGetLastError());
+        AS_CUDA(cudaMemcpyAsync(lc + 2 * c0, h->misc[1].p, n * sizeof(ulonglong2), cudaMemcpyDeviceToHost, h->stream));
+        AS_CUDA(cudaStreamSynchronize(h->stream));
+    }
+    return AS_OK;
+}
+
 extern "C" int as_sa_access_batch(as_gpu *h, const uint64_t *rows, size_t n, uint64_t *pos) {
     if (!h || !rows || !pos) return AS_EINVAL;
     if (n == 0) return AS_OK;
+    if (!h->ix.sa_lo) {
+        as_set_error("as_sa_access_batch: the handle has no suffix array");
+        return AS_EINVAL;
+    }
     AS_CUDA(cudaSetDevice(h->device));
     AS_TRY(as_scratch(h, &h->misc[0], n * sizeof(uint64_t)));
     AS_TRY(as_scratch(h, &h->misc[1], n * sizeof(uint64_t)));
