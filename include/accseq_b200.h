@@ -75,6 +75,13 @@ typedef struct as_open_opts {
     int32_t  reserved[5];
 } as_open_opts;
 int  as_gpu_open_opts(as_gpu **h, int device, const as_index_view *ix, const as_open_opts *opts);
+/* A handle WITHOUT an index: serves the aligners on explicit pairs (as_cigar_align_batch, as_edit_distance_batch) and,
+ * after as_gpu_attach_sa, as_sa_access_batch.  What libaccseq_compat's cigar_align / sa_access run on. */
+int  as_gpu_open_aligner(as_gpu **h, int device);
+/* Tables added to an open handle: a suffix array (n entries of 4, 5 or 8 bytes) for a handle opened without one, and the
+ * caller's sampled suffix array csa[i] = SA[csa_ratio*i] (dna_fmi.csa as fmi_read loads it, fmidx.c:266-271). */
+int  as_gpu_attach_sa(as_gpu *h, const void *sa, uint64_t n, int sa_entry_bytes);
+int  as_gpu_attach_csa(as_gpu *h, const uint64_t *csa, uint64_t csa_len, int csa_ratio);
 
 /* Build the index ON the GPU from the .cat text (asindex.c:97-110: forward + reverse complement per sequence,
  * one final '$') -- replaces fmi_build (fmidx.c:166-199: pSAscan suffix sort psascan/sa_use.cc:8-18, BWT
@@ -188,6 +195,9 @@ typedef struct as_stats {
     uint64_t fm_steps_exec;   /* backward-search steps the GPU really walked through the FM index; bs_steps counts the
                                * steps of the reference's loop (fmidx.c:300-310), the rest were decided by the text */
     uint64_t text_verified;   /* seeds whose one-row interval was finished by one SA + one text gather */
+    uint64_t overflow_queued; /* reads whose votes of one phase did not fit the shared-memory table (8 slots per lane of the
+                               * read's group) and were redone by the overflow pass over a table in global memory: repeat
+                               * families.  overflow_reads counts reads the overflow pass itself could not hold (never) */
 } as_stats;
 int as_gpu_stats(as_gpu *h, as_stats *out);          /* accumulated since open / last reset */
 int as_gpu_stats_reset(as_gpu *h);

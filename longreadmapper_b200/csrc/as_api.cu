@@ -464,11 +464,12 @@ extern "C" int as_gpu_stats(as_gpu *h, as_stats *out) {
     if (!h || !out) return AS_EINVAL;
     AS_CUDA(cudaSetDevice(h->device));
     AS_CUDA(cudaStreamSynchronize(h->stream));
-    unsigned long long v[14];
+    unsigned long long v[15];
     AS_CUDA(cudaMemcpy(v, h->d_stats, sizeof v, cudaMemcpyDeviceToHost));
     out->total = v[0]; out->valid = v[1]; out->n_flag4 = v[2]; out->n_flag16 = v[3]; out->sum_ed = v[4];
     out->dp_cells = v[5]; out->seeds = v[6]; out->sa_hits = v[7]; out->bs_steps = v[8]; out->overflow_reads = v[9];
     out->dp_cells_eval = v[10]; out->gact_redone = v[11]; out->fm_steps_exec = v[12]; out->text_verified = v[13];
+    out->overflow_queued = v[14];
     return AS_OK;
 }
 
@@ -489,6 +490,10 @@ extern "C" int as_vote_batch(as_gpu *h, const as_params *p, const char *reads, s
                              size_t n, uint64_t *best_key, uint64_t *best_val, int32_t *phases, int32_t *from_outer) {
     if (!h || !p || !reads || !lens || stride == 0) return AS_EINVAL;
     if (n == 0) return AS_OK;
+    if (!h->ix.lc || !h->ix.text2 || !(h->ix.sa_lo || h->d_csa_lo)) {
+        as_set_error("as_vote_batch: lookup-only handle (opened without lc table, suffix array or text)");
+        return AS_EINVAL;
+    }
     AS_CUDA(cudaSetDevice(h->device));
     uint32_t max_len = 0;
     for (size_t i = 0; i < n; i++)

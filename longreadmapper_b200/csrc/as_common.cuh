@@ -38,8 +38,11 @@ struct DevIndex {
     const unsigned long long *lc2;   /* deep table (as_lc2.cu): row | rows << 40 per hlen2-mer, LSB-first code; may be NULL */
     int hlen2;
     const unsigned long long *sax;   /* SA[row] | 12 preceding text bases << 40 (as_lc2.cu); may be NULL */
-    const uint32_t *sa_lo;      /* low 32 bits of SA[row] */
+    const uint32_t *sa_lo;      /* low 32 bits of SA[row]; NULL on a handle that keeps only the sampled SA */
     const uint8_t *sa_hi;       /* bits 32..39, NULL when N <= 2^32 */
+    const uint32_t *csa_lo;     /* sampled SA: SA[csa_ratio * i] (fmidx.c:152-163), low 32 bits; NULL when not sampled */
+    const uint8_t *csa_hi;
+    uint32_t csa_ratio;
     const uint32_t *text2;      /* .cat text, 2 bits per base, 16 bases per word, LSB first */
     const as_mta *mta;
     int mta_len;
@@ -109,6 +112,8 @@ as_gpu *as_handle_new(int device);                        /* as_index.cu: device
 int as_build_big(as_gpu *h, const char *content, uint64_t N, const as_mta *mta, int mta_len, int hlen,
                  uint64_t part_max);                      /* as_build_big.cu: partitioned suffix sort, 40-bit rows */
 int as_build_lc2(as_gpu *h);                              /* as_lc2.cu: deep k-mer table from the device index */
+int as_csa_sample(as_gpu *h, int csa_ratio);              /* as_lookup.cu: SA[csa_ratio * i] into the handle */
+int as_launch_split_sa(as_gpu *h, const uint8_t *d_in, int entry_bytes, uint64_t n, uint32_t *d_lo, uint8_t *d_hi);
 int as_launch_pack_text(as_gpu *h, const uint8_t *d_in, uint64_t n, uint32_t *d_out);   /* ASCII text -> 2-bit words */
 int as_scratch(as_gpu *h, ScratchBuf *b, size_t bytes);   /* ensure capacity (device memory) */
 int as_pinned(as_gpu *h, size_t bytes);                   /* ensure h->h_pin capacity */

@@ -371,6 +371,21 @@ as_gpu *as_handle_new(int device) {
     return h;
 }
 
+int as_launch_split_sa(as_gpu *h, const uint8_t *d_in, int entry_bytes, uint64_t n, uint32_t *d_lo, uint8_t *d_hi) {
+    int grid = (int)((n + 255) / 256 < 148 * 16 ? (n + 255) / 256 : 148 * 16);
+    k_split_sa<<<grid ? grid : 1, 256, 0, h->stream>>>(d_in, entry_bytes, n, d_lo, d_hi);
+    h->launches++;
+    AS_CUDA(cudaGetLastError());
+    return AS_OK;
+}
+
+/* a handle without an index: the aligners on explicit pairs (as_cigar_align_batch, as_edit_distance_batch) need none */
+extern "C" int as_gpu_open_aligner(as_gpu **out, int device) {
+    if (!out) return AS_EINVAL;
+    *out = as_handle_new(device);
+    return *out ? AS_OK : AS_ENODEV;
+}
+
 int as_launch_pack_text(as_gpu *h, const uint8_t *d_in, uint64_t n, uint32_t *d_out) {
     uint64_t nw = (n + 15) >> 4;
     int grid = (int)((nw + 255) / 256 < 148 * 16 ? (nw + 255) / 256 : 148 * 16);

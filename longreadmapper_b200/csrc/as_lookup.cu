@@ -241,28 +241,115 @@ __global__ void __launch_bounds__(256) k_csa_access(DevIndex ix, const uint32_t 
     }
 }
 
+/* SA[csa_ratio * i] from the device SA into the handle (replaces a previous sample) */
+int as_csa_sample(as_gpu *h, int csa_ratio) {
+    if (h->d_csa_lo) cudaFree(h->d_csa_lo);
+    if (h->d_csa_hi) cudaFree(h->d_csa_hi);
+    h->d_csa_lo = h->d_csa_hi = nullptr;
+    h->csa_ratio = 0;
+    h->ix.csa_lo = nullptr;
+    h->ix.csa_hi = nullptr;
+    h->ix.csa_ratio = 0;
+    const uint64_t len = h->ix.N / (uint64_t)csa_ratio + 1;
+    AS_CUDA(cudaMalloc(&h->d_csa_lo, len * sizeof(uint32_t)));
+    if (h->ix.sa_hi) AS_CUDA(cudaMalloc(&h->d_csa_hi, len));
+    uint64_t blocks = (len + 255) / 256, cap = (uint64_t)h->sm_count * 16;
+    k_csa_sample<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(h->ix, (uint64_t)csa_ratio, len,
+                                                                                (uint32_t *)h->d_csa_lo, (uint8_t *)h->d_csa_hi);
+    h->launches++;
+    AS_CUDA(cudaGetLastError());
+    h->csa_ratio = csa_ratio;
+    h->ix.csa_lo = (const uint32_t *)h->d_csa_lo;
+    h->ix.csa_hi = (const uint8_t *)h->d_csa_hi;
+    h->ix.csa_ratio = (uint32_t)csa_ratio;
+    return AS_OK;
+}
+
+/* the caller's sampled array (dna_fmi.csa as fmi_read loaded it, fmidx.c:266-271) instead of one sampled here */
+extern "C" int as_gpu_attach_csa(as_gpu *h, const uint64_t *csa, uint64_t csa_len, int csa_ratio) {
+    if (!h || !csa || csa_ratio <= 0) return AS_EINVAL;
+    AS_CUDA(cudaSetDevice(h->device));
+    if (csa_len < (h->ix.N + (uint64_t)csa_ratio - 1) / (uint64_t)csa_ratio) {
+        as_set_error("as_gpu_attach_csa: %llu samples do not cover %llu rows at ratio %d", (unsigned long long)csa_len,
+                     (unsigned long long)h->ix.N, csa_ratio);
+        return AS_EINVAL;
+    }
+    AS_CUDA(cudaStreamSynchronize(h->stream));
+    if (h->d_csa_lo) cudaFree(h->d_csa_lo);
+    if (h->d_csa_hi) cudaFree(h->d_csa_hi);
+    h->d_csa_lo = h->d_csa_hi = nullptr;
+    h->csa_ratio = 0;
+    uint32_t *lo = (uint32_t *)malloc(csa_len * sizeof(uint32_t));
+    uint8_t *hi = (uint8_t *)malloc(csa_len);
+    if (!lo || !hi) {
+        free(lo);
+        free(hi);
+        return AS_ENOMEM;
+    }
+    bool wide = false;
+    for (uint64_t i = 0; i < csa_len; i++) {
+        lo[i] = (uint32_t)csa[i];
+        hi[i] = (uint8_t)(csa[i] >> 32);
+        wide |= hi[i] != 0;
+    }
+    cudaError_t e = cudaMalloc(&h->d_csa_lo, csa_len * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMemcpy(h->d_csa_lo, lo, csa_len * sizeof(uint32_t), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && wide) e = cudaMalloc(&h->d_csa_hi, csa_len);
+    if (e == cudaSuccess && wide) e = cudaMemcpy(h->d_csa_hi, hi, csa_len, cudaMemcpyHostToDevice);
+    free(lo);
+    free(hi);
+    AS_CUDA(e);
+    h->csa_ratio = csa_ratio;
+    h->ix.csa_lo = (const uint32_t *)h->d_csa_lo;
+    h->ix.csa_hi = (const uint8_t *)h->d_csa_hi;
+    h->ix.csa_ratio = (uint32_t)csa_ratio;
+    return AS_OK;
+}
+
+/* a suffix array for a handle that was opened without one (or an aligner-only handle: then sa_access is all it serves) */
+extern "C" int as_gpu_attach_sa(as_gpu *h, const void *sa, uint64_t n, int entry_bytes) {
+    if (!h || !sa || n == 0 || (entry_bytes != 4 && entry_bytes != 5 && entry_bytes != 8)) return AS_EINVAL;
+    if (h->ix.N != 0 && n > h->ix.N) return AS_EINVAL;
+    AS_CUDA(cudaSetDevice(h->device));
+    AS_CUDA(cudaStreamSynchronize(h->stream));
+    if (h->d_sa_lo) cudaFree(h->d_sa_lo);
+    if (h->d_sa_hi) cudaFree(h->d_sa_hi);
+    h->d_sa_lo = h->d_sa_hi = nullptr;
+    h->ix.sa_lo = nullptr;
+    h->ix.sa_hi = nullptr;
+    const uint64_t rows = h->ix.N ? h->ix.N : n;
+    AS_CUDA(cudaMalloc(&h->d_sa_lo, rows * sizeof(uint32_t)));
+    AS_CUDA(cudaMemset(h->d_sa_lo, 0, rows * sizeof(uint32_t)));
+    if (entry_bytes > 4 && rows > (1ULL << 32)) {
+        AS_CUDA(cudaMalloc(&h->d_sa_hi, rows));
+        AS_CUDA(cudaMemset(h->d_sa_hi, 0, rows));
+    }
+    const uint64_t CH = 1ULL << 24;
+    AS_TRY(as_scratch(h, &h->misc[0], CH * 8));
+    for (uint64_t r0 = 0; r0 < n; r0 += CH) {
+        const uint64_t nr = n - r0 < CH ? n - r0 : CH;
+        AS_CUDA(cudaMemcpyAsync(h->misc[0].p, (const uint8_t *)sa + r0 * (uint64_t)entry_bytes, nr * (size_t)entry_bytes,
+                                cudaMemcpyHostToDevice, h->stream));
+        AS_TRY(as_launch_split_sa(h, (const uint8_t *)h->misc[0].p, entry_bytes, nr, (uint32_t *)h->d_sa_lo + r0,
+                                  h->d_sa_hi ? (uint8_t *)h->d_sa_hi + r0 : nullptr));
+        AS_CUDA(cudaStreamSynchronize(h->stream));
+    }
+    h->ix.sa_lo = (const uint32_t *)h->d_sa_lo;
+    h->ix.sa_hi = (const uint8_t *)h->d_sa_hi;
+    if (h->ix.N == 0) h->ix.N = n;
+    return AS_OK;
+}
+
 extern "C" int as_csa_access_batch(as_gpu *h, int csa_ratio, int literal, const uint64_t *rows, size_t n, uint64_t *pos) {
     if (!h || !rows || !pos || csa_ratio <= 0) return AS_EINVAL;
     if (n == 0) return AS_OK;
     AS_CUDA(cudaSetDevice(h->device));
-    if (!h->ix.sa_lo) {
-        as_set_error("as_csa_access_batch: the handle has no suffix array to sample");
-        return AS_EINVAL;
-    }
     if (h->csa_ratio != csa_ratio) {                                    /* (re)sample: _build_csa */
-        if (h->d_csa_lo) cudaFree(h->d_csa_lo);
-        if (h->d_csa_hi) cudaFree(h->d_csa_hi);
-        h->d_csa_lo = h->d_csa_hi = nullptr;
-        h->csa_ratio = 0;
-        const uint64_t len = h->ix.N / (uint64_t)csa_ratio + 1;
-        AS_CUDA(cudaMalloc(&h->d_csa_lo, len * sizeof(uint32_t)));
-        if (h->ix.sa_hi) AS_CUDA(cudaMalloc(&h->d_csa_hi, len));
-        uint64_t blocks = (len + 255) / 256, cap = (uint64_t)h->sm_count * 16;
-        k_csa_sample<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(h->ix, (uint64_t)csa_ratio, len,
-                                                                                    (uint32_t *)h->d_csa_lo, (uint8_t *)h->d_csa_hi);
-        h->launches++;
-        AS_CUDA(cudaGetLastError());
-        h->csa_ratio = csa_ratio;
+        if (!h->ix.sa_lo) {
+            as_set_error("as_csa_access_batch: the handle has neither a suffix array to sample nor an attached csa of ratio %d", csa_ratio);
+            return AS_EINVAL;
+        }
+        AS_TRY(as_csa_sample(h, csa_ratio));
     }
     AS_TRY(as_scratch(h, &h->misc[0], n * sizeof(uint64_t)));
     AS_TRY(as_scratch(h, &h->misc[1], n * sizeof(uint64_t)));

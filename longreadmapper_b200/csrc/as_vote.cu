@@ -165,6 +165,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
     const int left0 = sl - hl;
     const uint64_t hmask = (1ULL << (2 * hl)) - 1ULL;
     unsigned long long st_seeds = 0, st_steps = 0, st_hits = 0, st_ovf = 0;
+    unsigned int st_queued = 0;                  /* reads this warp handed to the overflow (BIG) pass */
     unsigned int st_fm = 0, st_txt = 0;          /* FM steps done here / tails decided by the text */
 
     /* state of the read this group owns */
@@ -587,6 +588,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                     a.out[read] = o;
                 } else {
                     a.ovf_list[atomicAdd(a.ovf_count, 1u)] = read;           /* redone by the BIG pass */
+                    st_queued++;
                 }
             }
             if (finished && overflow && BIG) st_ovf += (g == 0);
@@ -604,6 +606,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
         st_ovf += __shfl_xor_sync(0xFFFFFFFFu, st_ovf, d);
         st_fm += __shfl_xor_sync(0xFFFFFFFFu, st_fm, d);
         st_txt += __shfl_xor_sync(0xFFFFFFFFu, st_txt, d);
+        st_queued += __shfl_xor_sync(0xFFFFFFFFu, st_queued, d);
     }
     if (lane == 0) {
         if (st_seeds) atomicAdd(a.stats + 6, st_seeds);
@@ -612,6 +615,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
         if (st_ovf) atomicAdd(a.stats + 9, st_ovf);
         if (st_fm) atomicAdd(a.stats + 12, (unsigned long long)st_fm);
         if (st_txt) atomicAdd(a.stats + 13, (unsigned long long)st_txt);
+        if (st_queued) atomicAdd(a.stats + 14, (unsigned long long)st_queued);
     }
 }
 
@@ -638,6 +642,12 @@ int as_launch_vote(as_gpu *h, const as_params *p, const uint32_t *d_pack, size_t
     /* BIG table: every vote of one phase fits at load factor <= 1/2 */
     uint64_t seeds_per_phase = max_len > (uint32_t)sl ? ((uint64_t)(max_len - sl) + P - 1) / P : 1;
     uint64_t max_votes = seeds_per_phase * (uint64_t)(p->thres > 1 ? p->thres - 1 : 1);
+    /* the vote order key (seed index in the phase) * thres + (row offset) is a 32-bit word, and the overflow table holds
+     * at most 2^30 slots: batches beyond either are refused instead of silently breaking the TOP2 tie order */
+    if (seeds_per_phase * (uint64_t)p->thres >= (1ULL << 32) || 2 * max_votes > (1ULL << 30)) {
+        as_set_error("as_map_batch: a read of %u bases with thres %u needs more vote slots than the overflow table has", max_len, p->thres);
+        return AS_ERANGE;
+    }
     uint32_t big_cap = next_pow2(2 * max_votes);
     size_t big_stride = ((size_t)big_cap * 24 + 64 + 255) & ~(size_t)255;
     size_t budget = (size_t)2 << 30;

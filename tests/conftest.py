@@ -47,6 +47,25 @@ def make_repeat_rich(lm, seed):
     return a, b
 
 
+def make_high_copy(lm, seed):
+    """~400 kbp with exact repeat families of 12, 50 and 250 copies: reads inside them vote for more distinct buckets in
+    one phase than the shared-memory table of PART 1 holds (8 slots per lane), so they go through the overflow pass."""
+    g = lm.sim_genome(seed, 400_000)
+    lm.sim_plant_repeats(seed + 1, g, n_families=3, unit_len=2000, copies=12, divergence=0.0)
+    lm.sim_plant_repeats(seed + 2, g, n_families=2, unit_len=1000, copies=50, divergence=0.0)
+    lm.sim_plant_repeats(seed + 3, g, n_families=1, unit_len=400, copies=250, divergence=0.0)
+    lm.sim_plant_repeats(seed + 4, g, n_families=2, unit_len=6000, copies=14, divergence=0.002)
+    return g
+
+
+@pytest.fixture(scope="session")
+def idx_high_copy(native, orc):
+    g = make_high_copy(native, 71)
+    ix = orc.OracleIndex.build(["rep"], [g.tobytes()])
+    yield ix, [g]
+    ix.close()
+
+
 @pytest.fixture(scope="session")
 def idx_uniform(native, orc):
     g = make_uniform(native, 11, 200_000)

@@ -128,6 +128,35 @@ def test_vote_repeat_rich(native, gpu_repeat, idx_repeat, wide):
         check_vote(gpu_repeat, ix, reads, lens, flags=wide)
 
 
+@pytest.mark.parametrize("wide", [0, 16])
+def test_vote_overflow_pass_high_copy_repeats(native, idx_high_copy, wide):
+    """exact repeat families of 12, 50 and 250 copies: a phase of a read inside one votes for more distinct buckets than the
+    shared-memory table holds (8 per lane of the group), the read is queued and redone by the overflow pass
+    (k_vote<32, BIG>) over a table in global memory.  Same votes as the oracle, and the queue was really used."""
+    ix, gs = idx_high_copy
+    m = oracle_lib.gpu_mapper(native, ix, 0)
+    try:
+        queued = 0
+        for k, (n, lmin, lmax, e, sl, th) in enumerate([(1500, 150, 150, 0.01, 20, 300), (600, 150, 150, 0.02, 20, 1000),
+                                                          (400, 100, 250, 0.03, 16, 300), (60, 1000, 6000, 0.08, 20, 300),
+                                                          (40, 1000, 4000, 0.05, 20, 1000)]):
+            reads, lens, _ = reads_from(native, 1300 + k, gs, n, lmin, lmax, e, e, 0.7)
+            m.stats_reset()
+            check_vote(m, ix, reads, lens, sl, th, flags=wide)
+            st = m.stats()
+            assert st["overflow_reads"] == 0
+            queued += st["overflow_queued"]
+            if k < 2:
+                assert st["overflow_queued"] > 0, "no read took the overflow pass: the test does not reach it"
+        assert queued > 50
+        # and the whole path on them
+        reads, lens, stride = reads_from(native, 1350, gs, 1200, 100, 300, 0.0, 0.05, 0.6)
+        compare_map(native, m, ix, reads, lens, stride)
+        assert m.stats()["overflow_queued"] > 0
+    finally:
+        m.close()
+
+
 @pytest.mark.parametrize("seed_len,thres", [(12, 300), (16, 50), (24, 300), (32, 1000), (20, 2)])
 def test_vote_parameters(native, gpu_repeat, idx_repeat, seed_len, thres):
     ix, gs = idx_repeat
