@@ -175,6 +175,30 @@ typedef struct as_result {
 int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t stride, const uint32_t *lens, size_t n,
                  as_result *results, uint8_t *store_mem, size_t store_stride);
 
+/*
+ * as_map_batch_packed -- the same path for hosts that hold reads 2-bit packed (what the FASTQ ingest of libaccseq_host.so
+ * produces while it parses) and want records, not buffers, back: 44 B per 150-bp read cross PCIe on the way in and about
+ * 22 B on the way out, instead of 155 + 104 (refactor_reads_seq buffer in, as_result + run-byte rows out).
+ *   packed     read i at packed + i*wstride: 16 bases per 32-bit word, base j at bits [2(j&15), 2(j&15)+1] of word j>>4,
+ *              A0 C1 G2 T3 (bytes outside ACGT take the code of ((c>>1)&3)^((c>>2)&1), as the ASCII path does; the reference's
+ *              behaviour for them is undefined, lchash.c:38-45); bits past lens[i] must be zero; wstride >= ceil(max len / 16)
+ *   results    n compact records (below)
+ *   runs       run bytes ((len << 2) | class, as AS_F_RLE_CIGAR) of read 0, read 1, ... back to back: read i's start at the
+ *              sum of results[j].n_runs over j < i.  runs_cap = capacity; *runs_len = bytes written.  AS_ERANGE when the
+ *              capacity does not suffice (runs_len then holds the size needed; results are complete).
+ * Strand-1 reads are NOT handed back reverse-complemented: the emitter does that as it prints (as AS_F_KEEP_READS).
+ * Every as_result field can be recomputed from a record (as_result_from_compact in accseq_host.h); phases / from_outer /
+ * myers are not carried.
+ */
+typedef struct as_result_compact {
+    uint64_t pos;        /* bits 0..39 off (0-based forward offset, SAM POS - 1); bits 40..55 seq_id + 1 (0 = seq_lookup failed);
+                          * bits 56..63 flag (0, 16 or 4) */
+    int32_t  ed;         /* GACT score, -1 = failure */
+    uint32_t n_runs;     /* run bytes of this read */
+} as_result_compact;
+int as_map_batch_packed(as_gpu *h, const as_params *p, const uint32_t *packed, size_t wstride, const uint32_t *lens, size_t n,
+                        as_result_compact *results, uint8_t *runs, size_t runs_cap, uint64_t *runs_len);
+
 /* Same path with every buffer already resident in device memory (pointers are device addresses); used to
  * time the kernels without PCIe and by frameworks that keep reads on the GPU. */
 int as_map_batch_device(as_gpu *h, const as_params *p, char *d_reads, size_t stride, const uint32_t *d_lens,

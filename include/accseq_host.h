@@ -58,6 +58,11 @@ int  as_cigar_text_rle(const uint8_t *runs, int n_runs, char *buf, size_t buflen
 int  as_sam_record2(FILE *out, const as_host_index *ix, const char *qname, size_t qname_len, const char *seq,
                     const char *qual, uint32_t len, const as_result *r, const uint8_t *ops, unsigned map_flags);
 
+/* ---- 2-bit packing for as_map_batch_packed (layout: include/accseq_b200.h) and the as_result of a compact record ---- */
+void as_pack_read(const char *seq, uint32_t len, uint32_t *out, size_t nwords);      /* nwords >= ceil(len/16); the rest is zeroed */
+int  as_pack_reads(const char *ascii, size_t stride, const uint32_t *lens, size_t n, uint32_t *packed, size_t wstride);
+void as_result_from_compact(const as_result_compact *c, uint32_t len, const as_mta *mta, int mta_len, as_result *r);
+
 /* ---- FASTQ ingest (accaln.c:45-58 reads_load + alnmain.c:87-103 refactor_reads_seq) ---- */
 typedef struct as_read_batch {
     size_t    n;

@@ -26,6 +26,11 @@ RESULT_DTYPE = np.dtype([("loc", "<u8"), ("off", "<u8"), ("seq_id", "<i4"), ("st
 assert RESULT_DTYPE.itemsize == 56
 
 
+# as_result_compact (include/accseq_b200.h)
+COMPACT_DTYPE = np.dtype([("pos", "<u8"), ("ed", "<i4"), ("n_runs", "<u4")])
+assert COMPACT_DTYPE.itemsize == 16
+
+
 class AccSeqError(RuntimeError):
     pass
 
@@ -113,6 +118,7 @@ def cuda_lib():
     L.as_params_default.argtypes = [C.POINTER(Params)]
     L.as_params_default.restype = None
     L.as_map_batch.argtypes = [vp, C.POINTER(Params), vp, sz, vp, sz, vp, vp, sz]
+    L.as_map_batch_packed.argtypes = [vp, C.POINTER(Params), vp, sz, vp, sz, vp, vp, sz, C.POINTER(u64)]
     L.as_map_batch_device.argtypes = [vp, C.POINTER(Params), vp, sz, vp, sz, C.c_uint32, vp, vp, sz]
     L.as_gpu_stats.argtypes = [vp, C.POINTER(AsStats)]
     L.as_gpu_stats_reset.argtypes = [vp]
@@ -158,6 +164,9 @@ def host_lib():
     L.as_index_out_of.argtypes = [C.POINTER(AsHostIndex), vp]
     L.as_index_out_of.restype = None
     L.as_index_write.argtypes = [C.c_char_p, C.POINTER(AsHostIndex)]
+    L.as_pack_reads.argtypes = [vp, sz, vp, sz, vp, sz]
+    L.as_result_from_compact.argtypes = [vp, C.c_uint32, vp, C.c_int, vp]
+    L.as_result_from_compact.restype = None
     L.as_cigar_text.argtypes = [vp, C.c_int, C.c_char_p, sz]
     L.as_cigar_text_rle.argtypes = [vp, C.c_int, C.c_char_p, sz]
     _host = L
@@ -195,6 +204,31 @@ def sim_reads(seed, genome, n_reads, len_min, len_max, err_min, err_max, sub_fra
     if got != n_reads:
         raise AccSeqError("as_sim_reads: genome too short for these reads")
     return reads, lens, pos, strand
+
+
+def pack_reads(reads, lens, wstride=None):
+    """2-bit packing of a refactor_reads_seq buffer (uint8 [n, stride]) for as_map_batch_packed: uint32 [n, wstride]."""
+    reads = np.ascontiguousarray(reads)
+    lens = np.ascontiguousarray(lens, dtype=np.uint32)
+    n, stride = reads.shape
+    if wstride is None:
+        wstride = (int(lens.max()) + 15) // 16 if n else 1
+    out = np.zeros((n, wstride), dtype=np.uint32)
+    rc = host_lib().as_pack_reads(reads.ctypes.data, stride, lens.ctypes.data, n, out.ctypes.data, wstride)
+    if rc != 0:
+        raise AccSeqError(f"as_pack_reads failed ({rc})")
+    return out
+
+
+def results_from_compact(rec, lens, mta):
+    """as_result records (RESULT_DTYPE) recomputed from compact ones."""
+    rec = np.ascontiguousarray(rec)
+    out = np.zeros(rec.size, dtype=RESULT_DTYPE)
+    marr = (AsMta * max(1, len(mta)))(*[AsMta(int(o), int(s)) for (o, s) in mta])
+    H = host_lib()
+    for i in range(rec.size):
+        H.as_result_from_compact(rec[i:].ctypes.data, int(lens[i]), C.cast(marr, C.c_void_p), len(mta), out[i:].ctypes.data)
+    return out
 
 
 def cat_image(seqs):
@@ -368,6 +402,23 @@ class GpuMapper:
         self._check(self.L.as_map_batch(self.h, C.byref(p), reads.ctypes.data, stride, lens.ctypes.data, n,
                                         res.ctypes.data, _ptr(ops), store_stride or 0), "as_map_batch")
         return res, ops
+
+    def map_batch_packed(self, packed, lens, params=None, runs_cap=None):
+        """packed: uint32 [n, wstride] (pack_reads). Returns (compact records, dense run bytes)."""
+        p = params or self.params()
+        packed = np.ascontiguousarray(packed, dtype=np.uint32)
+        n, wstride = packed.shape
+        lens = np.ascontiguousarray(lens, dtype=np.uint32)
+        rec = np.zeros(n, dtype=COMPACT_DTYPE)
+        if runs_cap is None:
+            runs_cap = int(2 * lens.astype(np.int64).sum()) + 16
+        runs = np.zeros(runs_cap, dtype=np.uint8)
+        got = C.c_uint64(0)
+        rc = self.L.as_map_batch_packed(self.h, C.byref(p), packed.ctypes.data, wstride, lens.ctypes.data, n, rec.ctypes.data,
+                                        runs.ctypes.data, runs_cap, C.byref(got))
+        if rc != 0:
+            raise AccSeqError(f"as_map_batch_packed failed ({rc}): {self.L.as_last_error().decode()}")
+        return rec, runs[: int(got.value)]
 
     def map_batch_device(self, d_reads_ptr, stride, d_lens_ptr, n, max_len, d_res_ptr, d_store_ptr, store_stride,
                          params=None):

@@ -96,7 +96,7 @@ __global__ void __launch_bounds__(256) k_locus(DevIndex ix, char *__restrict__ a
             const size_t rr = base + (size_t)src;
             uint8_t *s = (uint8_t *)ascii + rr * stride;
             uint32_t *pw = pack + rr * wstride;
-            const uint32_t half = rl >> 1;
+            const uint32_t half = ascii ? rl >> 1 : 0u;                  /* packed-only batch (as_map_batch_packed): no ASCII copy */
             bool other = false;                                          /* a byte outside ACGT/acgt */
             for (uint32_t i = lane; i < half; i += 32) {
                 const uint32_t ca = comp_ascii(s[i]), cb = comp_ascii(s[rl - 1 - i]);
@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(256) k_locus(DevIndex ix, char *__restrict__ a
                 s[i] = (uint8_t)cb;
                 s[rl - 1 - i] = (uint8_t)ca;
             }
-            if ((rl & 1u) && lane == 0) {
+            if (ascii && (rl & 1u) && lane == 0) {
                 const uint32_t cm = comp_ascii(s[half]);
                 other |= cm == 'N';
                 s[half] = (uint8_t)cm;
@@ -138,7 +138,8 @@ __global__ void __launch_bounds__(256) k_locus(DevIndex ix, char *__restrict__ a
 __global__ void __launch_bounds__(256) k_locus_long(DevIndex ix, char *__restrict__ ascii, size_t stride,
                                                const uint32_t *__restrict__ lens, size_t n, uint32_t *__restrict__ pack,
                                                size_t wstride, const VoteOut *__restrict__ vote,
-                                               as_result *__restrict__ res, uint64_t *__restrict__ toff) {
+                                               as_result *__restrict__ res, uint64_t *__restrict__ toff,
+                                               uint32_t *__restrict__ tmp_rows) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint64_t warp0 = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
     const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
@@ -180,7 +181,24 @@ __global__ void __launch_bounds__(256) k_locus_long(DevIndex ix, char *__restric
             res[r] = o;
             toff[r] = seq_id < 0 ? AS_TOFF_NONE : fwd;
         }
-        if (strand == 1) {                                               /* alnmain.c:433-438 */
+        if (strand == 1 && !ascii) {
+            /* packed-only batch: out word w = complement of input bases [len-16w-16, len-16w), last first -- built in this
+             * warp's scratch row (an output word reads input words from the other end of the read), then copied back */
+            uint32_t *pw = pack + r * wstride;
+            uint32_t *tw = tmp_rows + warp0 * wstride;
+            const uint32_t nw = (len + 15) >> 4;
+            for (uint32_t w = lane; w < nw; w += 32) {
+                const long st = (long)len - 16 * (long)w - 16;
+                const uint32_t cnt = st >= 0 ? 16u : (uint32_t)(16 + st);
+                const uint32_t x = as_bases16(pw, (uint64_t)(st > 0 ? st : 0));
+                uint32_t y = ~rev2(x) >> (2u * (16u - cnt));
+                if (cnt < 16u) y &= (1u << (2u * cnt)) - 1u;
+                tw[w] = y;
+            }
+            __syncwarp();
+            for (uint32_t w = lane; w < nw; w += 32) pw[w] = tw[w];
+            __syncwarp();
+        } else if (strand == 1) {                                        /* alnmain.c:433-438 */
             uint8_t *s = (uint8_t *)ascii + r * stride;
             const uint32_t half = len >> 1;
             for (uint32_t i = lane; i < half; i += 32) {
@@ -205,8 +223,14 @@ int as_launch_locus(as_gpu *h, char *d_ascii, size_t stride, const uint32_t *d_l
     if (n == 0) return AS_OK;
     if (wstride > 32 + 3) {                              /* reads of more than 512 bases in the batch */
         uint64_t blocks = (n + 7) / 8, cap = (uint64_t)h->sm_count * 8;
-        k_locus_long<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(h->ix, d_ascii, stride, d_lens, n, d_pack,
-                                                                                   wstride, d_vote, d_res, d_toff);
+        const unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
+        uint32_t *tmp_rows = nullptr;
+        if (!d_ascii) {                                  /* one scratch row per warp for the packed reverse complement */
+            AS_TRY(as_scratch(h, &h->locus_tmp, (size_t)grid * 8 * wstride * sizeof(uint32_t)));
+            tmp_rows = (uint32_t *)h->locus_tmp.p;
+        }
+        k_locus_long<<<grid, 256, 0, h->stream>>>(h->ix, d_ascii, stride, d_lens, n, d_pack, wstride, d_vote, d_res, d_toff,
+                                                  tmp_rows);
         h->launches++;
         AS_CUDA(cudaGetLastError());
         return AS_OK;

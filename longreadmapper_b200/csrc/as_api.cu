@@ -27,9 +27,13 @@ static size_t pack_wstride(uint32_t max_len) { return ((size_t)max_len + 15) / 1
 
 /* all device-side stages of n reads, asynchronous on h->stream; ev[0..4] bracket the stages.  `slot0` is the index
  * of the first read inside the handle's per-read scratch (qpack / vote / toff), so chunks of one batch do not overlap. */
+__global__ void k_restride(const uint32_t *__restrict__ in, size_t win, const uint32_t *__restrict__ lens, size_t n,
+                           uint32_t *__restrict__ out, size_t ws);
+
 static int run_stages(as_gpu *h, const as_params *p, char *d_reads, size_t stride, const uint32_t *d_lens, size_t n,
                       uint32_t max_len, as_result *d_res, uint8_t *d_store, size_t store_stride, bool stop_after_vote,
-                      VoteOut **vote_out, cudaEvent_t *ev, size_t slot0, size_t slots) {
+                      VoteOut **vote_out, cudaEvent_t *ev, size_t slot0, size_t slots,
+                      const uint32_t *d_packed_in = nullptr, size_t wstride_in = 0) {
     const size_t ws = pack_wstride(max_len);
     AS_TRY(as_scratch(h, &h->qpack, slots * ws * sizeof(uint32_t)));
     AS_TRY(as_scratch(h, &h->vote, slots * sizeof(VoteOut)));
@@ -39,7 +43,14 @@ static int run_stages(as_gpu *h, const as_params *p, char *d_reads, size_t strid
     uint64_t *d_toff = (uint64_t *)h->toff.p + slot0;
     if (vote_out) *vote_out = d_vote;
     AS_CUDA(cudaEventRecord(ev[0], h->stream));
-    AS_TRY(as_launch_pack(h, d_reads, stride, d_lens, n, d_pack, ws));
+    if (d_packed_in) {                       /* reads arrived 2-bit packed (as_map_batch_packed): only the row stride changes */
+        const uint64_t total = (uint64_t)n * ws, blocks = (total + 255) / 256, cap = (uint64_t)h->sm_count * 32;
+        k_restride<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(d_packed_in, wstride_in, d_lens, n, d_pack, ws);
+        h->launches++;
+        AS_CUDA(cudaGetLastError());
+    } else {
+        AS_TRY(as_launch_pack(h, d_reads, stride, d_lens, n, d_pack, ws));
+    }
     AS_TRY(as_launch_vote(h, p, d_pack, ws, d_lens, n, max_len, d_vote));
     AS_CUDA(cudaEventRecord(ev[1], h->stream));
     if (stop_after_vote) return AS_OK;
@@ -418,6 +429,297 @@ static int map_batch_impl(as_gpu *h, const as_params *p, char *reads, size_t str
     h->last_ms[6] = ev_ms(h->ev_d2h0, h->ev[7]);
     h->last_ms[7] = ev_ms(h->ev[0], h->ev[6]);
     return AS_OK;
+}
+
+/* ---------------------------------------------------------------------------------------------- */
+/* packed reads in, compact records + dense run bytes out                                          */
+/* ---------------------------------------------------------------------------------------------- */
+/* host rows of `win` words -> device rows of `ws` words (3 words of slack for the funnel-shift readers); bits past the
+ * read's length are cleared whatever the host left there */
+__global__ void __launch_bounds__(256) k_restride(const uint32_t *__restrict__ in, size_t win, const uint32_t *__restrict__ lens,
+                                                  size_t n, uint32_t *__restrict__ out, size_t ws) {
+    const uint64_t total = (uint64_t)n * ws;
+    for (uint64_t g = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; g < total; g += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t r = g / ws;
+        const uint32_t w = (uint32_t)(g - r * ws), len = lens[r], b0 = w << 4;
+        uint32_t v = 0;
+        if (b0 < len && w < win) {
+            v = in[r * win + w];
+            if (len - b0 < 16) v &= (1u << (2 * (len - b0))) - 1u;
+        }
+        out[g] = v;
+    }
+}
+
+#define CR_READS 256         /* reads per block of the compaction kernels */
+/* pass 1: the compact record of every read, and the run bytes of each block of CR_READS reads */
+__global__ void __launch_bounds__(CR_READS) k_compact_records(const as_result *__restrict__ res, size_t n,
+                                                              as_result_compact *__restrict__ out,
+                                                              unsigned long long *__restrict__ block_sum) {
+    __shared__ unsigned long long s_w[CR_READS / 32];
+    const size_t i = (size_t)blockIdx.x * CR_READS + threadIdx.x;
+    unsigned long long mine = 0;
+    if (i < n) {
+        const as_result r = res[i];
+        as_result_compact c;
+        const uint32_t nr = r.n_cigar_op > 0 && r.seq_id >= 0 ? (uint32_t)r.n_cigar_op : 0u;
+        c.pos = (r.off & 0xFFFFFFFFFFULL) | ((uint64_t)(uint16_t)(r.seq_id + 1) << 40) | ((uint64_t)(uint8_t)r.flag << 56);
+        c.ed = r.ed;
+        c.n_runs = nr;
+        out[i] = c;
+        mine = nr;
+    }
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) mine += __shfl_xor_sync(0xFFFFFFFFu, mine, d);
+    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = mine;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long t = 0;
+        for (int w = 0; w < CR_READS / 32; w++) t += s_w[w];
+        block_sum[blockIdx.x] = t;
+    }
+}
+
+/* pass 2: exclusive scan of the block sums by one block, offset by the run bytes of the chunks before (*base, advanced
+ * here); the chunk's total lands in *total */
+__global__ void __launch_bounds__(1024) k_scan_block_sums(unsigned long long *__restrict__ block_sum, size_t nb,
+                                                          unsigned long long *__restrict__ base, unsigned long long *__restrict__ total) {
+    __shared__ unsigned long long s_w[32];
+    __shared__ unsigned long long s_carry;
+    const unsigned long long base0 = *base;                   /* run bytes of the chunks before this one */
+    __syncthreads();
+    if (threadIdx.x == 0) s_carry = base0;
+    __syncthreads();
+    for (size_t b0 = 0; b0 < nb; b0 += 1024) {
+        const size_t i = b0 + threadIdx.x;
+        const unsigned long long v = i < nb ? block_sum[i] : 0;
+        unsigned long long inc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned long long o = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+            if ((threadIdx.x & 31) >= d) inc += o;
+        }
+        if ((threadIdx.x & 31) == 31) s_w[threadIdx.x >> 5] = inc;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            unsigned long long w = s_w[threadIdx.x], wi = w;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const unsigned long long o = __shfl_up_sync(0xFFFFFFFFu, wi, d);
+                if (threadIdx.x >= d) wi += o;
+            }
+            s_w[threadIdx.x] = wi - w;                       /* exclusive over the warps */
+        }
+        __syncthreads();
+        const unsigned long long excl = s_carry + s_w[threadIdx.x >> 5] + inc - v;
+        if (i < nb) block_sum[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = excl + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        *total = s_carry - base0;
+        *base = s_carry;
+    }
+}
+
+/* pass 3: every warp places the run bytes of its 32 reads behind one another in the dense buffer */
+__global__ void __launch_bounds__(CR_READS) k_gather_runs(const as_result_compact *__restrict__ rec, size_t n,
+                                                          const uint8_t *__restrict__ rows, size_t stride,
+                                                          const unsigned long long *__restrict__ block_off,
+                                                          uint8_t *__restrict__ dense, unsigned long long cap) {
+    __shared__ unsigned long long s_w[CR_READS / 32];
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const size_t i = (size_t)blockIdx.x * CR_READS + threadIdx.x;
+    const uint32_t nr = i < n ? rec[i].n_runs : 0u;
+    unsigned long long inc = nr;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const unsigned long long o = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+        if (lane >= (uint32_t)d) inc += o;
+    }
+    if (lane == 31) s_w[warp] = inc;
+    __syncthreads();
+    unsigned long long base = block_off[blockIdx.x];
+    for (uint32_t w = 0; w < warp; w++) base += s_w[w];
+    const unsigned long long my_off = base + inc - nr;
+    for (int src = 0; src < 32; src++) {
+        const uint32_t cnt = __shfl_sync(0xFFFFFFFFu, nr, src);
+        if (cnt == 0) continue;
+        const unsigned long long off = __shfl_sync(0xFFFFFFFFu, my_off, src);
+        if (off + cnt > cap) continue;                       /* the caller's buffer is too small: reported through the total */
+        const uint8_t *s = rows + ((size_t)blockIdx.x * CR_READS + warp * 32 + (size_t)src) * stride;
+        for (uint32_t b = lane; b < cnt; b += 32) dense[off + b] = s[b];
+    }
+}
+
+static int map_batch_packed_impl(as_gpu *h, const as_params *p, const uint32_t *packed, size_t wstride, const uint32_t *lens,
+                                 size_t n, as_result_compact *results, uint8_t *runs, size_t runs_cap, uint64_t *runs_len);
+
+extern "C" int as_map_batch_packed(as_gpu *h, const as_params *p, const uint32_t *packed, size_t wstride, const uint32_t *lens,
+                                   size_t n, as_result_compact *results, uint8_t *runs, size_t runs_cap, uint64_t *runs_len) {
+    if (!h || !p || !packed || !lens || !results || wstride == 0 || (!runs && runs_cap) || !runs_len) {
+        as_set_error("as_map_batch_packed: NULL argument");
+        return AS_EINVAL;
+    }
+    if (!h->ix.lc || !h->ix.text2 || !(h->ix.sa_lo || h->d_csa_lo)) {
+        as_set_error("as_map_batch_packed: lookup-only handle (opened without lc table, suffix array or text)");
+        return AS_EINVAL;
+    }
+    if (p->flags & (AS_F_MYERS | AS_F_NO_ALIGN)) {
+        as_set_error("as_map_batch_packed: AS_F_MYERS / AS_F_NO_ALIGN have no field in the compact record; use as_map_batch");
+        return AS_EINVAL;
+    }
+    *runs_len = 0;
+    if (n == 0) return AS_OK;
+    AS_CUDA(cudaSetDevice(h->device));
+    AS_TRY(ensure_pipeline(h));
+    const int rc = map_batch_packed_impl(h, p, packed, wstride, lens, n, results, runs, runs_cap, runs_len);
+    if (rc != AS_OK && rc != AS_ERANGE) {
+        cudaStreamSynchronize(h->s_h2d);
+        cudaStreamSynchronize(h->stream);
+        cudaStreamSynchronize(h->s_d2h);
+        cudaGetLastError();
+    }
+    return rc;
+}
+
+/* chunk plan of the packed path: copies are a small fraction of the kernel time, so a small first chunk (its H2D is the
+ * only exposed one), two large ones, and a small last chunk (its D2H is the only exposed one) */
+static int plan_chunks_packed(const as_params *p, size_t n, size_t row_bytes, size_t *begin) {
+    int nc = 0;
+    begin[0] = 0;
+    if (p->chunk_reads) {
+        size_t fixed = p->chunk_reads;
+        if ((n + fixed - 1) / fixed > AS_MAX_CHUNKS) fixed = (n + AS_MAX_CHUNKS - 1) / AS_MAX_CHUNKS;
+        for (size_t r = 0; r < n; r += fixed) begin[++nc] = (r + fixed < n) ? r + fixed : n;
+        return nc;
+    }
+    const size_t min_reads = 32768;
+    size_t by_bytes = ((size_t)1 << 30) / (row_bytes ? row_bytes : 1);       /* long reads: at most ~1 GB of op rows per chunk */
+    if (by_bytes < 1024) by_bytes = 1024;
+    if (n < 4 * min_reads && n <= by_bytes) {
+        begin[++nc] = n;
+        return nc;
+    }
+    size_t edge = n / 8;
+    if (edge < min_reads) edge = min_reads;
+    size_t mid = (n - 2 * edge + 1) / 2;
+    if (mid > by_bytes) mid = by_bytes;
+    if (edge > mid) edge = mid;
+    size_t r = edge;
+    begin[++nc] = r;
+    while (n - r > edge + mid / 8 && nc < AS_MAX_CHUNKS - 2) {
+        const size_t take = n - r - edge < mid ? n - r - edge : mid;
+        r += take;
+        begin[++nc] = r;
+    }
+    begin[++nc] = n;
+    return nc;
+}
+
+static int map_batch_packed_impl(as_gpu *h, const as_params *p, const uint32_t *packed, size_t wstride, const uint32_t *lens,
+                                 size_t n, as_result_compact *results, uint8_t *runs, size_t runs_cap, uint64_t *runs_len) {
+    uint32_t max_len = 0;
+    for (size_t i = 0; i < n; i++) max_len = lens[i] > max_len ? lens[i] : max_len;
+    if (((size_t)max_len + 15) / 16 > wstride) {
+        as_set_error("as_map_batch_packed: a read of %u bases does not fit %zu words", max_len, wstride);
+        return AS_EINVAL;
+    }
+    const size_t ws = pack_wstride(max_len), store_stride = (2 * (size_t)max_len + 15) & ~(size_t)15;
+    size_t cb[AS_MAX_CHUNKS + 1];
+    const int nc = plan_chunks_packed(p, n, store_stride, cb);
+    h->n_chunks_last = nc;
+    size_t max_chunk = 0;
+    for (int c = 0; c < nc; c++) max_chunk = cb[c + 1] - cb[c] > max_chunk ? cb[c + 1] - cb[c] : max_chunk;
+    /* every buffer is sized before anything is enqueued (growing one waits for the stream).  The op rows and the
+     * as_result records are chunk-local scratch: the kernels of all chunks share one stream, so a chunk has read them
+     * before the next one writes.  The dense run bytes of the whole batch collect in one buffer (worst case: every
+     * column its own run), so no chunk ever waits for another one's copy to leave. */
+    AS_TRY(as_scratch(h, &h->pack_in, n * wstride * sizeof(uint32_t)));
+    AS_TRY(as_scratch(h, &h->lens, n * sizeof(uint32_t)));
+    AS_TRY(as_scratch(h, &h->qpack, n * ws * sizeof(uint32_t)));
+    AS_TRY(as_scratch(h, &h->vote, n * sizeof(VoteOut)));
+    AS_TRY(as_scratch(h, &h->toff, n * sizeof(uint64_t)));
+    AS_TRY(as_scratch(h, &h->results, max_chunk * sizeof(as_result)));
+    AS_TRY(as_scratch(h, &h->store, max_chunk * store_stride));
+    AS_TRY(as_scratch(h, &h->runs, n * store_stride));
+    AS_TRY(as_scratch(h, &h->cres, n * sizeof(as_result_compact)));
+    const size_t nblk_max = (max_chunk + CR_READS - 1) / CR_READS;
+    AS_TRY(as_scratch(h, &h->run_tot, (AS_MAX_CHUNKS + nblk_max + 8) * sizeof(unsigned long long)));
+    if (max_len > (uint32_t)p->gact_T) AS_TRY(as_gact_order_reserve(h, max_chunk));
+    if (!h->h_run_tot) {
+        AS_CUDA(cudaMallocHost((void **)&h->h_run_tot, AS_MAX_CHUNKS * sizeof(unsigned long long)));
+        AS_CUDA(cudaStreamCreateWithFlags(&h->s_d2h2, cudaStreamNonBlocking));
+    }
+    uint32_t *d_in = (uint32_t *)h->pack_in.p;
+    uint32_t *d_lens = (uint32_t *)h->lens.p;
+    as_result *d_res = (as_result *)h->results.p;
+    uint8_t *d_rows = (uint8_t *)h->store.p, *d_dense = (uint8_t *)h->runs.p;
+    as_result_compact *d_cres = (as_result_compact *)h->cres.p;
+    /* run_tot: [0] running base of the dense buffer, [1 .. AS_MAX_CHUNKS] total per chunk, then the per-block sums */
+    unsigned long long *d_base = (unsigned long long *)h->run_tot.p, *d_tot = d_base + 1, *d_bsum = d_base + 1 + AS_MAX_CHUNKS;
+
+    AS_CUDA(cudaEventRecord(h->ev[0], h->stream));
+    AS_CUDA(cudaStreamWaitEvent(h->s_h2d, h->ev[0], 0));
+    AS_CUDA(cudaStreamWaitEvent(h->s_d2h, h->ev[0], 0));
+    AS_CUDA(cudaStreamWaitEvent(h->s_d2h2, h->ev[0], 0));
+    for (int c = 0; c < nc; c++) {
+        const size_t r0 = cb[c], cn = cb[c + 1] - cb[c];
+        AS_CUDA(cudaMemcpyAsync(d_in + r0 * wstride, packed + r0 * wstride, cn * wstride * sizeof(uint32_t), cudaMemcpyHostToDevice, h->s_h2d));
+        AS_CUDA(cudaMemcpyAsync(d_lens + r0, lens + r0, cn * sizeof(uint32_t), cudaMemcpyHostToDevice, h->s_h2d));
+        AS_CUDA(cudaEventRecord(h->cev[c][5], h->s_h2d));
+    }
+    h->last_h2d_bytes = n * wstride * sizeof(uint32_t) + n * sizeof(uint32_t);
+    h->last_d2h_bytes = n * sizeof(as_result_compact) + (size_t)nc * sizeof(unsigned long long);
+    as_params q = *p;
+    q.flags |= AS_F_RLE_CIGAR | AS_F_KEEP_READS;
+    AS_CUDA(cudaMemsetAsync(d_base, 0, sizeof(unsigned long long), h->stream));
+    /* the kernels of every chunk are enqueued first ... */
+    for (int c = 0; c < nc; c++) {
+        const size_t r0 = cb[c], cn = cb[c + 1] - cb[c];
+        AS_CUDA(cudaStreamWaitEvent(h->stream, h->cev[c][5], 0));
+        AS_TRY(run_stages(h, &q, nullptr, 0, d_lens + r0, cn, max_len, d_res, d_rows, store_stride, false, nullptr, h->cev[c], r0, n,
+                          d_in + r0 * wstride, wstride));
+        AS_TRY(count_results(h, d_res, cn, nullptr));
+        const unsigned nblk = (unsigned)((cn + CR_READS - 1) / CR_READS);
+        k_compact_records<<<nblk, CR_READS, 0, h->stream>>>(d_res, cn, d_cres + r0, d_bsum);
+        k_scan_block_sums<<<1, 1024, 0, h->stream>>>(d_bsum, nblk, d_base, d_tot + c);
+        k_gather_runs<<<nblk, CR_READS, 0, h->stream>>>(d_cres + r0, cn, d_rows, store_stride, d_bsum, d_dense,
+                                                       (unsigned long long)(n * store_stride));
+        h->launches += 3;
+        AS_CUDA(cudaGetLastError());
+        AS_CUDA(cudaEventRecord(h->cev[c][6], h->stream));
+        AS_CUDA(cudaStreamWaitEvent(h->s_d2h, h->cev[c][6], 0));
+        if (c == 0) AS_CUDA(cudaEventRecord(h->ev_d2h0, h->s_d2h));
+        AS_CUDA(cudaMemcpyAsync(h->h_run_tot + c, d_tot + c, sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->s_d2h));
+        AS_CUDA(cudaEventRecord(h->cev[c][7], h->s_d2h));
+        AS_CUDA(cudaMemcpyAsync(results + r0, d_cres + r0, cn * sizeof(as_result_compact), cudaMemcpyDeviceToHost, h->s_d2h));
+    }
+    AS_CUDA(cudaEventRecord(h->ev[7], h->s_d2h));
+    /* ... then the dense run bytes of each chunk leave, on their own stream, as soon as the chunk's total is known here */
+    uint64_t host_off = 0;
+    int rc_out = AS_OK;
+    for (int c = 0; c < nc; c++) {
+        AS_CUDA(cudaEventSynchronize(h->cev[c][7]));
+        const uint64_t tot = h->h_run_tot[c];
+        if (host_off + tot > runs_cap) rc_out = AS_ERANGE;
+        else if (tot) AS_CUDA(cudaMemcpyAsync(runs + host_off, d_dense + host_off, tot, cudaMemcpyDeviceToHost, h->s_d2h2));
+        host_off += tot;
+    }
+    h->last_d2h_bytes += host_off;
+    AS_CUDA(cudaEventRecord(h->ev[8], h->s_d2h2));
+    AS_CUDA(cudaStreamWaitEvent(h->stream, h->ev[7], 0));
+    AS_CUDA(cudaStreamWaitEvent(h->stream, h->ev[8], 0));
+    AS_CUDA(cudaEventRecord(h->ev[6], h->stream));
+    AS_CUDA(cudaStreamSynchronize(h->stream));
+    finish_timing(h);
+    h->last_ms[5] = ev_ms(h->ev[0], h->cev[nc - 1][5]);
+    h->last_ms[6] = ev_ms(h->ev_d2h0, h->ev[6]);
+    h->last_ms[7] = ev_ms(h->ev[0], h->ev[6]);
+    *runs_len = host_off;
+    if (rc_out == AS_ERANGE) as_set_error("as_map_batch_packed: %llu run bytes do not fit runs_cap %zu", (unsigned long long)host_off, runs_cap);
+    return rc_out;
 }
 
 extern "C" int as_map_batch_device(as_gpu *h, const as_params *p, char *d_reads, size_t stride, const uint32_t *d_lens,

@@ -69,6 +69,8 @@ struct as_gpu {
     ScratchBuf reads, lens, results, store, qpack, tpack, toff, vote, counters, ovf_list, ovf_table, misc[6];
     ScratchBuf gact_planes, gact_tb;     /* bit-parallel GACT: traceback planes / packed tile ops, per resident warp */
     ScratchBuf gact_order;               /* bit-parallel GACT: reads by decreasing length (multi-tile batches) */
+    ScratchBuf locus_tmp;                /* packed-only long reads: one scratch row per warp for the reverse complement */
+    ScratchBuf pack_in, cres, runs, run_tot;   /* as_map_batch_packed: tight packed rows in, compact records + dense run bytes out */
     /* pinned staging for small D2H/H2D */
     void *h_pin = nullptr;
     size_t h_pin_cap = 0;
@@ -77,7 +79,7 @@ struct as_gpu {
     cudaEvent_t ev[10]{};
     float last_ms[8]{};
     /* chunked pipeline of as_map_batch: H2D of chunk i+1 | kernels of chunk i | D2H of chunk i-1 */
-    cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+    cudaStream_t s_h2d = nullptr, s_d2h = nullptr, s_d2h2 = nullptr;
     cudaEvent_t cev[AS_MAX_CHUNKS][8]{};   /* per chunk: [0..4] stage marks, [5] H2D done, [6] kernels done, [7] fixed D2H done */
     cudaEvent_t ev_d2h0 = nullptr;         /* first D2H issued */
     bool cev_ready = false;
@@ -86,6 +88,7 @@ struct as_gpu {
     bool timing_pending = false;           /* as_map_batch_device enqueued a call whose events were not read yet */
     int *d_chunk_max = nullptr;            /* per chunk: max n_cigar_op (trims the CIGAR-column D2H) */
     int *h_chunk_max = nullptr;            /* pinned mirror */
+    unsigned long long *h_run_tot = nullptr;   /* pinned: run bytes per chunk (as_map_batch_packed) */
     unsigned int *h_band = nullptr, *d_band = nullptr;   /* adaptive GACT band: mapped pinned word + its device alias */
     int sm_count = 148;
     size_t l2_bytes = 126u << 20;

@@ -171,7 +171,8 @@ extern "C" void as_gpu_close(as_gpu *h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     free_index(h);
     ScratchBuf *bufs[] = {&h->reads, &h->lens, &h->results, &h->store, &h->qpack, &h->tpack, &h->toff,
-                          &h->vote, &h->counters, &h->ovf_list, &h->ovf_table, &h->gact_planes, &h->gact_tb, &h->gact_order};
+                          &h->vote, &h->counters, &h->ovf_list, &h->ovf_table, &h->gact_planes, &h->gact_tb, &h->gact_order,
+                          &h->locus_tmp, &h->pack_in, &h->cres, &h->runs, &h->run_tot};
     for (ScratchBuf *b : bufs) free_scratch(b);
     for (ScratchBuf &b : h->misc) free_scratch(&b);
     if (h->h_pin) cudaFreeHost(h->h_pin);
@@ -184,9 +185,11 @@ extern "C" void as_gpu_close(as_gpu *h) {
     if (h->ev_d2h0) cudaEventDestroy(h->ev_d2h0);
     if (h->d_chunk_max) cudaFree(h->d_chunk_max);
     if (h->h_chunk_max) cudaFreeHost(h->h_chunk_max);
+    if (h->h_run_tot) cudaFreeHost(h->h_run_tot);
     if (h->h_band) cudaFreeHost(h->h_band);
     if (h->s_h2d) cudaStreamDestroy(h->s_h2d);
     if (h->s_d2h) cudaStreamDestroy(h->s_d2h);
+    if (h->s_d2h2) cudaStreamDestroy(h->s_d2h2);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     delete h;
 }

@@ -1,0 +1,67 @@
+/*
+ * pack.c -- host side of as_map_batch_packed: 2-bit packing of reads (the layout include/accseq_b200.h describes) and the
+ * as_result a compact record stands for.  Plain C, no CUDA.
+ */
+#include "accseq_host.h"
+
+#include <string.h>
+
+/* four ASCII bases -> eight bits: per byte ((c >> 1) & 3) ^ ((c >> 2) & 1) = A0 C1 G2 T3 (upper or lower case; the code the
+ * device's as_base_code gives every other byte too), then the four 2-bit codes gathered into the top byte by one 32-bit
+ * multiply: the partial products that matter land on bits 24-25, 26-27, 28-29, 30-31, the others below bit 24 or past bit 31 */
+static inline uint32_t pack4(uint32_t x) {
+    const uint32_t c = ((x >> 1) & 0x03030303u) ^ ((x >> 2) & 0x01010101u);
+    return (uint32_t)(c * 0x01041040u) >> 24;
+}
+
+static inline uint32_t pack8(uint64_t x) { return pack4((uint32_t)x) | pack4((uint32_t)(x >> 32)) << 8; }
+
+void as_pack_read(const char *seq, uint32_t len, uint32_t *out, size_t nwords) {
+    size_t w = 0;
+    uint32_t i = 0;
+    for (; i + 16 <= len && w < nwords; i += 16, w++) {
+        uint64_t a, b;
+        memcpy(&a, seq + i, 8);
+        memcpy(&b, seq + i + 8, 8);
+        out[w] = pack8(a) | pack8(b) << 16;
+    }
+    if (i < len && w < nwords) {
+        uint32_t v = 0;
+        for (uint32_t t = 0; i + t < len; t++) {
+            const uint32_t c = (uint8_t)seq[i + t];
+            v |= ((((c >> 1) & 3u) ^ ((c >> 2) & 1u))) << (2 * t);
+        }
+        out[w++] = v;
+    }
+    for (; w < nwords; w++) out[w] = 0;
+}
+
+int as_pack_reads(const char *ascii, size_t stride, const uint32_t *lens, size_t n, uint32_t *packed, size_t wstride) {
+    if (!ascii || !lens || !packed) return AS_EINVAL;
+    for (size_t r = 0; r < n; r++) {
+        if (((size_t)lens[r] + 15) / 16 > wstride || lens[r] > stride) return AS_EINVAL;
+        as_pack_read(ascii + r * stride, lens[r], packed + r * wstride, wstride);
+    }
+    return AS_OK;
+}
+
+/* the fields of as_result a compact record determines (alnmain.c:458-477; loc per seq_lookup, alnmain.c:151-176) */
+void as_result_from_compact(const as_result_compact *c, uint32_t len, const as_mta *mta, int mta_len, as_result *r) {
+    memset(r, 0, sizeof *r);
+    const int seq_id = (int)((c->pos >> 40) & 0xFFFFu) - 1;
+    r->off = c->pos & 0xFFFFFFFFFFULL;
+    r->seq_id = seq_id;
+    r->flag = (int)(c->pos >> 56);
+    r->strand = (r->flag & 16) ? 1 : 0;
+    r->mapq = (r->flag & 4) ? 0 : 255;
+    r->ed = c->ed;
+    r->valid = !(r->flag & 4);
+    r->n_cigar_op = (int32_t)c->n_runs;
+    r->myers = -2;
+    if (seq_id >= 0 && seq_id < mta_len && mta) {
+        const uint64_t start = mta[seq_id].offset, sl = mta[seq_id].seq_len;
+        /* a failed alignment keeps flag 4 but still has a locus; the strand is then not in the flag: it cannot be told
+         * from the record, and loc is reported for the forward copy */
+        r->loc = r->strand ? start + 2 * sl - r->off - len : start + r->off;
+    }
+}

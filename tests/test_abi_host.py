@@ -62,6 +62,27 @@ def test_no_cpu_fallback(native):
         native.GpuMapper.build([g], 0)
 
 
+def test_pack_reads_layout(native):
+    """as_pack_reads: base j of a read at bits [2(j&15), 2(j&15)+1] of word j>>4, A0 C1 G2 T3 for either case, other bytes the
+    code ((c>>1)&3)^((c>>2)&1) the device gives them, bits past the length zero"""
+    g = native.sim_genome(1, 5000)
+    reads, lens, _, _ = native.sim_reads(2, g, 60, 1, 333, 0.0, 0.0, 1.0)
+    reads[3, 0] = ord("N")
+    reads[4, :10] = np.frombuffer(b"acgtnACGTN", np.uint8)
+    pk = native.pack_reads(reads, lens, wstride=25)
+    for r in range(60):
+        L = int(lens[r])
+        c = reads[r, :L].astype(np.uint32)
+        code = ((c >> 1) & 3) ^ ((c >> 2) & 1)
+        got = (pk[r, np.arange(L) >> 4] >> (2 * (np.arange(L) & 15)).astype(np.uint32)) & 3
+        assert np.array_equal(got, code), r
+        if L & 15:
+            assert pk[r, L >> 4] >> (2 * (L & 15)) == 0
+        assert not pk[r, (L + 15) // 16:].any()
+    with pytest.raises(native.AccSeqError):
+        native.pack_reads(reads, lens, wstride=2)
+
+
 def test_params_default(native):
     p = native.Params()
     native.cuda_lib().as_params_default(C.byref(p))

@@ -314,6 +314,58 @@ def test_map_compact_output(native, gpu_repeat, idx_repeat, gact):
             assert int((runs[i, :m] >> 2).sum()) == n
 
 
+def check_packed_equals_full(native, m, ix, reads, lens, **knobs):
+    """as_map_batch_packed (2-bit reads in, compact records + dense run bytes out) against as_map_batch on the same reads:
+    every as_result field a record carries, and the run bytes equal to the AS_F_RLE_CIGAR rows read by read"""
+    flags = native.AS_F_RLE_CIGAR | native.AS_F_KEEP_READS
+    full, rows = m.map_batch(reads.copy(), lens, params=m.params(flags=flags))
+    rec, dense = m.map_batch_packed(native.pack_reads(reads, lens), lens, params=m.params(**knobs))
+    back = native.results_from_compact(rec, lens, [(o, s) for (_, o, s) in ix.mta])
+    mapped = full["seq_id"] >= 0
+    for f in ("off", "seq_id", "flag", "mapq", "ed", "valid"):
+        assert np.array_equal(back[f], full[f]), f
+    assert np.array_equal(back["strand"][full["flag"] != 4], full["strand"][full["flag"] != 4])
+    assert np.array_equal(back["loc"][mapped & (full["flag"] != 4)], full["loc"][mapped & (full["flag"] != 4)])
+    want_n = np.where(mapped, np.maximum(full["n_cigar_op"], 0), 0)
+    assert np.array_equal(rec["n_runs"], want_n.astype(np.uint32))
+    offs = np.concatenate([[0], np.cumsum(rec["n_runs"].astype(np.int64))])
+    assert offs[-1] == dense.size
+    for i in range(len(lens)):
+        assert np.array_equal(dense[offs[i]:offs[i + 1]], rows[i, : want_n[i]]), i
+    return rec, dense
+
+
+@pytest.mark.parametrize("chunk", [0, 777])
+def test_map_packed_compact_short(native, gpu_repeat, idx_repeat, chunk):
+    ix, gs = idx_repeat
+    reads, lens, _ = reads_from(native, 641, gs, 2500, 30, 300, 0.0, 0.1, 0.5)
+    rec, dense = check_packed_equals_full(native, gpu_repeat, ix, reads, lens, chunk_reads=chunk)
+    assert (rec["pos"] >> 56 == 16).sum() > 500
+    h2d, d2h = gpu_repeat.last_transfer()
+    assert h2d == len(lens) * (4 * ((int(lens.max()) + 15) // 16) + 4) and d2h < len(lens) * 16 + dense.size + 1024
+
+
+def test_map_packed_compact_long_and_edge(native, gpu_repeat, idx_repeat):
+    """reads of several tiles (packed reverse complement through the per-warp scratch row), reads with a byte outside ACGT,
+    reads that fail seq_lookup, a one-read batch, a too-small runs buffer"""
+    ix, (a, b) = idx_repeat
+    reads, lens, _ = reads_from(native, 701, [a, b], 70, 400, 5000, 0.05, 0.15, 0.34)
+    reads[3, 100] = ord("N")
+    reads[5, :60] = np.frombuffer(b"acgt" * 15, np.uint8)
+    check_packed_equals_full(native, gpu_repeat, ix, reads, lens)
+    check_packed_equals_full(native, gpu_repeat, ix, reads, lens, chunk_reads=9)
+    edge = np.zeros((4, 151), np.uint8)
+    edge[0, :150] = np.concatenate([a[-75:], b[:75]])
+    edge[1, :150] = np.frombuffer(b"ACGT", np.uint8)[np.random.default_rng(1).integers(0, 4, 150)]
+    edge[2, :21] = a[1000:1021]
+    edge[3, :150] = a[500:650]
+    el = np.array([150, 150, 21, 150], np.uint32)
+    check_packed_equals_full(native, gpu_repeat, ix, edge, el)
+    check_packed_equals_full(native, gpu_repeat, ix, edge[3:], el[3:])
+    with pytest.raises(native.AccSeqError):
+        gpu_repeat.map_batch_packed(native.pack_reads(reads, lens), lens, runs_cap=10)
+
+
 def test_map_empty_and_single(native, gpu_uniform, idx_uniform):
     ix, (g,) = idx_uniform
     res, ops = gpu_uniform.map_batch(np.zeros((0, 151), np.uint8), np.zeros(0, np.uint32))
