@@ -54,6 +54,10 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=0, help="reads in the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--knob", action="append", default=[], metavar="K=V",
+                    help="as_params scheduling knob (vote_ectx, gact_order, gact_blocks_per_sm, chunk_reads, chunk_tail); A/B runs")
+    ap.add_argument("--opt", action="append", default=[], metavar="K=V",
+                    help="as_open_opts field (lc2_hlen, no_sax, build_part_max, sampled_sa); A/B runs")
     ap.add_argument("--gact-band", type=int, default=None,
                     help="half-width of GACT's banded first pass (default: adaptive; -1 = full matrix only); results do not depend on it")
     return ap.parse_args()
@@ -286,7 +290,11 @@ def run_b200(args):
     # ---- inputs: the index replica of this rank (built on the GPU) and this rank's read shard ----
     g = lm.sim_genome(GENOME_SEED, wl["genome"])
     t0 = time.time()
-    mapper = lm.GpuMapper.build([g], local)
+    oo = {}
+    for kv in args.opt:
+        k, v = kv.split("=")
+        oo[k] = int(v)
+    mapper = lm.GpuMapper.build([g], local, opts=lm.open_opts(**oo) if oo else None)
     t_index = time.time() - t0
     dev = torch.device("cuda", local)
     reads, lens, truth_pos, truth_strand = lm.sim_reads(READS_SEED + 1000 * rank, g, n, wl["len"][0], wl["len"][1],
@@ -294,7 +302,11 @@ def run_b200(args):
     stride = reads.shape[1]
     max_len = int(lens.max())
     store_stride = 2 * max_len
-    params = mapper.params(band=args.gact_band)
+    knobs = {}
+    for kv in args.knob:
+        k, v = kv.split("=")
+        knobs[k] = int(v)
+    params = mapper.params(band=args.gact_band, **knobs)
 
     # one non-default stream for everything that is timed: the library launches on it (as_gpu_set_stream), the
     # restore copy and the CUDA events are issued on it
@@ -358,6 +370,7 @@ def run_b200(args):
     # ---- e2e: host buffers through the C ABI ----
     e2e = None
     e2e_full = None
+    e2e_ascii = None
     if not args.no_e2e:
         L = mapper.L
         import ctypes as C
@@ -375,7 +388,7 @@ def run_b200(args):
         wmax = int(res["n_cigar_op"].max()) if n else 0
 
         def run_e2e(flags, pipeline):
-            ep = mapper.params(band=args.gact_band, flags=flags)
+            ep = mapper.params(band=args.gact_band, flags=flags, **knobs)
             for q in hp[3:]:
                 np.ctypeslib.as_array(C.cast(q, C.POINTER(C.c_uint8)), shape=(n, stride))[:] = reads
 
@@ -413,11 +426,64 @@ def run_b200(args):
                     "ms_per_step": ems / args.steps, "same_results_as_device_path": bool(same), "pipeline": pipeline,
                     "stage_ms_last_step": {k: round(v, 3) for k, v in e2e_tm.items()}}
 
+        def run_e2e_packed():
+            """the call accaln_b200 makes: reads 2-bit packed by the ingest threads, compact records + dense run bytes back"""
+            wst = (max_len + 15) // 16
+            packed = lm.pack_reads(reads, lens, wst)
+            runs_cap = n * 64 if max_len <= 512 else int(lens.astype(np.int64).sum())
+            bufs = [L.as_host_alloc(x) for x in (n * wst * 4, n * 16, runs_cap)]
+            if not all(bufs):
+                raise SystemExit("bench.py: pinned allocation failed")
+            np.ctypeslib.as_array(C.cast(bufs[0], C.POINTER(C.c_uint32)), shape=(n, wst))[:] = packed
+            ep = mapper.params(band=args.gact_band, **knobs)
+            got = C.c_uint64(0)
+
+            def step():
+                rc = L.as_map_batch_packed(mapper.h, C.byref(ep), bufs[0], wst, hp[0], n, bufs[1], bufs[2], runs_cap, C.byref(got))
+                if rc != 0:
+                    raise SystemExit(f"as_map_batch_packed failed ({rc}): {L.as_last_error().decode()}")
+
+            for _ in range(n_e2e_warm):
+                step()
+            barrier()
+            f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            f0.record(stream)
+            for _ in range(args.steps):
+                step()
+            f1.record(stream)
+            barrier()
+            ems = shard.max_over_ranks(f0.elapsed_time(f1), dev)
+            e2e_tm = mapper.last_timing()
+            h2d_b, d2h_b = mapper.last_transfer()
+            rec = np.ctypeslib.as_array(C.cast(bufs[1], C.POINTER(C.c_uint8)), shape=(n * 16,)).view(lm.COMPACT_DTYPE).copy()
+            dense = np.ctypeslib.as_array(C.cast(bufs[2], C.POINTER(C.c_uint8)), shape=(int(got.value),)).copy()
+            # same records as the device-resident path; the dense run bytes add up to its CIGAR columns read by read
+            mapped = res["seq_id"] >= 0
+            same = bool(np.array_equal(rec["pos"] & ((1 << 40) - 1), res["off"] & ((1 << 40) - 1))
+                        and np.array_equal(((rec["pos"] >> 40) & 0xFFFF).astype(np.int64) - 1, res["seq_id"].astype(np.int64))
+                        and np.array_equal((rec["pos"] >> 56).astype(np.int32), res["flag"]) and np.array_equal(rec["ed"], res["ed"]))
+            offs = np.concatenate([[0], np.cumsum(rec["n_runs"].astype(np.int64))])
+            cols = np.add.reduceat((dense >> 2).astype(np.int64), offs[:-1][rec["n_runs"] > 0]) if dense.size else np.zeros(0, np.int64)
+            same = same and bool(offs[-1] == dense.size) and bool(np.array_equal(cols, res["n_cigar_op"][rec["n_runs"] > 0]))
+            same = same and bool(np.array_equal(rec["n_runs"] > 0, mapped & (res["n_cigar_op"] > 0)))
+            for q in bufs:
+                L.as_host_free(q)
+            return {"value": world * n / (ems / args.steps / 1e3), "unit": "reads/s",
+                    "h2d_bytes_per_step": h2d_b, "d2h_bytes_per_step": d2h_b, "bytes_per_read": round((h2d_b + d2h_b) / n, 1),
+                    "ms_per_step": ems / args.steps, "same_results_as_device_path": bool(same),
+                    "pipeline": "as_map_batch_packed: reads cross PCIe 2-bit packed (the ingest threads pack while they parse), "
+                                "16-byte compact records and the run bytes back to back come back; chunks: every kernel enqueued up front, "
+                                "H2D(i+1) | kernels(i) | D2H(i-1), the dense run bytes on a stream of their own",
+                    "stage_ms_last_step": {k: round(v, 3) for k, v in e2e_tm.items()},
+                    "host_us_last_step": {k: round(v, 1) for k, v in mapper.last_host_timing().items()}}
+
         chunked = "chunked: H2D(i+1) | kernels(i) | D2H(i-1) on three streams; "
-        # what the host driver (accaln_b200) calls: CIGAR as run bytes, reads not copied back (the SAM it prints is the same)
-        e2e = run_e2e(lm.AS_F_RLE_CIGAR | lm.AS_F_KEEP_READS,
-                      chunked + "AS_F_RLE_CIGAR | AS_F_KEEP_READS: CIGAR crosses PCIe as run bytes, strand-1 reads are "
-                      "reverse-complemented by the SAM emitter")
+        # what the host driver (accaln_b200) calls
+        e2e = run_e2e_packed()
+        # ASCII reads in (the refactor_reads_seq buffer), CIGAR as rows of run bytes, reads not copied back
+        e2e_ascii = run_e2e(lm.AS_F_RLE_CIGAR | lm.AS_F_KEEP_READS,
+                            chunked + "AS_F_RLE_CIGAR | AS_F_KEEP_READS: CIGAR crosses PCIe as run bytes, strand-1 reads are "
+                            "reverse-complemented by the SAM emitter")
         # the reference's buffer layout to the byte: one op byte per column, strand-1 reads reverse-complemented in place
         e2e_full = run_e2e(0, chunked + "CIGAR columns trimmed to the widest row of a chunk, reads copied back")
         for p in hp:
@@ -488,7 +554,7 @@ def run_b200(args):
                              f"+ GACT planes per pass > 126 MB, no flush needed",
                        "index": "built on the GPU (as_gpu_build), replicated per rank", "index_build_s": round(t_index, 2),
                        "host_numa_node_rank0": numa},
-            "clocks": clocks, "e2e": e2e, "e2e_full_copy": e2e_full, "gpu_launches": int(launches),
+            "clocks": clocks, "e2e": e2e, "e2e_ascii_rle": e2e_ascii, "e2e_full_copy": e2e_full, "gpu_launches": int(launches),
             "roofline": roofline,
             "gcups": stages["gact"]["gcups"],
             "quality": {"mapped_frac": float(ok.mean()), "exact_pos_strand_frac": exact, "within_50bp_strand_frac": near,

@@ -231,6 +231,13 @@ int as_gpu_stats_reset(as_gpu *h);
  * [5] span of the H2D copies  [6] span of the D2H copies (as_map_batch pipelines chunks: H2D of chunk i+1, kernels of
  *     chunk i and D2H of chunk i-1 overlap, so [5] and [6] overlap the kernel time)  [7] whole call */
 int as_gpu_last_timing(as_gpu *h, float ms[8]);
+/* When the events of chunk `chunk` of the last as_map_batch / as_map_batch_packed call fired, ms after the call's start:
+ * [0] kernels begin [1] PART 1 done [2] PART 2 done [3] GACT done [4] Myers done [5] H2D of the chunk done [6] kernels done
+ * [7] fixed-size D2H of the chunk done.  Returns the number of chunks (a negative code on error). */
+int as_gpu_last_chunk_timeline(as_gpu *h, int chunk, float ms[8]);
+/* Host-side time of the last as_map_batch_packed call, microseconds: [0] until every kernel and copy was enqueued,
+ * [1] waiting for the device, [2] reading the event times.  [0] + [1] + [2] = the caller's wall time of the call. */
+int as_gpu_last_host_timing(as_gpu *h, double us[3]);
 /* Bytes the last as_map_batch moved over PCIe in each direction. */
 int as_gpu_last_transfer(as_gpu *h, uint64_t *h2d_bytes, uint64_t *d2h_bytes);
 

@@ -123,6 +123,8 @@ def cuda_lib():
     L.as_gpu_stats.argtypes = [vp, C.POINTER(AsStats)]
     L.as_gpu_stats_reset.argtypes = [vp]
     L.as_gpu_last_timing.argtypes = [vp, C.POINTER(C.c_float * 8)]
+    L.as_gpu_last_chunk_timeline.argtypes = [vp, i32, C.POINTER(C.c_float * 8)]
+    L.as_gpu_last_host_timing.argtypes = [vp, C.POINTER(C.c_double * 3)]
     L.as_gpu_last_transfer.argtypes = [vp, C.POINTER(u64), C.POINTER(u64)]
     L.as_lc_aln_batch.argtypes = [vp, vp, i32, sz, vp, vp, vp]
     L.as_fmi_aln_batch.argtypes = [vp, vp, i32, sz, vp, vp, vp]
@@ -448,6 +450,11 @@ class GpuMapper:
         self._check(self.L.as_gpu_last_timing(self.h, C.byref(ms)), "as_gpu_last_timing")
         k = ("part1", "part2", "gact", "myers", "unused", "h2d", "d2h", "total")
         return dict(zip(k, [float(x) for x in ms]))
+
+    def last_host_timing(self):
+        us = (C.c_double * 3)()
+        self._check(self.L.as_gpu_last_host_timing(self.h, C.byref(us)), "as_gpu_last_host_timing")
+        return dict(zip(("enqueue_us", "wait_us", "events_us"), [float(x) for x in us]))
 
     def last_transfer(self):
         a, b = C.c_uint64(0), C.c_uint64(0)

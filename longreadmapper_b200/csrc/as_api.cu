@@ -4,6 +4,13 @@
  */
 #include "as_common.cuh"
 #include <stdlib.h>
+#include <time.h>
+
+static double now_us(void) {
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return 1e6 * (double)ts.tv_sec + 1e-3 * (double)ts.tv_nsec;
+}
 
 extern "C" void as_params_default(as_params *p) {
     if (!p) return;
@@ -27,8 +34,8 @@ static size_t pack_wstride(uint32_t max_len) { return ((size_t)max_len + 15) / 1
 
 /* all device-side stages of n reads, asynchronous on h->stream; ev[0..4] bracket the stages.  `slot0` is the index
  * of the first read inside the handle's per-read scratch (qpack / vote / toff), so chunks of one batch do not overlap. */
-__global__ void k_restride(const uint32_t *__restrict__ in, size_t win, const uint32_t *__restrict__ lens, size_t n,
-                           uint32_t *__restrict__ out, size_t ws);
+__global__ void k_restride(const uint32_t *__restrict__ in, size_t win, uint32_t *__restrict__ lens, size_t n,
+                           uint32_t *__restrict__ out, size_t ws, unsigned long long *__restrict__ bad);
 
 static int run_stages(as_gpu *h, const as_params *p, char *d_reads, size_t stride, const uint32_t *d_lens, size_t n,
                       uint32_t max_len, as_result *d_res, uint8_t *d_store, size_t store_stride, bool stop_after_vote,
@@ -45,7 +52,8 @@ static int run_stages(as_gpu *h, const as_params *p, char *d_reads, size_t strid
     AS_CUDA(cudaEventRecord(ev[0], h->stream));
     if (d_packed_in) {                       /* reads arrived 2-bit packed (as_map_batch_packed): only the row stride changes */
         const uint64_t total = (uint64_t)n * ws, blocks = (total + 255) / 256, cap = (uint64_t)h->sm_count * 32;
-        k_restride<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(d_packed_in, wstride_in, d_lens, n, d_pack, ws);
+        k_restride<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, h->stream>>>(d_packed_in, wstride_in, const_cast<uint32_t *>(d_lens), n,
+                                                                                   d_pack, ws, h->d_stats + 15);
         h->launches++;
         AS_CUDA(cudaGetLastError());
     } else {
@@ -436,12 +444,22 @@ static int map_batch_impl(as_gpu *h, const as_params *p, char *reads, size_t str
 /* ---------------------------------------------------------------------------------------------- */
 /* host rows of `win` words -> device rows of `ws` words (3 words of slack for the funnel-shift readers); bits past the
  * read's length are cleared whatever the host left there */
-__global__ void __launch_bounds__(256) k_restride(const uint32_t *__restrict__ in, size_t win, const uint32_t *__restrict__ lens,
-                                                  size_t n, uint32_t *__restrict__ out, size_t ws) {
+__global__ void __launch_bounds__(256) k_restride(const uint32_t *__restrict__ in, size_t win, uint32_t *__restrict__ lens,
+                                                  size_t n, uint32_t *__restrict__ out, size_t ws,
+                                                  unsigned long long *__restrict__ bad) {
     const uint64_t total = (uint64_t)n * ws;
     for (uint64_t g = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; g < total; g += (uint64_t)gridDim.x * blockDim.x) {
         const uint64_t r = g / ws;
-        const uint32_t w = (uint32_t)(g - r * ws), len = lens[r], b0 = w << 4;
+        const uint32_t w = (uint32_t)(g - r * ws), b0 = w << 4;
+        uint32_t len = lens[r];
+        if ((uint64_t)len > 16 * (uint64_t)win) {             /* does not fit its row: mapped as the row's bases, call fails */
+            len = (uint32_t)(16 * win);
+            if (w == ws - 1) {                                 /* one thread per row stores the clamped length; the others clamp
+                                                                * whichever of the two values they happen to read the same way */
+                lens[r] = len;
+                atomicAdd(bad, 1ULL);
+            }
+        }
         uint32_t v = 0;
         if (b0 < len && w < win) {
             v = in[r * win + w];
@@ -602,101 +620,139 @@ static int plan_chunks_packed(const as_params *p, size_t n, size_t row_bytes, si
         begin[++nc] = n;
         return nc;
     }
+    /* Chunks alternate between two lanes (streams) and share the GPU, so what matters is that both lanes stay busy: one
+     * eighth first -- its H2D is the only exposed one --, one eighth last -- its D2H is the only exposed one --, and three
+     * quarters in between as two chunks (more when the op rows of long reads would not fit); as_params.chunk_tail > 0
+     * sets the number of chunks in between (A/B runs).  Measured on c2 (1 M reads, kernels alone 3.9 ms): 4.58 ms with
+     * two chunks in between or four equal chunks, 4.6 with three, 4.7 with one or four, 5.0 with six. */
     size_t edge = n / 8;
     if (edge < min_reads) edge = min_reads;
-    size_t mid = (n - 2 * edge + 1) / 2;
-    if (mid > by_bytes) mid = by_bytes;
-    if (edge > mid) edge = mid;
+    if (edge > by_bytes) edge = by_bytes;
+    const size_t inner = n - 2 * edge;
+    int mids = p->chunk_tail > 0 ? p->chunk_tail : 2;
+    if ((inner + (size_t)mids - 1) / (size_t)mids > by_bytes) mids = (int)((inner + by_bytes - 1) / by_bytes);
+    if (mids < 1) mids = 1;
+    if (mids > AS_MAX_CHUNKS - 2) mids = AS_MAX_CHUNKS - 2;
     size_t r = edge;
     begin[++nc] = r;
-    while (n - r > edge + mid / 8 && nc < AS_MAX_CHUNKS - 2) {
-        const size_t take = n - r - edge < mid ? n - r - edge : mid;
-        r += take;
+    for (int k = 0; k < mids; k++) {
+        r = edge + (size_t)(((unsigned __int128)inner * (unsigned)(k + 1)) / (unsigned)mids);
         begin[++nc] = r;
     }
     begin[++nc] = n;
     return nc;
 }
 
+static int ensure_twin(as_gpu *h) {
+    if (h->twin) return AS_OK;
+    as_gpu *t = as_handle_new(h->device);
+    if (!t) return AS_ENODEV;
+    t->ix = h->ix;
+    t->opts = h->opts;
+    t->is_twin = true;
+    h->twin = t;
+    return AS_OK;
+}
+
 static int map_batch_packed_impl(as_gpu *h, const as_params *p, const uint32_t *packed, size_t wstride, const uint32_t *lens,
                                  size_t n, as_result_compact *results, uint8_t *runs, size_t runs_cap, uint64_t *runs_len) {
-    uint32_t max_len = 0;
-    for (size_t i = 0; i < n; i++) max_len = lens[i] > max_len ? lens[i] : max_len;
-    if (((size_t)max_len + 15) / 16 > wstride) {
-        as_set_error("as_map_batch_packed: a read of %u bases does not fit %zu words", max_len, wstride);
-        return AS_EINVAL;
-    }
-    const size_t ws = pack_wstride(max_len), store_stride = (2 * (size_t)max_len + 15) & ~(size_t)15;
+    const double t_in = now_us();
+    AS_TRY(ensure_twin(h));
+    h->twin->ix = h->ix;                                  /* tables attached since (as_gpu_attach_*) */
     size_t cb[AS_MAX_CHUNKS + 1];
-    const int nc = plan_chunks_packed(p, n, store_stride, cb);
+    const int nc = plan_chunks_packed(p, n, 32 * wstride, cb);          /* 32 * wstride >= 2 * max_len: the op row of a read */
     h->n_chunks_last = nc;
     size_t max_chunk = 0;
     for (int c = 0; c < nc; c++) max_chunk = cb[c + 1] - cb[c] > max_chunk ? cb[c + 1] - cb[c] : max_chunk;
-    /* every buffer is sized before anything is enqueued (growing one waits for the stream).  The op rows and the
-     * as_result records are chunk-local scratch: the kernels of all chunks share one stream, so a chunk has read them
-     * before the next one writes.  The dense run bytes of the whole batch collect in one buffer (worst case: every
-     * column its own run), so no chunk ever waits for another one's copy to leave. */
+    /* the reads start crossing PCIe before the host has looked at a single length */
     AS_TRY(as_scratch(h, &h->pack_in, n * wstride * sizeof(uint32_t)));
     AS_TRY(as_scratch(h, &h->lens, n * sizeof(uint32_t)));
-    AS_TRY(as_scratch(h, &h->qpack, n * ws * sizeof(uint32_t)));
-    AS_TRY(as_scratch(h, &h->vote, n * sizeof(VoteOut)));
-    AS_TRY(as_scratch(h, &h->toff, n * sizeof(uint64_t)));
-    AS_TRY(as_scratch(h, &h->results, max_chunk * sizeof(as_result)));
-    AS_TRY(as_scratch(h, &h->store, max_chunk * store_stride));
-    AS_TRY(as_scratch(h, &h->runs, n * store_stride));
-    AS_TRY(as_scratch(h, &h->cres, n * sizeof(as_result_compact)));
-    const size_t nblk_max = (max_chunk + CR_READS - 1) / CR_READS;
-    AS_TRY(as_scratch(h, &h->run_tot, (AS_MAX_CHUNKS + nblk_max + 8) * sizeof(unsigned long long)));
-    if (max_len > (uint32_t)p->gact_T) AS_TRY(as_gact_order_reserve(h, max_chunk));
-    if (!h->h_run_tot) {
-        AS_CUDA(cudaMallocHost((void **)&h->h_run_tot, AS_MAX_CHUNKS * sizeof(unsigned long long)));
-        AS_CUDA(cudaStreamCreateWithFlags(&h->s_d2h2, cudaStreamNonBlocking));
-    }
     uint32_t *d_in = (uint32_t *)h->pack_in.p;
     uint32_t *d_lens = (uint32_t *)h->lens.p;
-    as_result *d_res = (as_result *)h->results.p;
-    uint8_t *d_rows = (uint8_t *)h->store.p, *d_dense = (uint8_t *)h->runs.p;
-    as_result_compact *d_cres = (as_result_compact *)h->cres.p;
-    /* run_tot: [0] running base of the dense buffer, [1 .. AS_MAX_CHUNKS] total per chunk, then the per-block sums */
-    unsigned long long *d_base = (unsigned long long *)h->run_tot.p, *d_tot = d_base + 1, *d_bsum = d_base + 1 + AS_MAX_CHUNKS;
-
     AS_CUDA(cudaEventRecord(h->ev[0], h->stream));
     AS_CUDA(cudaStreamWaitEvent(h->s_h2d, h->ev[0], 0));
-    AS_CUDA(cudaStreamWaitEvent(h->s_d2h, h->ev[0], 0));
-    AS_CUDA(cudaStreamWaitEvent(h->s_d2h2, h->ev[0], 0));
     for (int c = 0; c < nc; c++) {
         const size_t r0 = cb[c], cn = cb[c + 1] - cb[c];
         AS_CUDA(cudaMemcpyAsync(d_in + r0 * wstride, packed + r0 * wstride, cn * wstride * sizeof(uint32_t), cudaMemcpyHostToDevice, h->s_h2d));
         AS_CUDA(cudaMemcpyAsync(d_lens + r0, lens + r0, cn * sizeof(uint32_t), cudaMemcpyHostToDevice, h->s_h2d));
         AS_CUDA(cudaEventRecord(h->cev[c][5], h->s_h2d));
     }
+    /* The host never reads the lengths (a scan of 1 M of them costs more than the kernels' launch): every buffer and
+     * launch shape is sized from the row width, max_len <= 16 * wstride; k_restride clamps a length that does not fit its
+     * row and raises a flag, which turns the call into AS_EINVAL. */
+    const uint32_t max_len = (uint32_t)(16 * wstride < 0xFFFFFFF0ull ? 16 * wstride : 0xFFFFFFF0ull);
+    const size_t ws = pack_wstride(max_len), store_stride = (2 * (size_t)max_len + 15) & ~(size_t)15;
+    /* every buffer is sized before anything is enqueued (growing one waits for the stream).  The op rows and the
+     * as_result records are chunk-local scratch: the kernels of all chunks share one stream, so a chunk has read them
+     * before the next one writes.  The dense run bytes of the whole batch collect in one buffer (worst case: every
+     * column its own run), so no chunk ever waits for another one's copy to leave. */
+    as_gpu *lane[2] = {h, nc > 1 ? h->twin : h};          /* chunk c runs on lane[c & 1] */
+    const size_t nblk_max = (max_chunk + CR_READS - 1) / CR_READS;
+    for (int k = 0; k < (nc > 1 ? 2 : 1); k++) {
+        as_gpu *g = lane[k];
+        AS_TRY(as_scratch(g, &g->qpack, n * ws * sizeof(uint32_t)));
+        AS_TRY(as_scratch(g, &g->vote, n * sizeof(VoteOut)));
+        AS_TRY(as_scratch(g, &g->toff, n * sizeof(uint64_t)));
+        AS_TRY(as_scratch(g, &g->results, max_chunk * sizeof(as_result)));
+        AS_TRY(as_scratch(g, &g->store, max_chunk * store_stride));
+        AS_TRY(as_scratch(g, &g->run_tot, (AS_MAX_CHUNKS + nblk_max + 8) * sizeof(unsigned long long)));
+        if (max_len > (uint32_t)p->gact_T) AS_TRY(as_gact_order_reserve(g, max_chunk));
+    }
+    AS_TRY(as_scratch(h, &h->runs, n * store_stride));
+    AS_TRY(as_scratch(h, &h->cres, n * sizeof(as_result_compact)));
+    if (!h->h_run_tot) {
+        AS_CUDA(cudaMallocHost((void **)&h->h_run_tot, (AS_MAX_CHUNKS + 2) * sizeof(unsigned long long)));
+        AS_CUDA(cudaStreamCreateWithFlags(&h->s_d2h2, cudaStreamNonBlocking));
+    }
+    uint8_t *d_dense = (uint8_t *)h->runs.p;
+    as_result_compact *d_cres = (as_result_compact *)h->cres.p;
+    /* run_tot of the first lane: [0] running base of the dense buffer, [1 .. AS_MAX_CHUNKS] total per chunk; the per-block
+     * sums behind them are per lane */
+    unsigned long long *d_base = (unsigned long long *)h->run_tot.p, *d_tot = d_base + 1;
+
+    AS_CUDA(cudaStreamWaitEvent(h->s_d2h, h->ev[0], 0));
+    AS_CUDA(cudaStreamWaitEvent(h->s_d2h2, h->ev[0], 0));
+    if (lane[1] != h) AS_CUDA(cudaStreamWaitEvent(lane[1]->stream, h->ev[0], 0));
     h->last_h2d_bytes = n * wstride * sizeof(uint32_t) + n * sizeof(uint32_t);
     h->last_d2h_bytes = n * sizeof(as_result_compact) + (size_t)nc * sizeof(unsigned long long);
     as_params q = *p;
     q.flags |= AS_F_RLE_CIGAR | AS_F_KEEP_READS;
     AS_CUDA(cudaMemsetAsync(d_base, 0, sizeof(unsigned long long), h->stream));
-    /* the kernels of every chunk are enqueued first ... */
+    AS_CUDA(cudaMemsetAsync(h->d_stats + 15, 0, sizeof(unsigned long long), h->stream));       /* reads too long for their row */
+    if (lane[1] != h) AS_CUDA(cudaMemsetAsync(lane[1]->d_stats + 15, 0, sizeof(unsigned long long), lane[1]->stream));
+    h->dbg_us[2] = now_us() - t_in;
+    /* the kernels of every chunk are enqueued first, chunks alternating between the two lanes: the kernels size their grids
+     * to fill the GPU, so a chunk's blocks start as the other lane's retire -- the tails overlap, the bulk does not */
     for (int c = 0; c < nc; c++) {
         const size_t r0 = cb[c], cn = cb[c + 1] - cb[c];
-        AS_CUDA(cudaStreamWaitEvent(h->stream, h->cev[c][5], 0));
-        AS_TRY(run_stages(h, &q, nullptr, 0, d_lens + r0, cn, max_len, d_res, d_rows, store_stride, false, nullptr, h->cev[c], r0, n,
+        if (c == 1) h->dbg_us[3] = now_us() - t_in;
+        as_gpu *g = lane[c & 1];
+        as_result *d_res = (as_result *)g->results.p;
+        uint8_t *d_rows = (uint8_t *)g->store.p;
+        unsigned long long *d_bsum = (unsigned long long *)g->run_tot.p + 1 + AS_MAX_CHUNKS;
+        AS_CUDA(cudaStreamWaitEvent(g->stream, h->cev[c][5], 0));
+        AS_TRY(run_stages(g, &q, nullptr, 0, d_lens + r0, cn, max_len, d_res, d_rows, store_stride, false, nullptr, h->cev[c], r0, n,
                           d_in + r0 * wstride, wstride));
-        AS_TRY(count_results(h, d_res, cn, nullptr));
+        AS_TRY(count_results(g, d_res, cn, nullptr));
         const unsigned nblk = (unsigned)((cn + CR_READS - 1) / CR_READS);
-        k_compact_records<<<nblk, CR_READS, 0, h->stream>>>(d_res, cn, d_cres + r0, d_bsum);
-        k_scan_block_sums<<<1, 1024, 0, h->stream>>>(d_bsum, nblk, d_base, d_tot + c);
-        k_gather_runs<<<nblk, CR_READS, 0, h->stream>>>(d_cres + r0, cn, d_rows, store_stride, d_bsum, d_dense,
+        k_compact_records<<<nblk, CR_READS, 0, g->stream>>>(d_res, cn, d_cres + r0, d_bsum);
+        if (c > 0) AS_CUDA(cudaStreamWaitEvent(g->stream, h->cev[c - 1][6], 0));     /* the dense offsets continue chunk c-1's */
+        k_scan_block_sums<<<1, 1024, 0, g->stream>>>(d_bsum, nblk, d_base, d_tot + c);
+        k_gather_runs<<<nblk, CR_READS, 0, g->stream>>>(d_cres + r0, cn, d_rows, store_stride, d_bsum, d_dense,
                                                        (unsigned long long)(n * store_stride));
-        h->launches += 3;
+        g->launches += 3;
         AS_CUDA(cudaGetLastError());
-        AS_CUDA(cudaEventRecord(h->cev[c][6], h->stream));
+        AS_CUDA(cudaEventRecord(h->cev[c][6], g->stream));
         AS_CUDA(cudaStreamWaitEvent(h->s_d2h, h->cev[c][6], 0));
         if (c == 0) AS_CUDA(cudaEventRecord(h->ev_d2h0, h->s_d2h));
         AS_CUDA(cudaMemcpyAsync(h->h_run_tot + c, d_tot + c, sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->s_d2h));
         AS_CUDA(cudaEventRecord(h->cev[c][7], h->s_d2h));
         AS_CUDA(cudaMemcpyAsync(results + r0, d_cres + r0, cn * sizeof(as_result_compact), cudaMemcpyDeviceToHost, h->s_d2h));
     }
+    AS_CUDA(cudaMemcpyAsync(h->h_run_tot + AS_MAX_CHUNKS, h->d_stats + 15, sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->s_d2h));
+    AS_CUDA(cudaMemcpyAsync(h->h_run_tot + AS_MAX_CHUNKS + 1, lane[1]->d_stats + 15, sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->s_d2h));
     AS_CUDA(cudaEventRecord(h->ev[7], h->s_d2h));
+    const double t_enq = now_us();
     /* ... then the dense run bytes of each chunk leave, on their own stream, as soon as the chunk's total is known here */
     uint64_t host_off = 0;
     int rc_out = AS_OK;
@@ -713,11 +769,20 @@ static int map_batch_packed_impl(as_gpu *h, const as_params *p, const uint32_t *
     AS_CUDA(cudaStreamWaitEvent(h->stream, h->ev[8], 0));
     AS_CUDA(cudaEventRecord(h->ev[6], h->stream));
     AS_CUDA(cudaStreamSynchronize(h->stream));
+    const double t_done = now_us();
     finish_timing(h);
+    h->last_host_us[0] = t_enq - t_in;          /* host time until every kernel of the call was enqueued */
+    h->last_host_us[1] = t_done - t_enq;        /* waiting for the device */
+    h->last_host_us[2] = now_us() - t_done;     /* reading the event times */
     h->last_ms[5] = ev_ms(h->ev[0], h->cev[nc - 1][5]);
     h->last_ms[6] = ev_ms(h->ev_d2h0, h->ev[6]);
     h->last_ms[7] = ev_ms(h->ev[0], h->ev[6]);
     *runs_len = host_off;
+    if (h->h_run_tot[AS_MAX_CHUNKS] + h->h_run_tot[AS_MAX_CHUNKS + 1]) {
+        as_set_error("as_map_batch_packed: %llu reads are longer than their row of %zu words holds",
+                     h->h_run_tot[AS_MAX_CHUNKS] + (lane[1] != h ? h->h_run_tot[AS_MAX_CHUNKS + 1] : 0), wstride);
+        return AS_EINVAL;
+    }
     if (rc_out == AS_ERANGE) as_set_error("as_map_batch_packed: %llu run bytes do not fit runs_cap %zu", (unsigned long long)host_off, runs_cap);
     return rc_out;
 }
@@ -755,6 +820,26 @@ extern "C" int as_gpu_last_timing(as_gpu *h, float ms[8]) {
     return AS_OK;
 }
 
+/* when the events of chunk `chunk` of the last as_map_batch* call fired, in ms after the call's start: [0] kernels begin,
+ * [1] PART 1 done, [2] PART 2 done, [3] GACT done, [4] Myers done, [5] the chunk's H2D done, [6] all kernels done,
+ * [7] the chunk's fixed-size D2H done.  Returns the number of chunks of the call. */
+extern "C" int as_gpu_last_chunk_timeline(as_gpu *h, int chunk, float ms[8]) {
+    if (!h || !ms) return AS_EINVAL;
+    if (chunk < 0 || chunk >= h->n_chunks_last) return h->n_chunks_last;
+    AS_CUDA(cudaSetDevice(h->device));
+    for (int i = 0; i < 8; i++) ms[i] = ev_ms(h->ev[0], h->cev[chunk][i]);
+    return h->n_chunks_last;
+}
+
+extern "C" int as_gpu_last_host_timing(as_gpu *h, double us[3]) {
+    if (!h || !us) return AS_EINVAL;
+    for (int i = 0; i < 3; i++) us[i] = h->last_host_us[i];
+    if (getenv("AS_DEBUG_HOST_US"))
+        fprintf(stderr, "host us: h2d enqueued %.0f, lens scanned %.0f, buffers sized %.0f, chunk 0 enqueued %.0f\n", h->dbg_us[0],
+                h->dbg_us[1], h->dbg_us[2], h->dbg_us[3]);
+    return AS_OK;
+}
+
 extern "C" int as_gpu_last_transfer(as_gpu *h, uint64_t *h2d_bytes, uint64_t *d2h_bytes) {
     if (!h) return AS_EINVAL;
     if (h2d_bytes) *h2d_bytes = h->last_h2d_bytes;
@@ -768,6 +853,12 @@ extern "C" int as_gpu_stats(as_gpu *h, as_stats *out) {
     AS_CUDA(cudaStreamSynchronize(h->stream));
     unsigned long long v[15];
     AS_CUDA(cudaMemcpy(v, h->d_stats, sizeof v, cudaMemcpyDeviceToHost));
+    if (h->twin) {
+        unsigned long long w[15];
+        AS_CUDA(cudaStreamSynchronize(h->twin->stream));
+        AS_CUDA(cudaMemcpy(w, h->twin->d_stats, sizeof w, cudaMemcpyDeviceToHost));
+        for (int i = 0; i < 15; i++) v[i] += w[i];
+    }
     out->total = v[0]; out->valid = v[1]; out->n_flag4 = v[2]; out->n_flag16 = v[3]; out->sum_ed = v[4];
     out->dp_cells = v[5]; out->seeds = v[6]; out->sa_hits = v[7]; out->bs_steps = v[8]; out->overflow_reads = v[9];
     out->dp_cells_eval = v[10]; out->gact_redone = v[11]; out->fm_steps_exec = v[12]; out->text_verified = v[13];
@@ -779,10 +870,11 @@ extern "C" int as_gpu_stats_reset(as_gpu *h) {
     if (!h) return AS_EINVAL;
     AS_CUDA(cudaSetDevice(h->device));
     AS_CUDA(cudaMemsetAsync(h->d_stats, 0, 16 * sizeof(unsigned long long), h->stream));
+    if (h->twin) AS_CUDA(cudaMemsetAsync(h->twin->d_stats, 0, 16 * sizeof(unsigned long long), h->twin->stream));
     return AS_OK;
 }
 
-extern "C" uint64_t as_gpu_launch_count(as_gpu *h) { return h ? h->launches : 0; }
+extern "C" uint64_t as_gpu_launch_count(as_gpu *h) { return h ? h->launches + (h->twin ? h->twin->launches : 0) : 0; }
 extern "C" uint64_t as_gpu_index_length(as_gpu *h) { return h ? h->ix.N : 0; }
 
 /* ---------------------------------------------------------------------------------------------- */

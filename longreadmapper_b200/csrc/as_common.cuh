@@ -78,6 +78,8 @@ struct as_gpu {
     unsigned long long *d_stats = nullptr;
     cudaEvent_t ev[10]{};
     float last_ms[8]{};
+    double dbg_us[4]{};
+    double last_host_us[3]{};   /* as_map_batch_packed: host time enqueueing / waiting / reading events */
     /* chunked pipeline of as_map_batch: H2D of chunk i+1 | kernels of chunk i | D2H of chunk i-1 */
     cudaStream_t s_h2d = nullptr, s_d2h = nullptr, s_d2h2 = nullptr;
     cudaEvent_t cev[AS_MAX_CHUNKS][8]{};   /* per chunk: [0..4] stage marks, [5] H2D done, [6] kernels done, [7] fixed D2H done */
@@ -93,6 +95,11 @@ struct as_gpu {
     int sm_count = 148;
     size_t l2_bytes = 126u << 20;
     uint64_t launches = 0;      /* kernels launched by this handle since open */
+    /* second lane of as_map_batch_packed: a handle that shares this one's index (ix is a struct of device pointers) but owns
+     * its own stream and scratch, so that consecutive chunks run on two streams and the tail of one chunk's kernels fills
+     * with the next chunk's blocks */
+    as_gpu *twin = nullptr;
+    bool is_twin = false;
 };
 
 /* error plumbing */

@@ -169,7 +169,11 @@ extern "C" void as_gpu_close(as_gpu *h) {
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
-    free_index(h);
+    if (h->twin) {
+        as_gpu_close(h->twin);
+        h->twin = nullptr;
+    }
+    if (!h->is_twin) free_index(h);
     ScratchBuf *bufs[] = {&h->reads, &h->lens, &h->results, &h->store, &h->qpack, &h->tpack, &h->toff,
                           &h->vote, &h->counters, &h->ovf_list, &h->ovf_table, &h->gact_planes, &h->gact_tb, &h->gact_order,
                           &h->locus_tmp, &h->pack_in, &h->cres, &h->runs, &h->run_tot};

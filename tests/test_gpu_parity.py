@@ -364,6 +364,12 @@ def test_map_packed_compact_long_and_edge(native, gpu_repeat, idx_repeat):
     check_packed_equals_full(native, gpu_repeat, ix, edge[3:], el[3:])
     with pytest.raises(native.AccSeqError):
         gpu_repeat.map_batch_packed(native.pack_reads(reads, lens), lens, runs_cap=10)
+    pk = native.pack_reads(edge, el)
+    bad = el.copy()
+    bad[1] = 16 * pk.shape[1] + 1                       # a length its row cannot hold: found on the device, the call fails
+    with pytest.raises(native.AccSeqError, match="longer than their row"):
+        gpu_repeat.map_batch_packed(pk, bad)
+    check_packed_equals_full(native, gpu_repeat, ix, edge, el)      # and the handle is fine afterwards
 
 
 def test_map_empty_and_single(native, gpu_uniform, idx_uniform):
