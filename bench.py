@@ -462,10 +462,12 @@ def run_b200(args):
             same = bool(np.array_equal(rec["pos"] & ((1 << 40) - 1), res["off"] & ((1 << 40) - 1))
                         and np.array_equal(((rec["pos"] >> 40) & 0xFFFF).astype(np.int64) - 1, res["seq_id"].astype(np.int64))
                         and np.array_equal((rec["pos"] >> 56).astype(np.int32), res["flag"]) and np.array_equal(rec["ed"], res["ed"]))
-            offs = np.concatenate([[0], np.cumsum(rec["n_runs"].astype(np.int64))])
-            cols = np.add.reduceat((dense >> 2).astype(np.int64), offs[:-1][rec["n_runs"] > 0]) if dense.size else np.zeros(0, np.int64)
-            same = same and bool(offs[-1] == dense.size) and bool(np.array_equal(cols, res["n_cigar_op"][rec["n_runs"] > 0]))
-            same = same and bool(np.array_equal(rec["n_runs"] > 0, mapped & (res["n_cigar_op"] > 0)))
+            nr = (rec["n_runs"] & 0x07FFFFFF).astype(np.int64)
+            offs = np.concatenate([[0], np.cumsum(nr)])
+            cols = np.add.reduceat((dense >> 2).astype(np.int64), offs[:-1][nr > 0]) if dense.size else np.zeros(0, np.int64)
+            same = same and bool(offs[-1] == dense.size) and bool(np.array_equal(cols, res["n_cigar_op"][nr > 0]))
+            same = same and bool(np.array_equal(nr > 0, mapped & (res["n_cigar_op"] > 0)))
+            same = same and bool(np.array_equal((rec["n_runs"] >> 31).astype(np.int32), res["strand"]))
             for q in bufs:
                 L.as_host_free(q)
             return {"value": world * n / (ems / args.steps / 1e3), "unit": "reads/s",

@@ -192,10 +192,16 @@ int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t stride, cons
  */
 typedef struct as_result_compact {
     uint64_t pos;        /* bits 0..39 off (0-based forward offset, SAM POS - 1); bits 40..55 seq_id + 1 (0 = seq_lookup failed);
-                          * bits 56..63 flag (0, 16 or 4) */
+                          * bits 56..63 the low 8 bits of flag (0, 16 or 4) */
     int32_t  ed;         /* GACT score, -1 = failure */
-    uint32_t n_runs;     /* run bytes of this read */
+    uint32_t n_runs;     /* bits 0..26 run bytes of this read; bits 27..30 flag bits 8..11 (none set by this path); bit 31 the
+                          * strand (a read whose alignment failed keeps FLAG 4, yet prints reverse-complemented, alnmain.c:433-438) */
 } as_result_compact;
+#define AS_RC_NRUNS(c)  ((c).n_runs & 0x07FFFFFFu)
+#define AS_RC_STRAND(c) ((c).n_runs >> 31)
+#define AS_RC_FLAG(c)   ((unsigned)((c).pos >> 56) | ((((c).n_runs >> 27) & 0xFu) << 8))
+#define AS_RC_SEQ_ID(c) ((int)(((c).pos >> 40) & 0xFFFFu) - 1)
+#define AS_RC_OFF(c)    ((c).pos & 0xFFFFFFFFFFULL)
 int as_map_batch_packed(as_gpu *h, const as_params *p, const uint32_t *packed, size_t wstride, const uint32_t *lens, size_t n,
                         as_result_compact *results, uint8_t *runs, size_t runs_cap, uint64_t *runs_len);
 

@@ -82,6 +82,36 @@ void as_fastq_close(as_fastq *fq);
 /* all records of a FASTA file (plain or gzip) as heap strings the caller frees: the input of accidx (asindex.c:78-117) */
 int  as_fasta_load(const char *path, int *nseq, char ***names, char ***seqs, uint64_t **lens);
 
+/* ---- multi-threaded ingest / emit around as_map_batch_packed (ingest.c, emit.c; OpenMP) ---- */
+typedef struct as_packed_batch {
+    size_t      n;
+    uint32_t    max_len;
+    size_t      wstride;       /* ceil(max_len / 16) words per read */
+    uint32_t   *packed;        /* n * wstride words, from alloc() (pinned when it is as_host_alloc) */
+    uint32_t   *lens;          /* n, from alloc() */
+    const char **name, **seq, **qual;   /* record text, NOT NUL-terminated: pointers into `text` */
+    uint32_t   *name_len;
+    const char *text;          /* the block the records live in: a slice of the mapped file, or an inflate buffer */
+    size_t      text_len;
+    int         text_owned;
+} as_packed_batch;
+typedef struct as_ingest as_ingest;
+/* plain or gzip 4-line FASTQ; `threads` parse and pack; a batch is the records of about block_bytes of text (0 = 256 MB) */
+as_ingest *as_ingest_open(const char *path, int threads, size_t block_bytes);
+/* next batch (b->n == 0 at the end).  AS_EIO: not 4-line FASTQ -- use the serial reader (as_fastq_*), which takes kseq's
+ * whole grammar */
+int  as_ingest_next(as_ingest *in, as_packed_batch *b, void *(*alloc)(size_t), void (*dealloc)(void *));
+void as_packed_batch_free(as_packed_batch *b, void (*dealloc)(void *));
+void as_ingest_close(as_ingest *in);
+
+typedef struct as_emitter as_emitter;
+as_emitter *as_emitter_new(int threads);
+void as_emitter_free(as_emitter *e);
+/* SAM text (alnmain.c:488-526) of a batch mapped by one or several as_map_batch_packed calls; see emit.c */
+int  as_emit_batch(as_emitter *e, const as_host_index *ix, const as_packed_batch *b, const as_result_compact *res, int n_shards,
+                   const size_t *shard_begin, const uint8_t *const *shard_runs, const uint64_t *shard_runs_len,
+                   const char **seg, size_t *seg_len);
+
 #ifdef __cplusplus
 }
 #endif

@@ -483,7 +483,7 @@ __global__ void __launch_bounds__(CR_READS) k_compact_records(const as_result *_
         const uint32_t nr = r.n_cigar_op > 0 && r.seq_id >= 0 ? (uint32_t)r.n_cigar_op : 0u;
         c.pos = (r.off & 0xFFFFFFFFFFULL) | ((uint64_t)(uint16_t)(r.seq_id + 1) << 40) | ((uint64_t)(uint8_t)r.flag << 56);
         c.ed = r.ed;
-        c.n_runs = nr;
+        c.n_runs = nr | ((((uint32_t)r.flag >> 8) & 0xFu) << 27) | (r.strand ? 0x80000000u : 0u);
         out[i] = c;
         mine = nr;
     }
@@ -549,7 +549,7 @@ __global__ void __launch_bounds__(CR_READS) k_gather_runs(const as_result_compac
     __shared__ unsigned long long s_w[CR_READS / 32];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const size_t i = (size_t)blockIdx.x * CR_READS + threadIdx.x;
-    const uint32_t nr = i < n ? rec[i].n_runs : 0u;
+    const uint32_t nr = i < n ? AS_RC_NRUNS(rec[i]) : 0u;
     unsigned long long inc = nr;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {

@@ -48,20 +48,18 @@ int as_pack_reads(const char *ascii, size_t stride, const uint32_t *lens, size_t
 /* the fields of as_result a compact record determines (alnmain.c:458-477; loc per seq_lookup, alnmain.c:151-176) */
 void as_result_from_compact(const as_result_compact *c, uint32_t len, const as_mta *mta, int mta_len, as_result *r) {
     memset(r, 0, sizeof *r);
-    const int seq_id = (int)((c->pos >> 40) & 0xFFFFu) - 1;
-    r->off = c->pos & 0xFFFFFFFFFFULL;
+    const int seq_id = AS_RC_SEQ_ID(*c);
+    r->off = AS_RC_OFF(*c);
     r->seq_id = seq_id;
-    r->flag = (int)(c->pos >> 56);
-    r->strand = (r->flag & 16) ? 1 : 0;
+    r->flag = (int)AS_RC_FLAG(*c);
+    r->strand = (int)AS_RC_STRAND(*c);
     r->mapq = (r->flag & 4) ? 0 : 255;
     r->ed = c->ed;
     r->valid = !(r->flag & 4);
-    r->n_cigar_op = (int32_t)c->n_runs;
+    r->n_cigar_op = (int32_t)AS_RC_NRUNS(*c);
     r->myers = -2;
     if (seq_id >= 0 && seq_id < mta_len && mta) {
         const uint64_t start = mta[seq_id].offset, sl = mta[seq_id].seq_len;
-        /* a failed alignment keeps flag 4 but still has a locus; the strand is then not in the flag: it cannot be told
-         * from the record, and loc is reported for the forward copy */
         r->loc = r->strand ? start + 2 * sl - r->off - len : start + r->off;
     }
 }

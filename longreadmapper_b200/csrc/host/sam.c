@@ -98,7 +98,8 @@ int as_sam_record2(FILE *out, const as_host_index *ix, const char *qname, size_t
         rc_heap = rc != seqbuf;
         for (uint32_t i = 0; i < len; i++) {
             const char c = seq[len - 1 - i];
-            rc[i] = c == 'A' ? 'T' : c == 'C' ? 'G' : c == 'G' ? 'C' : c == 'T' ? 'A' : 'N';
+            /* _rev_comp_in_place (alnmain.c:31-47): either case complements to upper case, anything else becomes N */
+            rc[i] = (c == 'A' || c == 'a') ? 'T' : (c == 'C' || c == 'c') ? 'G' : (c == 'G' || c == 'g') ? 'C' : (c == 'T' || c == 't') ? 'A' : 'N';
         }
         seq = rc;
     }

@@ -83,6 +83,34 @@ def test_pack_reads_layout(native):
         native.pack_reads(reads, lens, wstride=2)
 
 
+@pytest.mark.parametrize("threads,block", [(1, 5000), (3, 40000), (8, 7000), (5, 0)])
+def test_parallel_ingest_and_emit_equal_the_serial_reader_and_printer(native, tmp_path, threads, block):
+    """tests/compat/host_pipeline_check.c: ingest.c against fastq.c (kseq's grammar) record by record and word by word,
+    emit.c against sam.c byte by byte, on the golden FASTQ (plain and gzip) and on a FASTQ of mixed-length reads with
+    lower-case bases, N, CR LF line ends, comments after the name and no final newline"""
+    import subprocess
+    exe = os.path.join(ROOT, "tests", "_build", "host_pipeline_check")
+    if not os.path.exists(exe):
+        subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "tests"), "all"], check=True)
+    plain = str(tmp_path / "g.fq")
+    open(plain, "wb").write(gzip.open(os.path.join(GOLD, "reads.fq.gz"), "rb").read())
+    rng = np.random.default_rng(threads)
+    mixed = str(tmp_path / "m.fq")
+    with open(mixed, "wb") as f:
+        for i in range(900):
+            L = int(rng.integers(1, 4000)) if i % 7 else int(rng.integers(1, 40))
+            s = np.frombuffer(b"ACGTacgtN", np.uint8)[rng.integers(0, 9 if i % 5 == 0 else 4, L)].tobytes()
+            q = bytes(rng.integers(33, 74, L).astype(np.uint8))       # quality strings may start with '@' or '+'
+            eol = b"\r\n" if i % 11 == 0 else b"\n"
+            f.write(b"@r%d some comment\tx" % i + eol + s + eol + b"+" + (b"r%d" % i if i % 3 == 0 else b"") + eol + q)
+            if i != 899:
+                f.write(eol)
+    for path in (plain, os.path.join(GOLD, "reads.fq.gz"), mixed):
+        p = subprocess.run([exe, path, str(threads), str(block)], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        assert p.returncode == 0, p.stderr.decode()
+        assert b"host_pipeline_check ok" in p.stdout
+
+
 def test_params_default(native):
     p = native.Params()
     native.cuda_lib().as_params_default(C.byref(p))

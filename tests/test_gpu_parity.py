@@ -324,11 +324,13 @@ def check_packed_equals_full(native, m, ix, reads, lens, **knobs):
     mapped = full["seq_id"] >= 0
     for f in ("off", "seq_id", "flag", "mapq", "ed", "valid"):
         assert np.array_equal(back[f], full[f]), f
-    assert np.array_equal(back["strand"][full["flag"] != 4], full["strand"][full["flag"] != 4])
-    assert np.array_equal(back["loc"][mapped & (full["flag"] != 4)], full["loc"][mapped & (full["flag"] != 4)])
+    assert np.array_equal(back["strand"], full["strand"])
+    assert np.array_equal(back["loc"][mapped], full["loc"][mapped])
     want_n = np.where(mapped, np.maximum(full["n_cigar_op"], 0), 0)
-    assert np.array_equal(rec["n_runs"], want_n.astype(np.uint32))
-    offs = np.concatenate([[0], np.cumsum(rec["n_runs"].astype(np.int64))])
+    n_runs = rec["n_runs"] & 0x07FFFFFF
+    assert np.array_equal(n_runs, want_n.astype(np.uint32))
+    assert np.array_equal((rec["n_runs"] >> 31).astype(np.int32), full["strand"])
+    offs = np.concatenate([[0], np.cumsum(n_runs.astype(np.int64))])
     assert offs[-1] == dense.size
     for i in range(len(lens)):
         assert np.array_equal(dense[offs[i]:offs[i + 1]], rows[i, : want_n[i]]), i
