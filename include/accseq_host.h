@@ -82,7 +82,15 @@ void as_fastq_close(as_fastq *fq);
 /* all records of a FASTA file (plain or gzip) as heap strings the caller frees: the input of accidx (asindex.c:78-117) */
 int  as_fasta_load(const char *path, int *nseq, char ***names, char ***seqs, uint64_t **lens);
 
-/* ---- multi-threaded ingest / emit around as_map_batch_packed (ingest.c, emit.c; OpenMP) ---- */
+/* ---- a persistent thread pool whose idle workers sleep (pool.c) ---- */
+typedef struct as_pool as_pool;
+as_pool *as_pool_new(int threads);
+int  as_pool_threads(const as_pool *p);
+void as_pool_run(as_pool *p, void (*fn)(int t, int n, void *arg), void *arg);     /* fn(t, n, arg) for every t in [0, n) */
+void as_pool_free(as_pool *p);
+
+/* ---- multi-threaded ingest / emit around as_map_batch_packed (ingest.c, emit.c) ---- */
+struct as_ingest;
 typedef struct as_packed_batch {
     size_t      n;
     uint32_t    max_len;
@@ -94,6 +102,7 @@ typedef struct as_packed_batch {
     const char *text;          /* the block the records live in: a slice of the mapped file, or an inflate buffer */
     size_t      text_len;
     int         text_owned;
+    struct as_ingest *owner;   /* the ingest whose recycled buffers these are: it must outlive the batch */
 } as_packed_batch;
 typedef struct as_ingest as_ingest;
 /* plain or gzip 4-line FASTQ; `threads` parse and pack; a batch is the records of about block_bytes of text (0 = 256 MB) */

@@ -108,6 +108,59 @@ static int run_serial(const char *fq_path, as_gpu *h, as_params p, const as_host
 /* ------------------------------------------------------------------------------------------------
  * pipelined path
  * ---------------------------------------------------------------------------------------------- */
+/* Pinned buffers are recycled: cudaHostAlloc costs about a millisecond per 4 MB, more than mapping the reads they carry.
+ * A block keeps its capacity in a 64-byte header; pin_get hands out the smallest cached block that fits. */
+#define POOL_SLOTS 64
+static struct {
+    pthread_mutex_t mu;
+    void *blk[POOL_SLOTS];
+} g_pool = {PTHREAD_MUTEX_INITIALIZER, {0}};
+
+static void *pin_get(size_t bytes) {
+    pthread_mutex_lock(&g_pool.mu);
+    int best = -1;
+    for (int i = 0; i < POOL_SLOTS; i++) {
+        if (!g_pool.blk[i]) continue;
+        const size_t cap = *(size_t *)g_pool.blk[i];
+        if (cap >= bytes && cap <= 2 * bytes + (1 << 20) && (best < 0 || cap < *(size_t *)g_pool.blk[best])) best = i;
+    }
+    void *b = NULL;
+    if (best >= 0) {
+        b = g_pool.blk[best];
+        g_pool.blk[best] = NULL;
+    }
+    pthread_mutex_unlock(&g_pool.mu);
+    if (!b) {
+        const size_t cap = bytes + bytes / 8 + 4096;
+        b = as_host_alloc(cap + 64);
+        if (!b) return NULL;
+        *(size_t *)b = cap;
+    }
+    return (char *)b + 64;
+}
+
+static void pin_put(void *p) {
+    if (!p) return;
+    void *b = (char *)p - 64;
+    pthread_mutex_lock(&g_pool.mu);
+    for (int i = 0; i < POOL_SLOTS; i++)
+        if (!g_pool.blk[i]) {
+            g_pool.blk[i] = b;
+            b = NULL;
+            break;
+        }
+    pthread_mutex_unlock(&g_pool.mu);
+    if (b) as_host_free(b);
+}
+
+static void pin_drain(void) {
+    for (int i = 0; i < POOL_SLOTS; i++) {
+        if (g_pool.blk[i]) as_host_free(g_pool.blk[i]);
+        g_pool.blk[i] = NULL;
+    }
+}
+
+static double g_stage_s[4];        /* busy seconds of ingest / map / emit / write, for the closing Info line */
 typedef struct {
     as_packed_batch b;
     as_result_compact *res;        /* pinned, b.n records */
@@ -162,7 +215,9 @@ static void *ingest_main(void *v) {
     for (;;) {
         job *j = calloc(1, sizeof *j);
         if (in && a->rc == 0) {
-            const int rc = as_ingest_next(in, &j->b, as_host_alloc, as_host_free);
+            const double t0 = now_s();
+            const int rc = as_ingest_next(in, &j->b, pin_get, pin_put);
+            g_stage_s[0] += now_s() - t0;
             if (rc != AS_OK) a->rc = rc == AS_EIO ? 50 : 6;
         }
         if (!in || a->rc != 0 || j->b.n == 0) {
@@ -195,9 +250,18 @@ static void *shard_main(void *v) {
     for (size_t s = r0; s < r1 && a->rc == AS_OK; s += a->batch) {
         const size_t cn = r1 - s < a->batch ? r1 - s : a->batch;
         uint64_t got = 0;
+        const double t0 = now_s();
         a->rc = as_map_batch_packed(a->h, a->p, j->b.packed + s * j->b.wstride, j->b.wstride, j->b.lens + s, cn, j->res + s,
                                     j->runs[a->shard] + used, j->runs_cap[a->shard] - used, &got);
         used += got;
+        if (getenv("ACCSEQ_VERBOSE")) {
+            float ms[8];
+            double us[3];
+            as_gpu_last_timing(a->h, ms);
+            as_gpu_last_host_timing(a->h, us);
+            fprintf(stderr, "  shard %d: %zu reads, call %.2f ms (device total %.2f: part1 %.2f part2 %.2f gact %.2f h2d %.2f d2h %.2f; host enqueue %.0f us wait %.0f us)\n",
+                    a->shard, cn, 1e3 * (now_s() - t0), ms[7], ms[0], ms[1], ms[2], ms[5], ms[6], us[0], us[1]);
+        }
         if (a->rc != AS_OK && a->rc != AS_ERANGE)              /* as_last_error() is per thread: say it here */
             fprintf(stderr, "accaln_b200: as_map_batch_packed failed on GPU shard %d (%d): %s\n", a->shard, a->rc, as_last_error());
     }
@@ -223,15 +287,17 @@ static void *map_main(void *v) {
             const int G = (size_t)a->n_gpus < n ? a->n_gpus : (n ? (int)n : 1);
             j->n_shards = G;
             for (int s = 0; s <= G; s++) j->shard_begin[s] = (size_t)(((unsigned __int128)n * (unsigned)s) / (unsigned)G);
-            j->res = as_host_alloc(n * sizeof *j->res);
+            const double t0 = now_s();
+            if (getenv("ACCSEQ_VERBOSE")) fprintf(stderr, "map: batch of %zu reads at %.3f\n", n, now_s() - t_start);
+            j->res = pin_get(n * sizeof *j->res);
             int ok = j->res != NULL;
             for (int s = 0; s < G && ok; s++) {
-                /* run bytes: 2 per column would hold any CIGAR; short reads need a tenth of that, so start at 32 per read
-                 * plus half a byte per base and let AS_ERANGE ask for more */
+                /* run bytes: 2 per column would hold any CIGAR; reads at a few percent error need a twentieth of that, so start
+                 * at 16 per read plus an eighth of a byte per base and let AS_ERANGE ask for more */
                 uint64_t bases = 0;
                 for (size_t i = j->shard_begin[s]; i < j->shard_begin[s + 1]; i++) bases += j->b.lens[i];
-                j->runs_cap[s] = (j->shard_begin[s + 1] - j->shard_begin[s]) * 32 + (size_t)(bases / 2) + 4096;
-                j->runs[s] = as_host_alloc(j->runs_cap[s]);
+                j->runs_cap[s] = (j->shard_begin[s + 1] - j->shard_begin[s]) * 16 + (size_t)(bases / 8) + 4096;
+                j->runs[s] = pin_get(j->runs_cap[s]);
                 ok = j->runs[s] != NULL;
             }
             if (!ok) {
@@ -249,9 +315,9 @@ static void *map_main(void *v) {
                     if (sa[s].rc == AS_ERANGE) {                         /* a shard needed more room for its run bytes: redo it */
                         uint64_t bases = 0;
                         for (size_t i = j->shard_begin[s]; i < j->shard_begin[s + 1]; i++) bases += j->b.lens[i];
-                        as_host_free(j->runs[s]);
+                        pin_put(j->runs[s]);
                         j->runs_cap[s] = (size_t)(2 * bases) + 4096;
-                        j->runs[s] = as_host_alloc(j->runs_cap[s]);
+                        j->runs[s] = pin_get(j->runs_cap[s]);
                         if (!j->runs[s]) {
                             a->rc = 6;
                             break;
@@ -265,6 +331,7 @@ static void *map_main(void *v) {
                 }
             }
             j->rc = a->rc;
+            g_stage_s[1] += now_s() - t0;
         }
         const int last = j->last;
         chan_put(a->to_emit, j);
@@ -274,9 +341,9 @@ static void *map_main(void *v) {
 }
 
 static void job_free(job *j) {
-    as_packed_batch_free(&j->b, as_host_free);
-    as_host_free(j->res);
-    for (int s = 0; s < MAX_GPUS; s++) as_host_free(j->runs[s]);
+    as_packed_batch_free(&j->b, pin_put);
+    pin_put(j->res);
+    for (int s = 0; s < MAX_GPUS; s++) pin_put(j->runs[s]);
     free(j);
 }
 
@@ -367,9 +434,13 @@ int main(int argc, const char **argv) {
     int status = 0;
     if (!serial) {
         long ncpu = sysconf(_SC_NPROCESSORS_ONLN);
-        int threads = getenv("ACCSEQ_THREADS") ? atoi(getenv("ACCSEQ_THREADS")) : (int)(ncpu > 2 ? ncpu / 2 : 1);
+        /* parsing + packing a read costs about twice what printing it does: 5/8 of the cores parse, 3/8 print */
+        int threads = getenv("ACCSEQ_THREADS") ? atoi(getenv("ACCSEQ_THREADS")) : (int)(ncpu > 2 ? (5 * ncpu + 7) / 8 : 1);
+        int ethreads = getenv("ACCSEQ_THREADS") ? threads : (int)(ncpu > 2 ? (3 * ncpu + 7) / 8 : 1);
         if (threads < 1) threads = 1;
         if (threads > 64) threads = 64;
+        if (ethreads < 1) ethreads = 1;
+        if (ethreads > 64) ethreads = 64;
         chan c1, c2;
         chan_init(&c1);
         chan_init(&c2);
@@ -378,7 +449,7 @@ int main(int argc, const char **argv) {
         pthread_t t_in, t_map;
         pthread_create(&t_in, NULL, ingest_main, &ia);
         pthread_create(&t_map, NULL, map_main, &ma);
-        as_emitter *em = as_emitter_new(threads);
+        as_emitter *em = as_emitter_new(ethreads);
         const char *seg[64];
         size_t seg_len[64];
         int fallback = 0;
@@ -389,11 +460,25 @@ int main(int argc, const char **argv) {
             if (!j->last && j->rc == 0 && status == 0) {
                 const uint8_t *rp[MAX_GPUS];
                 for (int s = 0; s < j->n_shards; s++) rp[s] = j->runs[s];
+                const double t0 = now_s();
                 const int ns = as_emit_batch(em, ix, &j->b, j->res, j->n_shards, j->shard_begin, rp, j->runs_len, seg, seg_len);
+                const double t1 = now_s();
                 if (ns < 0) status = 6;
-                for (int s = 0; s < ns; s++)
-                    if (seg_len[s] && fwrite(seg[s], 1, seg_len[s], stdout) != seg_len[s]) status = 8;
+                /* the segments go straight to the descriptor: stdio would copy 350 bytes per read once more */
                 fflush(stdout);
+                for (int s = 0; s < ns && status == 0; s++) {
+                    size_t done = 0;
+                    while (done < seg_len[s]) {
+                        const ssize_t w = write(STDOUT_FILENO, seg[s] + done, seg_len[s] - done);
+                        if (w <= 0) {
+                            status = 8;
+                            break;
+                        }
+                        done += (size_t)w;
+                    }
+                }
+                g_stage_s[2] += t1 - t0;
+                g_stage_s[3] += now_s() - t1;
                 for (size_t i = 0; i < j->b.n; i++) valid += !(AS_RC_FLAG(j->res[i]) & 4u);
                 total += j->b.n;
             }
@@ -405,6 +490,9 @@ int main(int argc, const char **argv) {
         pthread_join(t_map, NULL);
         as_emitter_free(em);
         as_ingest_close(ia.in);
+        pin_drain();
+        fprintf(stderr, "[ %-7s %8.2lf ] stage busy seconds: ingest %.3f, map %.3f, emit %.3f, write %.3f (%d ingest threads, %d emit threads)\n",
+                "Info", now_s() - t_start, g_stage_s[0], g_stage_s[1], g_stage_s[2], g_stage_s[3], threads, ethreads);
         if (fallback) {
             logline("input is not 4-line FASTQ: one-thread reader");
             p.flags |= AS_F_RLE_CIGAR | AS_F_KEEP_READS;

@@ -1,5 +1,5 @@
 /*
- * emit.c -- multi-threaded SAM formatting of a packed batch's compact results (host tooling, plain C + OpenMP).
+ * emit.c -- multi-threaded SAM formatting of a packed batch's compact results (host tooling, plain C + the pool of pool.c).
  * Replaces the print loop alnmain.c:488-526 (one fprintf per record, parse_cigar per record) for batches mapped with
  * as_map_batch_packed: every thread formats a contiguous range of reads into its own buffer -- hand-rolled integer and
  * CIGAR printing, memcpy for SEQ/QUAL, the reverse complement of strand-1 reads done here (alnmain.c:27-60,433-438; QUAL is
@@ -55,13 +55,15 @@ typedef struct {
 
 struct as_emitter {
     int threads;
+    as_pool *pool;
     outbuf *out;
 };
 
 as_emitter *as_emitter_new(int threads) {
     as_emitter *e = calloc(1, sizeof *e);
     if (!e) return NULL;
-    e->threads = threads > 0 ? threads : 1;
+    e->pool = as_pool_new(threads > 0 ? threads : 1);
+    e->threads = as_pool_threads(e->pool);
     e->out = calloc((size_t)e->threads, sizeof *e->out);
     if (!e->out) {
         free(e);
@@ -73,6 +75,7 @@ as_emitter *as_emitter_new(int threads) {
 void as_emitter_free(as_emitter *e) {
     if (!e) return;
     for (int t = 0; t < e->threads; t++) free(e->out[t].buf);
+    as_pool_free(e->pool);
     free(e->out);
     free(e);
 }
@@ -131,6 +134,68 @@ static inline char *put_record(char *p, const as_host_index *ix, const char *nam
     return p;
 }
 
+typedef struct {
+    as_emitter *e;
+    const as_host_index *ix;
+    const as_packed_batch *b;
+    const as_result_compact *res;
+    int n_shards;
+    const size_t *shard_begin;
+    const uint8_t *const *shard_runs;
+    const uint64_t *shard_runs_len;
+    size_t *lo;
+    uint64_t *sum, *need;
+    int rc;
+} emit_job;
+
+static void job_sum(int t, int T, void *v) {
+    (void)T;
+    emit_job *j = v;
+    uint64_t s = 0, bytes = 0;
+    for (size_t i = j->lo[t]; i < j->lo[t + 1]; i++) {
+        s += AS_RC_NRUNS(j->res[i]);
+        bytes += 3ull * j->b->lens[i] + j->b->name_len[i] + 160;
+    }
+    j->sum[t] = s;
+    j->need[t] = bytes;
+}
+
+static void job_format(int t, int T, void *v) {
+    (void)T;
+    emit_job *j = v;
+    outbuf *o = &j->e->out[t];
+    if (o->cap < j->need[t] + 64) {
+        free(o->buf);
+        o->cap = j->need[t] + j->need[t] / 8 + 4096;
+        o->buf = malloc(o->cap);
+    }
+    o->len = 0;
+    if (!o->buf) {
+        o->cap = 0;
+        __atomic_store_n(&j->rc, AS_ENOMEM, __ATOMIC_RELAXED);
+        return;
+    }
+    /* the run bytes of this range's first read start, inside that read's shard, at (run bytes of all reads before it) -
+     * (run bytes of all shards before the read's shard) */
+    uint64_t before = 0, shards_before = 0;
+    for (int u = 0; u < t; u++) before += j->sum[u];
+    int s = 0;
+    while (s + 1 < j->n_shards && j->shard_begin[s + 1] <= j->lo[t]) shards_before += j->shard_runs_len[s++];
+    uint64_t off = before - shards_before;
+    char *p = o->buf;
+    const as_packed_batch *b = j->b;
+    for (size_t i = j->lo[t]; i < j->lo[t + 1]; i++) {
+        while (s + 1 < j->n_shards && j->shard_begin[s + 1] <= i) {       /* crossed into the next shard: its bytes start at 0 */
+            s++;
+            off = 0;
+        }
+        p = put_record(p, j->ix, b->name[i], b->name_len[i], b->seq[i], b->qual[i], b->lens[i], &j->res[i],
+                       j->shard_runs[s] ? j->shard_runs[s] + off : NULL);
+        off += AS_RC_NRUNS(j->res[i]);
+    }
+    o->len = (size_t)(p - o->buf);
+}
+
 /*
  * Formats reads [0, n) of a batch.  The results of the batch may come from several as_map_batch_packed calls (one per GPU
  * shard): shard s covers reads [shard_begin[s], shard_begin[s+1]), its run bytes lie back to back in shard_runs[s] and
@@ -144,69 +209,25 @@ int as_emit_batch(as_emitter *e, const as_host_index *ix, const as_packed_batch 
     if (!e || !ix || !b || !res || n_shards < 1 || !shard_begin || !shard_runs || !shard_runs_len || !seg || !seg_len)
         return AS_EINVAL;
     const int T = e->threads;
-    const size_t n = b->n;
-    /* thread t formats reads [lo[t], lo[t+1]).  The run bytes of its first read start, inside that read's shard, at
-     * (run bytes of all reads before lo[t]) - (run bytes of all shards before the read's shard) */
-    size_t *lo = malloc(((size_t)T + 1) * sizeof *lo);
-    uint64_t *sum = calloc((size_t)T + 1, sizeof *sum), *need = calloc((size_t)T + 1, sizeof *need);
-    if (!lo || !sum || !need) {
-        free(lo);
-        free(sum);
-        free(need);
+    emit_job j = {e, ix, b, res, n_shards, shard_begin, shard_runs, shard_runs_len, NULL, NULL, NULL, AS_OK};
+    j.lo = malloc(((size_t)T + 1) * sizeof *j.lo);                      /* thread t formats reads [lo[t], lo[t+1]) */
+    j.sum = calloc((size_t)T + 1, sizeof *j.sum);
+    j.need = calloc((size_t)T + 1, sizeof *j.need);
+    if (!j.lo || !j.sum || !j.need) {
+        free(j.lo);
+        free(j.sum);
+        free(j.need);
         return AS_ENOMEM;
     }
-    for (int t = 0; t <= T; t++) lo[t] = (size_t)(((unsigned __int128)n * (unsigned)t) / (unsigned)T);
-    int rc = AS_OK;
-#pragma omp parallel num_threads(T)
-    {
-#pragma omp for schedule(static, 1)
-        for (int t = 0; t < T; t++) {
-            uint64_t s = 0, bytes = 0;
-            for (size_t i = lo[t]; i < lo[t + 1]; i++) {
-                s += AS_RC_NRUNS(res[i]);
-                bytes += 3ull * b->lens[i] + b->name_len[i] + 160;
-            }
-            sum[t] = s;
-            need[t] = bytes;
-        }
-#pragma omp for schedule(static, 1)
-        for (int t = 0; t < T; t++) {
-            outbuf *o = &e->out[t];
-            if (o->cap < need[t] + 64) {
-                free(o->buf);
-                o->cap = need[t] + need[t] / 8 + 4096;
-                o->buf = malloc(o->cap);
-            }
-            o->len = 0;
-            if (!o->buf) {
-#pragma omp atomic write
-                rc = AS_ENOMEM;
-                continue;
-            }
-            uint64_t before = 0, shards_before = 0;
-            for (int u = 0; u < t; u++) before += sum[u];
-            int s = 0;
-            while (s + 1 < n_shards && shard_begin[s + 1] <= lo[t]) shards_before += shard_runs_len[s++];
-            uint64_t off = before - shards_before;
-            char *p = o->buf;
-            for (size_t i = lo[t]; i < lo[t + 1]; i++) {
-                while (s + 1 < n_shards && shard_begin[s + 1] <= i) {     /* crossed into the next shard: its bytes start at 0 */
-                    s++;
-                    off = 0;
-                }
-                p = put_record(p, ix, b->name[i], b->name_len[i], b->seq[i], b->qual[i], b->lens[i], &res[i],
-                               shard_runs[s] ? shard_runs[s] + off : NULL);
-                off += AS_RC_NRUNS(res[i]);
-            }
-            o->len = (size_t)(p - o->buf);
-        }
-    }
+    for (int t = 0; t <= T; t++) j.lo[t] = (size_t)(((unsigned __int128)b->n * (unsigned)t) / (unsigned)T);
+    as_pool_run(e->pool, job_sum, &j);
+    as_pool_run(e->pool, job_format, &j);
     for (int t = 0; t < T; t++) {
         seg[t] = e->out[t].buf;
         seg_len[t] = e->out[t].len;
     }
-    free(lo);
-    free(sum);
-    free(need);
-    return rc == AS_OK ? T : rc;
+    free(j.lo);
+    free(j.sum);
+    free(j.need);
+    return j.rc == AS_OK ? T : j.rc;
 }
