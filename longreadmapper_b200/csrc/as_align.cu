@@ -432,6 +432,7 @@ int as_launch_gact(as_gpu *h, const as_params *p, const uint32_t *d_qpack, size_
     a.TS = (a.TS + 2) & ~1;      /* even: lane stride TS-1 is odd, so a step's stores hit distinct banks */
     a.TQ = (int)(max_qlen < (uint32_t)T ? max_qlen : (uint32_t)T);
     a.ops = d_ops; a.ops_stride = ops_stride; a.n_ops = d_nops; a.score = d_score; a.res = d_res;
+    a.ops_zeroed = 1;            /* both callers clear the rows first (run_stages, as_cigar_align_batch) */
     AS_TRY(as_scratch(h, &h->misc[5], 64));
     AS_CUDA(cudaMemsetAsync(h->misc[5].p, 0, 64, h->stream));
     a.work_counter = (unsigned int *)h->misc[5].p;

@@ -977,6 +977,7 @@ extern "C" int as_cigar_align_batch(as_gpu *h, const as_params *p, const char *q
     AS_TRY(pair_offsets(h, n, tws));
     AS_TRY(as_scratch(h, &h->misc[3], 2 * n * sizeof(int32_t)));
     if (ops) AS_TRY(as_scratch(h, &h->store, n * ops_stride));
+    if (ops) AS_CUDA(cudaMemsetAsync(h->store.p, 0, n * ops_stride, h->stream));     /* the aligner writes only non-'=' ops of one-tile pairs */
     int32_t *d_no = (int32_t *)h->misc[3].p;
     const uint32_t *d_l = (const uint32_t *)h->misc[2].p;
     AS_TRY(as_launch_gact(h, p, (const uint32_t *)h->qpack.p, qws, d_l, (const uint32_t *)h->tpack.p, (const uint64_t *)h->toff.p,

@@ -157,6 +157,7 @@ struct GactArgs {
     int TQ;                      /* min(T, longest query) */
     uint8_t *ops;
     size_t ops_stride;
+    int ops_zeroed;              /* the op rows were cleared before the launch: single-tile reads only write their non-'=' ops */
     int32_t *n_ops, *score;      /* pair mode outputs (may be NULL) */
     as_result *res;              /* map mode output (may be NULL) */
     unsigned int *work_counter;

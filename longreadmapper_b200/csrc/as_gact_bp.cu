@@ -83,9 +83,86 @@ struct TileOut {
  * One attempt at one tile: fill (NBW words per column; SLIDE: the words slide down the diagonal, else they are the
  * whole tile), end cell, traceback into the warp's slab `tb` (16 ops per word, walk order).
  */
-template <int NBW, bool SLIDE, bool TRACK>
+#define BP_FW 16                      /* diagonal steps looked at per round of the run-skipping walk */
+/*
+ * Run-skipping traceback for tiles that are their read's only one (every op is committed, the walk runs from the far corner
+ * to the origin).  Reads at a few percent error are mostly diagonal runs of '=': a round fetches the plane words of the
+ * next BP_FW cells down the diagonal with independent loads, keeps one bit of each (op != '='), and one FFS gives the
+ * length of the run; only the cell that ends a run is decoded.  The ops are not materialised: a '=' column is the zero the
+ * row already holds (the rows are cleared before the launch), every other op leaves as an event (walk position, code) in
+ * the warp's slab, and the caller writes those few bytes once the column count is known.  Same cells, same codes, same
+ * order as the cell-by-cell walk: the planes decide, not the walker.
+ */
+template <int NBW, bool SLIDE>
+__device__ __forceinline__ void fast_walk(const TileGeom &g, const uint2 *__restrict__ planes, uint32_t *__restrict__ tb,
+                                          int KB, TileOut &out, int &n_events) {
+    int ci = g.done ? 0 : g.Tq, cj = g.done ? 0 : g.Tt;
+    int pos = 0, ne = 0, walkcost = 0;
+    bool oob = false;
+    while (__any_sync(0xFFFFFFFFu, ci > 0 && cj > 0)) {
+        if (SLIDE && ci > 0 && cj > 0 && abs(ci - cj) > KB) {   /* left the band: planes there were never written */
+            oob = true;
+            ci = cj = 0;
+        }
+        const int K = (ci > 0 && cj > 0) ? min(min(ci, cj), BP_FW) : 0;
+        uint32_t mask = 0;
+#pragma unroll
+        for (int k = 0; k < BP_FW; k++) {
+            if (k < K) {
+                const int col = cj - 1 - k, row = ci - 1 - k;
+                const int cwlo = SLIDE ? (col - KB > 0 ? (col - KB) >> 5 : 0) : 0;      /* band of column j = col+1 */
+                int sl = (row >> 5) - cwlo;
+                if (SLIDE) sl = min(max(sl, 0), NBW - 1);
+                const uint2 v = planes[((size_t)col * NBW + sl) * 32];
+                mask |= (((v.x | v.y) >> (row & 31)) & 1u) << k;
+            }
+        }
+        mask |= 1u << K;                                         /* sentinel: the run ends with the round at the latest */
+        const int run = __ffs((int)mask) - 1;
+        pos += run;
+        ci -= run;
+        cj -= run;
+        if (run < K) {                                           /* the cell that ended the run: its code (never '=') */
+            const int col = cj - 1, row = ci - 1;
+            const int cwlo = SLIDE ? (col - KB > 0 ? (col - KB) >> 5 : 0) : 0;
+            int sl = (row >> 5) - cwlo;
+            if (SLIDE) sl = min(max(sl, 0), NBW - 1);
+            const uint2 v = planes[((size_t)col * NBW + sl) * 32];
+            const uint32_t op = ((v.x >> (row & 31)) & 1u) | (((v.y >> (row & 31)) & 1u) << 1);
+            tb[(size_t)ne * 32] = ((uint32_t)pos << 2) | op;
+            ne++;
+            pos++;
+            walkcost++;
+            ci -= (op != 2u);
+            cj -= (op != 1u);
+        }
+    }
+    /* the rest of a border: row 0 is all 'D' (left), column 0 all 'I' (up) */
+    while (__any_sync(0xFFFFFFFFu, (ci | cj) != 0)) {
+        if ((ci | cj) != 0) {
+            const uint32_t op = ci == 0 ? 2u : 1u;
+            tb[(size_t)ne * 32] = ((uint32_t)pos << 2) | op;
+            ne++;
+            pos++;
+            walkcost++;
+            ci -= (op == 1u);
+            cj -= (op == 2u);
+        }
+    }
+    __syncwarp();
+    n_events = ne;
+    out.m = pos;
+    out.ai = g.Tq;
+    out.aj = g.Tt;
+    out.tscore = walkcost;
+    out.walkcost = walkcost;
+    out.bad = SLIDE && !g.done && (oob || walkcost > KB);
+}
+
+template <int NBW, bool SLIDE, bool TRACK, bool FAST = false>
 __device__ __forceinline__ void tile_pass(const TileGeom &g, uint2 *__restrict__ planes, uint32_t *__restrict__ tb,
-                                          uint2 (*win)[32], uint32_t lane, unsigned long long &st_eval, TileOut &out) {
+                                          uint2 (*win)[32], uint32_t lane, unsigned long long &st_eval, TileOut &out,
+                                          int *n_events = nullptr) {
     const int Tq = g.Tq, Tt = g.Tt, KB = SLIDE ? g.KB : 0x3FFFFFFF;
     uint32_t qlo[NBW], qhi[NBW], Pv[NBW], Mv[NBW];
 #pragma unroll
@@ -163,6 +240,10 @@ __device__ __forceinline__ void tile_pass(const TileGeom &g, uint2 *__restrict__
     }
     __syncwarp();
     if (!g.done) st_eval += (unsigned long long)(32 * NBW) * (unsigned long long)Tt;
+    if (FAST) {                                 /* every lane's tile is its read's only one */
+        fast_walk<NBW, SLIDE>(g, planes, tb, KB, out, *n_events);
+        return;
+    }
 
     /* ---- end cell (non-last tiles): min (D, distance from the corner, edge) over the interior edges ---- */
     int ei = Tq, ej = Tt;
@@ -343,6 +424,17 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
 
             TileOut o;
             bool full = !BANDED;
+            /* reads of one tile (all 32 of the warp): the run-skipping walk, ops left as events */
+            const bool fast = a.ops_zeroed && __all_sync(0xFFFFFFFFu, done || (g.last && g.i0 == 0 && g.j0 == 0));
+            int n_events = 0;
+            if (fast) {
+                if (BANDED) {
+                    tile_pass<NB, true, false, true>(g, planes, tb, win, lane, st_eval, o, &n_events);
+                    full = __any_sync(0xFFFFFFFFu, o.bad);
+                    st_retry += (full && lane == 0);
+                }
+                if (full) tile_pass<W, false, false, true>(g, planes, tb, win, lane, st_eval, o, &n_events);
+            } else {
             if (BANDED) {
                 /* the lean instantiation pays off for short reads only: in the wide kernels a third copy of the tile code
                  * costs more registers (occupancy) than the bookkeeping it saves */
@@ -353,6 +445,7 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
                 st_retry += (full && lane == 0);
             }
             if (full) tile_pass<W, false, true>(g, planes, tb, win, lane, st_eval, o);
+            }
             if (!done) {
                 st_cells += (unsigned long long)g.Tq * (unsigned long long)g.Tt;
                 st_tiles++;
@@ -366,7 +459,17 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
                 if (o.m == 0 && !g.last) { score = -1; done = true; }
                 else mym = o.m;
             }
-            if (a.ops) {
+            if (a.ops && fast) {
+                /* the row holds '=' everywhere already: place the few other ops, walk position p -> column mym-1-p */
+                const int maxe = __reduce_max_sync(0xFFFFFFFFu, mym > 0 ? n_events : 0);
+                for (int e = 0; e < maxe; e++) {
+                    if (e < n_events && mym > 0) {
+                        const uint32_t wd = tb[(size_t)e * 32];
+                        const size_t col = (size_t)(mym - 1) - (size_t)(wd >> 2);
+                        if (col < a.ops_stride) ops[col] = (uint8_t)(wd & 3u);
+                    }
+                }
+            } else if (a.ops) {
                 /* one op: walk index p = mym-1-x of the slab -> byte slot n+x of the row */
                 auto put_one = [&](int x) {
                     const int p = mym - 1 - x;
