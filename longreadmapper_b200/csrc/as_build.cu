@@ -412,7 +412,7 @@ __global__ void __launch_bounds__(256) k_export_lc(DevIndex ix, uint64_t code0, 
 __global__ void __launch_bounds__(256) k_export_sa(DevIndex ix, uint64_t row0, uint64_t n, uint64_t stride, int entry_bytes,
                                                    uint8_t *__restrict__ out) {
     for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
-        const uint64_t v = as_sa(ix, row0 + i * stride);
+        const uint64_t v = as_locate(ix, row0 + i * stride);
         uint8_t *p = out + i * (uint64_t)entry_bytes;
         for (int b = 0; b < entry_bytes; b++) p[b] = (uint8_t)(v >> (8 * b));
     }

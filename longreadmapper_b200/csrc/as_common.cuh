@@ -355,6 +355,35 @@ __device__ __forceinline__ uint64_t as_sa(const DevIndex &ix, uint64_t row) {
     return v;
 }
 
+/* SA[row] on any handle: the suffix array itself, or -- on a handle that keeps only the sampled array (as_open_opts.sampled_sa,
+ * fmidx.c:152-163) -- csa_access' walk (fmidx.c:315-331, in the form its own test expects: LF(row) = C[ch] + occ(ch, row)):
+ * follow LF until a sampled row; every step reads ONE FM sector (the row's BWT code and its occ come from the same block). */
+__device__ __forceinline__ uint64_t as_locate(const DevIndex &ix, uint64_t row) {
+    if (ix.sa_lo) return as_sa(ix, row);
+    const uint64_t ratio = ix.csa_ratio;
+    uint64_t counter = 0;
+    while (row % ratio != 0) {
+        if (row == ix.primary) return counter;                          /* bwt[row] == '$': the suffix starts at 0 */
+        uint4 cnt;
+        uint64_t lo, hi;
+        as_ld_block(ix.fm + (row >> 6), cnt, lo, hi);
+        const uint32_t r = (uint32_t)row & 63u;
+        const uint32_t c = (uint32_t)((lo >> r) & 1u) | ((uint32_t)((hi >> r) & 1u) << 1);
+        uint64_t m = ((c & 1u) ? lo : ~lo) & ((c & 2u) ? hi : ~hi);
+        m &= (r == 63u) ? ~0ULL : ((1ULL << (r + 1)) - 1ULL);
+        const uint32_t base = c == 0 ? cnt.x : c == 1 ? cnt.y : c == 2 ? cnt.z : cnt.w;
+        uint64_t occ = __ldg(ix.super + 4 * (row >> AS_SB_SHIFT) + c) + base + (uint64_t)__popcll(m);
+        if (c == 0 && (ix.primary >> 6) == (row >> 6) && ((uint32_t)ix.primary & 63u) <= r) occ -= 1;   /* '$' is stored as A */
+        const uint64_t cc = c == 0 ? ix.C[0] : c == 1 ? ix.C[1] : c == 2 ? ix.C[2] : ix.C[3];
+        row = cc + occ;
+        counter++;
+    }
+    const uint64_t j = row / ratio;
+    uint64_t v = __ldg(ix.csa_lo + j);
+    if (ix.csa_hi) v |= (uint64_t)__ldg(ix.csa_hi + j) << 32;
+    return v + counter;
+}
+
 /* 2-bit packed sequences: 16 bases per u32, base i at bits [2(i&15), 2(i&15)+1] of word i>>4 */
 __device__ __forceinline__ uint32_t as_base_at(const uint32_t *w, uint64_t i) {
     return (__ldg(w + (i >> 4)) >> (2u * ((uint32_t)i & 15u))) & 3u;

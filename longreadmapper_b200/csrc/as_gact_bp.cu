@@ -159,6 +159,122 @@ __device__ __forceinline__ void fast_walk(const TileGeom &g, const uint2 *__rest
     out.bad = SLIDE && !g.done && (oob || walkcost > KB);
 }
 
+#define BP_DC 16                      /* one-word diagonal band: rows [j - BP_DC, j - BP_DC + 31] of column j */
+/*
+ * One-word DIAGONAL band for tiles that are their read's only one (first attempt of reads at a few percent error).  The
+ * 32-row window of column j starts at row top(j) = max(1, j - BP_DC): it stands still for the first BP_DC + 1 columns (its
+ * top neighbour is then the matrix's own row 0, whose horizontal delta is +1 exactly) and moves down ONE ROW per column
+ * afterwards -- Pv, Mv shift right by a bit, the row that enters at the bottom starts from Pv = 1 (+1: an upper bound), the
+ * row above the window is taken as +1 per column too, and the column step itself is the unchanged Myers/Hyyro step.  So
+ * the argument of the word-sliding band applies bit for bit: computed values are never below the true ones and are exact
+ * wherever the true value is <= KB = BP_DC - 1, every cell with |i-j| <= KB is in the window, and a walk that stays inside
+ * |i-j| <= KB at a cost <= KB reads only exact values and exact tie-breaks.  Otherwise the tile goes to the wider bands.
+ * Half the words of the two-word band, half the plane bytes ([column][lane], one uint2 per column), and bit b of a word is
+ * the DIAGONAL i - j + BP_DC of the sliding part, which is what the run-skipping walk follows.
+ */
+__device__ __forceinline__ void tile_diag1(const TileGeom &g, uint2 *__restrict__ planes, uint32_t *__restrict__ tb,
+                                           unsigned long long &st_eval, TileOut &out, int &n_events) {
+    const int Tq = g.Tq, Tt = g.Tt;
+    constexpr int KB = BP_DC - 1;
+    uint32_t qlo_a, qhi_a, qlo_b, qhi_b;                     /* query planes of words w0, w0 + 1 */
+    load_qword(g.qp, g.i0, 0, Tq, qlo_a, qhi_a);
+    load_qword(g.qp, g.i0, 1, Tq, qlo_b, qhi_b);
+    uint32_t Pv = 0xFFFFFFFFu, Mv = 0u, tw = 0;
+    int w0 = 0;
+    uint32_t sh = 0;                                         /* top(j) - 1 - 32 * w0: where the window starts in word w0 */
+    uint2 *pcol = planes;
+    for (int j = 1; j <= g.maxTt; j++, pcol += 32) {
+        if (j > BP_DC + 1) {                                 /* warp-uniform: the window moves down one row */
+            Pv = (Pv >> 1) | 0x80000000u;
+            Mv >>= 1;
+            if (++sh == 32u) {
+                sh = 0;
+                w0++;
+                qlo_a = qlo_b;
+                qhi_a = qhi_b;
+                load_qword(g.qp, g.i0, w0 + 1, Tq, qlo_b, qhi_b);
+            }
+        }
+        if (j <= Tt) {
+            if (((j - 1) & 15) == 0) tw = as_bases16(g.tbase, g.toff + (uint64_t)(g.j0 + j - 1));
+            const uint32_t tl = 0u - (tw & 1u), th = 0u - ((tw >> 1) & 1u);
+            tw >>= 2;
+            const uint32_t ql = __funnelshift_r(qlo_a, qlo_b, sh), qh = __funnelshift_r(qhi_a, qhi_b, sh);
+            const uint32_t eq = ~((ql ^ tl) | (qh ^ th));
+            const uint32_t xv = eq | Mv;
+            const uint32_t xh = (((eq & Pv) + Pv) ^ Pv) | eq;
+            const uint32_t ph = ((Mv | ~(xh | Pv)) << 1) | 1u;  /* the row above the window: +1 */
+            const uint32_t mh = (Pv & xh) << 1;
+            const uint32_t nd0 = ~(xh | Mv);                 /* ~D0 */
+            const uint32_t npv = mh | ~(xv | ph);
+            Mv = ph & xv;
+            Pv = npv;
+            uint2 o;
+            o.x = ~eq & (npv | nd0);
+            o.y = ~eq & (~npv | nd0);
+            *pcol = o;
+        }
+    }
+    __syncwarp();
+    if (!g.done) st_eval += 32ull * (unsigned long long)Tt;
+
+    /* ---- run-skipping walk; cell (ci, cj) is bit ci - max(1, cj - BP_DC) of column cj's word ---- */
+    int ci = g.done ? 0 : Tq, cj = g.done ? 0 : Tt;
+    int pos = 0, ne = 0, walkcost = 0;
+    bool oob = false;
+    while (__any_sync(0xFFFFFFFFu, ci > 0 && cj > 0)) {
+        if (ci > 0 && cj > 0 && abs(ci - cj) > KB) {
+            oob = true;
+            ci = cj = 0;
+        }
+        const int K = (ci > 0 && cj > 0) ? min(min(ci, cj), BP_FW) : 0;
+        uint32_t mask = 0;
+#pragma unroll
+        for (int k = 0; k < BP_FW; k++) {
+            if (k < K) {
+                const int c2 = cj - k, b = (ci - k) - max(1, c2 - BP_DC);
+                const uint2 v = planes[(size_t)(c2 - 1) * 32];
+                mask |= (((v.x | v.y) >> b) & 1u) << k;
+            }
+        }
+        mask |= 1u << K;
+        const int run = __ffs((int)mask) - 1;
+        pos += run;
+        ci -= run;
+        cj -= run;
+        if (run < K) {
+            const int b = ci - max(1, cj - BP_DC);
+            const uint2 v = planes[(size_t)(cj - 1) * 32];
+            const uint32_t op = ((v.x >> b) & 1u) | (((v.y >> b) & 1u) << 1);
+            tb[(size_t)ne * 32] = ((uint32_t)pos << 2) | op;
+            ne++;
+            pos++;
+            walkcost++;
+            ci -= (op != 2u);
+            cj -= (op != 1u);
+        }
+    }
+    while (__any_sync(0xFFFFFFFFu, (ci | cj) != 0)) {
+        if ((ci | cj) != 0) {
+            const uint32_t op = ci == 0 ? 2u : 1u;
+            tb[(size_t)ne * 32] = ((uint32_t)pos << 2) | op;
+            ne++;
+            pos++;
+            walkcost++;
+            ci -= (op == 1u);
+            cj -= (op == 2u);
+        }
+    }
+    __syncwarp();
+    n_events = ne;
+    out.m = pos;
+    out.ai = Tq;
+    out.aj = Tt;
+    out.tscore = walkcost;
+    out.walkcost = walkcost;
+    out.bad = !g.done && (oob || walkcost > KB);
+}
+
 template <int NBW, bool SLIDE, bool TRACK, bool FAST = false>
 __device__ __forceinline__ void tile_pass(const TileGeom &g, uint2 *__restrict__ planes, uint32_t *__restrict__ tb,
                                           uint2 (*win)[32], uint32_t lane, unsigned long long &st_eval, TileOut &out,
@@ -369,7 +485,7 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
     uint32_t *tb = tb_all + gwarp * tb_per_warp + lane;                    /* [word*32]: 16 ops per word, walk order */
     uint2 (*win)[32] = s_win[threadIdx.x >> 5];
     unsigned long long st_cells = 0, st_eval = 0;
-    unsigned int st_retry = 0, st_tiles = 0, st_wtiles = 0, st_half = 0;
+    unsigned int st_retry = 0, st_tiles = 0, st_wtiles = 0, st_half = 0, st_diag = 0, st_diag_retry = 0;
     TileGeom g;
     g.T = a.T;
     g.inner = a.T - a.O;
@@ -402,6 +518,7 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
         /* column ops leave as aligned 32-bit words: omis = misalignment of the row, oacc = the word being filled */
         const uint32_t omis = (uint32_t)(reinterpret_cast<uintptr_t>(ops) & 3u);
         uint32_t oacc = 0;
+        bool by_events = false;          /* the read's ops were placed as events: no partial word is pending */
         if (!done && qlen == 0 && tlen == 0) done = true;
 
         while (__any_sync(0xFFFFFFFFu, !done)) {
@@ -428,7 +545,14 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
             const bool fast = a.ops_zeroed && __all_sync(0xFFFFFFFFu, done || (g.last && g.i0 == 0 && g.j0 == 0));
             int n_events = 0;
             if (fast) {
-                if (BANDED) {
+                bool wider = true;
+                if (BANDED && NB == 2) {                     /* lowest band level: the one-word diagonal band first */
+                    tile_diag1(g, planes, tb, st_eval, o, n_events);
+                    wider = __any_sync(0xFFFFFFFFu, o.bad);
+                    st_diag += (lane == 0);
+                    st_diag_retry += (wider && lane == 0);
+                }
+                if (BANDED && wider) {
                     tile_pass<NB, true, false, true>(g, planes, tb, win, lane, st_eval, o, &n_events);
                     full = __any_sync(0xFFFFFFFFu, o.bad);
                     st_retry += (full && lane == 0);
@@ -459,6 +583,7 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
                 if (o.m == 0 && !g.last) { score = -1; done = true; }
                 else mym = o.m;
             }
+            if (fast) by_events = true;
             if (a.ops && fast) {
                 /* the row holds '=' everywhere already: place the few other ops, walk position p -> column mym-1-p */
                 const int maxe = __reduce_max_sync(0xFFFFFFFFu, mym > 0 ? n_events : 0);
@@ -519,7 +644,7 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
             }
             __syncwarp();
         }
-        if (ops && (((uint32_t)n + omis) & 3u)) {                  /* the last, partial word */
+        if (ops && !by_events && (((uint32_t)n + omis) & 3u)) {    /* the last, partial word */
             const uint32_t vp = (uint32_t)n + omis;
             put_bytes(ops, (long)(vp & ~3u) - (long)omis, oacc, 0, (int)(vp & 3u), a.ops_stride);
         }
@@ -568,7 +693,9 @@ __global__ void k_gact_policy(volatile unsigned int *host_band, const unsigned i
 template <int W, int NB>
 static int launch_bp(as_gpu *h, GactArgs &a, size_t n, int blocks_per_sm, unsigned int cur_band) {
     const size_t planes_per_warp = (size_t)a.TS * W * 32;                 /* uint2; the band's slab is the smaller one */
-    const size_t tb_per_warp = (size_t)((a.TS + a.TQ + 15) / 16 + 2) * 32;  /* u32 */
+    /* u32 per lane: 16 ops per word of the cell-by-cell walk; one word per EVENT of the run-skipping walk of one-tile reads,
+     * which can be every op of the walk (two unrelated sequences) */
+    const size_t tb_per_warp = (size_t)(a.ops_zeroed ? a.TS + a.TQ + 2 : (a.TS + a.TQ + 15) / 16 + 2) * 32;
     size_t warps_needed = (n + 31) / 32;
     size_t blocks = (warps_needed + BP_THREADS / 32 - 1) / (BP_THREADS / 32);
     if (blocks_per_sm <= 0) {        /* reads are claimed from a work counter: the grid is the resident blocks */

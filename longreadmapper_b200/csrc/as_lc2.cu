@@ -149,5 +149,17 @@ int as_build_lc2(as_gpu *h) {
     ix.sax = nullptr;
     if (!ix.text2 || !ix.sa_lo || ix.N < 2) return AS_OK;
     AS_TRY(build_lc2_table(h));
-    return build_sax(h);
+    AS_TRY(build_sax(h));
+    if (h->opts.sampled_sa > 0) {
+        /* as_open_opts.sampled_sa: keep SA[r * i] only (_build_csa, fmidx.c:152-163).  The deep table above was built from
+         * the full array; from here on positions come from csa_access' LF walk (as_locate). */
+        AS_TRY(as_csa_sample(h, h->opts.sampled_sa));
+        AS_CUDA(cudaStreamSynchronize(h->stream));
+        if (h->d_sa_lo) cudaFree(h->d_sa_lo);
+        if (h->d_sa_hi) cudaFree(h->d_sa_hi);
+        h->d_sa_lo = h->d_sa_hi = nullptr;
+        ix.sa_lo = nullptr;
+        ix.sa_hi = nullptr;
+    }
+    return AS_OK;
 }

@@ -88,7 +88,7 @@ __global__ void __launch_bounds__(256) k_sa_access(DevIndex ix, const uint64_t *
                                                    uint64_t *__restrict__ pos) {
     for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
         uint64_t r = rows[i];
-        pos[i] = r < ix.N ? as_sa(ix, r) : 0;                           /* fmidx.c:20-23: out of scope -> 0 */
+        pos[i] = r < ix.N ? as_locate(ix, r) : 0;                           /* fmidx.c:20-23: out of scope -> 0 */
     }
 }
 
@@ -168,7 +168,7 @@ extern "C" int as_lc_build(as_gpu *h, int hlen, uint64_t *lc) {
 extern "C" int as_sa_access_batch(as_gpu *h, const uint64_t *rows, size_t n, uint64_t *pos) {
     if (!h || !rows || !pos) return AS_EINVAL;
     if (n == 0) return AS_OK;
-    if (!h->ix.sa_lo) {
+    if (!h->ix.sa_lo && !h->ix.csa_lo) {
         as_set_error("as_sa_access_batch: the handle has no suffix array");
         return AS_EINVAL;
     }

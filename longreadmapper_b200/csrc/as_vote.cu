@@ -307,7 +307,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                                 pr[r] = e & 0xFFFFFFFFFFULL;
                                 pv[r] = (uint32_t)(e >> 40) >> (2 * (12 - nrem));
                             } else {
-                                pr[r] = as_sa(ix, kk + (uint64_t)r);
+                                pr[r] = as_locate(ix, kk + (uint64_t)r);
                             }
                             in_text &= pr[r] >= (uint64_t)nrem;
                         }
@@ -340,7 +340,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                                 if (nsurv == 1) {
                                     if (from_e) {
                                         const uint64_t row = kk + rsurv;
-                                        pos1 = (ix.sax ? (__ldg(ix.sax + row) & 0xFFFFFFFFFFULL) : as_sa(ix, row)) - (uint64_t)nrem;
+                                        pos1 = (ix.sax ? (__ldg(ix.sax + row) & 0xFFFFFFFFFFULL) : as_locate(ix, row)) - (uint64_t)nrem;
                                     }
                                     have_pos = true;
                                     hit_pos = pos1;
@@ -376,7 +376,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                 const bool valid = rr_eff != 0;
                 uint64_t key = 0;
                 if (valid) {
-                    key = (have_pos ? hit_pos : as_sa(ix, kk)) - (uint64_t)j;   /* alnmain.c:363-365, u64 wrap kept */
+                    key = (have_pos ? hit_pos : as_locate(ix, kk)) - (uint64_t)j;   /* alnmain.c:363-365, u64 wrap kept */
                     st_hits++;
                 }
                 const uint64_t tag = valid ? ((key >> 4) | ((uint64_t)(lane / G) << 60)) : (0xF000000000000000ULL | lane);
@@ -408,7 +408,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
             } else if (!__any_sync(FULL, rr_eff > 1)) {
                 /* every surviving seed of the warp has exactly one SA row */
                 if (rr_eff) {
-                    uint64_t key = (have_pos ? hit_pos : as_sa(ix, kk)) - (uint64_t)j;   /* alnmain.c:363-365, u64 wrap kept */
+                    uint64_t key = (have_pos ? hit_pos : as_locate(ix, kk)) - (uint64_t)j;   /* alnmain.c:363-365, u64 wrap kept */
                     st_hits++;
                     if (!table_insert<USED_T>(t, key >> 4, (uint32_t)key & 15u, m * a.thres)) ok = false;
                 }
@@ -443,7 +443,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                         const uint32_t oj = (uint32_t)iter + om * (uint32_t)P;
                         const uint32_t off = v - ob;
                         uint64_t row = (((uint64_t)okh << 32) | okl) + off;
-                        uint64_t key = (opk ? (((uint64_t)oph << 32) | opl) : as_sa(ix, row)) - (uint64_t)oj;
+                        uint64_t key = (opk ? (((uint64_t)oph << 32) | opl) : as_locate(ix, row)) - (uint64_t)oj;
                         st_hits++;
                         if (!table_insert<USED_T>(t, key >> 4, (uint32_t)key & 15u, om * a.thres + off)) ok = false;
                     }

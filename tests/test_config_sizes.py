@@ -355,3 +355,28 @@ def test_c4_c5_oracle_sample_human_scale(native, c4_index):
         print(f"c5 human-scale sample: valid {ok.mean():.3f}, within 50 bp of truth (oracle == gpu) {near.mean():.3f}")
     finally:
         ox.close()
+
+
+@pytest.mark.gpu
+def test_c4_sampled_sa_human_scale(native, c4_index):
+    """SURVEY 8(f)-4 at the size it is meant for: a second human-scale handle that keeps SA[8 i] only (3.9 GB instead of the
+    31 GB suffix array + 50 GB SA + context table) maps 200 000 reads of c4 to the same records and CIGARs as the full one"""
+    import torch
+    m, g = c4_index["m"], c4_index["g"]
+    free0, _ = torch.cuda.mem_get_info(0)
+    if free0 < 75 * 2**30:
+        pytest.skip("not enough free HBM for a second human-scale index build")
+    reads, lens, _, _ = native.sim_reads(16, g, 200_000, 150, 150, 0.02, 0.02, 0.8)
+    res, ops = m.map_batch(reads.copy(), lens, params=m.params())
+    samp = native.GpuMapper.build_cat(c4_index["cat"], c4_index["mta"], 0, opts=native.open_opts(sampled_sa=8))
+    try:
+        free1, _ = torch.cuda.mem_get_info(0)
+        used_gb = (free0 - free1) / 2**30
+        print(f"human-scale index with sampled_sa=8: {used_gb:.1f} GB of HBM")
+        assert used_gb < 48
+        res2, ops2 = samp.map_batch(reads.copy(), lens, params=samp.params())
+        assert np.array_equal(res, res2)
+        live = np.arange(ops.shape[1])[None, :] < np.maximum(res["n_cigar_op"], 0)[:, None]
+        assert np.array_equal(ops * live, ops2 * live)
+    finally:
+        samp.close()
