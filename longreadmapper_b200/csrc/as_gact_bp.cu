@@ -169,83 +169,142 @@ __device__ __forceinline__ void fast_walk(const TileGeom &g, const uint2 *__rest
  * the argument of the word-sliding band applies bit for bit: computed values are never below the true ones and are exact
  * wherever the true value is <= KB = BP_DC - 1, every cell with |i-j| <= KB is in the window, and a walk that stays inside
  * |i-j| <= KB at a cost <= KB reads only exact values and exact tie-breaks.  Otherwise the tile goes to the wider bands.
- * Half the words of the two-word band, half the plane bytes ([column][lane], one uint2 per column), and bit b of a word is
- * the DIAGONAL i - j + BP_DC of the sliding part, which is what the run-skipping walk follows.
+ * Half the words of the two-word band, and bit b of a word is the DIAGONAL i - j + BP_DC of the sliding part, which is what
+ * the run-skipping walk follows.
+ *
+ * Planes: only the 16 diagonals around the main one are KEPT -- bits [s(j), s(j) + 16) of both op-code planes, s(j) =
+ * clamp(j - top(j) - 8, 0, 16), one 32-bit word per column and lane ([column][lane]): 19 KB per warp for 150-bp reads, so
+ * the slabs of all resident warps (80 MB) stay in the 126 MB L2 and the walk never waits for DRAM.  A walk that needs a
+ * diagonal outside the kept 16 (more than seven net indels) is flagged like one that leaves the band.
  */
-__device__ __forceinline__ void tile_diag1(const TileGeom &g, uint2 *__restrict__ planes, uint32_t *__restrict__ tb,
+__device__ __forceinline__ int diag1_top(int j) { return j - BP_DC > 1 ? j - BP_DC : 1; }
+__device__ __forceinline__ int diag1_s(int j) {               /* first kept bit of column j's word */
+    const int s = j - diag1_top(j) - 8;
+    return s < 0 ? 0 : (s > 16 ? 16 : s);
+}
+__device__ __forceinline__ void tile_diag1(const TileGeom &g, uint2 *__restrict__ planes2, uint32_t *__restrict__ tb,
                                            unsigned long long &st_eval, TileOut &out, int &n_events) {
+    /* [column][lane] of u32 in the warp's slab: planes2 = slab + lane in uint2 units = slab + 2 * lane in u32 units */
+    uint32_t *planes = reinterpret_cast<uint32_t *>(planes2) - (threadIdx.x & 31u);
     const int Tq = g.Tq, Tt = g.Tt;
     constexpr int KB = BP_DC - 1;
     uint32_t qlo_a, qhi_a, qlo_b, qhi_b;                     /* query planes of words w0, w0 + 1 */
     load_qword(g.qp, g.i0, 0, Tq, qlo_a, qhi_a);
     load_qword(g.qp, g.i0, 1, Tq, qlo_b, qhi_b);
     uint32_t Pv = 0xFFFFFFFFu, Mv = 0u, tw = 0;
-    int w0 = 0;
-    uint32_t sh = 0;                                         /* top(j) - 1 - 32 * w0: where the window starts in word w0 */
-    uint2 *pcol = planes;
-    for (int j = 1; j <= g.maxTt; j++, pcol += 32) {
-        if (j > BP_DC + 1) {                                 /* warp-uniform: the window moves down one row */
-            Pv = (Pv >> 1) | 0x80000000u;
-            Mv >>= 1;
-            if (++sh == 32u) {
-                sh = 0;
-                w0++;
-                qlo_a = qlo_b;
-                qhi_a = qhi_b;
-                load_qword(g.qp, g.i0, w0 + 1, Tq, qlo_b, qhi_b);
+    /* one column: the Myers/Hyyro step on the window (ql, qh = the query planes of its 32 rows), the kept 16 diagonals of
+     * the two op-code planes stored as one word.  (x << 1) | 1 and x << 1 are written as multiply-adds: they go to the FMA
+     * pipe, which idles while the ALU pipe carries the logic ops. */
+#define DIAG1_STEP(QL, QH, SS, PDST)                                                                   \
+    do {                                                                                               \
+        const uint32_t tl_ = 0u - (tw & 1u), th_ = 0u - ((tw >> 1) & 1u);                              \
+        tw >>= 2;                                                                                      \
+        const uint32_t eq_ = ~(((QL) ^ tl_) | ((QH) ^ th_));                                          \
+        const uint32_t xv_ = eq_ | Mv;                                                                 \
+        const uint32_t xh_ = (((eq_ & Pv) + Pv) ^ Pv) | eq_;                                           \
+        const uint32_t ph_ = (Mv | ~(xh_ | Pv)) * 2u + 1u;   /* the row above the window: +1 */       \
+        const uint32_t mh_ = (Pv & xh_) * 2u;                                                          \
+        const uint32_t nd0_ = ~(xh_ | Mv);                   /* ~D0 */                                 \
+        const uint32_t npv_ = mh_ | ~(xv_ | ph_);                                                      \
+        Mv = ph_ & xv_;                                                                                \
+        Pv = npv_;                                                                                     \
+        if (act) *(PDST) = (SS) == 8u ? __byte_perm(~eq_ & (npv_ | nd0_), ~eq_ & (~npv_ | nd0_), 0x6521)          \
+                                      : __byte_perm((~eq_ & (npv_ | nd0_)) >> (SS), (~eq_ & (~npv_ | nd0_)) >> (SS), 0x5410); \
+    } while (0)
+    /* ---- columns 1 .. 17: the window stands on rows 1 .. 32 ---- */
+    const int jA = g.maxTt < BP_DC + 1 ? g.maxTt : BP_DC + 1;
+    for (int j = 1; j <= jA; j++) {
+        const bool act = j <= Tt;
+        if (act && ((j - 1) & 15) == 0) tw = as_bases16(g.tbase, g.toff + (uint64_t)(g.j0 + j - 1));
+        const uint32_t ss = (uint32_t)(j - 9 > 0 ? j - 9 : 0);        /* diag1_s(j) for top(j) = 1 */
+        uint32_t pv0 = Pv, mv0 = Mv;
+        DIAG1_STEP(qlo_a, qhi_a, ss, planes + (size_t)(j - 1) * 32);
+        if (!act) { Pv = pv0; Mv = mv0; }
+    }
+    /* ---- columns 18 ..: the window moves down one row per column; 16 columns per target word, the query words change
+     * every 32 columns, on a target-word boundary (column 49, 81, ...) ---- */
+    for (int j0 = BP_DC + 2; j0 <= g.maxTt; j0 = ((j0 - 1) | 15) + 2) {
+        const int jend = ((j0 - 1) | 15) + 1 < g.maxTt ? ((j0 - 1) | 15) + 1 : g.maxTt;     /* last column of this target word */
+        if (j0 <= Tt && ((j0 - 1) & 15) == 0) tw = as_bases16(g.tbase, g.toff + (uint64_t)(g.j0 + j0 - 1));
+        uint32_t sh = (uint32_t)(j0 - (BP_DC + 1)) & 31u;              /* window start inside query word a, this column */
+        if (sh == 0) {                                                 /* crossed into the next query word */
+            const int w0 = (j0 - (BP_DC + 1)) >> 5;
+            qlo_a = qlo_b;
+            qhi_a = qhi_b;
+            load_qword(g.qp, g.i0, w0 + 1, Tq, qlo_b, qhi_b);
+        }
+        uint32_t *pc = planes + (size_t)(j0 - 1) * 32;
+#pragma unroll 4
+        for (int j = j0; j <= jend; j++, sh++, pc += 32) {
+            const bool act = j <= Tt;
+            if (act) {
+                Pv = __funnelshift_r(Pv, 1u, 1u);           /* (Pv >> 1) | 0x80000000: the entering row starts at +1 */
+                Mv >>= 1;
+                const uint32_t ql = __funnelshift_r(qlo_a, qlo_b, sh), qh = __funnelshift_r(qhi_a, qhi_b, sh);
+                DIAG1_STEP(ql, qh, 8u, pc);
             }
         }
-        if (j <= Tt) {
-            if (((j - 1) & 15) == 0) tw = as_bases16(g.tbase, g.toff + (uint64_t)(g.j0 + j - 1));
-            const uint32_t tl = 0u - (tw & 1u), th = 0u - ((tw >> 1) & 1u);
-            tw >>= 2;
-            const uint32_t ql = __funnelshift_r(qlo_a, qlo_b, sh), qh = __funnelshift_r(qhi_a, qhi_b, sh);
-            const uint32_t eq = ~((ql ^ tl) | (qh ^ th));
-            const uint32_t xv = eq | Mv;
-            const uint32_t xh = (((eq & Pv) + Pv) ^ Pv) | eq;
-            const uint32_t ph = ((Mv | ~(xh | Pv)) << 1) | 1u;  /* the row above the window: +1 */
-            const uint32_t mh = (Pv & xh) << 1;
-            const uint32_t nd0 = ~(xh | Mv);                 /* ~D0 */
-            const uint32_t npv = mh | ~(xv | ph);
-            Mv = ph & xv;
-            Pv = npv;
-            uint2 o;
-            o.x = ~eq & (npv | nd0);
-            o.y = ~eq & (~npv | nd0);
-            *pcol = o;
-        }
     }
+#undef DIAG1_STEP
     __syncwarp();
     if (!g.done) st_eval += 32ull * (unsigned long long)Tt;
 
-    /* ---- run-skipping walk; cell (ci, cj) is bit ci - max(1, cj - BP_DC) of column cj's word ---- */
+    /* ---- run-skipping walk.  Cell (ci, cj) is bit b of column cj's kept word: b = (ci - cj) + 8 from column 17 on (the
+     * window slides with the diagonal), b = ci - 1 - max(0, cj - 9) before.  A round looks at the next BP_FW cells down the
+     * diagonal and keeps three bits of each: X (both planes set), indel (one plane set) and the low plane.  Substitutions
+     * stay on the diagonal, so all of them up to the first indel are recorded from the masks; only an indel ends a round. */
     int ci = g.done ? 0 : Tq, cj = g.done ? 0 : Tt;
     int pos = 0, ne = 0, walkcost = 0;
     bool oob = false;
     while (__any_sync(0xFFFFFFFFu, ci > 0 && cj > 0)) {
-        if (ci > 0 && cj > 0 && abs(ci - cj) > KB) {
+        if (ci > 0 && cj > 0 && abs(ci - cj) > 7) {          /* outside the 16 kept diagonals (a fortiori outside the band) */
             oob = true;
             ci = cj = 0;
         }
         const int K = (ci > 0 && cj > 0) ? min(min(ci, cj), BP_FW) : 0;
-        uint32_t mask = 0;
+        const int dv = ci - cj + 8;
+        uint32_t mx = 0, mi = 0, ml = 0;                     /* bit k: cell k of the round is X / an indel / has its low plane set */
+        /* warp-uniform choice: the one-bit-position loop unless some lane's round reaches into the first 16 columns */
+        if (!__any_sync(0xFFFFFFFFu, K > 0 && cj - K < 16)) {
+            const uint32_t *pb = planes + (ptrdiff_t)(cj - 1) * 32;
 #pragma unroll
-        for (int k = 0; k < BP_FW; k++) {
-            if (k < K) {
-                const int c2 = cj - k, b = (ci - k) - max(1, c2 - BP_DC);
-                const uint2 v = planes[(size_t)(c2 - 1) * 32];
-                mask |= (((v.x | v.y) >> b) & 1u) << k;
+            for (int k = BP_FW - 1; k >= 0; k--) {
+                uint32_t u = 0;
+                if (k < K) u = pb[-k * 32] >> dv;
+                const uint32_t t = u >> 16;
+                mx = mx * 2u + (u & t & 1u);
+                mi = mi * 2u + ((u ^ t) & 1u);
+                ml = ml * 2u + (u & 1u);
+            }
+        } else {
+#pragma unroll
+            for (int k = BP_FW - 1; k >= 0; k--) {
+                uint32_t u = 0;
+                if (k < K) {
+                    const int c2 = cj - k;
+                    const int bb = c2 >= 17 ? dv : (ci - k) - 1 - max(0, c2 - 9);
+                    u = planes[(size_t)(c2 - 1) * 32] >> bb;
+                }
+                const uint32_t t = u >> 16;
+                mx = mx * 2u + (u & t & 1u);
+                mi = mi * 2u + ((u ^ t) & 1u);
+                ml = ml * 2u + (u & 1u);
             }
         }
-        mask |= 1u << K;
-        const int run = __ffs((int)mask) - 1;
+        const int run = __ffs((int)(mi | (1u << K))) - 1;    /* cells before the first indel (or the end of the round) */
+        uint32_t xs = mx & ((1u << run) - 1u);
+        while (xs) {                                         /* substitutions on the way, in walk order */
+            const int k = __ffs((int)xs) - 1;
+            xs &= xs - 1u;
+            tb[(size_t)ne * 32] = ((uint32_t)(pos + k) << 2) | 3u;
+            ne++;
+            walkcost++;
+        }
         pos += run;
         ci -= run;
         cj -= run;
-        if (run < K) {
-            const int b = ci - max(1, cj - BP_DC);
-            const uint2 v = planes[(size_t)(cj - 1) * 32];
-            const uint32_t op = ((v.x >> b) & 1u) | (((v.y >> b) & 1u) << 1);
+        if (run < K) {                                       /* the indel: low plane set = 'I' (up), else 'D' (left) */
+            const uint32_t op = ((ml >> run) & 1u) ? 1u : 2u;
             tb[(size_t)ne * 32] = ((uint32_t)pos << 2) | op;
             ne++;
             pos++;
