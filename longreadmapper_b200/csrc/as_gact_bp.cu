@@ -601,9 +601,11 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
             TileOut o;
             bool full = !BANDED;
             /* reads of one tile (all 32 of the warp): the run-skipping walk, ops left as events */
-            const bool fast = a.ops_zeroed && __all_sync(0xFFFFFFFFu, done || (g.last && g.i0 == 0 && g.j0 == 0));
+            /* (compiled into the short-read kernels only: in the wide ones the extra code costs registers -- 96 -> 124 and
+             * 128 -> 157 per thread -- and their tiles are rarely a read's only one) */
+            const bool fast = W <= 5 && a.ops_zeroed && __all_sync(0xFFFFFFFFu, done || (g.last && g.i0 == 0 && g.j0 == 0));
             int n_events = 0;
-            if (fast) {
+            if (W <= 5 && fast) {
                 bool wider = true;
                 if (BANDED && NB == 2) {                     /* lowest band level: the one-word diagonal band first */
                     tile_diag1(g, planes, tb, st_eval, o, n_events);
@@ -643,7 +645,7 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
                 else mym = o.m;
             }
             if (fast) by_events = true;
-            if (a.ops && fast) {
+            if (W <= 5 && a.ops && fast) {
                 /* the row holds '=' everywhere already: place the few other ops, walk position p -> column mym-1-p */
                 const int maxe = __reduce_max_sync(0xFFFFFFFFu, mym > 0 ? n_events : 0);
                 for (int e = 0; e < maxe; e++) {
@@ -754,7 +756,7 @@ static int launch_bp(as_gpu *h, GactArgs &a, size_t n, int blocks_per_sm, unsign
     const size_t planes_per_warp = (size_t)a.TS * W * 32;                 /* uint2; the band's slab is the smaller one */
     /* u32 per lane: 16 ops per word of the cell-by-cell walk; one word per EVENT of the run-skipping walk of one-tile reads,
      * which can be every op of the walk (two unrelated sequences) */
-    const size_t tb_per_warp = (size_t)(a.ops_zeroed ? a.TS + a.TQ + 2 : (a.TS + a.TQ + 15) / 16 + 2) * 32;
+    const size_t tb_per_warp = (size_t)(W <= 5 && a.ops_zeroed ? a.TS + a.TQ + 2 : (a.TS + a.TQ + 15) / 16 + 2) * 32;
     size_t warps_needed = (n + 31) / 32;
     size_t blocks = (warps_needed + BP_THREADS / 32 - 1) / (BP_THREADS / 32);
     if (blocks_per_sm <= 0) {        /* reads are claimed from a work counter: the grid is the resident blocks */
