@@ -121,6 +121,15 @@ int  as_emit_batch(as_emitter *e, const as_host_index *ix, const as_packed_batch
                    const size_t *shard_begin, const uint8_t *const *shard_runs, const uint64_t *shard_runs_len,
                    const char **seg, size_t *seg_len);
 
+/* Paired-end records (DESIGN.md "Paired-end mode"; the reference's pair_end() is a stub, alnmain.c:552-555): mate 1 then
+ * mate 2 of every pair, FLAG |= 0x1, 0x40 / 0x80, 0x8 / 0x20 from the mate, 0x2 when both mates map to one sequence on
+ * opposite strands within max_insert; RNEXT / PNEXT / TLEN in the columns the reference prints as `*`, 0, 0. */
+int  as_emit_pairs(as_emitter *e, const as_host_index *ix, size_t n, const char *const *name1, const uint32_t *name1_len,
+                   const char *const *seq1, const char *const *qual1, const uint32_t *len1, const as_result_compact *res1,
+                   const uint8_t *runs1, const char *const *name2, const uint32_t *name2_len, const char *const *seq2,
+                   const char *const *qual2, const uint32_t *len2, const as_result_compact *res2, const uint8_t *runs2,
+                   long max_insert, const char **out, size_t *out_len);
+
 #ifdef __cplusplus
 }
 #endif

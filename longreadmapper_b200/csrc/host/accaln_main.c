@@ -2,6 +2,7 @@
  * accaln_main.c -- `accaln_b200`: the alnmain.c-shaped host driver over the C ABI (plain C, no CUDA headers).
  *
  *   accaln_b200 ref.fa reads.fq [batch_size seed_len thres]          (argv of the reference: alnmain.c:560-571)
+ *   accaln_b200 ref.fa r1.fq r2.fq [batch_size seed_len thres]       (paired end: a stub in the reference, alnmain.c:552-555)
  *
  * Same inputs (the five index files accidx wrote beside ref.fa, a FASTQ), same stdout (SAM: header alnmain.c:62-75,
  * records alnmain.c:488-526) and the same closing `Sensitivity: valid/total` line on stderr (alnmain.c:541).  What
@@ -103,6 +104,106 @@ static int run_serial(const char *fq_path, as_gpu *h, as_params p, const as_host
     *total_out = total;
     *valid_out = valid;
     return 0;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * paired-end mode (DESIGN.md "Paired-end mode"): the reference dispatches argc == 4 to pair_end(), a stub that returns -1
+ * (alnmain.c:552-571), so there is no behaviour to match -- this is the mode its API reserves fields for (context.read2,
+ * result.r_name / r_off, accaln.h:74,97-99), built on the single-end path: both mates go through as_map_batch_packed
+ * exactly as single reads do, then the records are printed pair by pair with the mate fields filled in.
+ * ---------------------------------------------------------------------------------------------- */
+static int run_paired(const char *fq1, const char *fq2, as_gpu **gpus, int n_dev, const as_params *p, const as_host_index *ix,
+                      unsigned long batch, unsigned long long *total_out, unsigned long long *valid_out) {
+    as_fastq *f1 = as_fastq_open(fq1), *f2 = as_fastq_open(fq2);
+    if (!f1 || !f2) {
+        fprintf(stderr, "accaln_b200: cannot open %s\n", f1 ? fq2 : fq1);
+        return 4;
+    }
+    const long max_insert = getenv("ACCSEQ_MAX_INSERT") ? atol(getenv("ACCSEQ_MAX_INSERT")) : 1000;
+    as_emitter *em = as_emitter_new(1);
+    unsigned long long total = 0, valid = 0;
+    int status = 0;
+    while (status == 0) {
+        as_read_batch b[2];
+        const int r1 = as_fastq_next_batch(f1, batch, &b[0], NULL), r2 = as_fastq_next_batch(f2, batch, &b[1], NULL);
+        if (r1 != AS_OK || r2 != AS_OK) {
+            fprintf(stderr, "accaln_b200: malformed FASTQ record after %llu pairs\n", total);
+            status = 5;
+            break;
+        }
+        if (b[0].n != b[1].n) {
+            fprintf(stderr, "accaln_b200: %s and %s do not hold the same number of reads\n", fq1, fq2);
+            status = 5;
+            break;
+        }
+        const size_t n = b[0].n;
+        if (n == 0) break;
+        uint32_t *packed[2] = {0};
+        as_result_compact *res[2] = {0};
+        uint8_t *runs[2] = {0};
+        uint32_t *nlen[2] = {0};
+        for (int m = 0; m < 2 && status == 0; m++) {
+            const size_t wst = ((size_t)b[m].max_len + 15) / 16 ? ((size_t)b[m].max_len + 15) / 16 : 1;
+            uint64_t bases = 0, got = 0;
+            for (size_t i = 0; i < n; i++) bases += b[m].lens[i];
+            const size_t cap = (size_t)(2 * bases) + 4096;
+            packed[m] = as_host_alloc(n * wst * sizeof(uint32_t));
+            res[m] = as_host_alloc(n * sizeof(as_result_compact));
+            runs[m] = as_host_alloc(cap);
+            nlen[m] = malloc(n * sizeof(uint32_t));
+            if (!packed[m] || !res[m] || !runs[m] || !nlen[m]) {
+                status = 6;
+                break;
+            }
+            for (size_t i = 0; i < n; i++) nlen[m][i] = (uint32_t)strlen(b[m].names[i]);
+            as_pack_reads(b[m].seqs, b[m].stride, b[m].lens, n, packed[m], wst);
+            /* mate 1 on the first device, mate 2 on the second when there is one: the two files are independent batches */
+            const int rc = as_map_batch_packed(gpus[n_dev > 1 ? m : 0], p, packed[m], wst, b[m].lens, n, res[m], runs[m], cap, &got);
+            if (rc != AS_OK) {
+                fprintf(stderr, "accaln_b200: as_map_batch_packed failed (%d): %s\n", rc, as_last_error());
+                status = 7;
+            }
+        }
+        if (status == 0) {
+            const char **seq[2], **qual[2];
+            for (int m = 0; m < 2; m++) {
+                seq[m] = malloc(n * sizeof(char *));
+                qual[m] = malloc(n * sizeof(char *));
+                for (size_t i = 0; i < n; i++) {
+                    seq[m][i] = b[m].seqs + i * b[m].stride;
+                    qual[m][i] = b[m].quals[i];
+                }
+            }
+            const char *text;
+            size_t text_len;
+            if (as_emit_pairs(em, ix, n, (const char *const *)b[0].names, nlen[0], seq[0], qual[0], b[0].lens, res[0], runs[0],
+                              (const char *const *)b[1].names, nlen[1], seq[1], qual[1], b[1].lens, res[1], runs[1], max_insert,
+                              &text, &text_len) != AS_OK)
+                status = 6;
+            else if (fwrite(text, 1, text_len, stdout) != text_len)
+                status = 8;
+            fflush(stdout);
+            for (size_t i = 0; i < n; i++) valid += !(AS_RC_FLAG(res[0][i]) & 4u) + !(AS_RC_FLAG(res[1][i]) & 4u);
+            total += 2 * n;
+            for (int m = 0; m < 2; m++) {
+                free(seq[m]);
+                free(qual[m]);
+            }
+        }
+        for (int m = 0; m < 2; m++) {
+            as_host_free(packed[m]);
+            as_host_free(res[m]);
+            as_host_free(runs[m]);
+            free(nlen[m]);
+            as_read_batch_free(&b[m], NULL);
+        }
+    }
+    as_emitter_free(em);
+    as_fastq_close(f1);
+    as_fastq_close(f2);
+    *total_out = total;
+    *valid_out = valid;
+    return status;
 }
 
 /* ------------------------------------------------------------------------------------------------
@@ -372,20 +473,23 @@ static int parse_devices(const char *spec, int *dev, int have) {
 }
 
 int main(int argc, const char **argv) {
-    if (argc != 3 && argc != 6) {
-        /* argc == 4 is the reference's paired-end invocation (alnmain.c:560-571): its pair_end() is a stub that returns -1
-         * (alnmain.c:552-555), so there is no behaviour to reproduce; refused here */
-        fprintf(stderr, "usage: %s ref.fa reads.fq [batch_size seed_len thres]\n", argv[0]);
+    /* argc 3 / 6: single end (alnmain.c:560-571).  argc 4 / 7: the reference's paired-end invocation `ref.fa r1.fq r2.fq`, which
+     * it dispatches to a stub (alnmain.c:552-555); here it runs run_paired() above */
+    if (argc != 3 && argc != 6 && argc != 4 && argc != 7) {
+        fprintf(stderr, "usage: %s ref.fa reads.fq [batch_size seed_len thres]\n       %s ref.fa reads_1.fq reads_2.fq [batch_size seed_len thres]\n",
+                argv[0], argv[0]);
         return 1;
     }
+    const int paired = argc == 4 || argc == 7;
+    const int a0 = paired ? 4 : 3;                            /* index of batch_size in argv */
     t_start = now_s();
     as_params p;
     as_params_default(&p);
     unsigned long batch = 1000000ul;
-    if (argc == 6) {
-        batch = strtoul(argv[3], NULL, 10);
-        p.seed_len = (uint32_t)strtoul(argv[4], NULL, 10);
-        p.thres = (uint32_t)strtoul(argv[5], NULL, 10);
+    if (argc == a0 + 3) {
+        batch = strtoul(argv[a0], NULL, 10);
+        p.seed_len = (uint32_t)strtoul(argv[a0 + 1], NULL, 10);
+        p.thres = (uint32_t)strtoul(argv[a0 + 2], NULL, 10);
     } else {
         FILE *fp = fopen("params", "r");                      /* alnmain.c:574-588 */
         if (fp) {
@@ -413,8 +517,9 @@ int main(int argc, const char **argv) {
         dev[0] = getenv("ACCSEQ_DEVICE") ? atoi(getenv("ACCSEQ_DEVICE")) : 0;
         n_dev = 1;
     }
-    const int serial = getenv("ACCALN_FULL_COPY") || getenv("ACCALN_SERIAL") || getenv("ACCSEQ_MYERS");
+    const int serial = !paired && (getenv("ACCALN_FULL_COPY") || getenv("ACCALN_SERIAL") || getenv("ACCSEQ_MYERS"));
     if (serial) n_dev = 1;
+    if (paired && n_dev > 2) n_dev = 2;
     as_gpu *gpus[MAX_GPUS] = {0};
     for (int g = 0; g < n_dev; g++) {                         /* the index is replicated: one copy per device */
         rc = as_gpu_open(&gpus[g], dev[g], &ix->view);
@@ -432,7 +537,9 @@ int main(int argc, const char **argv) {
     logline("Begin processing queries");
     unsigned long long total = 0, valid = 0;
     int status = 0;
-    if (!serial) {
+    if (paired) {
+        status = run_paired(argv[2], argv[3], gpus, n_dev, &p, ix, batch, &total, &valid);
+    } else if (!serial) {
         long ncpu = sysconf(_SC_NPROCESSORS_ONLN);
         /* parsing + packing a read costs about twice what printing it does: 5/8 of the cores parse, 3/8 print */
         int threads = getenv("ACCSEQ_THREADS") ? atoi(getenv("ACCSEQ_THREADS")) : (int)(ncpu > 2 ? (5 * ncpu + 7) / 8 : 1);

@@ -81,10 +81,19 @@ void as_emitter_free(as_emitter *e) {
 }
 
 /* one SAM record of alnmain.c:500-524 at p; the caller guarantees room for 3*len + name + 160 bytes */
+/* paired-end fields of a record (DESIGN.md "Paired-end mode"): what FLAG gains, and RNEXT / PNEXT / TLEN */
+typedef struct {
+    unsigned flag_or;
+    const char *rnext;           /* "=", a sequence name, or "*" */
+    uint64_t pnext;
+    int64_t tlen;
+} mate_info;
+
 static inline char *put_record(char *p, const as_host_index *ix, const char *name, uint32_t name_len, const char *seq,
-                               const char *qual, uint32_t len, const as_result_compact *c, const uint8_t *runs) {
+                               const char *qual, uint32_t len, const as_result_compact *c, const uint8_t *runs,
+                               const mate_info *mate) {
     const int seq_id = AS_RC_SEQ_ID(*c);
-    const unsigned flag = AS_RC_FLAG(*c);
+    const unsigned flag = AS_RC_FLAG(*c) | (mate ? mate->flag_or : 0u);
     const uint32_t n_runs = AS_RC_NRUNS(*c);
     memcpy(p, name, name_len);
     p += name_len;
@@ -113,8 +122,25 @@ static inline char *put_record(char *p, const as_host_index *ix, const char *nam
     } else {
         p = q;
     }
-    memcpy(p, "\t*\t0\t0\t", 7);
-    p += 7;
+    if (!mate) {
+        memcpy(p, "\t*\t0\t0\t", 7);                                  /* r_name "*", 0L, 0 (alnmain.c:517-519) */
+        p += 7;
+    } else {
+        *p++ = '\t';
+        const size_t l = strlen(mate->rnext);
+        memcpy(p, mate->rnext, l);
+        p += l;
+        *p++ = '\t';
+        p = put_u64(p, mate->pnext);
+        *p++ = '\t';
+        if (mate->tlen < 0) {
+            *p++ = '-';
+            p = put_u64(p, (uint64_t)(-mate->tlen));
+        } else {
+            p = put_u64(p, (uint64_t)mate->tlen);
+        }
+        *p++ = '\t';
+    }
     if (AS_RC_STRAND(*c) && seq_id >= 0) {                                    /* strand 1: SEQ is printed reverse-complemented */
         for (uint32_t i = 0; i < len; i++) {
             const unsigned char x = COMP[(unsigned char)seq[len - 1 - i]];
@@ -190,7 +216,7 @@ static void job_format(int t, int T, void *v) {
             off = 0;
         }
         p = put_record(p, j->ix, b->name[i], b->name_len[i], b->seq[i], b->qual[i], b->lens[i], &j->res[i],
-                       j->shard_runs[s] ? j->shard_runs[s] + off : NULL);
+                       j->shard_runs[s] ? j->shard_runs[s] + off : NULL, NULL);
         off += AS_RC_NRUNS(j->res[i]);
     }
     o->len = (size_t)(p - o->buf);
@@ -230,4 +256,73 @@ int as_emit_batch(as_emitter *e, const as_host_index *ix, const as_packed_batch 
     free(j.sum);
     free(j.need);
     return j.rc == AS_OK ? T : j.rc;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * paired-end records (DESIGN.md "Paired-end mode": the reference's pair_end() is a stub, alnmain.c:552-555; the fields it
+ * reserves are result.r_name / r_off, accaln.h:97-99)
+ * ---------------------------------------------------------------------------------------------- */
+static void mate_fields(const as_host_index *ix, const as_result_compact *me, uint32_t my_len, const as_result_compact *ot,
+                        uint32_t ot_len, int first, long max_insert, mate_info *m) {
+    const int my_id = AS_RC_SEQ_ID(*me), ot_id = AS_RC_SEQ_ID(*ot);
+    const unsigned my_f = AS_RC_FLAG(*me), ot_f = AS_RC_FLAG(*ot);
+    const int my_un = (my_f & 4u) != 0 || my_id < 0, ot_un = (ot_f & 4u) != 0 || ot_id < 0;
+    unsigned f = 0x1u | (first ? 0x40u : 0x80u);
+    if (ot_un) f |= 0x8u;
+    else if (AS_RC_STRAND(*ot)) f |= 0x20u;
+    m->rnext = "*";
+    m->pnext = 0;
+    m->tlen = 0;
+    if (!ot_un) {
+        m->rnext = (!my_un && my_id == ot_id) ? "=" : (ot_id < ix->view.mta_len ? ix->names[ot_id] : "*");
+        m->pnext = AS_RC_OFF(*ot) + 1;
+    }
+    if (!my_un && !ot_un && my_id == ot_id) {
+        const int64_t a0 = (int64_t)AS_RC_OFF(*me), a1 = a0 + my_len, b0 = (int64_t)AS_RC_OFF(*ot), b1 = b0 + ot_len;
+        const int64_t lo = a0 < b0 ? a0 : b0, hi = a1 > b1 ? a1 : b1;
+        const int64_t span = hi - lo;
+        /* the leftmost mate carries +span, the other -span; on a tie the first mate is the leftmost */
+        const int leftmost = a0 < b0 || (a0 == b0 && first);
+        m->tlen = leftmost ? span : -span;
+        if (AS_RC_STRAND(*me) != AS_RC_STRAND(*ot) && span <= max_insert) f |= 0x2u;
+    }
+    m->flag_or = f;
+}
+
+/* SAM text of n read pairs, mate 1 then mate 2 of each pair; res1 / res2 and runs1 / runs2 are the results of ONE
+ * as_map_batch_packed call per mate file (run bytes back to back).  One buffer, grown as needed; *out / *out_len stay
+ * valid until the next call on this emitter. */
+int as_emit_pairs(as_emitter *e, const as_host_index *ix, size_t n, const char *const *name1, const uint32_t *name1_len,
+                  const char *const *seq1, const char *const *qual1, const uint32_t *len1, const as_result_compact *res1,
+                  const uint8_t *runs1, const char *const *name2, const uint32_t *name2_len, const char *const *seq2,
+                  const char *const *qual2, const uint32_t *len2, const as_result_compact *res2, const uint8_t *runs2,
+                  long max_insert, const char **out, size_t *out_len) {
+    if (!e || !ix || !res1 || !res2 || !out || !out_len) return AS_EINVAL;
+    uint64_t need = 0;
+    for (size_t i = 0; i < n; i++) need += 3ull * len1[i] + name1_len[i] + 3ull * len2[i] + name2_len[i] + 2 * 260;
+    outbuf *o = &e->out[0];
+    if (o->cap < need + 64) {
+        free(o->buf);
+        o->cap = need + need / 8 + 4096;
+        o->buf = malloc(o->cap);
+        if (!o->buf) {
+            o->cap = 0;
+            return AS_ENOMEM;
+        }
+    }
+    char *p = o->buf;
+    uint64_t off1 = 0, off2 = 0;
+    for (size_t i = 0; i < n; i++) {
+        mate_info m1, m2;
+        mate_fields(ix, &res1[i], len1[i], &res2[i], len2[i], 1, max_insert, &m1);
+        mate_fields(ix, &res2[i], len2[i], &res1[i], len1[i], 0, max_insert, &m2);
+        p = put_record(p, ix, name1[i], name1_len[i], seq1[i], qual1[i], len1[i], &res1[i], runs1 ? runs1 + off1 : NULL, &m1);
+        p = put_record(p, ix, name2[i], name2_len[i], seq2[i], qual2[i], len2[i], &res2[i], runs2 ? runs2 + off2 : NULL, &m2);
+        off1 += AS_RC_NRUNS(res1[i]);
+        off2 += AS_RC_NRUNS(res2[i]);
+    }
+    o->len = (size_t)(p - o->buf);
+    *out = o->buf;
+    *out_len = o->len;
+    return AS_OK;
 }
