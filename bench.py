@@ -34,6 +34,11 @@ WORKLOADS = {
     # name: genome bases, reads per rank, read length range, error range, substitution fraction
     "c1": dict(genome=1_000_000, reads=10_000, len=(150, 150), err=(0.01, 0.01), sub=0.9),
     "c2": dict(genome=4_600_000, reads=1_000_000, len=(150, 150), err=(0.02, 0.02), sub=0.8),
+    # c2 with planted repeat families (about 40 % of the genome, the share of a mammalian genome): 12-copy 1.5 kbp units at
+    # 1 % divergence, 50- and 250-copy exact 300-bp units.  Reads inside the high-copy families overflow the shared-memory
+    # vote table and are redone by k_vote<32,BIG>: this workload times that path.  NOT a BASELINE config.
+    "c2r": dict(genome=4_600_000, reads=1_000_000, len=(150, 150), err=(0.02, 0.02), sub=0.8,
+                repeats=[(60, 1500, 12, 0.01), (20, 300, 50, 0.0), (6, 300, 250, 0.0)]),
     "c3": dict(genome=100_000_000, reads=100_000, len=(10_000, 10_000), err=(0.10, 0.10), sub=1 / 3),
     # human scale: a 6.2 G-row .cat, 40-bit SA rows, 64-bit backward search; the index (~45 GB) is replicated per GPU
     "c4": dict(genome=3_100_000_000, reads=10_000_000, len=(150, 150), err=(0.02, 0.02), sub=0.8),
@@ -43,6 +48,16 @@ GENOME_SEED = 20240
 READS_SEED = 777
 
 
+def make_genome(wl_name):
+    """the workload's genome: seeded uniform bases (scripts/dna_txt_gen.py's distribution), plus planted repeat families"""
+    import longreadmapper_b200 as lm
+    wl = WORKLOADS[wl_name]
+    g = lm.sim_genome(GENOME_SEED, wl["genome"])
+    for k, (fam, unit, copies, div) in enumerate(wl.get("repeats", [])):
+        lm.sim_plant_repeats(GENOME_SEED + 1 + k, g, n_families=fam, unit_len=unit, copies=copies, divergence=div)
+    return g
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -50,6 +65,9 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: every rank maps its own batch of the workload's size (default); strong: ONE batch of that size "
+                         "cut into contiguous per-rank shards (config 4 as BASELINE.json words it)")
     ap.add_argument("--reads", type=int, default=0, help="override reads per rank (smaller = NOT the named config)")
     ap.add_argument("--cpu-sample", type=int, default=0, help="reads in the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
@@ -200,7 +218,7 @@ def cpu_reference_run(wl_name, sample_reads, procs, workdir):
     import oracle_lib
     import longreadmapper_b200 as lm
     wl = WORKLOADS[wl_name]
-    g = lm.sim_genome(GENOME_SEED, wl["genome"])
+    g = make_genome(wl_name)
     reads, lens, _, _ = lm.sim_reads(READS_SEED, g, sample_reads, wl["len"][0], wl["len"][1], wl["err"][0], wl["err"][1],
                                      wl["sub"])
     t0 = time.time()
@@ -309,7 +327,7 @@ def program_e2e(wl_name, g, reads, lens, n_gpus, workdir, copies):
 
 def auto_cpu_sample(wl_name, cores, budget_s):
     # measured single-thread rates of the reference build (SURVEY 6 + GACT stand-in): ~6k reads/s at 150 bp, ~8/s at 10 kbp
-    rate = {"c1": 6000.0, "c2": 6000.0, "c3": 8.0}[wl_name]
+    rate = {"c1": 6000.0, "c2": 6000.0, "c2r": 3000.0, "c3": 8.0}[wl_name]
     return int(max(cores * 50, min(WORKLOADS[wl_name]["reads"], rate * cores * budget_s)))
 
 
@@ -354,7 +372,8 @@ def config_of(wl, args):
 def workload_name(wl, args):
     w = WORKLOADS[wl]
     n = args.reads or w["reads"]
-    return (f"{wl}: {w['genome'] / 1e6:g} Mbp uniform synthetic genome (dna_txt_gen.py distribution, seeded), "
+    rep = ", repeat families planted " + str(w["repeats"]) if w.get("repeats") else ""
+    return (f"{wl}: {w['genome'] / 1e6:g} Mbp uniform synthetic genome (dna_txt_gen.py distribution, seeded){rep}, "
             f"{n} reads/GPU of {w['len'][0]}-{w['len'][1]} bp at {w['err'][0] * 100:g}-{w['err'][1] * 100:g}% error")
 
 
@@ -386,9 +405,17 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     wl = WORKLOADS[args.workload]
     n = args.reads or wl["reads"]
+    n_job = world * n
+    strong = args.scaling == "strong" and world > 1
+    if strong:
+        # the config as written: ONE batch of the workload's reads, cut into contiguous shards (shard.py:shard_range)
+        from longreadmapper_b200.shard import shard_range
+        n_job = n
+        lo, hi = shard_range(n_job, rank, world)
+        n = hi - lo
 
     # ---- inputs: the index replica of this rank (built on the GPU) and this rank's read shard ----
-    g = lm.sim_genome(GENOME_SEED, wl["genome"])
+    g = make_genome(args.workload)
     t0 = time.time()
     oo = {}
     for kv in args.opt:
@@ -397,8 +424,13 @@ def run_b200(args):
     mapper = lm.GpuMapper.build([g], local, opts=lm.open_opts(**oo) if oo else None)
     t_index = time.time() - t0
     dev = torch.device("cuda", local)
-    reads, lens, truth_pos, truth_strand = lm.sim_reads(READS_SEED + 1000 * rank, g, n, wl["len"][0], wl["len"][1],
-                                                        wl["err"][0], wl["err"][1], wl["sub"])
+    if strong:
+        reads, lens, truth_pos, truth_strand = (np.ascontiguousarray(x[lo:hi]) for x in
+                                                lm.sim_reads(READS_SEED, g, n_job, wl["len"][0], wl["len"][1], wl["err"][0],
+                                                             wl["err"][1], wl["sub"]))
+    else:
+        reads, lens, truth_pos, truth_strand = lm.sim_reads(READS_SEED + 1000 * rank, g, n, wl["len"][0], wl["len"][1],
+                                                            wl["err"][0], wl["err"][1], wl["sub"])
     stride = reads.shape[1]
     max_len = int(lens.max())
     store_stride = 2 * max_len
@@ -458,7 +490,7 @@ def run_b200(args):
     # the one collective of the design: shard statistics (alnmain.c:541 Sensitivity line)
     st = shard.reduce_stats(st, dev)
     ms_per_step = ms / args.steps
-    value = world * n / (ms_per_step / 1e3)
+    value = n_job / (ms_per_step / 1e3)
 
     # correctness of what was timed: the results of the last step against the simulated truth
     res = np.frombuffer(d_res.cpu().numpy().tobytes(), dtype=lm.RESULT_DTYPE)
@@ -521,7 +553,7 @@ def run_b200(args):
             else:
                 # the CIGAR columns that came back equal the device path's, column by column up to n_cigar_op
                 same = bool(np.array_equal(hres, res)) and bool(np.array_equal(hops[:, :wmax], dops[:, :wmax]))
-            return {"value": world * n / (ems / args.steps / 1e3), "unit": "reads/s",
+            return {"value": n_job / (ems / args.steps / 1e3), "unit": "reads/s",
                     "h2d_bytes_per_step": h2d_b, "d2h_bytes_per_step": d2h_b,
                     "ms_per_step": ems / args.steps, "same_results_as_device_path": bool(same), "pipeline": pipeline,
                     "stage_ms_last_step": {k: round(v, 3) for k, v in e2e_tm.items()}}
@@ -570,7 +602,7 @@ def run_b200(args):
             same = same and bool(np.array_equal((rec["n_runs"] >> 31).astype(np.int32), res["strand"]))
             for q in bufs:
                 L.as_host_free(q)
-            return {"value": world * n / (ems / args.steps / 1e3), "unit": "reads/s",
+            return {"value": n_job / (ems / args.steps / 1e3), "unit": "reads/s",
                     "h2d_bytes_per_step": h2d_b, "d2h_bytes_per_step": d2h_b, "bytes_per_read": round((h2d_b + d2h_b) / n, 1),
                     "ms_per_step": ems / args.steps, "same_results_as_device_path": bool(same),
                     "pipeline": "as_map_batch_packed: reads cross PCIe 2-bit packed (the ingest threads pack while they parse), "
@@ -657,10 +689,10 @@ def run_b200(args):
                 "stages": stages, "sm_clock_mhz_under_load": sm_clock / 1e6}
 
     line = {"metric": "mapped reads/sec", "value": value, "unit": "reads/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if strong else "weak",
             "vs_baseline": None, "dtype": "u64/i32", "data": "synthetic",
             "config": config_of(args.workload, args),
-            "run": {"l2": f"inputs exceed L2: reads {n * stride / 1e6:.0f} MB + lc table 268 MB + SA {4 * (2 * wl['genome'] + 1) / 1e6:.0f} MB "
+            "run": {"reads_per_step_whole_job": n_job, "l2": f"inputs exceed L2: reads {n * stride / 1e6:.0f} MB + lc table 268 MB + SA {4 * (2 * wl['genome'] + 1) / 1e6:.0f} MB "
                           f"+ GACT planes per pass > 126 MB, no flush needed",
                     "index": "built on the GPU (as_gpu_build), replicated per rank", "index_build_s": round(t_index, 2),
                     "host_numa_node_rank0": numa, "knobs": knobs, "open_opts": oo},
@@ -670,7 +702,7 @@ def run_b200(args):
             "quality": {"mapped_frac": float(ok.mean()), "exact_pos_strand_frac": exact, "within_50bp_strand_frac": near,
                         "valid_total": [st["valid"], st["total"]]},
             "stats_per_step_per_gpu": {k: per_step[k] for k in ("seeds", "bs_steps", "fm_steps_exec", "text_verified", "sa_hits", "dp_cells",
-                                                                   "dp_cells_eval", "gact_redone", "overflow_reads")}}
+                                                                   "dp_cells_eval", "gact_redone", "overflow_reads", "overflow_queued")}}
 
     if world > 1:
         dist.barrier()

@@ -72,7 +72,9 @@ typedef struct as_open_opts {
     int32_t  sampled_sa;      /* 0: the full suffix array stays in HBM (5 bytes/row, + 8 for the SA + context table);
                                * r > 0: keep only SA[r*i] (csa, fmidx.c:152-163) and resolve vote positions by the LF walk of
                                * csa_access (fmidx.c:315-331): no SA, no SA + context table -- ~1/r of the SA bytes per GPU */
-    int32_t  reserved[5];
+    int32_t  l2_fetch_gran;   /* > 0: cudaLimitMaxL2FetchGranularity of the device (32, 64 or 128 bytes); 0 leaves the device's
+                               * setting alone.  PART 1 is random 8-byte gathers: anything fetched beyond the 32-byte sector is waste */
+    int32_t  reserved[4];
 } as_open_opts;
 int  as_gpu_open_opts(as_gpu **h, int device, const as_index_view *ix, const as_open_opts *opts);
 /* A handle WITHOUT an index: serves the aligners on explicit pairs (as_cigar_align_batch, as_edit_distance_batch) and,
@@ -206,7 +208,11 @@ int as_map_batch_packed(as_gpu *h, const as_params *p, const uint32_t *packed, s
                         as_result_compact *results, uint8_t *runs, size_t runs_cap, uint64_t *runs_len);
 
 /* Same path with every buffer already resident in device memory (pointers are device addresses); used to
- * time the kernels without PCIe and by frameworks that keep reads on the GPU. */
+ * time the kernels without PCIe and by frameworks that keep reads on the GPU.
+ * d_reads: the packing kernel reads the batch as aligned 32-bit words, so the allocation that holds it must start on a
+ * 4-byte boundary and end on one (cudaMalloc and every sub-allocator built on it do; a row pointer need not be aligned).
+ * Bytes outside ACGT/acgt are outside the reference's defined behaviour (DESIGN.md parity exclusions): they seed and
+ * align as the 2-bit code of their bits 1-2 ('N' -> G), print unchanged in SEQ. */
 int as_map_batch_device(as_gpu *h, const as_params *p, char *d_reads, size_t stride, const uint32_t *d_lens,
                         size_t n, uint32_t max_len, as_result *d_results, uint8_t *d_store, size_t store_stride);
 

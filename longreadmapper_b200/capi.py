@@ -59,12 +59,13 @@ class Params(C.Structure):
 
 class OpenOpts(C.Structure):
     _fields_ = [("lc2_hlen", C.c_int32), ("no_sax", C.c_int32), ("build_part_max", C.c_uint64), ("sampled_sa", C.c_int32),
-                ("reserved", C.c_int32 * 5)]
+                ("l2_fetch_gran", C.c_int32), ("reserved", C.c_int32 * 4)]
 
 
-def open_opts(lc2_hlen=0, no_sax=0, build_part_max=0, sampled_sa=0):
+def open_opts(lc2_hlen=0, no_sax=0, build_part_max=0, sampled_sa=0, l2_fetch_gran=0):
     o = OpenOpts()
     o.lc2_hlen, o.no_sax, o.build_part_max, o.sampled_sa = int(lc2_hlen), int(no_sax), int(build_part_max), int(sampled_sa)
+    o.l2_fetch_gran = int(l2_fetch_gran)
     return o
 
 

@@ -11,14 +11,19 @@
  * bases is what lc_access + (h2 - hlen) steps of fmi_aln (fmidx.c:295-313) would have reached, including the
  * reference's k = 1 start, which drops the occurrence that ends on the text's last base (see k_lc_codes, as_build.cu).
  *
- * Entry: bits 0..39 = first row k, bits 40..63 = info, 0 = absent.  info >> 22 is a tag:
- *   0: info = rows in the interval, 0x3FFFFF = "2^22-1 or more" (PART 1 then takes the 12-mer table and walks);
- *   1: ONE row, and info & 0x3FFFFF = the 11 text bases in front of SA[k] (base SA-11 lowest);
- *   2: TWO rows, bits 0..9 / 10..19 = the 5 text bases in front of SA[k] / SA[k+1].
+ * Entry: bits 40..63 = info, 0 = absent.  info >> 22 is a tag:
+ *   0: bits 0..39 = first row k, info = rows in the interval, 0x3FFFFF = "2^22-1 or more" (PART 1 then takes the 12-mer
+ *      table and walks);
+ *   1: ONE row: bits 0..39 = SA[k] ITSELF (the text position, not the row) and info & 0x3FFFFF = the 11 text bases in
+ *      front of it (base SA-11 lowest);
+ *   2: TWO rows: bits 0..39 = k, info bits 0..9 / 10..19 = the 5 text bases in front of SA[k] / SA[k+1].
  * Tags 1 and 2 let PART 1 decide the rest of the walk from the entry itself (a row survives iff the seed's remaining
- * bases equal the text in front of it): a seed that dies there -- most seeds of a noisy long read, whose h2-mer
- * exists in a human-size genome by chance -- costs ONE gather; only survivors fetch their position.  Rows closer to the
- * text start than the context is long keep tag 0.  Built from the device index alone (SA + 2-bit text), so handles
+ * bases equal the text in front of it).  A one-row entry finishes its seed with NO further gather: the vote needs the
+ * position, never the row (on the 4.6 Mbp genome 87 % of the h2-mers a read presents have one row, and PART 1 runs at
+ * the DRAM's random-transaction rate -- tools/gather_probe.cu -- so a gather saved is time saved); a seed that dies at
+ * a two-row entry -- most seeds of a noisy long read, whose h2-mer exists in a human-size genome by chance -- costs ONE
+ * gather and only survivors fetch their position.  Rows closer to the text start than the longest possible rest of a
+ * seed (32 bases) keep tag 0.  Built from the device index alone (SA + 2-bit text), so handles
  * opened from the reference's files get it too.
  */
 #include "as_common.cuh"
@@ -65,7 +70,10 @@ __global__ void __launch_bounds__(256) k_lc2_fill(DevIndex ix, int h, unsigned l
                     uint64_t info = cnt >= LC2_SAT ? LC2_SAT : cnt;
                     if (cnt == 1) {
                         const uint64_t p = as_sa(ix, k);
-                        if (p >= 11) info = (1ULL << 22) | (as_bases16(ix.text2, p - 11) & 0x3FFFFFu);
+                        if (p >= 32) {
+                            info = (1ULL << 22) | (as_bases16(ix.text2, p - 11) & 0x3FFFFFu);
+                            k = p;                    /* tag 1 carries the position */
+                        }
                     } else if (cnt == 2) {
                         const uint64_t p0 = as_sa(ix, k), p1 = as_sa(ix, k + 1);
                         if (p0 >= 5 && p1 >= 5)
@@ -147,6 +155,7 @@ int as_build_lc2(as_gpu *h) {
     ix.lc2 = nullptr;
     ix.hlen2 = 0;
     ix.sax = nullptr;
+    if (h->opts.l2_fetch_gran > 0) AS_CUDA(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)h->opts.l2_fetch_gran));
     if (!ix.text2 || !ix.sa_lo || ix.N < 2) return AS_OK;
     AS_TRY(build_lc2_table(h));
     AS_TRY(build_sax(h));

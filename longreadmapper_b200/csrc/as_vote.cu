@@ -30,6 +30,16 @@
 #ifndef VOTE_MIN_BLOCKS
 #define VOTE_MIN_BLOCKS 6
 #endif
+/* A/B switches (tools/ab_vote.sh): VOTE_PF = while a one-round phase is resolved, the deep-table entries of the read's
+ * NEXT phase are requested into L2 (the next phase's seed is this one moved by a base, so its table index comes out of
+ * the register that holds this seed); VOTE_L2HINT = deep-table loads carry an evict-first L2 policy and the SA + context
+ * loads an evict-last one, so the table stream does not wash the small tables out of L2 */
+#ifndef VOTE_PF
+#define VOTE_PF 1
+#endif
+#ifndef VOTE_L2HINT
+#define VOTE_L2HINT 0
+#endif
 #define MAXP 34                      /* seed_len <= 32 -> at most 33 phases */
 #define EMPTY_BUCKET 0xFFFFFFFFFFFFFFFFULL
 
@@ -62,6 +72,12 @@ struct VoteArgs {
     int use2;                    /* seeds start from the deep table (DevIndex.lc2) instead of the 12-mer table */
     int use_ectx;                /* decide one- and two-row entries from the context bases they carry (as_lc2.cu) */
 };
+
+__device__ __forceinline__ unsigned long long vote_ld_hint(const unsigned long long *p, unsigned long long pol) {
+    unsigned long long v;
+    asm volatile("ld.global.nc.L2::cache_hint.b64 %0, [%1], %2;" : "=l"(v) : "l"(p), "l"(pol));
+    return v;
+}
 
 __device__ __forceinline__ uint32_t hash_bucket(uint64_t b, uint32_t shift) {
     return (uint32_t)((b * 0x9E3779B97F4A7C15ULL) >> shift);
@@ -164,6 +180,16 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
     const int hl = a.use2 ? ix.hlen2 : ix.hlen;          /* bases answered by the table */
     const int left0 = sl - hl;
     const uint64_t hmask = (1ULL << (2 * hl)) - 1ULL;
+#if VOTE_L2HINT
+    unsigned long long pol_first, pol_last;
+    asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_first));
+    asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_last));
+#define VOTE_LD_LC2(p) vote_ld_hint(p, pol_first)
+#define VOTE_LD_SAX(p) vote_ld_hint(p, pol_last)
+#else
+#define VOTE_LD_LC2(p) __ldg(p)
+#define VOTE_LD_SAX(p) __ldg(p)
+#endif
     unsigned long long st_seeds = 0, st_steps = 0, st_hits = 0, st_ovf = 0;
     unsigned int st_queued = 0;                  /* reads this warp handed to the overflow (BIG) pass */
     unsigned int st_fm = 0, st_txt = 0;          /* FM steps done here / tails decided by the text */
@@ -209,6 +235,11 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
         const uint32_t m_count = have ? span_q + ((uint32_t)iter < span_r ? 1u : 0u) : 0u;
         const uint32_t m_max = warp_max_u32(m_count);
         bool ok = true, reg_vote = false;
+#if VOTE_PF
+        /* next phase = same seeds one base on (j + 1): sl + 1 <= 32 bases are in the seed register.  Wasted only for the
+         * phase that ends the read (one in ~6 on 150-bp reads at 2 %) */
+        const bool pf_next = m_max <= (uint32_t)G && sl < 32 && iter + 1 < P;
+#endif
         uint32_t v0val = 0, v1val = 0;
         uint64_t c0key = 0;
         for (uint32_t c0 = 0; c0 < m_max; c0 += G) {
@@ -224,7 +255,10 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                 int tt = left0 - 1;                                             /* next seed base to walk */
                 if (a.use2) {
                     /* deep table: the interval lc_access + (hlen2 - hlen) steps of fmi_aln would have reached */
-                    const unsigned long long e = __ldg(ix.lc2 + ((seed >> (2 * left0)) & hmask));
+                    const unsigned long long e = VOTE_LD_LC2(ix.lc2 + ((seed >> (2 * left0)) & hmask));
+#if VOTE_PF
+                    if (pf_next) asm volatile("prefetch.global.L2 [%0];" ::"l"(ix.lc2 + ((seed >> (2 * left0 + 2)) & hmask)));
+#endif
                     const uint32_t info = (uint32_t)(e >> 40);
                     etag = info >> 22;                                          /* as_lc2.cu: 0 count, 1 / 2 rows + context */
                     ectx = info & 0x3FFFFFu;
@@ -257,9 +291,16 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                      * further SA access.  st_steps still counts the steps the reference's loop executes (up to and
                      * including the failing one); st_fm counts the FM steps actually done here. */
                     bool fail = false;
-                    /* entry with context that covers the rest of the seed: no FM step is taken (the interval has <= 2 rows) */
-                    const bool e_ok = a.use_ectx && etag != 0 && tt >= 0 && tt < (etag == 1 ? 11 : 5);
+                    /* entry with context that covers the rest of the seed: no FM step is taken (the interval has <= 2 rows);
+                     * a one-row entry carries the row's text POSITION in place of the row (as_lc2.cu): its seed needs no
+                     * further gather unless more than 11 bases are left (then one text gather) */
+                    const bool e_pos = etag == 1;
+                    const bool e_ok = tt >= 0 && ((e_pos && tt < 11) || (a.use_ectx && etag == 2 && tt < 5));
                     const uint32_t vw = (SMALL || ix.sax != nullptr || e_ok) ? (uint32_t)VOTE_VW : 1u;
+                    if (e_pos && tt < 0) {                                      /* the table answered the whole seed */
+                        have_pos = true;
+                        hit_pos = kk;
+                    }
                     if (SMALL) {
                         uint32_t k32 = (uint32_t)kk, l32 = (uint32_t)ll;
                         while (tt >= 0 && l32 - k32 >= vw) {
@@ -292,18 +333,21 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                         /* the table entry itself carries the context of its one or two rows (as_lc2.cu, tags 1 and 2):
                          * nothing is fetched to decide, and only a surviving row's position is */
                         const bool from_e = e_ok;
-                        const bool ctx = from_e || (ix.sax != nullptr && nrem <= 12);
+                        const bool ctx = from_e || (!e_pos && ix.sax != nullptr && nrem <= 12);
                         bool in_text = true;
 #pragma unroll
                         for (int r = 0; r < VOTE_VW; r++) {
                             pv[r] = 0;
                             if ((uint32_t)r >= wdt) {
                                 pr[r] = ~0ULL;
+                            } else if (e_pos) {
+                                pr[r] = kk;                                      /* the position; >= 32 by construction */
+                                pv[r] = ectx >> (2 * (11 - (nrem < 11 ? nrem : 11)));
                             } else if (from_e) {
                                 pr[r] = 1ULL << 62;                             /* not known yet; the builder checked SA >= context */
-                                pv[r] = (etag == 1 ? ectx : ((ectx >> (10 * r)) & 0x3FFu)) >> (2 * ((etag == 1 ? 11 : 5) - nrem));
+                                pv[r] = ((ectx >> (10 * r)) & 0x3FFu) >> (2 * (5 - nrem));            /* tag 2 */
                             } else if (ctx) {
-                                const unsigned long long e = __ldg(ix.sax + kk + (uint64_t)r);
+                                const unsigned long long e = VOTE_LD_SAX(ix.sax + kk + (uint64_t)r);
                                 pr[r] = e & 0xFFFFFFFFFFULL;
                                 pv[r] = (uint32_t)(e >> 40) >> (2 * (12 - nrem));
                             } else {
@@ -338,7 +382,7 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                                 st_txt++;
                                 resolved = true;
                                 if (nsurv == 1) {
-                                    if (from_e) {
+                                    if (from_e && !e_pos) {
                                         const uint64_t row = kk + rsurv;
                                         pos1 = (ix.sax ? (__ldg(ix.sax + row) & 0xFFFFFFFFFFULL) : as_locate(ix, row)) - (uint64_t)nrem;
                                     }
