@@ -131,6 +131,8 @@ typedef struct as_params {
     int32_t  gact_blocks_per_sm;  /* resident GACT blocks per SM; 0 = occupancy query (default) */
     uint32_t chunk_reads;         /* as_map_batch: fixed chunk size; 0 = the ramp-up / ramp-down plan (default) */
     int32_t  chunk_tail;          /* as_map_batch: how many times the last chunk is split 2:1; -1 = default (1) */
+    int32_t  vote_thread;         /* PART 1 of short reads (<= 8 seeds per phase) by the thread-per-read kernel, the rest by the
+                                   * group kernel: -1 = when it applies (default), 0 = group kernel only */
 } as_params;
 #define AS_F_MYERS        1u   /* also run the edlib-equivalent NW distance with k=(int)(0.05*len*2) per read */
 #define AS_F_NO_ALIGN     2u   /* stop after PART 1+2 (no GACT): results carry loc/off/strand/flag only */
@@ -234,6 +236,8 @@ typedef struct as_stats {
     uint64_t overflow_queued; /* reads whose votes of one phase did not fit the shared-memory table (8 slots per lane of the
                                * read's group) and were redone by the overflow pass over a table in global memory: repeat
                                * families.  overflow_reads counts reads the overflow pass itself could not hold (never) */
+    uint64_t vote_deferred;   /* short reads the thread-per-read PART 1 kernel handed to the group kernel (a seed with more
+                               * than two hits, more distinct vote buckets in a phase or in the outer list than a thread keeps) */
 } as_stats;
 int as_gpu_stats(as_gpu *h, as_stats *out);          /* accumulated since open / last reset */
 int as_gpu_stats_reset(as_gpu *h);

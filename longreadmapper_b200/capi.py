@@ -54,7 +54,8 @@ class AsIndexOut(C.Structure):
 class Params(C.Structure):
     _fields_ = [("seed_len", C.c_uint32), ("thres", C.c_uint32), ("gact_T", C.c_int32), ("gact_O", C.c_int32),
                 ("flags", C.c_uint32), ("gact_band", C.c_int32), ("vote_ectx", C.c_int32), ("gact_order", C.c_int32),
-                ("gact_blocks_per_sm", C.c_int32), ("chunk_reads", C.c_uint32), ("chunk_tail", C.c_int32)]
+                ("gact_blocks_per_sm", C.c_int32), ("chunk_reads", C.c_uint32), ("chunk_tail", C.c_int32),
+                ("vote_thread", C.c_int32)]
 
 
 class OpenOpts(C.Structure):
@@ -72,7 +73,7 @@ def open_opts(lc2_hlen=0, no_sax=0, build_part_max=0, sampled_sa=0, l2_fetch_gra
 class AsStats(C.Structure):
     _fields_ = [(k, C.c_uint64) for k in ("total", "valid", "n_flag4", "n_flag16", "sum_ed", "dp_cells", "seeds",
                                            "sa_hits", "bs_steps", "overflow_reads", "dp_cells_eval", "gact_redone", "fm_steps_exec", "text_verified",
-                                           "overflow_queued")]
+                                           "overflow_queued", "vote_deferred")]
 
 
 class AsHostIndex(C.Structure):
@@ -377,7 +378,7 @@ class GpuMapper:
         self.L.as_params_default(C.byref(p))
         p.seed_len, p.thres, p.flags = seed_len, thres, flags
         for k, v in knobs.items():
-            if k not in ("vote_ectx", "gact_order", "gact_blocks_per_sm", "chunk_reads", "chunk_tail"):
+            if k not in ("vote_ectx", "gact_order", "gact_blocks_per_sm", "chunk_reads", "chunk_tail", "vote_thread"):
                 raise TypeError(f"unknown as_params field {k}")
             setattr(p, k, int(v))
         if band is not None:

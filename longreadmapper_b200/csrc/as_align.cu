@@ -442,6 +442,9 @@ int as_launch_gact(as_gpu *h, const as_params *p, const uint32_t *d_qpack, size_
     a.blocks_per_sm = p->gact_blocks_per_sm;
     a.fail_count = nullptr;
     a.order = nullptr;
+    a.retry_list = nullptr;
+    a.retry_count = nullptr;
+    a.n_dev = nullptr;
     /* two implementations of the same tile DP: bit-parallel, one read per lane (as_gact_bp.cu) for batches that fill
      * the GPU with lanes; anti-diagonal, one read per warp (below) for small batches */
     const bool force_warp = (p->flags & AS_F_GACT_WARP) != 0, force_bp = (p->flags & AS_F_GACT_BITPAR) != 0;

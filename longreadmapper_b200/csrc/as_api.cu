@@ -25,6 +25,7 @@ extern "C" void as_params_default(as_params *p) {
     p->gact_blocks_per_sm = 0;
     p->chunk_reads = 0;
     p->chunk_tail = -1;
+    p->vote_thread = -1;
 }
 
 __global__ void k_rle_ops(uint8_t *__restrict__ ops, size_t stride, as_result *__restrict__ res, size_t n);
@@ -856,26 +857,27 @@ extern "C" int as_gpu_stats(as_gpu *h, as_stats *out) {
     if (!h || !out) return AS_EINVAL;
     AS_CUDA(cudaSetDevice(h->device));
     AS_CUDA(cudaStreamSynchronize(h->stream));
-    unsigned long long v[15];
+    unsigned long long v[17];
     AS_CUDA(cudaMemcpy(v, h->d_stats, sizeof v, cudaMemcpyDeviceToHost));
     if (h->twin) {
-        unsigned long long w[15];
+        unsigned long long w[17];
         AS_CUDA(cudaStreamSynchronize(h->twin->stream));
         AS_CUDA(cudaMemcpy(w, h->twin->d_stats, sizeof w, cudaMemcpyDeviceToHost));
-        for (int i = 0; i < 15; i++) v[i] += w[i];
+        for (int i = 0; i < 17; i++) v[i] += w[i];
     }
     out->total = v[0]; out->valid = v[1]; out->n_flag4 = v[2]; out->n_flag16 = v[3]; out->sum_ed = v[4];
     out->dp_cells = v[5]; out->seeds = v[6]; out->sa_hits = v[7]; out->bs_steps = v[8]; out->overflow_reads = v[9];
     out->dp_cells_eval = v[10]; out->gact_redone = v[11]; out->fm_steps_exec = v[12]; out->text_verified = v[13];
     out->overflow_queued = v[14];
+    out->vote_deferred = v[16];         /* v[15]: reads too long for their row (as_map_batch_packed) */
     return AS_OK;
 }
 
 extern "C" int as_gpu_stats_reset(as_gpu *h) {
     if (!h) return AS_EINVAL;
     AS_CUDA(cudaSetDevice(h->device));
-    AS_CUDA(cudaMemsetAsync(h->d_stats, 0, 16 * sizeof(unsigned long long), h->stream));
-    if (h->twin) AS_CUDA(cudaMemsetAsync(h->twin->d_stats, 0, 16 * sizeof(unsigned long long), h->twin->stream));
+    AS_CUDA(cudaMemsetAsync(h->d_stats, 0, 24 * sizeof(unsigned long long), h->stream));
+    if (h->twin) AS_CUDA(cudaMemsetAsync(h->twin->d_stats, 0, 24 * sizeof(unsigned long long), h->twin->stream));
     return AS_OK;
 }
 

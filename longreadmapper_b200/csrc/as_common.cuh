@@ -69,6 +69,8 @@ struct as_gpu {
     ScratchBuf reads, lens, results, store, qpack, tpack, toff, vote, counters, ovf_list, ovf_table, misc[6];
     ScratchBuf gact_planes, gact_tb;     /* bit-parallel GACT: traceback planes / packed tile ops, per resident warp */
     ScratchBuf gact_order;               /* bit-parallel GACT: reads by decreasing length (multi-tile batches) */
+    ScratchBuf vote_dlist;               /* PART 1: reads the thread-per-read kernel deferred to the group kernel */
+    ScratchBuf gact_retry;               /* bit-parallel GACT: one-tile reads the one-word diagonal band could not prove exact */
     ScratchBuf locus_tmp;                /* packed-only long reads: one scratch row per warp for the reverse complement */
     ScratchBuf pack_in, cres, runs, run_tot;   /* as_map_batch_packed: tight packed rows in, compact records + dense run bytes out */
     /* pinned staging for small D2H/H2D */
@@ -169,6 +171,11 @@ struct GactArgs {
     int blocks_per_sm;           /* as_params.gact_blocks_per_sm: 0 = occupancy query */
     unsigned int *fail_count;    /* policy counters of the launch: warp-tiles refilled, warp-tiles, lane-tiles served by
                                   * half the band, lane-tiles */
+    /* one-tile reads, lowest band level: a read whose one-word diagonal band cannot be proven exact is queued here and
+     * aligned by a second launch with wider bands, instead of making its whole warp fill the tile again */
+    uint32_t *retry_list;
+    unsigned int *retry_count;
+    const unsigned int *n_dev;   /* non-NULL: slots [0, *n_dev) of `order` are the launch's reads (the queue above) */
 };
 #define AS_GACT_BAND0 16
 

@@ -555,9 +555,10 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
         uint32_t base = 0;
         if (lane == 0) base = atomicAdd(a.work_counter, 32u);
         base = __shfl_sync(0xFFFFFFFFu, base, 0);
-        if (base >= a.n) break;
+        const size_t n_slots = a.n_dev ? (size_t)*a.n_dev : a.n;
+        if (base >= n_slots) break;
         const size_t slot = (size_t)base + lane;
-        bool done = slot >= a.n;
+        bool done = slot >= n_slots;
         const size_t read = done ? 0 : (a.order ? (size_t)a.order[slot] : slot);
         int qlen = 0, tlen = 0;
         g.toff = 0;
@@ -568,7 +569,7 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
             /* seq_lookup failed: flag 4 was set by PART 2; reference behaviour is undefined (alnmain.c:409,430-446) */
             if (g.toff == AS_TOFF_NONE) done = true;
         }
-        const bool skipped = done;
+        bool skipped = done;
         g.qp = a.qpack + (done ? 0 : read * a.q_wstride);
         uint8_t *ops = (a.ops && !done) ? a.ops + read * a.ops_stride : nullptr;
         int n = 0, score = 0;
@@ -609,7 +610,21 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
                 bool wider = true;
                 if (BANDED && NB == 2) {                     /* lowest band level: the one-word diagonal band first */
                     tile_diag1(g, planes, tb, st_eval, o, n_events);
-                    wider = __any_sync(0xFFFFFFFFu, o.bad);
+                    if (a.retry_list) {
+                        /* the reads this band cannot prove exact leave for the second launch (wider bands); the warp goes on */
+                        if (!done && o.bad) {
+                            a.retry_list[atomicAdd(a.retry_count, 1u)] = (uint32_t)read;
+                            done = true;
+                            skipped = true;
+                            g.done = true;
+                            o.m = 0;
+                            o.tscore = 0;
+                            n_events = 0;
+                        }
+                        wider = false;
+                    } else {
+                        wider = __any_sync(0xFFFFFFFFu, o.bad);
+                    }
                     st_diag += (lane == 0);
                     st_diag_retry += (wider && lane == 0);
                 }
@@ -742,11 +757,15 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
  * Widen when more than a quarter of the warp-tiles were filled twice; narrow when at most one lane-tile in 256 would
  * fail at half the band (about one warp-tile in eight refilled).  The verdict goes to pinned host memory, which the
  * launcher reads when it picks the next launch's instantiation; results never depend on it. */
-__global__ void k_gact_policy(volatile unsigned int *host_band, const unsigned int *cnt, unsigned int cur) {
+__global__ void k_gact_policy(volatile unsigned int *host_band, const unsigned int *cnt, unsigned int cur,
+                              const unsigned int *queued, unsigned int n_reads) {
     const unsigned long long retry = cnt[0], wtiles = cnt[1], half = cnt[2], tiles = cnt[3];
     if (wtiles == 0) return;
     unsigned int kb = cur;
-    if (4ull * retry > wtiles) kb = cur >= 128 ? 256 : cur * 2;
+    /* one-tile reads at the lowest level queue their failures instead of refilling (retry stays 0): widen when more than
+     * a quarter of the READS had to be queued -- the one-word pass is then mostly wasted */
+    if (queued && 4ull * *queued > n_reads) kb = cur * 2;
+    else if (4ull * retry > wtiles) kb = cur >= 128 ? 256 : cur * 2;
     else if (cur > 16 && 256ull * (tiles - half) <= tiles) kb = cur / 2;
     *host_band = kb;
 }
@@ -777,7 +796,7 @@ static int launch_bp(as_gpu *h, GactArgs &a, size_t n, int blocks_per_sm, unsign
     h->launches++;
     AS_CUDA(cudaGetLastError());
     if (a.band == 0) {
-        k_gact_policy<<<1, 1, 0, h->stream>>>(h->d_band, cnt + 1, cur_band);
+        k_gact_policy<<<1, 1, 0, h->stream>>>(h->d_band, cnt + 1, cur_band, a.retry_count, (unsigned int)n);
         h->launches++;
         AS_CUDA(cudaGetLastError());
     }
@@ -852,6 +871,25 @@ int as_launch_gact_bp(as_gpu *h, GactArgs &a, size_t n, uint32_t max_qlen, uint3
     }
     unsigned int kb = a.band < 0 ? 0xFFFFu : a.band > 0 ? (unsigned int)a.band : *(volatile unsigned int *)h->h_band;
     if (kb == 0) kb = AS_GACT_BAND0;
+    if (words <= 5 && kb <= 16 && a.ops_zeroed && max_qlen <= (uint32_t)a.T && max_tlen <= (uint32_t)a.T) {
+        /* every read is one tile and the first attempt is the one-word diagonal band: reads it cannot prove exact (a few
+         * per cent on real genomes: chimeric or mis-placed reads, diverged repeat copies) are queued and aligned by a second
+         * launch over the queue with the 32-wide band / the whole matrix.  Before, one such read made its 32-read warp fill
+         * the tile twice more, and a per-cent of them pushed the adaptive band up for everybody (c2r: GACT 0.75 -> 2.26 ms) */
+        AS_TRY(as_scratch(h, &h->gact_retry, n * sizeof(uint32_t)));
+        unsigned int *cnt = a.work_counter;                       /* 16 words, zeroed by as_launch_gact */
+        a.retry_list = (uint32_t *)h->gact_retry.p;
+        a.retry_count = cnt + 5;
+        AS_TRY(launch_bp_w<5>(h, a, n, bps, kb));
+        GactArgs b = a;
+        b.retry_list = nullptr;
+        b.retry_count = nullptr;
+        b.order = (const uint32_t *)h->gact_retry.p;
+        b.n_dev = cnt + 5;
+        b.work_counter = cnt + 6;                                 /* its policy counters: cnt + 7 .. 10, not read */
+        b.band = 32;
+        return launch_bp_w<5>(h, b, n, bps, 32);
+    }
     if (words <= 5) return launch_bp_w<5>(h, a, n, bps, kb);
     if (words <= 10) return launch_bp_w<10>(h, a, n, bps, kb);
     return launch_bp_w<16>(h, a, n, bps, kb);

@@ -30,15 +30,8 @@
 #ifndef VOTE_MIN_BLOCKS
 #define VOTE_MIN_BLOCKS 6
 #endif
-/* A/B switches (tools/ab_vote.sh): VOTE_PF = while a one-round phase is resolved, the deep-table entries of the read's
- * NEXT phase are requested into L2 (the next phase's seed is this one moved by a base, so its table index comes out of
- * the register that holds this seed); VOTE_L2HINT = deep-table loads carry an evict-first L2 policy and the SA + context
- * loads an evict-last one, so the table stream does not wash the small tables out of L2 */
-#ifndef VOTE_PF
-#define VOTE_PF 1
-#endif
-#ifndef VOTE_L2HINT
-#define VOTE_L2HINT 0
+#ifndef VOTE_CARVEOUT
+#define VOTE_CARVEOUT (-1)               /* >= 0: preferred shared-memory carve-out of the kernel, per cent */
 #endif
 #define MAXP 34                      /* seed_len <= 32 -> at most 33 phases */
 #define EMPTY_BUCKET 0xFFFFFFFFFFFFFFFFULL
@@ -69,15 +62,15 @@ struct VoteArgs {
     size_t big_stride;
     uint32_t big_cap;
     unsigned long long *stats;   /* as_stats layout */
+    /* group kernel in list mode: its reads are list[0 .. *list_count) (the reads the thread-per-read kernel deferred) */
+    const uint32_t *list;
+    const unsigned int *list_count;
+    /* thread-per-read kernel: reads it hands to the group kernel */
+    uint32_t *dlist;
+    unsigned int *dlist_count;
     int use2;                    /* seeds start from the deep table (DevIndex.lc2) instead of the 12-mer table */
     int use_ectx;                /* decide one- and two-row entries from the context bases they carry (as_lc2.cu) */
 };
-
-__device__ __forceinline__ unsigned long long vote_ld_hint(const unsigned long long *p, unsigned long long pol) {
-    unsigned long long v;
-    asm volatile("ld.global.nc.L2::cache_hint.b64 %0, [%1], %2;" : "=l"(v) : "l"(p), "l"(pol));
-    return v;
-}
 
 __device__ __forceinline__ uint32_t hash_bucket(uint64_t b, uint32_t shift) {
     return (uint32_t)((b * 0x9E3779B97F4A7C15ULL) >> shift);
@@ -113,6 +106,175 @@ __device__ __forceinline__ void top2_push(uint64_t &a0, uint64_t &a1, uint64_t c
 /* warp-wide max of a small unsigned value (all 32 lanes take part) */
 __device__ __forceinline__ uint32_t warp_max_u32(uint32_t v) {
     return __reduce_max_sync(0xFFFFFFFFu, v);                       /* REDUX.MAX: one instruction */
+}
+
+/*
+ * One seed of a phase: the SA interval lc_aln / fmi_aln reach for it (lchash.c:89-104, fmidx.c:295-313), or -- when the text
+ * decided the tail of a one-row walk -- the position of its only hit.  Shared by the two PART 1 kernels: the group kernel
+ * loads the table entry here, the thread-per-read kernel hands in the entry it loaded ahead (have_e).
+ * Out: rr rows [kk, ll] survive (rr == 0: none); have_pos: rr == 1 and hit_pos = SA of that row (no SA access needed).
+ */
+template <bool SMALL>
+__device__ __forceinline__ void vote_resolve_seed(const DevIndex &ix, const VoteArgs &a, const BsTab *s_tab, const uint32_t *s_tabChi,
+                                                  const int sl, const int left0, const uint64_t hmask, const uint64_t seed,
+                                                  const bool have_e, const unsigned long long e_in, uint64_t &kk, uint64_t &ll,
+                                                  uint64_t &rr, bool &have_pos, uint64_t &hit_pos, unsigned long long &st_seeds,
+                                                  unsigned long long &st_steps, unsigned int &st_fm, unsigned int &st_txt) {
+    bool absent = false;
+    uint32_t etag = 0, ectx = 0;
+    int tt = left0 - 1;                                             /* next seed base to walk */
+    if (a.use2) {
+        /* deep table: the interval lc_access + (hlen2 - hlen) steps of fmi_aln would have reached */
+        const unsigned long long e = have_e ? e_in : __ldg(ix.lc2 + ((seed >> (2 * left0)) & hmask));
+        const uint32_t info = (uint32_t)(e >> 40);
+        etag = info >> 22;                                          /* as_lc2.cu: 0 count, 1 / 2 rows + context */
+        ectx = info & 0x3FFFFFu;
+        const uint32_t cnt = etag ? etag : ectx;
+        kk = e & 0xFFFFFFFFFFULL;
+        ll = kk + cnt - 1;
+        absent = e == 0;
+        if (info == 0x3FFFFFu) {                                     /* too many rows for the entry: 12-mer table */
+            tt = sl - ix.hlen - 1;
+            const ulonglong2 kl = __ldg(ix.lc + ((seed >> (2 * (tt + 1))) & ((1ULL << (2 * ix.hlen)) - 1ULL)));
+            kk = kl.x;
+            ll = kl.y;
+            absent = (kk == 0 && ll == 0);
+        } else if (!absent) {
+            st_steps += (unsigned)(ix.hlen2 - ix.hlen);            /* steps of the reference's loop it stands for */
+        }
+    } else if (left0 >= 0) {                                        /* lchash.c:93-101 */
+        ulonglong2 kl = __ldg(ix.lc + ((seed >> (2 * left0)) & hmask));
+        kk = kl.x;
+        ll = kl.y;
+        absent = (kk == 0 && ll == 0);
+    }
+    st_seeds++;
+    if (!absent) {
+        /* Backward search (fmidx.c:300-310) until the interval is empty, the seed is used up, or at most
+         * VOTE_VW rows are left.  A row r of the interval survives the rest of the walk iff the remaining bases
+         * [0,tt] of the seed equal the tt+1 bases in front of SA[r] -- the text decides -- and the row it
+         * maps to has SA value SA[r]-(tt+1).  So the tail of the walk is one SA
+         * gather and one text gather instead of 2(tt+1) dependent sector gathers, and the vote needs no
+         * further SA access.  st_steps still counts the steps the reference's loop executes (up to and
+         * including the failing one); st_fm counts the FM steps actually done here. */
+        bool fail = false;
+        /* entry with context that covers the rest of the seed: no FM step is taken (the interval has <= 2 rows);
+         * a one-row entry carries the row's text POSITION in place of the row (as_lc2.cu): its seed needs no
+         * further gather unless more than 11 bases are left (then one text gather) */
+        const bool e_pos = etag == 1;
+        const bool e_ok = tt >= 0 && ((e_pos && tt < 11) || (a.use_ectx && etag == 2 && tt < 5));
+        const uint32_t vw = (SMALL || ix.sax != nullptr || e_ok) ? (uint32_t)VOTE_VW : 1u;
+        if (e_pos && tt < 0) {                                      /* the table answered the whole seed */
+            have_pos = true;
+            hit_pos = kk;
+        }
+        if (SMALL) {
+            uint32_t k32 = (uint32_t)kk, l32 = (uint32_t)ll;
+            while (tt >= 0 && l32 - k32 >= vw) {
+                const uint32_t c = (uint32_t)(seed >> (2 * tt)) & 3u;
+                as_bs_step32t(ix, *reinterpret_cast<const uint4 *>(s_tab + c), k32, l32);
+                st_steps++;
+                st_fm++;
+                tt--;
+                if (k32 > l32) { fail = true; break; }
+            }
+            kk = k32;
+            ll = l32;
+        } else {
+            while (tt >= 0 && ll - kk >= (uint64_t)vw) {
+                const uint32_t c = (uint32_t)(seed >> (2 * tt)) & 3u;
+                as_bs_step64t(ix, *reinterpret_cast<const uint4 *>(s_tab + c), s_tabChi[c], c, kk, ll);
+                st_steps++;
+                st_fm++;
+                tt--;
+                if (kk > ll) { fail = true; break; }
+            }
+        }
+        if (!fail && tt >= 0) {
+            /* 1..VOTE_VW rows left, tt+1 bases to go: every row's tail is read off the text -- the SA gathers
+             * of the rows are independent, so are the text gathers, where the FM walk is a chain */
+            const int nrem = tt + 1;
+            const uint32_t wdt = (uint32_t)(ll - kk) + 1u;
+            uint64_t pr[VOTE_VW];
+            uint32_t pv[VOTE_VW];                  /* with sax: the nrem bases in front of SA[r], no text gather */
+            /* the table entry itself carries the context of its one or two rows (as_lc2.cu, tags 1 and 2):
+             * nothing is fetched to decide, and only a surviving row's position is */
+            const bool from_e = e_ok;
+            const bool ctx = from_e || (!e_pos && ix.sax != nullptr && nrem <= 12);
+            bool in_text = true;
+#pragma unroll
+            for (int r = 0; r < VOTE_VW; r++) {
+                pv[r] = 0;
+                if ((uint32_t)r >= wdt) {
+                    pr[r] = ~0ULL;
+                } else if (e_pos) {
+                    pr[r] = kk;                                      /* the position; >= 32 by construction */
+                    pv[r] = ectx >> (2 * (11 - (nrem < 11 ? nrem : 11)));
+                } else if (from_e) {
+                    pr[r] = 1ULL << 62;                             /* not known yet; the builder checked SA >= context */
+                    pv[r] = ((ectx >> (10 * r)) & 0x3FFu) >> (2 * (5 - nrem));            /* tag 2 */
+                } else if (ctx) {
+                    const unsigned long long e = __ldg(ix.sax + kk + (uint64_t)r);
+                    pr[r] = e & 0xFFFFFFFFFFULL;
+                    pv[r] = (uint32_t)(e >> 40) >> (2 * (12 - nrem));
+                } else {
+                    pr[r] = as_locate(ix, kk + (uint64_t)r);
+                }
+                in_text &= pr[r] >= (uint64_t)nrem;
+            }
+            bool resolved = false;
+            if (in_text) {
+                int nsurv = 0, steps = 0;
+                uint64_t pos1 = 0;
+                uint32_t rsurv = 0;
+#pragma unroll
+                for (int r = 0; r < VOTE_VW; r++) {
+                    if ((uint32_t)r < wdt) {
+                        int sr;
+                        if (nrem <= 16) {
+                            const uint32_t tb = ctx ? pv[r] : as_bases16(ix.text2, pr[r] - (uint64_t)nrem);
+                            const uint32_t x = ((uint32_t)seed ^ tb) & (nrem == 16 ? 0xFFFFFFFFu : ((1u << (2 * nrem)) - 1u));
+                            sr = x == 0 ? nrem : nrem - ((31 - __clz(x)) >> 1);
+                            if (x == 0) { nsurv++; pos1 = pr[r] - (uint64_t)nrem; rsurv = (uint32_t)r; }
+                        } else {
+                            const uint64_t x = (seed ^ as_bases32(ix.text2, pr[r] - (uint64_t)nrem)) & ((1ULL << (2 * nrem)) - 1ULL);
+                            sr = x == 0 ? nrem : nrem - ((63 - __clzll((long long)x)) >> 1);
+                            if (x == 0) { nsurv++; pos1 = pr[r] - (uint64_t)nrem; rsurv = (uint32_t)r; }
+                        }
+                        steps = max(steps, sr);      /* the reference's loop stops when the last row drops out */
+                    }
+                }
+                if (nsurv <= 1) {
+                    st_steps += steps;
+                    st_txt++;
+                    resolved = true;
+                    if (nsurv == 1) {
+                        if (from_e && !e_pos) {
+                            const uint64_t row = kk + rsurv;
+                            pos1 = (ix.sax ? (__ldg(ix.sax + row) & 0xFFFFFFFFFFULL) : as_locate(ix, row)) - (uint64_t)nrem;
+                        }
+                        have_pos = true;
+                        hit_pos = pos1;
+                        ll = kk;                                    /* one row survives: rr = 1 */
+                    } else {
+                        fail = true;
+                    }
+                }
+            }
+            if (!resolved) {       /* two or more rows survive, or the text starts inside the seed: walk it */
+                while (tt >= 0) {
+                    const uint32_t c = (uint32_t)(seed >> (2 * tt)) & 3u;
+                    as_bs_step64t(ix, *reinterpret_cast<const uint4 *>(s_tab + c), s_tabChi[c], c, kk, ll);
+                    st_steps++;
+                    st_fm++;
+                    tt--;
+                    if (kk > ll) { fail = true; break; }
+                }
+            }
+        }
+        if (fail) { kk = 1; ll = 0; }
+        rr = kk > ll ? 0 : ll - kk + 1;
+    }
 }
 
 /*
@@ -180,16 +342,6 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
     const int hl = a.use2 ? ix.hlen2 : ix.hlen;          /* bases answered by the table */
     const int left0 = sl - hl;
     const uint64_t hmask = (1ULL << (2 * hl)) - 1ULL;
-#if VOTE_L2HINT
-    unsigned long long pol_first, pol_last;
-    asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_first));
-    asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_last));
-#define VOTE_LD_LC2(p) vote_ld_hint(p, pol_first)
-#define VOTE_LD_SAX(p) vote_ld_hint(p, pol_last)
-#else
-#define VOTE_LD_LC2(p) __ldg(p)
-#define VOTE_LD_SAX(p) __ldg(p)
-#endif
     unsigned long long st_seeds = 0, st_steps = 0, st_hits = 0, st_ovf = 0;
     unsigned int st_queued = 0;                  /* reads this warp handed to the overflow (BIG) pass */
     unsigned int st_fm = 0, st_txt = 0;          /* FM steps done here / tails decided by the text */
@@ -212,9 +364,9 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                 claim_end = claim_next + VOTE_CLAIM;
             }
             const uint32_t widx = claim_next++;
-            const uint32_t limit = BIG ? *a.ovf_count : (uint32_t)a.n;
+            const uint32_t limit = BIG ? *a.ovf_count : (a.list_count ? *a.list_count : (uint32_t)a.n);
             if (widx < limit) {
-                read = BIG ? a.ovf_list[widx] : widx;
+                read = BIG ? a.ovf_list[widx] : (a.list ? a.list[widx] : widx);
                 len = a.lens[read];
                 pr = a.pack + (size_t)read * a.wstride;
                 num_seeds = len / (uint32_t)P;                                   /* alnmain.c:371 */
@@ -235,11 +387,6 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
         const uint32_t m_count = have ? span_q + ((uint32_t)iter < span_r ? 1u : 0u) : 0u;
         const uint32_t m_max = warp_max_u32(m_count);
         bool ok = true, reg_vote = false;
-#if VOTE_PF
-        /* next phase = same seeds one base on (j + 1): sl + 1 <= 32 bases are in the seed register.  Wasted only for the
-         * phase that ends the read (one in ~6 on 150-bp reads at 2 %) */
-        const bool pf_next = m_max <= (uint32_t)G && sl < 32 && iter + 1 < P;
-#endif
         uint32_t v0val = 0, v1val = 0;
         uint64_t c0key = 0;
         for (uint32_t c0 = 0; c0 < m_max; c0 += G) {
@@ -250,164 +397,8 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
             uint64_t hit_pos = 0;
             if (m < m_count) {
                 const uint64_t seed = as_bases32(pr, j);
-                bool absent = false;
-                uint32_t etag = 0, ectx = 0;
-                int tt = left0 - 1;                                             /* next seed base to walk */
-                if (a.use2) {
-                    /* deep table: the interval lc_access + (hlen2 - hlen) steps of fmi_aln would have reached */
-                    const unsigned long long e = VOTE_LD_LC2(ix.lc2 + ((seed >> (2 * left0)) & hmask));
-#if VOTE_PF
-                    if (pf_next) asm volatile("prefetch.global.L2 [%0];" ::"l"(ix.lc2 + ((seed >> (2 * left0 + 2)) & hmask)));
-#endif
-                    const uint32_t info = (uint32_t)(e >> 40);
-                    etag = info >> 22;                                          /* as_lc2.cu: 0 count, 1 / 2 rows + context */
-                    ectx = info & 0x3FFFFFu;
-                    const uint32_t cnt = etag ? etag : ectx;
-                    kk = e & 0xFFFFFFFFFFULL;
-                    ll = kk + cnt - 1;
-                    absent = e == 0;
-                    if (info == 0x3FFFFFu) {                                     /* too many rows for the entry: 12-mer table */
-                        tt = sl - ix.hlen - 1;
-                        const ulonglong2 kl = __ldg(ix.lc + ((seed >> (2 * (tt + 1))) & ((1ULL << (2 * ix.hlen)) - 1ULL)));
-                        kk = kl.x;
-                        ll = kl.y;
-                        absent = (kk == 0 && ll == 0);
-                    } else if (!absent) {
-                        st_steps += (unsigned)(ix.hlen2 - ix.hlen);            /* steps of the reference's loop it stands for */
-                    }
-                } else if (left0 >= 0) {                                        /* lchash.c:93-101 */
-                    ulonglong2 kl = __ldg(ix.lc + ((seed >> (2 * left0)) & hmask));
-                    kk = kl.x;
-                    ll = kl.y;
-                    absent = (kk == 0 && ll == 0);
-                }
-                st_seeds++;
-                if (!absent) {
-                    /* Backward search (fmidx.c:300-310) until the interval is empty, the seed is used up, or at most
-                     * VOTE_VW rows are left.  A row r of the interval survives the rest of the walk iff the remaining bases
-                     * [0,tt] of the seed equal the tt+1 bases in front of SA[r] -- the text decides -- and the row it
-                     * maps to has SA value SA[r]-(tt+1).  So the tail of the walk is one SA
-                     * gather and one text gather instead of 2(tt+1) dependent sector gathers, and the vote needs no
-                     * further SA access.  st_steps still counts the steps the reference's loop executes (up to and
-                     * including the failing one); st_fm counts the FM steps actually done here. */
-                    bool fail = false;
-                    /* entry with context that covers the rest of the seed: no FM step is taken (the interval has <= 2 rows);
-                     * a one-row entry carries the row's text POSITION in place of the row (as_lc2.cu): its seed needs no
-                     * further gather unless more than 11 bases are left (then one text gather) */
-                    const bool e_pos = etag == 1;
-                    const bool e_ok = tt >= 0 && ((e_pos && tt < 11) || (a.use_ectx && etag == 2 && tt < 5));
-                    const uint32_t vw = (SMALL || ix.sax != nullptr || e_ok) ? (uint32_t)VOTE_VW : 1u;
-                    if (e_pos && tt < 0) {                                      /* the table answered the whole seed */
-                        have_pos = true;
-                        hit_pos = kk;
-                    }
-                    if (SMALL) {
-                        uint32_t k32 = (uint32_t)kk, l32 = (uint32_t)ll;
-                        while (tt >= 0 && l32 - k32 >= vw) {
-                            const uint32_t c = (uint32_t)(seed >> (2 * tt)) & 3u;
-                            as_bs_step32t(ix, *reinterpret_cast<const uint4 *>(s_tab + c), k32, l32);
-                            st_steps++;
-                            st_fm++;
-                            tt--;
-                            if (k32 > l32) { fail = true; break; }
-                        }
-                        kk = k32;
-                        ll = l32;
-                    } else {
-                        while (tt >= 0 && ll - kk >= (uint64_t)vw) {
-                            const uint32_t c = (uint32_t)(seed >> (2 * tt)) & 3u;
-                            as_bs_step64t(ix, *reinterpret_cast<const uint4 *>(s_tab + c), s_tabChi[c], c, kk, ll);
-                            st_steps++;
-                            st_fm++;
-                            tt--;
-                            if (kk > ll) { fail = true; break; }
-                        }
-                    }
-                    if (!fail && tt >= 0) {
-                        /* 1..VOTE_VW rows left, tt+1 bases to go: every row's tail is read off the text -- the SA gathers
-                         * of the rows are independent, so are the text gathers, where the FM walk is a chain */
-                        const int nrem = tt + 1;
-                        const uint32_t wdt = (uint32_t)(ll - kk) + 1u;
-                        uint64_t pr[VOTE_VW];
-                        uint32_t pv[VOTE_VW];                  /* with sax: the nrem bases in front of SA[r], no text gather */
-                        /* the table entry itself carries the context of its one or two rows (as_lc2.cu, tags 1 and 2):
-                         * nothing is fetched to decide, and only a surviving row's position is */
-                        const bool from_e = e_ok;
-                        const bool ctx = from_e || (!e_pos && ix.sax != nullptr && nrem <= 12);
-                        bool in_text = true;
-#pragma unroll
-                        for (int r = 0; r < VOTE_VW; r++) {
-                            pv[r] = 0;
-                            if ((uint32_t)r >= wdt) {
-                                pr[r] = ~0ULL;
-                            } else if (e_pos) {
-                                pr[r] = kk;                                      /* the position; >= 32 by construction */
-                                pv[r] = ectx >> (2 * (11 - (nrem < 11 ? nrem : 11)));
-                            } else if (from_e) {
-                                pr[r] = 1ULL << 62;                             /* not known yet; the builder checked SA >= context */
-                                pv[r] = ((ectx >> (10 * r)) & 0x3FFu) >> (2 * (5 - nrem));            /* tag 2 */
-                            } else if (ctx) {
-                                const unsigned long long e = VOTE_LD_SAX(ix.sax + kk + (uint64_t)r);
-                                pr[r] = e & 0xFFFFFFFFFFULL;
-                                pv[r] = (uint32_t)(e >> 40) >> (2 * (12 - nrem));
-                            } else {
-                                pr[r] = as_locate(ix, kk + (uint64_t)r);
-                            }
-                            in_text &= pr[r] >= (uint64_t)nrem;
-                        }
-                        bool resolved = false;
-                        if (in_text) {
-                            int nsurv = 0, steps = 0;
-                            uint64_t pos1 = 0;
-                            uint32_t rsurv = 0;
-#pragma unroll
-                            for (int r = 0; r < VOTE_VW; r++) {
-                                if ((uint32_t)r < wdt) {
-                                    int sr;
-                                    if (nrem <= 16) {
-                                        const uint32_t tb = ctx ? pv[r] : as_bases16(ix.text2, pr[r] - (uint64_t)nrem);
-                                        const uint32_t x = ((uint32_t)seed ^ tb) & (nrem == 16 ? 0xFFFFFFFFu : ((1u << (2 * nrem)) - 1u));
-                                        sr = x == 0 ? nrem : nrem - ((31 - __clz(x)) >> 1);
-                                        if (x == 0) { nsurv++; pos1 = pr[r] - (uint64_t)nrem; rsurv = (uint32_t)r; }
-                                    } else {
-                                        const uint64_t x = (seed ^ as_bases32(ix.text2, pr[r] - (uint64_t)nrem)) & ((1ULL << (2 * nrem)) - 1ULL);
-                                        sr = x == 0 ? nrem : nrem - ((63 - __clzll((long long)x)) >> 1);
-                                        if (x == 0) { nsurv++; pos1 = pr[r] - (uint64_t)nrem; rsurv = (uint32_t)r; }
-                                    }
-                                    steps = max(steps, sr);      /* the reference's loop stops when the last row drops out */
-                                }
-                            }
-                            if (nsurv <= 1) {
-                                st_steps += steps;
-                                st_txt++;
-                                resolved = true;
-                                if (nsurv == 1) {
-                                    if (from_e && !e_pos) {
-                                        const uint64_t row = kk + rsurv;
-                                        pos1 = (ix.sax ? (__ldg(ix.sax + row) & 0xFFFFFFFFFFULL) : as_locate(ix, row)) - (uint64_t)nrem;
-                                    }
-                                    have_pos = true;
-                                    hit_pos = pos1;
-                                    ll = kk;                                    /* one row survives: rr = 1 */
-                                } else {
-                                    fail = true;
-                                }
-                            }
-                        }
-                        if (!resolved) {       /* two or more rows survive, or the text starts inside the seed: walk it */
-                            while (tt >= 0) {
-                                const uint32_t c = (uint32_t)(seed >> (2 * tt)) & 3u;
-                                as_bs_step64t(ix, *reinterpret_cast<const uint4 *>(s_tab + c), s_tabChi[c], c, kk, ll);
-                                st_steps++;
-                                st_fm++;
-                                tt--;
-                                if (kk > ll) { fail = true; break; }
-                            }
-                        }
-                    }
-                    if (fail) { kk = 1; ll = 0; }
-                    rr = kk > ll ? 0 : ll - kk + 1;
-                }
+                vote_resolve_seed<SMALL>(ix, a, s_tab, s_tabChi, sl, left0, hmask, seed, false, 0ULL, kk, ll, rr, have_pos, hit_pos,
+                                         st_seeds, st_steps, st_fm, st_txt);
             }
             __syncwarp();
             const uint32_t rr_eff = (rr > 0 && rr < a.thres) ? (uint32_t)rr : 0u;   /* alnmain.c:360 */
@@ -467,30 +458,45 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                 const uint32_t base = incl - rr_eff;
                 const uint32_t V = __shfl_sync(gmask, incl, G - 1, G);
                 const uint32_t V_max = warp_max_u32(V);
-                for (uint32_t v0 = 0; v0 < V_max; v0 += G) {
-                    const uint32_t v = v0 + g;
-                    /* owner = largest lane whose exclusive base <= v */
-                    uint32_t lo = 0;
+                /* the overflow pass has one warp per read and four per SM: VU rows per lane are located before any is
+                 * inserted, so their SA gathers (and the inserts' first atomics) overlap instead of queueing up */
+                constexpr int VU = BIG ? 4 : 1;
+                for (uint32_t v0 = 0; v0 < V_max; v0 += G * VU) {
+                    uint64_t vkey[VU];
+                    uint32_t vord[VU];
+                    bool vok[VU];
 #pragma unroll
-                    for (int d = G >> 1; d >= 1; d >>= 1) {
-                        uint32_t b = __shfl_sync(gmask, base, lo + d, G);
-                        if (b <= v) lo += d;
+                    for (int u = 0; u < VU; u++) {
+                        const uint32_t v = v0 + (uint32_t)u * G + g;
+                        /* owner = largest lane whose exclusive base <= v */
+                        uint32_t lo = 0;
+#pragma unroll
+                        for (int d = G >> 1; d >= 1; d >>= 1) {
+                            uint32_t b = __shfl_sync(gmask, base, lo + d, G);
+                            if (b <= v) lo += d;
+                        }
+                        const uint32_t ob = __shfl_sync(gmask, base, lo, G);
+                        const uint32_t okl = __shfl_sync(gmask, (uint32_t)kk, lo, G);
+                        const uint32_t okh = __shfl_sync(gmask, (uint32_t)(kk >> 32), lo, G);
+                        const uint32_t opl = __shfl_sync(gmask, (uint32_t)hit_pos, lo, G);
+                        const uint32_t oph = __shfl_sync(gmask, (uint32_t)(hit_pos >> 32), lo, G);
+                        const bool opk = __shfl_sync(gmask, (int)have_pos, lo, G) != 0;
+                        vok[u] = v < V;
+                        vkey[u] = 0;
+                        vord[u] = 0;
+                        if (v < V) {
+                            const uint32_t om = c0 + lo;
+                            const uint32_t oj = (uint32_t)iter + om * (uint32_t)P;
+                            const uint32_t off = v - ob;
+                            uint64_t row = (((uint64_t)okh << 32) | okl) + off;
+                            vkey[u] = (opk ? (((uint64_t)oph << 32) | opl) : as_locate(ix, row)) - (uint64_t)oj;
+                            vord[u] = om * a.thres + off;
+                            st_hits++;
+                        }
                     }
-                    const uint32_t ob = __shfl_sync(gmask, base, lo, G);
-                    const uint32_t okl = __shfl_sync(gmask, (uint32_t)kk, lo, G);
-                    const uint32_t okh = __shfl_sync(gmask, (uint32_t)(kk >> 32), lo, G);
-                    const uint32_t opl = __shfl_sync(gmask, (uint32_t)hit_pos, lo, G);
-                    const uint32_t oph = __shfl_sync(gmask, (uint32_t)(hit_pos >> 32), lo, G);
-                    const bool opk = __shfl_sync(gmask, (int)have_pos, lo, G) != 0;
-                    if (v < V) {
-                        const uint32_t om = c0 + lo;
-                        const uint32_t oj = (uint32_t)iter + om * (uint32_t)P;
-                        const uint32_t off = v - ob;
-                        uint64_t row = (((uint64_t)okh << 32) | okl) + off;
-                        uint64_t key = (opk ? (((uint64_t)oph << 32) | opl) : as_locate(ix, row)) - (uint64_t)oj;
-                        st_hits++;
-                        if (!table_insert<USED_T>(t, key >> 4, (uint32_t)key & 15u, om * a.thres + off)) ok = false;
-                    }
+#pragma unroll
+                    for (int u = 0; u < VU; u++)
+                        if (vok[u] && !table_insert<USED_T>(t, vkey[u] >> 4, (uint32_t)vkey[u] & 15u, vord[u])) ok = false;
                 }
             }
         }
@@ -663,6 +669,333 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
     }
 }
 
+
+/* ------------------------------------------------------------------------------------------------------------------------
+ * Thread-per-read PART 1 for short reads (at most VT_M seeds per phase: 150-bp reads at seed_len 20 have seven).
+ *
+ * The group kernel above spends ~185 warp instructions per read and phase on cooperation -- ballots, MATCH.ANY, butterflies,
+ * shared-memory tables, warp-uniform loop bounds over four reads in four different states -- for seven table lookups and
+ * seven votes.  Here a LANE owns a read: it requests the table entries of all the phase's seeds at once (seven independent
+ * gathers in flight per lane, 224 per warp), resolves them one after the other with the same vote_resolve_seed the group
+ * kernel uses, and keeps the phase's vote list (histo.c:26-56: buckets in first-seen order, a count and the smallest key
+ * each) and the read's outer list in registers -- votes are cast in seed order by one thread, so first-seen order is just
+ * the order of insertion and TOP2 (histo.c:84-96) is one scan.  Lanes that finish a read take the next one at the top of
+ * the trip, so a warp's 32 reads are in 32 different phases and nobody waits for the slowest.
+ *
+ * What does not fit a thread goes to the group kernel through a queue (list mode): a seed with more than two rows left
+ * after the walk (its votes would have to be spread), a phase with more than VT_NV distinct buckets, a read whose outer
+ * list outgrows VT_NO.  On the uniform 4.6 Mbp genome that is a few reads in a thousand; repeat families send theirs there.
+ * ---------------------------------------------------------------------------------------------------------------------- */
+#define VT_THREADS 128
+#define VT_M 8                        /* seeds per phase a thread takes */
+#define VT_W 16                       /* packed words of a read kept in shared memory */
+#define VT_NV 4                       /* distinct buckets of a phase kept in registers */
+#define VT_NO 4                       /* distinct buckets of the outer list kept in registers */
+#ifndef VT_MIN_BLOCKS
+#define VT_MIN_BLOCKS 4
+#endif
+
+/* 32 bases from base i of a packed read in shared memory (as_bases32 for __shared__ words) */
+__device__ __forceinline__ uint64_t vt_bases32(const uint32_t *w, uint32_t i) {
+    const uint32_t *p = w + (i >> 4);
+    const uint32_t x = p[0], y = p[1], z = p[2], sh = 2u * (i & 15u);
+    return (uint64_t)__funnelshift_r(x, y, sh) | ((uint64_t)__funnelshift_r(y, z, sh) << 32);
+}
+
+template <bool SMALL>
+__global__ void __launch_bounds__(VT_THREADS, VT_MIN_BLOCKS) k_vote_t(DevIndex ix, VoteArgs a) {
+    constexpr uint32_t FULL = 0xFFFFFFFFu;
+    __shared__ uint32_t s_rd[VT_THREADS * (VT_W + 1)];      /* row stride 17 words: a warp's accesses fall in 32 banks */
+    __shared__ BsTab s_tab[4];
+    __shared__ uint32_t s_tabChi[4];
+    const uint32_t lane = threadIdx.x & 31u;
+    uint32_t *rd = s_rd + threadIdx.x * (VT_W + 1);
+    as_bs_tab_init(ix, s_tab, s_tabChi, threadIdx.x);
+    __syncthreads();
+
+    const int sl = a.sl, P = sl + 1;
+    const int hl = a.use2 ? ix.hlen2 : ix.hlen;            /* bases answered by the table; <= sl (launcher) */
+    const int left0 = sl - hl;
+    const uint64_t hmask = (1ULL << (2 * hl)) - 1ULL;
+    const uint32_t nw = a.wstride < (size_t)VT_W ? (uint32_t)a.wstride : (uint32_t)VT_W;
+    unsigned long long st_seeds = 0, st_steps = 0, st_hits = 0;
+    unsigned int st_fm = 0, st_txt = 0, st_deferred = 0;
+
+    bool have = false, drained = false;
+    uint32_t read = 0, num_seeds = 0, span_q = 0, span_r = 0, n_outer = 0;
+    int iter = 0;
+    uint64_t okey[VT_NO];
+    uint32_t oval[VT_NO];
+    unsigned long long r_seeds = 0, r_steps = 0;           /* counters of the read in hand: dropped if it is deferred */
+    unsigned int r_hits = 0, r_fm = 0, r_txt = 0;
+#pragma unroll
+    for (int e = 0; e < VT_NO; e++) { okey[e] = 0; oval[e] = 0; }
+
+    for (;;) {
+        /* ---- lanes without a read take the next ones: one atomic per warp and trip ---- */
+        const uint32_t need = __ballot_sync(FULL, !have && !drained);
+        if (need) {
+            const int leader = __ffs((int)need) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(a.work_counter, (uint32_t)__popc(need));
+            base = __shfl_sync(FULL, base, leader);
+            if (!have && !drained) {
+                const uint32_t widx = base + (uint32_t)__popc(need & ((1u << lane) - 1u));
+                if (widx < (uint32_t)a.n) {
+                    read = widx;
+                    const uint32_t len = a.lens[read];
+                    const uint32_t *src = a.pack + (size_t)read * a.wstride;
+                    for (uint32_t w = 0; w < nw; w++) rd[w] = __ldg(src + w);
+                    num_seeds = len / (uint32_t)P;                               /* alnmain.c:371 */
+                    const uint32_t span = len > (uint32_t)sl ? len - (uint32_t)sl : 0;   /* seeds start at j < len - sl (:353) */
+                    span_q = span / (uint32_t)P;
+                    span_r = span - span_q * (uint32_t)P;
+                    n_outer = 0;
+                    iter = 0;
+                    r_seeds = r_steps = 0;
+                    r_hits = r_fm = r_txt = 0;
+                    have = true;
+                } else {
+                    drained = true;
+                }
+            }
+        }
+        if (!__any_sync(FULL, have)) break;
+
+        /* ---- one phase of this lane's read: seeds iter, iter+P, ... (alnmain.c:353) ---- */
+        const uint32_t m_count = have ? span_q + ((uint32_t)iter < span_r ? 1u : 0u) : 0u;     /* <= VT_M (launcher) */
+        unsigned long long ent[VT_M];
+        uint32_t sd[VT_M];                                   /* low 16 bases of the seeds: what a table entry's context is compared with */
+#pragma unroll
+        for (int m = 0; m < VT_M; m++) {
+            ent[m] = 0;
+            sd[m] = 0;
+            if (a.use2 && (uint32_t)m < m_count) {          /* without the deep table vote_resolve_seed reads the 12-mer table */
+                const uint64_t seed = vt_bases32(rd, (uint32_t)iter + (uint32_t)m * (uint32_t)P);
+                ent[m] = __ldg(ix.lc2 + ((seed >> (2 * left0)) & hmask));
+                sd[m] = (uint32_t)seed;
+            }
+        }
+        uint64_t vb[VT_NV];
+        uint32_t vc[VT_NV];                  /* count << 8 | first vote (2 * seed + row) << 4 | smallest low nibble of the keys */
+        uint32_t nv = 0;
+        bool defer = false;
+        /* histo_add (histo.c:42-56) into the phase's list; `ord` = 2 * seed index + row: the list's first-seen order */
+        auto cast = [&](uint64_t key, uint32_t ord) {
+            const uint64_t b = key >> 4;
+            const uint32_t lw = (uint32_t)key & 15u;
+            bool found = false;
+#pragma unroll
+            for (int i = 0; i < VT_NV; i++) {
+                if ((uint32_t)i < nv && vb[i] == b) {
+                    const uint32_t c = vc[i];
+                    vc[i] = ((c & ~0xFFu) + 0x100u) | min(c & 0xF0u, ord << 4) | min(c & 15u, lw);
+                    found = true;
+                }
+            }
+            if (!found) {
+                if (nv == VT_NV) {
+                    defer = true;
+                } else {
+#pragma unroll
+                    for (int i = 0; i < VT_NV; i++) {
+                        if ((uint32_t)i == nv) {
+                            vb[i] = b;
+                            vc[i] = 0x100u | (ord << 4) | lw;
+                        }
+                    }
+                    nv++;
+                }
+            }
+        };
+        /* pass A, every seed: an absent entry, or a one-row entry whose context covers the rest of the seed, is finished on
+         * the spot (as_lc2.cu tag 1: the entry holds the hit's position and the 11 bases in front of it); the others are
+         * marked for pass B.  Same counters as vote_resolve_seed keeps for these two cases. */
+        uint32_t todo = 0;
+        const bool fastpath = a.use2 && left0 <= 11 && a.thres > 1u;
+#pragma unroll
+        for (int m = 0; m < VT_M; m++) {
+            if ((uint32_t)m < m_count) {
+                const unsigned long long e = ent[m];
+                const uint32_t info = (uint32_t)(e >> 40);
+                if (fastpath && e == 0) {
+                    r_seeds++;
+                } else if (fastpath && (info >> 22) == 1u) {
+                    r_seeds++;
+                    r_steps += (unsigned)(ix.hlen2 - ix.hlen);
+                    uint32_t x = 0;
+                    if (left0 > 0) {
+                        x = (sd[m] ^ ((info & 0x3FFFFFu) >> (2 * (11 - left0)))) & ((1u << (2 * left0)) - 1u);
+                        r_steps += (unsigned)(x == 0 ? left0 : left0 - ((31 - __clz(x)) >> 1));
+                        r_txt++;
+                    }
+                    if (x == 0) {
+                        const uint32_t j = (uint32_t)iter + (uint32_t)m * (uint32_t)P;
+                        r_hits++;
+                        cast((e & 0xFFFFFFFFFFULL) - (uint64_t)left0 - (uint64_t)j, 2u * (uint32_t)m);    /* alnmain.c:363-365 */
+                    }
+                } else {
+                    todo |= 1u << m;
+                }
+            }
+        }
+        /* pass B, the marked seeds of each lane in turn (backward-search steps, two-row intervals, text gathers): the
+         * lines they start from are requested for all of them first, so the resolver finds them in L1 */
+        if (a.use2) {
+#pragma unroll
+            for (int m = 0; m < VT_M; m++) {
+                const unsigned long long e = ent[m];
+                const uint32_t info = (uint32_t)(e >> 40), etag = info >> 22;
+                if (((todo >> m) & 1u) && e != 0 && etag != 1u && info != 0x3FFFFFu) {
+                    const uint64_t k0 = e & 0xFFFFFFFFFFULL;
+                    const uint32_t cnt = etag ? etag : (info & 0x3FFFFFu);
+                    if (cnt <= (uint32_t)VOTE_VW) {
+                        /* a two-row entry that decides from its own context (use_ectx) fetches a position for survivors only */
+                        if (etag == 2u && a.use_ectx && left0 >= 1 && left0 <= 5) continue;
+                        if (ix.sax) asm volatile("prefetch.global.L1 [%0];" ::"l"(ix.sax + k0));
+                        else if (ix.sa_lo) asm volatile("prefetch.global.L1 [%0];" ::"l"(ix.sa_lo + k0));
+                    } else {
+                        asm volatile("prefetch.global.L1 [%0];" ::"l"(ix.fm + ((k0 - 1) >> 6)));
+                        asm volatile("prefetch.global.L1 [%0];" ::"l"(ix.fm + ((k0 + cnt - 1) >> 6)));
+                    }
+                }
+            }
+        }
+        while (__any_sync(FULL, todo != 0)) {
+            if (todo) {
+                const uint32_t m = (uint32_t)__ffs((int)todo) - 1u;
+                todo &= todo - 1u;
+                unsigned long long em = ent[0];
+#pragma unroll
+                for (int q = 1; q < VT_M; q++)
+                    if (m == (uint32_t)q) em = ent[q];
+                const uint32_t j = (uint32_t)iter + m * (uint32_t)P;
+                const uint64_t seed = vt_bases32(rd, j);
+                uint64_t kk = 1, ll = ix.N - 1, rr = 0, hit_pos = 0;             /* alnmain.c:354 */
+                bool have_pos = false;
+                vote_resolve_seed<SMALL>(ix, a, s_tab, s_tabChi, sl, left0, hmask, seed, a.use2 != 0, em, kk, ll, rr, have_pos, hit_pos,
+                                         r_seeds, r_steps, r_fm, r_txt);
+                const uint32_t rr_eff = (rr > 0 && rr < a.thres) ? (uint32_t)rr : 0u;   /* alnmain.c:360 */
+                if (rr_eff > 2u) defer = true;
+                for (uint32_t r = 0; r < rr_eff && r < 2u; r++) {
+                    r_hits++;
+                    cast((have_pos ? hit_pos : as_locate(ix, kk + r)) - (uint64_t)j, 2u * m + r);          /* alnmain.c:363-365 */
+                }
+            }
+        }
+        /* ---- TOP2 of the phase (histo.c:84-96): largest count, first seen wins a tie ---- */
+        uint32_t t0 = 0, t1 = 0;
+        uint64_t c0key = 0;
+#pragma unroll
+        for (int i = 0; i < VT_NV; i++) {
+            if ((uint32_t)i < nv) {
+                const uint32_t c = ((vc[i] >> 8) << 4) | (15u - ((vc[i] >> 4) & 15u));
+                if (c > t0) {
+                    t1 = t0;
+                    t0 = c;
+                    c0key = (vb[i] << 4) | (vc[i] & 15u);
+                } else if (c > t1) {
+                    t1 = c;
+                }
+            }
+        }
+        const uint32_t v0val = t0 >> 4, v1val = t1 >> 4;
+        /* ---- phase control (alnmain.c:371-404), as in the group kernel ---- */
+        bool broke = false;
+        uint64_t best_key = 0, best_val = 0;
+        if (have && !defer && num_seeds > 0) {                                   /* alnmain.c:373 */
+            const uint64_t v = (uint64_t)v0val + v1val;
+            if (5ull * v > 3ull * (uint64_t)num_seeds) {                        /* score > 0.6 in integers, see k_vote */
+                best_key = c0key;
+                best_val = v0val;
+                broke = true;
+            } else if (v0val != 0) {                                            /* :386-388 histo_add(outer, cand[0].key) */
+                const uint64_t b = c0key >> 4;
+                bool found = false;
+#pragma unroll
+                for (int e = 0; e < VT_NO; e++) {
+                    if ((uint32_t)e < n_outer && (okey[e] >> 4) == b) {
+                        oval[e] += 1;
+                        if (c0key < okey[e]) okey[e] = c0key;
+                        found = true;
+                    }
+                }
+                if (!found) {
+                    if (n_outer == VT_NO) {
+                        defer = true;
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < VT_NO; e++) {
+                            if ((uint32_t)e == n_outer) {
+                                okey[e] = c0key;
+                                oval[e] = 1;
+                            }
+                        }
+                        n_outer++;
+                    }
+                }
+            }
+        }
+        if (have) {
+            bool finished;
+            if (defer) {
+                a.dlist[atomicAdd(a.dlist_count, 1u)] = read;                    /* redone by the group kernel */
+                st_deferred++;
+                finished = true;
+            } else {
+                if (!broke) iter++;                                            /* a break leaves iter where it was */
+                finished = broke || iter >= P;
+                if (finished) {
+                    int from_outer = 0;
+                    if (iter >= P - 1) {                                        /* alnmain.c:400-403 */
+                        uint64_t bk = 0;
+                        uint32_t bv = 0;
+#pragma unroll
+                        for (int e = 0; e < VT_NO; e++) {
+                            if ((uint32_t)e < n_outer && oval[e] > bv) {
+                                bv = oval[e];
+                                bk = okey[e];
+                            }
+                        }
+                        best_key = bk;
+                        best_val = bv;
+                        from_outer = 1;
+                    }
+                    VoteOut o;
+                    o.best_key = best_key;
+                    o.best_val = best_val;
+                    o.phases = iter;
+                    o.from_outer = from_outer;
+                    a.out[read] = o;
+                    st_seeds += r_seeds;
+                    st_steps += r_steps;
+                    st_hits += r_hits;
+                    st_fm += r_fm;
+                    st_txt += r_txt;
+                }
+            }
+            if (finished) have = false;
+        }
+    }
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) {
+        st_seeds += __shfl_xor_sync(FULL, st_seeds, d);
+        st_steps += __shfl_xor_sync(FULL, st_steps, d);
+        st_hits += __shfl_xor_sync(FULL, st_hits, d);
+        st_fm += __shfl_xor_sync(FULL, st_fm, d);
+        st_txt += __shfl_xor_sync(FULL, st_txt, d);
+        st_deferred += __shfl_xor_sync(FULL, st_deferred, d);
+    }
+    if (lane == 0) {
+        if (st_seeds) atomicAdd(a.stats + 6, st_seeds);
+        if (st_hits) atomicAdd(a.stats + 7, st_hits);
+        if (st_steps) atomicAdd(a.stats + 8, st_steps);
+        if (st_fm) atomicAdd(a.stats + 12, (unsigned long long)st_fm);
+        if (st_txt) atomicAdd(a.stats + 13, (unsigned long long)st_txt);
+        if (st_deferred) atomicAdd(a.stats + 16, (unsigned long long)st_deferred);
+    }
+}
+
 static uint32_t next_pow2(uint64_t v) {
     uint32_t p = 64;
     while (p < v && p < (1u << 30)) p <<= 1;
@@ -692,11 +1025,18 @@ int as_launch_vote(as_gpu *h, const as_params *p, const uint32_t *d_pack, size_t
         as_set_error("as_map_batch: a read of %u bases with thres %u needs more vote slots than the overflow table has", max_len, p->thres);
         return AS_ERANGE;
     }
-    uint32_t big_cap = next_pow2(2 * max_votes);
+    uint32_t big_cap = next_pow2(max_votes + max_votes / 4);            /* load factor <= 0.8 */
     size_t big_stride = ((size_t)big_cap * 24 + 64 + 255) & ~(size_t)255;
     size_t budget = (size_t)2 << 30;
     size_t big_warps = budget / big_stride;
-    if (big_warps > (size_t)h->sm_count * 4) big_warps = (size_t)h->sm_count * 4;
+    /* one warp per queued read.  The pass is latency-bound (a located row and a compare-and-swap per vote), so its time
+     * falls with the warps in flight -- as long as their tables stay in L2: 16 warps per SM on 8192-slot tables (465 MB) ran
+     * SLOWER than 4 (c2r: 38 vs 29 ms).  Up to 8 warps per SM within 96 MB of tables */
+    if (big_warps > (size_t)h->sm_count * 8) big_warps = (size_t)h->sm_count * 8;
+    {
+        const size_t l2_warps = ((size_t)96 << 20) / big_stride;
+        if (big_warps > l2_warps) big_warps = l2_warps > (size_t)h->sm_count ? l2_warps : (size_t)h->sm_count;
+    }
     if (big_warps > n) big_warps = n;
     if (big_warps < 1) big_warps = 1;
     AS_TRY(as_scratch(h, &h->ovf_table, big_warps * big_stride));
@@ -716,6 +1056,10 @@ int as_launch_vote(as_gpu *h, const as_params *p, const uint32_t *d_pack, size_t
     a.big_stride = big_stride;
     a.big_cap = big_cap;
     a.stats = h->d_stats;
+    a.list = nullptr;
+    a.list_count = nullptr;
+    a.dlist = nullptr;
+    a.dlist_count = nullptr;
     a.use2 = (h->ix.lc2 && sl >= h->ix.hlen2 && !(p->flags & AS_F_NO_LC2)) ? 1 : 0;
     /* Deciding a seed from its table entry saves the SA/context gather of every seed that dies there, at the price of
      * fetching a survivor's position after the compare instead of along with the context.  It pays when that gather is
@@ -723,18 +1067,46 @@ int as_launch_vote(as_gpu *h, const as_params *p, const uint32_t *d_pack, size_t
     a.use_ectx = h->ix.N * 8ULL > 2ULL * (unsigned long long)h->l2_bytes ? 1 : 0;
     if (p->vote_ectx >= 0) a.use_ectx = p->vote_ectx != 0;
 
+    /* indexes of one super block (<= 2^30 rows) take the 32-bit backward-search path */
+    const bool small = h->ix.N <= (1ULL << AS_SB_SHIFT) && !(p->flags & AS_F_WIDE_INDEX);
     /* lanes per read from the seeds of one phase of the longest read */
     int G = seeds_per_phase <= 8 ? 8 : seeds_per_phase <= 16 ? 16 : 32;
     uint64_t groups_needed = n;
     uint64_t groups_per_block = VOTE_THREADS / G;
     uint64_t blocks = (groups_needed + groups_per_block - 1) / groups_per_block;
     unsigned grid = 0;
-    /* indexes of one super block (<= 2^30 rows) take the 32-bit backward-search path */
-    const bool small = h->ix.N <= (1ULL << AS_SB_SHIFT) && !(p->flags & AS_F_WIDE_INDEX);
+    /* Short reads: the thread-per-read kernel takes the batch; what it defers comes back as a list for the group kernel.
+     * Applies when every phase has at most VT_M seeds, the words a seed can touch fit the shared-memory row, and the table
+     * (deep or 12-mer) is not longer than the seed (counters: [3] work counter of the list pass, [4] length of the list) */
+    const bool thread_ok = sl >= (a.use2 ? h->ix.hlen2 : h->ix.hlen) && seeds_per_phase <= VT_M && sl < 32 && max_len > (uint32_t)sl &&
+                           ((max_len - (uint32_t)sl - 1u) >> 4) + 3u <= (uint32_t)VT_W && p->vote_thread != 0;
+    if (thread_ok) {
+        AS_TRY(as_scratch(h, &h->vote_dlist, n * sizeof(uint32_t)));
+        a.dlist = (uint32_t *)h->vote_dlist.p;
+        a.dlist_count = (unsigned int *)h->counters.p + 4;
+        int occ = 0;
+        uint64_t tb = (n + VT_THREADS - 1) / VT_THREADS;
+        if (small) {
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_vote_t<true>, VT_THREADS, 0) != cudaSuccess || occ < 1) occ = VT_MIN_BLOCKS;
+            const uint64_t cap = (uint64_t)h->sm_count * (uint64_t)occ;
+            k_vote_t<true><<<(unsigned)(tb < cap ? tb : cap), VT_THREADS, 0, h->stream>>>(h->ix, a);
+        } else {
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_vote_t<false>, VT_THREADS, 0) != cudaSuccess || occ < 1) occ = VT_MIN_BLOCKS;
+            const uint64_t cap = (uint64_t)h->sm_count * (uint64_t)occ;
+            k_vote_t<false><<<(unsigned)(tb < cap ? tb : cap), VT_THREADS, 0, h->stream>>>(h->ix, a);
+        }
+        h->launches++;
+        AS_CUDA(cudaGetLastError());
+        a.list = a.dlist;
+        a.list_count = a.dlist_count;
+        a.work_counter = (unsigned int *)h->counters.p + 3;
+    }
     /* reads are claimed from a work counter, so the grid is exactly the resident blocks (registers / shared memory) */
 #define VOTE_LAUNCH1(GG, SM)                                                                                     \
     do {                                                                                                         \
         int occ = 0;                                                                                             \
+        if (VOTE_CARVEOUT >= 0)                                                                                  \
+            cudaFuncSetAttribute(k_vote<GG, false, SM>, cudaFuncAttributePreferredSharedMemoryCarveout, VOTE_CARVEOUT); \
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_vote<GG, false, SM>, VOTE_THREADS, 0) != cudaSuccess || \
             occ < 1)                                                                                             \
             occ = VOTE_MIN_BLOCKS;                                                                               \

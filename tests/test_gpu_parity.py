@@ -157,6 +157,40 @@ def test_vote_overflow_pass_high_copy_repeats(native, idx_high_copy, wide):
         m.close()
 
 
+@pytest.mark.parametrize("h2", [0, 13])
+@pytest.mark.parametrize("wide", [0, 16])
+def test_vote_thread_kernel_equals_group_kernel(native, idx_repeat, idx_high_copy, h2, wide):
+    """Short reads take the thread-per-read PART 1 kernel (k_vote_t), which hands what a thread cannot hold (a seed with more
+    than two hits, more than 4 distinct buckets in a phase or in the outer list) to the group kernel through a
+    queue; as_params.vote_thread = 0 sends everything through the group kernel.  Both equal the oracle, on the repeat-rich
+    genome (with and without the deep table) and on the high-copy families (thread -> group -> overflow pass), and a larger
+    batch gives the same votes either way."""
+    for (ix, gs), seed in ((idx_repeat, 1500), (idx_high_copy, 1600)):
+        m = oracle_lib.gpu_mapper(native, ix, 0, native.open_opts(lc2_hlen=h2) if h2 else None)
+        try:
+            for k, (lmin, lmax, e, sl, th) in enumerate([(150, 150, 0.02, 20, 300), (100, 150, 0.05, 20, 300), (36, 120, 0.03, 16, 50),
+                                                        (150, 187, 0.01, 20, 1000), (21, 40, 0.0, 20, 300), (150, 150, 0.02, 24, 2)]):
+                reads, lens, _ = reads_from(native, seed + k, gs, 250, lmin, lmax, e, e, 0.7)
+                m.stats_reset()
+                l0 = m.launch_count()
+                check_vote(m, ix, reads, lens, sl, th, flags=wide)
+                d_thread = m.launch_count() - l0            # pack, k_vote_t, group kernel over the queue, overflow pass
+                assert m.stats()["vote_deferred"] < len(lens)
+                l0 = m.launch_count()
+                check_vote(m, ix, reads, lens, sl, th, flags=wide, vote_thread=0)
+                assert d_thread == m.launch_count() - l0 + 1, "the thread-per-read kernel did not run"
+            reads, lens, _ = reads_from(native, seed + 50, gs, 20000, 150, 150, 0.02, 0.02, 0.8)
+            m.stats_reset()
+            a = m.vote_batch(reads, lens, m.params(flags=wide))
+            st = m.stats()
+            b = m.vote_batch(reads, lens, m.params(flags=wide, vote_thread=0))
+            for x, y in zip(a, b):
+                assert np.array_equal(x, y)
+            assert 0 < st["vote_deferred"] < len(lens)
+        finally:
+            m.close()
+
+
 @pytest.mark.parametrize("seed_len,thres", [(12, 300), (16, 50), (24, 300), (32, 1000), (20, 2)])
 def test_vote_parameters(native, gpu_repeat, idx_repeat, seed_len, thres):
     ix, gs = idx_repeat

@@ -36,10 +36,11 @@ __global__ void __launch_bounds__(128) k_gather(const unsigned long long *__rest
 }
 
 template <int U, bool DEP>
-static void run(const unsigned long long *tab, uint64_t entries, unsigned long long *out, int sm, const char *tag, size_t smem = 0) {
+static void run(const unsigned long long *tab, uint64_t entries, unsigned long long *out, int sm, const char *tag, int bps = 0) {
     int occ = 0;
-    CK(cudaFuncSetAttribute(k_gather<U, DEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 << 10));
+    const size_t smem = 0;
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_gather<U, DEP>, 128, smem));
+    if (bps > 0 && bps < occ) occ = bps;          /* fewer resident blocks per SM: the grid is all that is resident */
     const int grid = sm * occ;
     const int rounds = 256 / U * 4;
     cudaEvent_t a, b;
@@ -62,10 +63,10 @@ int main(int argc, char **argv) {
     CK(cudaSetDevice(dev));
     CK(cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev));
     size_t max_gb = argc > 1 ? (size_t)atoi(argv[1]) : 32;
-    const size_t sizes_mb[] = {32, 74, 512, 8192, 32768};
+    const size_t sizes_mb[] = {32, 64, 128, 512, 8192, 32768};
     unsigned long long *out;
     CK(cudaMalloc(&out, 64));
-    for (int gran : {0, 32, 64, 128}) {
+    for (int gran : {0, 32}) {
         if (gran) CK(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, gran));
         size_t got = 0;
         CK(cudaDeviceGetLimit(&got, cudaLimitMaxL2FetchGranularity));
@@ -85,8 +86,9 @@ int main(int argc, char **argv) {
             run<4, true>(tab, entries, out, sm, tag);
             run<8, false>(tab, entries, out, sm, tag);
             /* k_vote's occupancy: 6 blocks of 4 warps per SM */
-            run<1, true>(tab, entries, out, sm, tag, 36 << 10);
-            run<2, true>(tab, entries, out, sm, tag, 36 << 10);
+            run<1, true>(tab, entries, out, sm, tag, 6);
+            run<2, true>(tab, entries, out, sm, tag, 6);
+            run<4, true>(tab, entries, out, sm, tag, 6);
             CK(cudaFree(tab));
         }
     }
