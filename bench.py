@@ -704,6 +704,10 @@ def run_b200(args):
             "stats_per_step_per_gpu": {k: per_step[k] for k in ("seeds", "bs_steps", "fm_steps_exec", "text_verified", "sa_hits", "dp_cells",
                                                                    "dp_cells_eval", "gact_redone", "overflow_reads", "overflow_queued", "vote_deferred")}}
 
+    # the program leg builds its own index on the same GPUs: give the memory back first (human scale: ~120 GB per handle)
+    mapper.close()
+    del d_pristine, d_reads, d_lens, d_res, d_store
+    torch.cuda.empty_cache()
     if world > 1:
         dist.barrier()
     if rank == 0 and not args.no_program and wl["len"][1] <= 512:
@@ -727,7 +731,6 @@ def run_b200(args):
         line["cpu_baseline"] = None
     if rank == 0:
         print(json.dumps(line))
-    mapper.close()
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -65,7 +65,7 @@ void as_gpu_close(as_gpu *h);
 /* Open-time options (what used to be environment variables: a drop-in library must not read its host's environment).
  * Zero-initialised = the defaults; as_gpu_open / as_gpu_build use the defaults. */
 typedef struct as_open_opts {
-    int32_t  lc2_hlen;        /* depth of the deep k-mer table: 0 = min(16, ceil(log4 N)+1); <= hlen disables it; 13..16 forces */
+    int32_t  lc2_hlen;        /* depth of the deep k-mer table: 0 = min(16, ceil(log4 N)+1), +1 while the table stays within 4 GB; <= hlen disables it; 13..16 forces */
     int32_t  no_sax;          /* 1: do not build the SA + context table (PART 1 then gathers SA and text separately) */
     uint64_t build_part_max;  /* as_gpu_build only: > 0 forces the partitioned suffix sort with at most this many suffixes
                                * per partition (the path texts of >= 2^32-1 rows take) */
@@ -132,7 +132,8 @@ typedef struct as_params {
     uint32_t chunk_reads;         /* as_map_batch: fixed chunk size; 0 = the ramp-up / ramp-down plan (default) */
     int32_t  chunk_tail;          /* as_map_batch: how many times the last chunk is split 2:1; -1 = default (1) */
     int32_t  vote_thread;         /* PART 1 of short reads (<= 8 seeds per phase) by the thread-per-read kernel, the rest by the
-                                   * group kernel: -1 = when it applies (default), 0 = group kernel only */
+                                   * group kernel: -1 = when it applies and the index has at most 2^30 rows (default), 0 = group
+                                   * kernel only, 1 = whenever it applies */
 } as_params;
 #define AS_F_MYERS        1u   /* also run the edlib-equivalent NW distance with k=(int)(0.05*len*2) per read */
 #define AS_F_NO_ALIGN     2u   /* stop after PART 1+2 (no GACT): results carry loc/off/strand/flag only */

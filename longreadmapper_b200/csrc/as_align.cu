@@ -261,6 +261,11 @@ __global__ void __launch_bounds__(32) k_gact(GactArgs a) {
         uint32_t read = 0;
         if (L == 0) read = atomicAdd(a.work_counter, 1u);
         read = __shfl_sync(0xFFFFFFFFu, read, 0);
+        if (a.n_dev) {                                           /* list mode: the reads queued by k_gact_bp */
+            const uint32_t cnt = *a.n_dev;
+            if (read >= cnt || (a.retry_mode == 1 && cnt > AS_GACT_RETRY_WARP_MAX)) break;
+            read = a.order[read];
+        }
         if (read >= a.n) break;
         const int qlen = (int)a.qlens[read];
         const int tlen = a.tlens ? (int)a.tlens[read] : qlen;
@@ -396,7 +401,7 @@ __global__ void __launch_bounds__(32) k_gact(GactArgs a) {
 template <int R>
 static int launch_gact_r(as_gpu *h, const GactArgs &a, size_t n) {
     int rc;
-    uint64_t cap = (uint64_t)h->sm_count * 32;
+    uint64_t cap = a.n_dev ? AS_GACT_RETRY_WARP_MAX : (uint64_t)h->sm_count * 32;
     unsigned grid = (unsigned)(n < cap ? n : cap);
     if constexpr (R <= 8) {
         size_t smem = (size_t)32 * a.TS * 2 + 2 * (size_t)a.TS + a.TQ + 16;
@@ -412,6 +417,38 @@ static int launch_gact_r(as_gpu *h, const GactArgs &a, size_t n) {
     h->launches++;
     AS_CUDA(cudaGetLastError());
     return AS_OK;
+}
+
+static int gact_warp_dispatch(as_gpu *h, const GactArgs &a, size_t n, uint32_t max_qlen) {
+    /* rows per lane: the whole tile when some query reaches T rows, else just enough for the longest query */
+    const int T = a.T;
+    int rows = (int)(max_qlen < (uint32_t)T ? max_qlen : (uint32_t)T);
+    int R = (rows + 31) / 32;
+    if (max_qlen >= (uint32_t)T) R = T / 32;
+    if (R < 1) R = 1;
+    /* a shorter tile buffer for short queries would not change results: T only bounds Tq/Tt */
+    switch (R) {
+    case 1: return launch_gact_r<1>(h, a, n);
+    case 2: return launch_gact_r<2>(h, a, n);
+    case 3: return launch_gact_r<3>(h, a, n);
+    case 4: return launch_gact_r<4>(h, a, n);
+    case 5: return launch_gact_r<5>(h, a, n);
+    case 6: return launch_gact_r<6>(h, a, n);
+    case 7: return launch_gact_r<7>(h, a, n);
+    case 8: return launch_gact_r<8>(h, a, n);
+    case 9: return launch_gact_r<9>(h, a, n);
+    case 10: return launch_gact_r<10>(h, a, n);
+    case 11: return launch_gact_r<11>(h, a, n);
+    case 12: return launch_gact_r<12>(h, a, n);
+    case 13: return launch_gact_r<13>(h, a, n);
+    case 14: return launch_gact_r<14>(h, a, n);
+    case 15: return launch_gact_r<15>(h, a, n);
+    default: return launch_gact_r<16>(h, a, n);
+    }
+}
+
+int as_launch_gact_warp_list(as_gpu *h, const GactArgs &a, uint32_t max_qlen) {
+    return gact_warp_dispatch(h, a, a.n, max_qlen);
 }
 
 int as_launch_gact(as_gpu *h, const as_params *p, const uint32_t *d_qpack, size_t q_wstride, const uint32_t *d_qlens,
@@ -445,32 +482,10 @@ int as_launch_gact(as_gpu *h, const as_params *p, const uint32_t *d_qpack, size_
     a.retry_list = nullptr;
     a.retry_count = nullptr;
     a.n_dev = nullptr;
+    a.retry_mode = 0;
     /* two implementations of the same tile DP: bit-parallel, one read per lane (as_gact_bp.cu) for batches that fill
      * the GPU with lanes; anti-diagonal, one read per warp (below) for small batches */
     const bool force_warp = (p->flags & AS_F_GACT_WARP) != 0, force_bp = (p->flags & AS_F_GACT_BITPAR) != 0;
     if (!force_warp && (force_bp || n >= 2048)) return as_launch_gact_bp(h, a, n, max_qlen, max_tlen);
-    /* rows per lane: the whole tile when some query reaches T rows, else just enough for the longest query */
-    int rows = (int)(max_qlen < (uint32_t)T ? max_qlen : (uint32_t)T);
-    int R = (rows + 31) / 32;
-    if (max_qlen >= (uint32_t)T) R = T / 32;
-    if (R < 1) R = 1;
-    /* a shorter tile buffer for short queries would not change results: T only bounds Tq/Tt */
-    switch (R) {
-    case 1: return launch_gact_r<1>(h, a, n);
-    case 2: return launch_gact_r<2>(h, a, n);
-    case 3: return launch_gact_r<3>(h, a, n);
-    case 4: return launch_gact_r<4>(h, a, n);
-    case 5: return launch_gact_r<5>(h, a, n);
-    case 6: return launch_gact_r<6>(h, a, n);
-    case 7: return launch_gact_r<7>(h, a, n);
-    case 8: return launch_gact_r<8>(h, a, n);
-    case 9: return launch_gact_r<9>(h, a, n);
-    case 10: return launch_gact_r<10>(h, a, n);
-    case 11: return launch_gact_r<11>(h, a, n);
-    case 12: return launch_gact_r<12>(h, a, n);
-    case 13: return launch_gact_r<13>(h, a, n);
-    case 14: return launch_gact_r<14>(h, a, n);
-    case 15: return launch_gact_r<15>(h, a, n);
-    default: return launch_gact_r<16>(h, a, n);
-    }
+    return gact_warp_dispatch(h, a, n, max_qlen);
 }

@@ -176,12 +176,17 @@ struct GactArgs {
     uint32_t *retry_list;
     unsigned int *retry_count;
     const unsigned int *n_dev;   /* non-NULL: slots [0, *n_dev) of `order` are the launch's reads (the queue above) */
+    int retry_mode;              /* launches over the queue: 1 = only when it holds at most AS_GACT_RETRY_WARP_MAX reads (the
+                                  * warp-per-read kernel: a handful of reads finish in microseconds), 2 = only when more */
 };
+#define AS_GACT_RETRY_WARP_MAX 1024u
 #define AS_GACT_BAND0 16
 
 /* bit-parallel GACT (as_gact_bp.cu): one read per lane; `a` is filled by as_launch_gact */
 int as_launch_gact_bp(as_gpu *h, GactArgs &a, size_t n, uint32_t max_qlen, uint32_t max_tlen);
 int as_gact_order_reserve(as_gpu *h, size_t n);
+/* warp-per-read GACT (as_align.cu) over the reads a.order[0 .. *a.n_dev) */
+int as_launch_gact_warp_list(as_gpu *h, const GactArgs &a, uint32_t max_qlen);
 int as_launch_myers(as_gpu *h, const uint32_t *d_qpack, size_t q_wstride, const uint32_t *d_qlens,
                     const uint32_t *d_tbase, const uint64_t *d_toff, const uint32_t *d_tlens, size_t n,
                     uint32_t max_qlen, const int32_t *d_ks, int32_t *d_dist, as_result *d_res);

@@ -556,7 +556,7 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
         if (lane == 0) base = atomicAdd(a.work_counter, 32u);
         base = __shfl_sync(0xFFFFFFFFu, base, 0);
         const size_t n_slots = a.n_dev ? (size_t)*a.n_dev : a.n;
-        if (base >= n_slots) break;
+        if (base >= n_slots || (a.retry_mode == 2 && n_slots <= AS_GACT_RETRY_WARP_MAX)) break;
         const size_t slot = (size_t)base + lane;
         bool done = slot >= n_slots;
         const size_t read = done ? 0 : (a.order ? (size_t)a.order[slot] : slot);
@@ -888,7 +888,15 @@ int as_launch_gact_bp(as_gpu *h, GactArgs &a, size_t n, uint32_t max_qlen, uint3
         b.n_dev = cnt + 5;
         b.work_counter = cnt + 6;                                 /* its policy counters: cnt + 7 .. 10, not read */
         b.band = 32;
-        return launch_bp_w<5>(h, b, n, bps, 32);
+        /* a short queue (uniform genomes: a few reads per million) goes to the warp-per-read kernel: 32 lanes on a read
+         * finish it in microseconds, where one lane of a bit-parallel warp took 0.18 ms for the same handful -- paid once per
+         * chunk of the host-buffer path.  A long queue (repeat-rich genomes) keeps the bit-parallel kernel. */
+        b.retry_mode = 2;
+        AS_TRY(launch_bp_w<5>(h, b, n, bps, 32));
+        GactArgs c = b;
+        c.retry_mode = 1;
+        c.work_counter = cnt + 11;
+        return as_launch_gact_warp_list(h, c, max_qlen);
     }
     if (words <= 5) return launch_bp_w<5>(h, a, n, bps, kb);
     if (words <= 10) return launch_bp_w<10>(h, a, n, bps, kb);

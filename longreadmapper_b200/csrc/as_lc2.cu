@@ -1,6 +1,6 @@
 /*
- * as_lc2.cu -- the deep k-mer table: the SA interval of every h2-mer, h2 chosen so that 4^h2 is about 4x the rows
- * (13 for the 4.6 Mbp genome, 16 for 3.1 Gbp), 8 bytes per entry.
+ * as_lc2.cu -- the deep k-mer table: the SA interval of every h2-mer, h2 chosen so that 4^h2 is about 4x the rows, one
+ * level more while the table stays within 4 GB (14 for the 4.6 Mbp genome, 16 for 3.1 Gbp), 8 bytes per entry.
  *
  * The reference's lchash (lchash.c:52-104) answers the last hlen = 12 bases of a seed from a 256 MiB table and walks
  * the other 8 through the FM index -- 16 dependent sector gathers on a genome where a 12-mer still has hundreds of
@@ -128,6 +128,9 @@ static int build_lc2_table(as_gpu *h) {
     int h2 = 1;
     while (h2 < 16 && (1ULL << (2 * h2)) < ix.N) h2++;           /* ceil(log4 N) */
     h2 += 1;
+    /* one level deeper while the table stays small (<= 4 GB): fewer entries of several rows, i.e. fewer seeds that need a
+     * second gather or a backward-search step (4.6 Mbp genome: h2 13 -> 14, PART 1 1.51 -> 1.27 ms per 1 M reads) */
+    if (h2 < 16 && (8ULL << (2 * (h2 + 1))) <= (4ULL << 30)) h2++;
     if (h2 > 16) h2 = 16;
     if (h->opts.lc2_hlen > 0) h2 = h->opts.lc2_hlen;
     if (h2 <= ix.hlen || h2 > 16) return AS_OK;                   /* nothing deeper than the reference's table to offer */

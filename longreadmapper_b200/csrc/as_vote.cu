@@ -1031,11 +1031,13 @@ int as_launch_vote(as_gpu *h, const as_params *p, const uint32_t *d_pack, size_t
     size_t big_warps = budget / big_stride;
     /* one warp per queued read.  The pass is latency-bound (a located row and a compare-and-swap per vote), so its time
      * falls with the warps in flight -- as long as their tables stay in L2: 16 warps per SM on 8192-slot tables (465 MB) ran
-     * SLOWER than 4 (c2r: 38 vs 29 ms).  Up to 8 warps per SM within 96 MB of tables */
-    if (big_warps > (size_t)h->sm_count * 8) big_warps = (size_t)h->sm_count * 8;
+     * SLOWER than 4 (c2r: 38 vs 29 ms).  Short reads: up to 8 warps per SM within 96 MB of tables; long reads (tables of
+     * megabytes each): 4 per SM within the 2 GB budget, as before */
     {
         const size_t l2_warps = ((size_t)96 << 20) / big_stride;
-        if (big_warps > l2_warps) big_warps = l2_warps > (size_t)h->sm_count ? l2_warps : (size_t)h->sm_count;
+        size_t cap = (size_t)h->sm_count * 4;
+        if (l2_warps >= (size_t)h->sm_count) cap = l2_warps < (size_t)h->sm_count * 8 ? l2_warps : (size_t)h->sm_count * 8;
+        if (big_warps > cap) big_warps = cap;
     }
     if (big_warps > n) big_warps = n;
     if (big_warps < 1) big_warps = 1;
@@ -1079,7 +1081,10 @@ int as_launch_vote(as_gpu *h, const as_params *p, const uint32_t *d_pack, size_t
      * Applies when every phase has at most VT_M seeds, the words a seed can touch fit the shared-memory row, and the table
      * (deep or 12-mer) is not longer than the seed (counters: [3] work counter of the list pass, [4] length of the list) */
     const bool thread_ok = sl >= (a.use2 ? h->ix.hlen2 : h->ix.hlen) && seeds_per_phase <= VT_M && sl < 32 && max_len > (uint32_t)sl &&
-                           ((max_len - (uint32_t)sl - 1u) >> 4) + 3u <= (uint32_t)VT_W && p->vote_thread != 0;
+                           ((max_len - (uint32_t)sl - 1u) >> 4) + 3u <= (uint32_t)VT_W &&
+                           /* default: indexes of one super block.  At human scale PART 1 runs at the DRAM's random-gather rate
+                            * in either kernel (c4: 33.7 ms here, 32.6 ms in the group kernel) */
+                           (p->vote_thread > 0 || (p->vote_thread < 0 && small));
     if (thread_ok) {
         AS_TRY(as_scratch(h, &h->vote_dlist, n * sizeof(uint32_t)));
         a.dlist = (uint32_t *)h->vote_dlist.p;

@@ -173,7 +173,7 @@ def test_vote_thread_kernel_equals_group_kernel(native, idx_repeat, idx_high_cop
                 reads, lens, _ = reads_from(native, seed + k, gs, 250, lmin, lmax, e, e, 0.7)
                 m.stats_reset()
                 l0 = m.launch_count()
-                check_vote(m, ix, reads, lens, sl, th, flags=wide)
+                check_vote(m, ix, reads, lens, sl, th, flags=wide, vote_thread=1)     # 1: also on the 64-bit path (default: small indexes)
                 d_thread = m.launch_count() - l0            # pack, k_vote_t, group kernel over the queue, overflow pass
                 assert m.stats()["vote_deferred"] < len(lens)
                 l0 = m.launch_count()
@@ -181,7 +181,7 @@ def test_vote_thread_kernel_equals_group_kernel(native, idx_repeat, idx_high_cop
                 assert d_thread == m.launch_count() - l0 + 1, "the thread-per-read kernel did not run"
             reads, lens, _ = reads_from(native, seed + 50, gs, 20000, 150, 150, 0.02, 0.02, 0.8)
             m.stats_reset()
-            a = m.vote_batch(reads, lens, m.params(flags=wide))
+            a = m.vote_batch(reads, lens, m.params(flags=wide, vote_thread=1))
             st = m.stats()
             b = m.vote_batch(reads, lens, m.params(flags=wide, vote_thread=0))
             for x, y in zip(a, b):

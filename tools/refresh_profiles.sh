@@ -7,6 +7,8 @@ mkdir -p $O
 python -m pytest tests -m gpu -q 2>&1 | tail -4 > $O/${T}_gputests.txt
 python bench.py > $O/${T}_bench.json 2> $O/${T}_bench.err
 python bench.py --impl reference --steps 2 --warmup 1 > $O/${T}_bench_reference_arm.json 2> $O/${T}_ref.err
+python bench.py --no-cpu --no-program --workload c2r > $O/${T}_bench_c2r_repeat_rich.json 2>> $O/${T}_bench.err
+tools/gather_probe 8 > $O/${T}_gather_probe.txt 2>&1
 python bench.py --no-cpu --no-program --workload c3 --reads 20000 > $O/${T}_bench_c3_20k.json 2>> $O/${T}_bench.err
 python bench.py --no-cpu --no-program --workload c3 --steps 3 > $O/${T}_bench_c3_full.json 2>> $O/${T}_bench.err
 python bench.py --no-cpu --no-program --workload c5 --steps 2 --warmup 1 > $O/${T}_bench_c5_1gpu.json 2>> $O/${T}_bench.err
@@ -16,6 +18,6 @@ python bench.py --no-cpu --no-program --no-e2e --steps 2 --warmup 1 > $O/${T}_pl
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${T}_launches.csv \
     python bench.py --no-cpu --no-program --no-e2e --steps 2 --warmup 1 > $O/${T}_ncu_list.log 2>&1
 python bench.py --no-cpu --no-e2e --no-program --steps 1 --warmup 1 > $O/${T}_plain2.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:'k_vote|k_gact_bp' -c 3 -o $O/${T}_full -f \
+ncu --set full --clock-control none --import-source on -k regex:'k_vote|k_gact_bp' -c 5 -o $O/${T}_full -f \
     python bench.py --no-cpu --no-e2e --no-program --steps 1 --warmup 1 > $O/${T}_ncu_full.log 2>&1
 ls -la $O | tail -14
