@@ -291,6 +291,22 @@ int as_cigar_align_batch(as_gpu *h, const as_params *p, const char *q, size_t q_
 int as_edit_distance_batch(as_gpu *h, const char *q, size_t q_stride, const uint32_t *qlens,
                            const char *t, size_t t_stride, const uint32_t *tlens, size_t n,
                            const int32_t *ks, int32_t *dist);
+/* The same distances (the same kernel) for callers that cannot allocate -- code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc.  NO COUNTERPART IN THE REFERENCE.
+ * Needs no handle and calls no cudaMalloc / cudaFree / allocating routine: the scratch the batched entry takes from the
+ * handle (2-bit packed sequences, offsets, checked lengths) is one file-scope device array of fixed size (~5.8 MB that every
+ * GPU loading the library holds until exit).  Limits: n <= AS_NOALLOC_MAX_PAIRS (more: AS_ERANGE, nothing launched), every
+ * length <= AS_NOALLOC_MAX_LEN (a pair beyond it gets dist[i] = AS_ERANGE).  All pointers are DEVICE addresses on the current
+ * device (q / t: ASCII rows as in as_edit_distance_batch, inside allocations that start and end on 4-byte boundaries; d_ks
+ * may be NULL); the work is only enqueued on `cuda_stream` (a cudaStream_t, NULL = the default stream) -- synchronise it
+ * before reading d_dist.  Every call shares the one array, which keeps the last call's contents: calls that overlap on the
+ * GPU (two streams, two threads) race; calls on one stream, or otherwise ordered, do not.  The first call on a device
+ * resolves the array's device address (cudaGetSymbolAddress), so make one call before starting a graph capture. */
+#define AS_NOALLOC_MAX_PAIRS 32768
+#define AS_NOALLOC_MAX_LEN   256
+int as_edit_distance_device_noalloc(void *cuda_stream, const char *d_q, size_t q_stride, const uint32_t *d_qlens,
+                                    const char *d_t, size_t t_stride, const uint32_t *d_tlens, size_t n,
+                                    const int32_t *d_ks, int32_t *d_dist);
 
 /* pinned host memory helpers */
 void *as_host_alloc(size_t bytes);

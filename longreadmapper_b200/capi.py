@@ -135,6 +135,8 @@ def cuda_lib():
     L.as_vote_batch.argtypes = [vp, C.POINTER(Params), vp, sz, vp, sz, vp, vp, vp, vp]
     L.as_cigar_align_batch.argtypes = [vp, C.POINTER(Params), vp, sz, vp, vp, sz, vp, sz, vp, sz, vp, vp]
     L.as_edit_distance_batch.argtypes = [vp, vp, sz, vp, vp, sz, vp, sz, vp, vp]
+    L.as_edit_distance_device_noalloc.argtypes = [vp, vp, sz, vp, vp, sz, vp, sz, vp, vp]
+    L.as_edit_distance_device_noalloc.restype = C.c_int
     L.as_host_alloc.argtypes = [sz]
     L.as_host_alloc.restype = vp
     L.as_host_free.argtypes = [vp]

@@ -260,3 +260,100 @@ int as_launch_myers(as_gpu *h, const uint32_t *d_qpack, size_t q_wstride, const 
     AS_CUDA(cudaGetLastError());
     return AS_OK;
 }
+
+/* ------------------------------------------------------------------------------------------------------------------------
+ * as_edit_distance_device_noalloc: k_myers_short for callers that cannot allocate (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * The scratch as_edit_distance_batch takes from the handle's growable buffers -- the 2-bit packed queries and
+ * targets, the targets' base offsets, the checked lengths -- lives in ONE file-scope device array of fixed size, so the call
+ * allocates nothing: AS_NOALLOC_MAX_PAIRS pairs of at most AS_NOALLOC_MAX_LEN bases each, ~5.8 MB held by every GPU that
+ * loads the library until the process exits.  Every call shares the array (it keeps the last call's contents; nothing in it
+ * has to start at zero, every word a call reads it has written first), so calls that overlap on the GPU race.
+ * ---------------------------------------------------------------------------------------------------------------------- */
+#define NA_WS ((AS_NOALLOC_MAX_LEN + 15) / 16 + 4)          /* packed words per sequence, with the readers' slack */
+struct NoallocScratch {
+    uint32_t qpack[(size_t)AS_NOALLOC_MAX_PAIRS * NA_WS];
+    uint32_t tpack[(size_t)AS_NOALLOC_MAX_PAIRS * NA_WS];
+    unsigned long long toff[AS_NOALLOC_MAX_PAIRS];
+    uint32_t qlens[AS_NOALLOC_MAX_PAIRS];
+    uint32_t tlens[AS_NOALLOC_MAX_PAIRS];
+    uint32_t bad[AS_NOALLOC_MAX_PAIRS];                      /* 1: a length of the pair exceeds AS_NOALLOC_MAX_LEN */
+};
+static __device__ __align__(256) NoallocScratch g_noalloc_scratch;
+
+/* thread per packed word: word w of pair i of the queries (z == 0) or the targets (z == 1) */
+__global__ void __launch_bounds__(256) k_noalloc_pack(const char *__restrict__ q, size_t q_stride, const uint32_t *__restrict__ qlens,
+                                                      const char *__restrict__ t, size_t t_stride, const uint32_t *__restrict__ tlens,
+                                                      size_t n, NoallocScratch *s) {
+    const size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (idx >= n * NA_WS) return;
+    const size_t i = idx / NA_WS;
+    const uint32_t w = (uint32_t)(idx - i * NA_WS);
+    const uint32_t ql = qlens[i], tl = tlens[i];
+    const bool bad = ql > AS_NOALLOC_MAX_LEN || tl > AS_NOALLOC_MAX_LEN;
+    if (w == 0) {
+        s->qlens[i] = bad ? 0u : ql;
+        s->tlens[i] = bad ? 0u : tl;
+        s->bad[i] = bad ? 1u : 0u;
+        s->toff[i] = (unsigned long long)i * (16ull * NA_WS);
+    }
+    uint32_t vq = 0, vt = 0;
+    if (!bad && 16u * w < ql) vq = as_pack16(reinterpret_cast<const uint8_t *>(q) + i * q_stride + 16u * w, min(16u, ql - 16u * w));
+    if (!bad && 16u * w < tl) vt = as_pack16(reinterpret_cast<const uint8_t *>(t) + i * t_stride + 16u * w, min(16u, tl - 16u * w));
+    s->qpack[idx] = vq;
+    s->tpack[idx] = vt;
+}
+
+__global__ void __launch_bounds__(256) k_noalloc_flag(const NoallocScratch *s, size_t n, int32_t *__restrict__ dist) {
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i < n && s->bad[i]) dist[i] = AS_ERANGE;
+}
+
+extern "C" int as_edit_distance_device_noalloc(void *cuda_stream, const char *d_q, size_t q_stride, const uint32_t *d_qlens,
+                                               const char *d_t, size_t t_stride, const uint32_t *d_tlens, size_t n,
+                                               const int32_t *d_ks, int32_t *d_dist) {
+    /* per device: the array's DEVICE address (its name is a host-side stand-in in host code) and the SM count */
+    static NoallocScratch *s_ptr[64];
+    static int s_sm[64];
+    if (!d_q || !d_t || !d_qlens || !d_tlens || !d_dist) return AS_EINVAL;
+    if (n > AS_NOALLOC_MAX_PAIRS) {
+        as_set_error("as_edit_distance_device_noalloc: %zu pairs; the static scratch holds at most %d (of at most %d bases each)", n,
+                     AS_NOALLOC_MAX_PAIRS, AS_NOALLOC_MAX_LEN);
+        return AS_ERANGE;
+    }
+    if (q_stride < 1 || t_stride < 1) return AS_EINVAL;
+    int dev = -1;
+    AS_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return AS_EINVAL;
+    if (!s_ptr[dev]) {                   /* set-up, once per device, with that device current */
+        int major = 0, sm = 0;
+        AS_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+        if (major != 10) {
+            as_set_error("as_edit_distance_device_noalloc: device %d is not sm_100 (no CPU fallback)", dev);
+            return AS_ENODEV;
+        }
+        AS_CUDA(cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev));
+        NoallocScratch *p = nullptr;
+        AS_CUDA(cudaGetSymbolAddress((void **)&p, g_noalloc_scratch));
+        s_sm[dev] = sm;
+        s_ptr[dev] = p;
+    }
+    if (n == 0) return AS_OK;
+    NoallocScratch *s = s_ptr[dev];
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    const size_t words = n * NA_WS;
+    k_noalloc_pack<<<(unsigned)((words + 255) / 256), 256, 0, st>>>(d_q, q_stride, d_qlens, d_t, t_stride, d_tlens, n, s);
+    AS_CUDA(cudaGetLastError());
+    MyersArgs a;
+    a.qpack = s->qpack; a.q_wstride = NA_WS; a.qlens = s->qlens;
+    a.tbase = s->tpack; a.toff = (const uint64_t *)s->toff; a.tlens = s->tlens; a.n = n;
+    a.ks = d_ks; a.k_from_len = 0;
+    a.dist = d_dist; a.res = nullptr;
+    a.work_counter = nullptr;            /* k_myers_short takes a grid-stride loop, no work counter */
+    const uint64_t blocks = (n + 127) / 128, cap = (uint64_t)s_sm[dev] * 16;
+    k_myers_short<<<(unsigned)(blocks < cap ? blocks : cap), 128, 0, st>>>(a);
+    AS_CUDA(cudaGetLastError());
+    k_noalloc_flag<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(s, n, d_dist);
+    AS_CUDA(cudaGetLastError());
+    return AS_OK;
+}
