@@ -134,6 +134,8 @@ typedef struct as_params {
     int32_t  vote_thread;         /* PART 1 of short reads (<= 8 seeds per phase) by the thread-per-read kernel, the rest by the
                                    * group kernel: -1 = when it applies and the index has at most 2^30 rows (default), 0 = group
                                    * kernel only, 1 = whenever it applies */
+    int32_t  gact_runs;           /* as_map_batch_packed: one-tile reads leave their run bytes straight from GACT's traceback
+                                   * (no op bytes, no run-length pass): -1 / 1 = on (default), 0 = off */
 } as_params;
 #define AS_F_MYERS        1u   /* also run the edlib-equivalent NW distance with k=(int)(0.05*len*2) per read */
 #define AS_F_NO_ALIGN     2u   /* stop after PART 1+2 (no GACT): results carry loc/off/strand/flag only */

@@ -483,6 +483,8 @@ int as_launch_gact(as_gpu *h, const as_params *p, const uint32_t *d_qpack, size_
     a.retry_count = nullptr;
     a.n_dev = nullptr;
     a.retry_mode = 0;
+    a.emit_runs = h->gact_emit_runs ? 1 : 0;
+    h->gact_emit_runs = false;
     /* two implementations of the same tile DP: bit-parallel, one read per lane (as_gact_bp.cu) for batches that fill
      * the GPU with lanes; anti-diagonal, one read per warp (below) for small batches */
     const bool force_warp = (p->flags & AS_F_GACT_WARP) != 0, force_bp = (p->flags & AS_F_GACT_BITPAR) != 0;

@@ -26,6 +26,7 @@ extern "C" void as_params_default(as_params *p) {
     p->chunk_reads = 0;
     p->chunk_tail = -1;
     p->vote_thread = -1;
+    p->gact_runs = -1;
 }
 
 __global__ void k_rle_ops(uint8_t *__restrict__ ops, size_t stride, as_result *__restrict__ res, size_t n);
@@ -67,7 +68,11 @@ static int run_stages(as_gpu *h, const as_params *p, char *d_reads, size_t strid
     AS_CUDA(cudaEventRecord(ev[2], h->stream));
     /* columns past n_cigar_op stay zero in DEVICE storage, so equal inputs give equal bytes whatever ran before
      * (the reference leaves them uninitialised, alnmain.c:316-320) */
-    if (!(p->flags & AS_F_NO_ALIGN) && d_store) AS_CUDA(cudaMemsetAsync(d_store, 0, n * store_stride, h->stream));
+    /* packed path (the caller reads nothing but the run bytes): one-tile reads leave run bytes straight from GACT's traceback
+     * events, every other path writes all the columns it reports -- nothing reads a byte it did not write, no clearing */
+    const bool emit_runs = d_packed_in && (p->flags & AS_F_RLE_CIGAR) && d_store && !(p->flags & AS_F_NO_ALIGN) && p->gact_runs != 0;
+    if (!(p->flags & AS_F_NO_ALIGN) && d_store && !emit_runs) AS_CUDA(cudaMemsetAsync(d_store, 0, n * store_stride, h->stream));
+    h->gact_emit_runs = emit_runs;
     if (!(p->flags & AS_F_NO_ALIGN))
         AS_TRY(as_launch_gact(h, p, d_pack, ws, d_lens, h->ix.text2, d_toff, nullptr, n, max_len, max_len, d_store,
                               store_stride, nullptr, nullptr, d_res));
@@ -102,6 +107,10 @@ __global__ void __launch_bounds__(256) k_rle_ops(uint8_t *__restrict__ ops, size
     for (size_t r = (size_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (size_t)gridDim.x * blockDim.x) {
         const int nops = res[r].n_cigar_op;
         if (nops <= 0) continue;
+        if (nops & AS_NOPS_RUNS) {                 /* GACT wrote the run bytes itself (GactArgs.emit_runs) */
+            res[r].n_cigar_op = nops & ~AS_NOPS_RUNS;
+            continue;
+        }
         uint8_t *row = ops + r * stride;
         int out = 0, open_cls = -1, open_len = 0;
         for (int base = 0; base < nops; base += 4) {
@@ -146,6 +155,10 @@ __global__ void __launch_bounds__(256) k_rle_ops_warp(uint8_t *__restrict__ ops,
     for (size_t r = warp0; r < n; r += nwarps) {
         const int nops = res[r].n_cigar_op;
         if (nops <= 0) continue;
+        if (nops & AS_NOPS_RUNS) {
+            if (lane == 0) res[r].n_cigar_op = nops & ~AS_NOPS_RUNS;
+            continue;
+        }
         uint8_t *row = ops + r * stride;
         int out = 0, open_cls = -1, open_len = 0;
         for (int base = 0; base < nops; base += 32) {

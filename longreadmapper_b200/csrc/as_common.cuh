@@ -69,6 +69,7 @@ struct as_gpu {
     ScratchBuf reads, lens, results, store, qpack, tpack, toff, vote, counters, ovf_list, ovf_table, misc[6];
     ScratchBuf gact_planes, gact_tb;     /* bit-parallel GACT: traceback planes / packed tile ops, per resident warp */
     ScratchBuf gact_order;               /* bit-parallel GACT: reads by decreasing length (multi-tile batches) */
+    bool gact_emit_runs = false;         /* run_stages -> as_launch_gact: the caller only reads run bytes (AS_F_RLE_CIGAR, dense gather) */
     ScratchBuf vote_dlist;               /* PART 1: reads the thread-per-read kernel deferred to the group kernel */
     ScratchBuf gact_retry;               /* bit-parallel GACT: one-tile reads the one-word diagonal band could not prove exact */
     ScratchBuf locus_tmp;                /* packed-only long reads: one scratch row per warp for the reverse complement */
@@ -176,10 +177,13 @@ struct GactArgs {
     uint32_t *retry_list;
     unsigned int *retry_count;
     const unsigned int *n_dev;   /* non-NULL: slots [0, *n_dev) of `order` are the launch's reads (the queue above) */
+    int emit_runs;               /* one-tile reads of the short-read kernels leave their CIGAR as RUN BYTES (k_rle_ops' format)
+                                  * at the start of their row and n_cigar_op = runs | AS_NOPS_RUNS; the rows need no clearing */
     int retry_mode;              /* launches over the queue: 1 = only when it holds at most AS_GACT_RETRY_WARP_MAX reads (the
                                   * warp-per-read kernel: a handful of reads finish in microseconds), 2 = only when more */
 };
 #define AS_GACT_RETRY_WARP_MAX 1024u
+#define AS_NOPS_RUNS 0x40000000      /* as_result.n_cigar_op on the device, between GACT and k_rle_ops: the row already holds run bytes */
 #define AS_GACT_BAND0 16
 
 /* bit-parallel GACT (as_gact_bp.cu): one read per lane; `a` is filled by as_launch_gact */

@@ -579,6 +579,7 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
         const uint32_t omis = (uint32_t)(reinterpret_cast<uintptr_t>(ops) & 3u);
         uint32_t oacc = 0;
         bool by_events = false;          /* the read's ops were placed as events: no partial word is pending */
+        int n_runs_out = -1;             /* emit_runs: run bytes written | AS_NOPS_RUNS */
         if (!done && qlen == 0 && tlen == 0) done = true;
 
         while (__any_sync(0xFFFFFFFFu, !done)) {
@@ -660,7 +661,42 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
                 else mym = o.m;
             }
             if (fast) by_events = true;
-            if (W <= 5 && a.ops && fast) {
+            if (W <= 5 && a.ops && fast && a.emit_runs) {
+                /* the caller wants run bytes (k_rle_ops' format: (len << 2) | class, class 0 M for '=' and 'X', 1 I, 2 D, runs
+                 * of more than 63 continue in the next byte): the events ARE the run boundaries, so the lane writes the few
+                 * bytes of its read directly -- no cleared row, no op bytes, no second pass over them.  Events are in walk
+                 * order (last column first): taken from the back they run forward along the row. */
+                if (mym > 0) {
+                    int out = 0, cur = 0, e = n_events - 1;
+                    auto emit = [&](int len, uint32_t cls) {
+                        while (len > 0) {
+                            const int l = len > 63 ? 63 : len;
+                            if ((size_t)out < a.ops_stride) ops[out] = (uint8_t)(((uint32_t)l << 2) | cls);
+                            out++;
+                            len -= l;
+                        }
+                    };
+                    while (e >= 0) {
+                        const uint32_t wd = tb[(size_t)e * 32];
+                        const uint32_t op = wd & 3u;
+                        if (op == 3u) { e--; continue; }                       /* 'X' is part of an M run */
+                        const int col = mym - 1 - (int)(wd >> 2);
+                        emit(col - cur, 0u);
+                        int len = 1;
+                        e--;
+                        while (e >= 0) {                                        /* the indel goes on while the class and the columns do */
+                            const uint32_t w2 = tb[(size_t)e * 32];
+                            if ((w2 & 3u) != op || mym - 1 - (int)(w2 >> 2) != col + len) break;
+                            len++;
+                            e--;
+                        }
+                        emit(len, op);
+                        cur = col + len;
+                    }
+                    emit(mym - cur, 0u);
+                    n_runs_out = out | AS_NOPS_RUNS;
+                }
+            } else if (W <= 5 && a.ops && fast) {
                 /* the row holds '=' everywhere already: place the few other ops, walk position p -> column mym-1-p */
                 const int maxe = __reduce_max_sync(0xFFFFFFFFu, mym > 0 ? n_events : 0);
                 for (int e = 0; e < maxe; e++) {
@@ -728,7 +764,7 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
             if (a.res) {                                        /* PART 3, alnmain.c:458-477 */
                 as_result *r = a.res + read;
                 r->ed = score;
-                r->n_cigar_op = n;
+                r->n_cigar_op = n_runs_out >= 0 ? n_runs_out : n;
                 if (score == -1) { r->valid = 0; r->flag = 4; r->mapq = 0; }
             }
             if (a.n_ops) a.n_ops[read] = n;

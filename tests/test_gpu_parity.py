@@ -381,6 +381,32 @@ def test_map_packed_compact_short(native, gpu_repeat, idx_repeat, chunk):
     assert h2d == len(lens) * (4 * ((int(lens.max()) + 15) // 16) + 4) and d2h < len(lens) * 16 + dense.size + 1024
 
 
+@pytest.mark.parametrize("knobs", [dict(), dict(gact_runs=0), dict(chunk_reads=3000), dict(T=64, O=24), dict(band=-1)])
+def test_map_packed_runs_straight_from_gact(native, gpu_repeat, idx_repeat, knobs):
+    """Reads of one tile in the short-read kernels (<= 160 bases) leave their run bytes straight from GACT's traceback events
+    (GactArgs.emit_runs: no op bytes, no cleared rows, no run-length pass); the reads the one-word band cannot prove exact go
+    through the retry queue (a few: warp-per-read kernel; many: bit-parallel), and with T = 64 most reads take several tiles
+    and keep the op-byte path.  Run bytes and records equal as_map_batch's AS_F_RLE_CIGAR rows in every case, also with the
+    direct path switched off (gact_runs = 0) -- including indel runs next to substitutions and runs longer than 63 columns."""
+    ix, gs = idx_repeat
+    tk = {k: knobs[k] for k in ("T", "O", "band") if k in knobs}
+    kn = {k: v for k, v in knobs.items() if k not in tk}
+    for seed, (lmin, lmax, emin, emax, sub) in enumerate([(30, 150, 0.0, 0.03, 0.5), (100, 160, 0.05, 0.15, 0.34), (150, 150, 0.0, 0.0, 1.0)]):
+        reads, lens, _ = reads_from(native, 660 + seed, gs, 2200, lmin, lmax, emin, emax, sub)
+        flags = native.AS_F_RLE_CIGAR | native.AS_F_KEEP_READS
+        full, rows = gpu_repeat.map_batch(reads.copy(), lens, params=gpu_repeat.params(flags=flags, **tk))
+        rec, dense = gpu_repeat.map_batch_packed(native.pack_reads(reads, lens), lens, params=gpu_repeat.params(**tk, **kn))
+        mapped = full["seq_id"] >= 0
+        want_n = np.where(mapped, np.maximum(full["n_cigar_op"], 0), 0)
+        n_runs = (rec["n_runs"] & 0x07FFFFFF).astype(np.int64)
+        assert np.array_equal(n_runs, want_n)
+        assert np.array_equal(rec["ed"], full["ed"])
+        offs = np.concatenate([[0], np.cumsum(n_runs)])
+        assert offs[-1] == dense.size
+        for i in range(len(lens)):
+            assert np.array_equal(dense[offs[i]:offs[i + 1]], rows[i, : want_n[i]]), (seed, i)
+
+
 def test_map_packed_compact_long_and_edge(native, gpu_repeat, idx_repeat):
     """reads of several tiles (packed reverse complement through the per-warp scratch row), reads with a byte outside ACGT,
     reads that fail seq_lookup, a one-read batch, a too-small runs buffer"""
