@@ -234,6 +234,30 @@ __device__ __forceinline__ void tile_diag1(const TileGeom &g, uint2 *__restrict_
             load_qword(g.qp, g.i0, w0 + 1, Tq, qlo_b, qhi_b);
         }
         uint32_t *pc = planes + (size_t)(j0 - 1) * 32;
+        /* a whole target word of 16 columns that every lane of the warp still needs (all but the first and the last chunk of
+         * a warp of equally long reads): fully unrolled, the window's position inside the query words is a constant (0 or 16
+         * plus the column), no per-column length test, store offsets are immediates */
+        if (jend - j0 == 15 && (sh & 15u) == 0 && __all_sync(0xFFFFFFFFu, jend <= Tt)) {
+            const bool act = true;
+            if (sh == 0) {
+#pragma unroll
+                for (int c = 0; c < 16; c++) {
+                    Pv = __funnelshift_r(Pv, 1u, 1u);
+                    Mv >>= 1;
+                    const uint32_t ql = c ? __funnelshift_r(qlo_a, qlo_b, c) : qlo_a, qh = c ? __funnelshift_r(qhi_a, qhi_b, c) : qhi_a;
+                    DIAG1_STEP(ql, qh, 8u, pc + 32 * c);
+                }
+            } else {
+#pragma unroll
+                for (int c = 0; c < 16; c++) {
+                    Pv = __funnelshift_r(Pv, 1u, 1u);
+                    Mv >>= 1;
+                    const uint32_t ql = __funnelshift_r(qlo_a, qlo_b, 16 + c), qh = __funnelshift_r(qhi_a, qhi_b, 16 + c);
+                    DIAG1_STEP(ql, qh, 8u, pc + 32 * c);
+                }
+            }
+            continue;
+        }
 #pragma unroll 4
         for (int j = j0; j <= jend; j++, sh++, pc += 32) {
             const bool act = j <= Tt;
@@ -263,7 +287,9 @@ __device__ __forceinline__ void tile_diag1(const TileGeom &g, uint2 *__restrict_
         }
         const int K = (ci > 0 && cj > 0) ? min(min(ci, cj), BP_FW) : 0;
         const int dv = ci - cj + 8;
-        uint32_t mx = 0, mi = 0, ml = 0;                     /* bit k: cell k of the round is X / an indel / has its low plane set */
+        /* bit k of the low half of acc = low op-code plane of cell k of the round, bit 16 + k = high plane: a cell costs a
+         * load, a shift, an AND and a multiply-add (the two fields grow side by side, 16 cells fill them exactly) */
+        uint32_t acc = 0;
         /* warp-uniform choice: the one-bit-position loop unless some lane's round reaches into the first 16 columns */
         if (!__any_sync(0xFFFFFFFFu, K > 0 && cj - K < 16)) {
             const uint32_t *pb = planes + (ptrdiff_t)(cj - 1) * 32;
@@ -271,10 +297,7 @@ __device__ __forceinline__ void tile_diag1(const TileGeom &g, uint2 *__restrict_
             for (int k = BP_FW - 1; k >= 0; k--) {
                 uint32_t u = 0;
                 if (k < K) u = pb[-k * 32] >> dv;
-                const uint32_t t = u >> 16;
-                mx = mx * 2u + (u & t & 1u);
-                mi = mi * 2u + ((u ^ t) & 1u);
-                ml = ml * 2u + (u & 1u);
+                acc = acc * 2u + (u & 0x00010001u);
             }
         } else {
 #pragma unroll
@@ -285,12 +308,11 @@ __device__ __forceinline__ void tile_diag1(const TileGeom &g, uint2 *__restrict_
                     const int bb = c2 >= 17 ? dv : (ci - k) - 1 - max(0, c2 - 9);
                     u = planes[(size_t)(c2 - 1) * 32] >> bb;
                 }
-                const uint32_t t = u >> 16;
-                mx = mx * 2u + (u & t & 1u);
-                mi = mi * 2u + ((u ^ t) & 1u);
-                ml = ml * 2u + (u & 1u);
+                acc = acc * 2u + (u & 0x00010001u);
             }
         }
+        const uint32_t ml = acc & 0xFFFFu, mh = acc >> 16;    /* bit k: cell k has its low / high plane set */
+        const uint32_t mx = ml & mh, mi = ml ^ mh;            /* X (both planes) / an indel (one plane) */
         const int run = __ffs((int)(mi | (1u << K))) - 1;    /* cells before the first indel (or the end of the round) */
         uint32_t xs = mx & ((1u << run) - 1u);
         while (xs) {                                         /* substitutions on the way, in walk order */
