@@ -172,10 +172,11 @@ __device__ __forceinline__ void fast_walk(const TileGeom &g, const uint2 *__rest
  * Half the words of the two-word band, and bit b of a word is the DIAGONAL i - j + BP_DC of the sliding part, which is what
  * the run-skipping walk follows.
  *
- * Planes: only the 16 diagonals around the main one are KEPT -- bits [s(j), s(j) + 16) of both op-code planes, s(j) =
- * clamp(j - top(j) - 8, 0, 16), one 32-bit word per column and lane ([column][lane]): 19 KB per warp for 150-bp reads, so
- * the slabs of all resident warps (80 MB) stay in the 126 MB L2 and the walk never waits for DRAM.  A walk that needs a
- * diagonal outside the kept 16 (more than seven net indels) is flagged like one that leaves the band.
+ * Planes: only the 16 diagonals around the main one are KEPT -- bits [s(j), s(j) + 16) of Pv' (low half) and of ~D0 (high
+ * half), s(j) = clamp(j - top(j) - 8, 0, 16), one 32-bit word per column and lane ([column][lane]): 19 KB per warp for
+ * 150-bp reads, so the slabs of all resident warps (80 MB) stay in the 126 MB L2.  The op codes themselves are not formed in
+ * the fill: the walk finds the '=' runs from the sequences and reads a word only at a mismatch, where (Pv', ~D0) is the op.
+ * A walk that needs a diagonal outside the kept 16 (more than seven net indels) is flagged like one that leaves the band.
  */
 __device__ __forceinline__ int diag1_top(int j) { return j - BP_DC > 1 ? j - BP_DC : 1; }
 __device__ __forceinline__ int diag1_s(int j) {               /* first kept bit of column j's word */
@@ -193,7 +194,7 @@ __device__ __forceinline__ void tile_diag1(const TileGeom &g, uint2 *__restrict_
     load_qword(g.qp, g.i0, 1, Tq, qlo_b, qhi_b);
     uint32_t Pv = 0xFFFFFFFFu, Mv = 0u, tw = 0;
     /* one column: the Myers/Hyyro step on the window (ql, qh = the query planes of its 32 rows), the kept 16 diagonals of
-     * the two op-code planes stored as one word.  (x << 1) | 1 and x << 1 are written as multiply-adds: they go to the FMA
+     * Pv' and ~D0 stored as one word.  (x << 1) | 1 and x << 1 are written as multiply-adds: they go to the FMA
      * pipe, which idles while the ALU pipe carries the logic ops. */
 #define DIAG1_STEP(QL, QH, SS, PDST)                                                                   \
     do {                                                                                               \
@@ -208,42 +209,54 @@ __device__ __forceinline__ void tile_diag1(const TileGeom &g, uint2 *__restrict_
         const uint32_t npv_ = mh_ | ~(xv_ | ph_);                                                      \
         Mv = ph_ & xv_;                                                                                \
         Pv = npv_;                                                                                     \
-        if (act) *(PDST) = (SS) == 8u ? __byte_perm(~eq_ & (npv_ | nd0_), ~eq_ & (~npv_ | nd0_), 0x6521)          \
-                                      : __byte_perm((~eq_ & (npv_ | nd0_)) >> (SS), (~eq_ & (~npv_ | nd0_)) >> (SS), 0x5410); \
+        if (act) *(PDST) = (SS) == 8u ? __byte_perm(npv_, nd0_, 0x6521) : __byte_perm(npv_ >> (SS), nd0_ >> (SS), 0x5410); \
     } while (0)
-    /* ---- columns 1 .. 17: the window stands on rows 1 .. 32 ---- */
-    const int jA = g.maxTt < BP_DC + 1 ? g.maxTt : BP_DC + 1;
-    for (int j = 1; j <= jA; j++) {
-        const bool act = j <= Tt;
-        if (act && ((j - 1) & 15) == 0) tw = as_bases16(g.tbase, g.toff + (uint64_t)(g.j0 + j - 1));
-        const uint32_t ss = (uint32_t)(j - 9 > 0 ? j - 9 : 0);        /* diag1_s(j) for top(j) = 1 */
-        uint32_t pv0 = Pv, mv0 = Mv;
-        DIAG1_STEP(qlo_a, qhi_a, ss, planes + (size_t)(j - 1) * 32);
-        if (!act) { Pv = pv0; Mv = mv0; }
+    /* ---- columns 1 .. 16: the window stands on rows 1 .. 32 (column 17 too: it opens the first 16-column chunk below).
+     * Every lane of the warp has them (done lanes ride along into their own slab words): fully unrolled, the kept
+     * diagonals' shift is an immediate ---- */
+    if (__all_sync(0xFFFFFFFFu, g.done || Tt >= 16)) {
+        const bool act = true;
+        if (!g.done) tw = as_bases16(g.tbase, g.toff + (uint64_t)g.j0);
+#pragma unroll
+        for (int c = 0; c < 16; c++) DIAG1_STEP(qlo_a, qhi_a, (uint32_t)(c > 8 ? c - 8 : 0), planes + 32 * c);
+    } else {
+        const int jA = g.maxTt < 16 ? g.maxTt : 16;
+        for (int j = 1; j <= jA; j++) {
+            const bool act = j <= Tt;
+            if (act && j == 1) tw = as_bases16(g.tbase, g.toff + (uint64_t)g.j0);
+            const uint32_t ss = (uint32_t)(j - 9 > 0 ? j - 9 : 0);        /* diag1_s(j) for top(j) = 1 */
+            uint32_t pv0 = Pv, mv0 = Mv;
+            DIAG1_STEP(qlo_a, qhi_a, ss, planes + (size_t)(j - 1) * 32);
+            if (!act) { Pv = pv0; Mv = mv0; }
+        }
     }
-    /* ---- columns 18 ..: the window moves down one row per column; 16 columns per target word, the query words change
-     * every 32 columns, on a target-word boundary (column 49, 81, ...) ---- */
-    for (int j0 = BP_DC + 2; j0 <= g.maxTt; j0 = ((j0 - 1) | 15) + 2) {
-        const int jend = ((j0 - 1) | 15) + 1 < g.maxTt ? ((j0 - 1) | 15) + 1 : g.maxTt;     /* last column of this target word */
-        if (j0 <= Tt && ((j0 - 1) & 15) == 0) tw = as_bases16(g.tbase, g.toff + (uint64_t)(g.j0 + j0 - 1));
+    /* ---- columns 17 ..: 16 columns per target word.  Column 17 still stands on rows 1 .. 32 (its kept bits start at 8, like
+     * every later column's); from column 18 on the window moves down one row per column; the query words change every 32
+     * columns, on a target-word boundary (column 49, 81, ...) ---- */
+    for (int j0 = BP_DC + 1; j0 <= g.maxTt; j0 += 16) {
+        const int jend = j0 + 15 < g.maxTt ? j0 + 15 : g.maxTt;              /* last column of this target word */
+        const bool first = j0 == BP_DC + 1;
+        if (j0 <= Tt) tw = as_bases16(g.tbase, g.toff + (uint64_t)(g.j0 + j0 - 1));
         uint32_t sh = (uint32_t)(j0 - (BP_DC + 1)) & 31u;              /* window start inside query word a, this column */
-        if (sh == 0) {                                                 /* crossed into the next query word */
+        if (sh == 0 && !first) {                                       /* crossed into the next query word */
             const int w0 = (j0 - (BP_DC + 1)) >> 5;
             qlo_a = qlo_b;
             qhi_a = qhi_b;
             load_qword(g.qp, g.i0, w0 + 1, Tq, qlo_b, qhi_b);
         }
         uint32_t *pc = planes + (size_t)(j0 - 1) * 32;
-        /* a whole target word of 16 columns that every lane of the warp still needs (all but the first and the last chunk of
-         * a warp of equally long reads): fully unrolled, the window's position inside the query words is a constant (0 or 16
-         * plus the column), no per-column length test, store offsets are immediates */
-        if (jend - j0 == 15 && (sh & 15u) == 0 && __all_sync(0xFFFFFFFFu, jend <= Tt)) {
+        /* a whole target word of 16 columns that every lane of the warp still needs (all but the last chunk of a warp of
+         * equally long reads): fully unrolled, the window's position inside the query words is a constant (0 or 16 plus the
+         * column), no per-column length test, store offsets are immediates */
+        if (jend - j0 == 15 && __all_sync(0xFFFFFFFFu, g.done || jend <= Tt)) {
             const bool act = true;
             if (sh == 0) {
 #pragma unroll
                 for (int c = 0; c < 16; c++) {
-                    Pv = __funnelshift_r(Pv, 1u, 1u);
-                    Mv >>= 1;
+                    if (c || !first) {
+                        Pv = __funnelshift_r(Pv, 1u, 1u);
+                        Mv >>= 1;
+                    }
                     const uint32_t ql = c ? __funnelshift_r(qlo_a, qlo_b, c) : qlo_a, qh = c ? __funnelshift_r(qhi_a, qhi_b, c) : qhi_a;
                     DIAG1_STEP(ql, qh, 8u, pc + 32 * c);
                 }
@@ -262,8 +275,10 @@ __device__ __forceinline__ void tile_diag1(const TileGeom &g, uint2 *__restrict_
         for (int j = j0; j <= jend; j++, sh++, pc += 32) {
             const bool act = j <= Tt;
             if (act) {
-                Pv = __funnelshift_r(Pv, 1u, 1u);           /* (Pv >> 1) | 0x80000000: the entering row starts at +1 */
-                Mv >>= 1;
+                if (j > BP_DC + 1) {
+                    Pv = __funnelshift_r(Pv, 1u, 1u);       /* (Pv >> 1) | 0x80000000: the entering row starts at +1 */
+                    Mv >>= 1;
+                }
                 const uint32_t ql = __funnelshift_r(qlo_a, qlo_b, sh), qh = __funnelshift_r(qhi_a, qhi_b, sh);
                 DIAG1_STEP(ql, qh, 8u, pc);
             }
@@ -273,66 +288,48 @@ __device__ __forceinline__ void tile_diag1(const TileGeom &g, uint2 *__restrict_
     __syncwarp();
     if (!g.done) st_eval += 32ull * (unsigned long long)Tt;
 
-    /* ---- run-skipping walk.  Cell (ci, cj) is bit b of column cj's kept word: b = (ci - cj) + 8 from column 17 on (the
-     * window slides with the diagonal), b = ci - 1 - max(0, cj - 9) before.  A round looks at the next BP_FW cells down the
-     * diagonal and keeps three bits of each: X (both planes set), indel (one plane set) and the low plane.  Substitutions
-     * stay on the diagonal, so all of them up to the first indel are recorded from the masks; only an indel ends a round. */
+    /* ---- run-skipping walk.  A cell's op is '=' exactly where its two bases are equal (both op-code planes are masked by
+     * ~Eq: a match always takes the diagonal at no cost), so the runs of '=' down a diagonal are the common suffixes of
+     * q[0, ci) and t[0, cj): a round XORs the 16 packed bases that end at row ci with the 16 that end at column cj and one
+     * CLZ gives the run.  The planes are read only at the cell that ends a run -- a mismatch, whose op the DP decides:
+     * 'X' where D = D[i-1][j-1] + 1 (~D0), else 'I' (up) where Pv', else 'D' (left).  Cell (ci, cj) is bit b of column cj's
+     * kept word, b = (ci - cj) + 8 from column 17 on (the window slides with the diagonal), b = ci - 1 - max(0, cj - 9)
+     * before; the low half holds Pv', the high half ~D0. */
     int ci = g.done ? 0 : Tq, cj = g.done ? 0 : Tt;
     int pos = 0, ne = 0, walkcost = 0;
     bool oob = false;
+    /* (this pass only sees tiles that start at the origin: i0 = j0 = 0) */
+    const int tlow = g.toff < 16 ? (int)g.toff : 16;         /* target bases in front of the tile, as far as a round can reach */
     while (__any_sync(0xFFFFFFFFu, ci > 0 && cj > 0)) {
         if (ci > 0 && cj > 0 && abs(ci - cj) > 7) {          /* outside the 16 kept diagonals (a fortiori outside the band) */
             oob = true;
             ci = cj = 0;
         }
-        const int K = (ci > 0 && cj > 0) ? min(min(ci, cj), BP_FW) : 0;
-        const int dv = ci - cj + 8;
-        /* bit k of the low half of acc = low op-code plane of cell k of the round, bit 16 + k = high plane: a cell costs a
-         * load, a shift, an AND and a multiply-add (the two fields grow side by side, 16 cells fill them exactly) */
-        uint32_t acc = 0;
-        /* warp-uniform choice: the one-bit-position loop unless some lane's round reaches into the first 16 columns */
-        if (!__any_sync(0xFFFFFFFFu, K > 0 && cj - K < 16)) {
-            const uint32_t *pb = planes + (ptrdiff_t)(cj - 1) * 32;
-#pragma unroll
-            for (int k = BP_FW - 1; k >= 0; k--) {
-                uint32_t u = 0;
-                if (k < K) u = pb[-k * 32] >> dv;
-                acc = acc * 2u + (u & 0x00010001u);
+        if (ci > 0 && cj > 0) {
+            const int K = min(min(ci, cj), 16);
+            /* the 16 bases that end at row ci / column cj, the last one in the top two bits (a start before the first word
+             * of the sequence is loaded from base 0 and shifted up; cells past K are cut off by the sentinel) */
+            const int nq = max(16 - ci, 0), nt = max(16 - cj - tlow, 0);        /* bases missing in front of the sequence */
+            const uint32_t q16 = as_bases16(g.qp, (uint64_t)(uint32_t)(ci + nq - 16)) << (2 * nq);
+            const uint32_t t16 = as_bases16(g.tbase, g.toff + (uint64_t)(uint32_t)(cj + tlow + nt - 16) - (uint64_t)(uint32_t)tlow) << (2 * nt);
+            const uint32_t x = q16 ^ t16;
+            uint32_t m = (x | (x >> 1)) & 0x55555555u;       /* bit 30 - 2k: cell k of the round (k = 0: (ci, cj)) mismatches */
+            if (K < 16) m |= 1u << (30 - 2 * K);             /* sentinel: the run ends with the round at the latest */
+            const int run = __clz((int)m) >> 1;
+            pos += run;
+            ci -= run;
+            cj -= run;
+            if (run < K) {                                   /* the mismatch that ended the run */
+                const int bb = cj >= 17 ? ci - cj + 8 : ci - 1 - max(0, cj - 9);
+                const uint32_t u = planes[(size_t)(cj - 1) * 32] >> bb;
+                const uint32_t op = (u & 0x10000u) ? 3u : ((u & 1u) ? 1u : 2u);
+                tb[(size_t)ne * 32] = ((uint32_t)pos << 2) | op;
+                ne++;
+                pos++;
+                walkcost++;
+                ci -= (op != 2u);
+                cj -= (op != 1u);
             }
-        } else {
-#pragma unroll
-            for (int k = BP_FW - 1; k >= 0; k--) {
-                uint32_t u = 0;
-                if (k < K) {
-                    const int c2 = cj - k;
-                    const int bb = c2 >= 17 ? dv : (ci - k) - 1 - max(0, c2 - 9);
-                    u = planes[(size_t)(c2 - 1) * 32] >> bb;
-                }
-                acc = acc * 2u + (u & 0x00010001u);
-            }
-        }
-        const uint32_t ml = acc & 0xFFFFu, mh = acc >> 16;    /* bit k: cell k has its low / high plane set */
-        const uint32_t mx = ml & mh, mi = ml ^ mh;            /* X (both planes) / an indel (one plane) */
-        const int run = __ffs((int)(mi | (1u << K))) - 1;    /* cells before the first indel (or the end of the round) */
-        uint32_t xs = mx & ((1u << run) - 1u);
-        while (xs) {                                         /* substitutions on the way, in walk order */
-            const int k = __ffs((int)xs) - 1;
-            xs &= xs - 1u;
-            tb[(size_t)ne * 32] = ((uint32_t)(pos + k) << 2) | 3u;
-            ne++;
-            walkcost++;
-        }
-        pos += run;
-        ci -= run;
-        cj -= run;
-        if (run < K) {                                       /* the indel: low plane set = 'I' (up), else 'D' (left) */
-            const uint32_t op = ((ml >> run) & 1u) ? 1u : 2u;
-            tb[(size_t)ne * 32] = ((uint32_t)pos << 2) | op;
-            ne++;
-            pos++;
-            walkcost++;
-            ci -= (op != 2u);
-            cj -= (op != 1u);
         }
     }
     while (__any_sync(0xFFFFFFFFu, (ci | cj) != 0)) {
