@@ -702,7 +702,7 @@ def run_b200(args):
             "quality": {"mapped_frac": float(ok.mean()), "exact_pos_strand_frac": exact, "within_50bp_strand_frac": near,
                         "valid_total": [st["valid"], st["total"]]},
             "stats_per_step_per_gpu": {k: per_step[k] for k in ("seeds", "bs_steps", "fm_steps_exec", "text_verified", "sa_hits", "dp_cells",
-                                                                   "dp_cells_eval", "gact_redone", "overflow_reads", "overflow_queued", "vote_deferred")}}
+                                                                   "dp_cells_eval", "gact_redone", "gact_queued", "overflow_reads", "overflow_queued", "vote_deferred")}}
 
     # the program leg builds its own index on the same GPUs: give the memory back first (human scale: ~120 GB per handle)
     mapper.close()

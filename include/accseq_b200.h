@@ -241,6 +241,8 @@ typedef struct as_stats {
                                * families.  overflow_reads counts reads the overflow pass itself could not hold (never) */
     uint64_t vote_deferred;   /* short reads the thread-per-read PART 1 kernel handed to the group kernel (a seed with more
                                * than two hits, more distinct vote buckets in a phase or in the outer list than a thread keeps) */
+    uint64_t gact_queued;     /* one-tile reads the one-word band of GACT's first attempt could not prove exact (walk cost > 15 or
+                               * more than 7 net indels) and that the second launch aligned again with wider bands */
 } as_stats;
 int as_gpu_stats(as_gpu *h, as_stats *out);          /* accumulated since open / last reset */
 int as_gpu_stats_reset(as_gpu *h);

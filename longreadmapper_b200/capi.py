@@ -73,7 +73,7 @@ def open_opts(lc2_hlen=0, no_sax=0, build_part_max=0, sampled_sa=0, l2_fetch_gra
 class AsStats(C.Structure):
     _fields_ = [(k, C.c_uint64) for k in ("total", "valid", "n_flag4", "n_flag16", "sum_ed", "dp_cells", "seeds",
                                            "sa_hits", "bs_steps", "overflow_reads", "dp_cells_eval", "gact_redone", "fm_steps_exec", "text_verified",
-                                           "overflow_queued", "vote_deferred")]
+                                           "overflow_queued", "vote_deferred", "gact_queued")]
 
 
 class AsHostIndex(C.Structure):

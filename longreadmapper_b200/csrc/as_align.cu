@@ -17,15 +17,14 @@
 /* PART 2: locus lookup + strand fix                                                               */
 /* ---------------------------------------------------------------------------------------------- */
 __device__ __forceinline__ uint32_t comp_ascii(uint32_t c) {             /* alnmain.c:31-51 */
-    switch (c) {
-    case 'A': case 'a': return 'T';
-    case 'C': case 'c': return 'G';
-    case 'G': case 'g': return 'C';
-    case 'T': case 't': return 'A';
-    default: return 'N';
-    }
+    /* branch-free (a switch made the 32 lanes of a warp take five different paths per byte): the 2-bit code of the byte
+     * picks the letter it would have to be and its complement out of two constants; anything else is 'N' */
+    const uint32_t code = ((c >> 1) ^ (c >> 2)) & 3u;                    /* A 0, C 1, G 2, T 3 (as_pack4) */
+    const uint32_t sel = code | 0x4440u;                                 /* byte `code` of the constant, zeros above it */
+    const uint32_t is = __byte_perm(0x54474341u, 0u, sel);               /* "ACGT"[code] */
+    const uint32_t comp = __byte_perm(0x41434754u, 0u, sel);             /* "TGCA"[code] */
+    return (c & 0xDFu) == is ? comp : (uint32_t)'N';
 }
-
 
 /* reverse the sixteen 2-bit groups of a word */
 __device__ __forceinline__ uint32_t rev2(uint32_t x) {
@@ -87,49 +86,91 @@ __global__ void __launch_bounds__(256) k_locus(DevIndex ix, char *__restrict__ a
             res[r] = o;
             toff[r] = seq_id < 0 ? AS_TOFF_NONE : fwd;
         }
-        /* ---- strand-1 reads of this warp's 32, one after the other (alnmain.c:433-438) ---- */
+        /* ---- strand-1 reads (alnmain.c:433-438) ---- */
+        if (!ascii && wstride <= 16) {
+            /* packed-only batch of short reads (as_map_batch_packed): every lane turns its own read -- all its words are
+             * requested before any is written, so the 32 reads' loads are in flight together instead of one read per round
+             * trip.  Out word w = complement of input bases [len-16w-16, len-16w), last first. */
+            uint32_t *pw = pack + r * wstride;
+            const uint32_t nw = strand == 1 ? (len + 15) >> 4 : 0u;
+            uint32_t y[16];
+#pragma unroll
+            for (int w = 0; w < 16; w++) {
+                y[w] = 0;
+                if ((uint32_t)w < nw) {
+                    const int st = (int)len - 16 * w - 16;
+                    const uint32_t cnt = st >= 0 ? 16u : (uint32_t)(16 + st);
+                    const uint32_t x = as_bases16(pw, (uint64_t)(st > 0 ? st : 0));
+                    y[w] = ~rev2(x) >> (2u * (16u - cnt));
+                    if (cnt < 16u) y[w] &= (1u << (2u * cnt)) - 1u;
+                }
+            }
+#pragma unroll
+            for (int w = 0; w < 16; w++)
+                if ((uint32_t)w < nw) pw[w] = y[w];
+            continue;
+        }
+        /* ... of this warp's 32, four at a time: a group of 8 lanes turns one read -- ASCII reverse complement by mirrored
+         * pairs, then the packed copy straight from the packed words (all of a read's words are loaded before any is stored:
+         * an output word reads input words from the other end of the read).  A round is a chain of dependent round trips to
+         * memory (load, complement, store, re-pack), so four reads per round is four times fewer of them. */
         uint32_t todo = __ballot_sync(0xFFFFFFFFu, strand == 1);
+        const uint32_t grp = lane >> 3, sub = lane & 7u, gmask = 0xFFu << (8u * grp);
         while (todo) {
-            const int src = __ffs((int)todo) - 1;
-            todo &= todo - 1;
+            /* this group's read of the round: the (grp+1)-th set bit of todo, if there is one */
+            uint32_t t = todo;
+            for (uint32_t k = 0; k < grp; k++) t &= t - 1;
+            const bool mine = t != 0;
+            const int src = mine ? __ffs((int)t) - 1 : 0;
             const uint32_t rl = __shfl_sync(0xFFFFFFFFu, len, src);
             const size_t rr = base + (size_t)src;
             uint8_t *s = (uint8_t *)ascii + rr * stride;
             uint32_t *pw = pack + rr * wstride;
-            const uint32_t half = ascii ? rl >> 1 : 0u;                  /* packed-only batch (as_map_batch_packed): no ASCII copy */
+            const uint32_t half = (ascii && mine) ? rl >> 1 : 0u;          /* packed-only batch (as_map_batch_packed): no ASCII copy */
             bool other = false;                                          /* a byte outside ACGT/acgt */
-            for (uint32_t i = lane; i < half; i += 32) {
+            for (uint32_t i = sub; i < half; i += 8) {
                 const uint32_t ca = comp_ascii(s[i]), cb = comp_ascii(s[rl - 1 - i]);
                 other |= (ca == 'N') | (cb == 'N');
                 s[i] = (uint8_t)cb;
                 s[rl - 1 - i] = (uint8_t)ca;
             }
-            if (ascii && (rl & 1u) && lane == 0) {
-                const uint32_t cm = comp_ascii(s[half]);
+            if (ascii && mine && (rl & 1u) && sub == 0) {
+                const uint32_t cm = comp_ascii(s[rl >> 1]);
                 other |= cm == 'N';
-                s[half] = (uint8_t)cm;
+                s[rl >> 1] = (uint8_t)cm;
             }
-            const uint32_t nw = (rl + 15) >> 4;
-            if (!__any_sync(0xFFFFFFFFu, other) && nw <= 32) {
-                /* out word w = complement of input bases [rl-16w-16, rl-16w), last first */
-                uint32_t y = 0;
-                if (lane < nw) {
-                    const int st = (int)rl - 16 * (int)lane - 16;
+            const uint32_t nw = mine ? (rl + 15) >> 4 : 0u;
+            const bool repack = (__ballot_sync(0xFFFFFFFFu, other) & gmask) != 0 || nw > 32;
+            /* out word w = complement of input bases [rl-16w-16, rl-16w), last first */
+            uint32_t y[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const uint32_t w = sub + 8u * q;
+                y[q] = 0;
+                if (!repack && w < nw) {
+                    const int st = (int)rl - 16 * (int)w - 16;
                     const uint32_t cnt = st >= 0 ? 16u : (uint32_t)(16 + st);
                     const uint32_t x = as_bases16(pw, (uint64_t)(st > 0 ? st : 0));
-                    y = ~rev2(x) >> (2u * (16u - cnt));
-                    if (cnt < 16u) y &= (1u << (2u * cnt)) - 1u;
+                    y[q] = ~rev2(x) >> (2u * (16u - cnt));
+                    if (cnt < 16u) y[q] &= (1u << (2u * cnt)) - 1u;
                 }
-                __syncwarp();
-                if (lane < nw) pw[lane] = y;
+            }
+            __syncwarp();
+            if (!repack) {
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const uint32_t w = sub + 8u * q;
+                    if (w < nw) pw[w] = y[q];
+                }
             } else {
-                __syncwarp();
-                for (uint32_t w = lane; w < nw; w += 32) {
+                for (uint32_t w = sub; w < nw; w += 8) {
                     const uint32_t b0 = w << 4, lim = rl - b0 < 16 ? rl - b0 : 16;
                     pw[w] = as_pack16(s + b0, lim);
                 }
             }
             __syncwarp();
+            /* retire the (up to) four reads of this round */
+            for (int k = 0; k < 4 && todo; k++) todo &= todo - 1;
         }
     }
 }

@@ -870,19 +870,20 @@ extern "C" int as_gpu_stats(as_gpu *h, as_stats *out) {
     if (!h || !out) return AS_EINVAL;
     AS_CUDA(cudaSetDevice(h->device));
     AS_CUDA(cudaStreamSynchronize(h->stream));
-    unsigned long long v[17];
+    unsigned long long v[18];
     AS_CUDA(cudaMemcpy(v, h->d_stats, sizeof v, cudaMemcpyDeviceToHost));
     if (h->twin) {
-        unsigned long long w[17];
+        unsigned long long w[18];
         AS_CUDA(cudaStreamSynchronize(h->twin->stream));
         AS_CUDA(cudaMemcpy(w, h->twin->d_stats, sizeof w, cudaMemcpyDeviceToHost));
-        for (int i = 0; i < 17; i++) v[i] += w[i];
+        for (int i = 0; i < 18; i++) v[i] += w[i];
     }
     out->total = v[0]; out->valid = v[1]; out->n_flag4 = v[2]; out->n_flag16 = v[3]; out->sum_ed = v[4];
     out->dp_cells = v[5]; out->seeds = v[6]; out->sa_hits = v[7]; out->bs_steps = v[8]; out->overflow_reads = v[9];
     out->dp_cells_eval = v[10]; out->gact_redone = v[11]; out->fm_steps_exec = v[12]; out->text_verified = v[13];
     out->overflow_queued = v[14];
     out->vote_deferred = v[16];         /* v[15]: reads too long for their row (as_map_batch_packed) */
+    out->gact_queued = v[17];
     return AS_OK;
 }
 

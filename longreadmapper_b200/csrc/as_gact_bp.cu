@@ -196,10 +196,16 @@ __device__ __forceinline__ void tile_diag1(const TileGeom &g, uint2 *__restrict_
     /* one column: the Myers/Hyyro step on the window (ql, qh = the query planes of its 32 rows), the kept 16 diagonals of
      * Pv' and ~D0 stored as one word.  (x << 1) | 1 and x << 1 are written as multiply-adds: they go to the FMA
      * pipe, which idles while the ALU pipe carries the logic ops. */
-#define DIAG1_STEP(QL, QH, SS, PDST)                                                                   \
+#define DIAG1_STEP(QL, QH, SS, PDST) DIAG1_STEP_C(QL, QH, SS, PDST, 0u - (tw & 1u), 0u - ((tw >> 1) & 1u), tw >>= 2)
+    /* column c of a target word that stays in its register (the unrolled chunks): both masks are a shift left (FMA pipe, as a
+     * multiply) and an arithmetic shift right, the word is not consumed */
+#define DIAG1_STEP_U(QL, QH, SS, PDST, C)                                                              \
+    DIAG1_STEP_C(QL, QH, SS, PDST, (uint32_t)((int32_t)(tw * (1u << (31 - 2 * (C)))) >> 31),           \
+                 (uint32_t)((int32_t)(tw * (1u << (30 - 2 * (C)))) >> 31), (void)0)
+#define DIAG1_STEP_C(QL, QH, SS, PDST, TL, TH, NEXT)                                                   \
     do {                                                                                               \
-        const uint32_t tl_ = 0u - (tw & 1u), th_ = 0u - ((tw >> 1) & 1u);                              \
-        tw >>= 2;                                                                                      \
+        const uint32_t tl_ = (TL), th_ = (TH);                                                         \
+        NEXT;                                                                                          \
         const uint32_t eq_ = ~(((QL) ^ tl_) | ((QH) ^ th_));                                          \
         const uint32_t xv_ = eq_ | Mv;                                                                 \
         const uint32_t xh_ = (((eq_ & Pv) + Pv) ^ Pv) | eq_;                                           \
@@ -218,7 +224,7 @@ __device__ __forceinline__ void tile_diag1(const TileGeom &g, uint2 *__restrict_
         const bool act = true;
         if (!g.done) tw = as_bases16(g.tbase, g.toff + (uint64_t)g.j0);
 #pragma unroll
-        for (int c = 0; c < 16; c++) DIAG1_STEP(qlo_a, qhi_a, (uint32_t)(c > 8 ? c - 8 : 0), planes + 32 * c);
+        for (int c = 0; c < 16; c++) DIAG1_STEP_U(qlo_a, qhi_a, (uint32_t)(c > 8 ? c - 8 : 0), planes + 32 * c, c);
     } else {
         const int jA = g.maxTt < 16 ? g.maxTt : 16;
         for (int j = 1; j <= jA; j++) {
@@ -258,7 +264,7 @@ __device__ __forceinline__ void tile_diag1(const TileGeom &g, uint2 *__restrict_
                         Mv >>= 1;
                     }
                     const uint32_t ql = c ? __funnelshift_r(qlo_a, qlo_b, c) : qlo_a, qh = c ? __funnelshift_r(qhi_a, qhi_b, c) : qhi_a;
-                    DIAG1_STEP(ql, qh, 8u, pc + 32 * c);
+                    DIAG1_STEP_U(ql, qh, 8u, pc + 32 * c, c);
                 }
             } else {
 #pragma unroll
@@ -266,7 +272,7 @@ __device__ __forceinline__ void tile_diag1(const TileGeom &g, uint2 *__restrict_
                     Pv = __funnelshift_r(Pv, 1u, 1u);
                     Mv >>= 1;
                     const uint32_t ql = __funnelshift_r(qlo_a, qlo_b, 16 + c), qh = __funnelshift_r(qhi_a, qhi_b, 16 + c);
-                    DIAG1_STEP(ql, qh, 8u, pc + 32 * c);
+                    DIAG1_STEP_U(ql, qh, 8u, pc + 32 * c, c);
                 }
             }
             continue;
@@ -285,6 +291,8 @@ __device__ __forceinline__ void tile_diag1(const TileGeom &g, uint2 *__restrict_
         }
     }
 #undef DIAG1_STEP
+#undef DIAG1_STEP_U
+#undef DIAG1_STEP_C
     __syncwarp();
     if (!g.done) st_eval += 32ull * (unsigned long long)Tt;
 
@@ -554,6 +562,8 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
     constexpr bool BANDED = NB < W;
     __shared__ uint2 s_win[BP_THREADS / 32][BP_WIN][32];
     __shared__ uint32_t s_lut[256];      /* 4 walk-order op codes (one byte of the slab) -> 4 op bytes in forward order */
+    /* second launch over a retry queue that the warp-per-read kernel takes (short queue): nothing to do, leave at once */
+    if (a.retry_mode == 2 && a.n_dev && *a.n_dev <= AS_GACT_RETRY_WARP_MAX) return;
     for (uint32_t e = threadIdx.x; e < 256; e += BP_THREADS)
         s_lut[e] = ((e >> 6) & 3u) | (((e >> 4) & 3u) << 8) | (((e >> 2) & 3u) << 16) | ((e & 3u) << 24);
     __syncthreads();
@@ -813,7 +823,8 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
  * fail at half the band (about one warp-tile in eight refilled).  The verdict goes to pinned host memory, which the
  * launcher reads when it picks the next launch's instantiation; results never depend on it. */
 __global__ void k_gact_policy(volatile unsigned int *host_band, const unsigned int *cnt, unsigned int cur,
-                              const unsigned int *queued, unsigned int n_reads) {
+                              const unsigned int *queued, unsigned int n_reads, unsigned long long *stats) {
+    if (queued && *queued) atomicAdd(stats + 17, (unsigned long long)*queued);        /* as_stats.gact_queued */
     const unsigned long long retry = cnt[0], wtiles = cnt[1], half = cnt[2], tiles = cnt[3];
     if (wtiles == 0) return;
     unsigned int kb = cur;
@@ -851,7 +862,7 @@ static int launch_bp(as_gpu *h, GactArgs &a, size_t n, int blocks_per_sm, unsign
     h->launches++;
     AS_CUDA(cudaGetLastError());
     if (a.band == 0) {
-        k_gact_policy<<<1, 1, 0, h->stream>>>(h->d_band, cnt + 1, cur_band, a.retry_count, (unsigned int)n);
+        k_gact_policy<<<1, 1, 0, h->stream>>>(h->d_band, cnt + 1, cur_band, a.retry_count, (unsigned int)n, a.stats);
         h->launches++;
         AS_CUDA(cudaGetLastError());
     }
