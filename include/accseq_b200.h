@@ -130,7 +130,9 @@ typedef struct as_params {
     int32_t  gact_order; /* hand reads to GACT by decreasing length: -1 = only for reads of several tiles (default), 0, 1 */
     int32_t  gact_blocks_per_sm;  /* resident GACT blocks per SM; 0 = occupancy query (default) */
     uint32_t chunk_reads;         /* as_map_batch: fixed chunk size; 0 = the ramp-up / ramp-down plan (default) */
-    int32_t  chunk_tail;          /* as_map_batch: how many times the last chunk is split 2:1; -1 = default (1) */
+    int32_t  chunk_tail;          /* as_map_batch: how many times the last chunk is split 2:1; -1 = default (1).
+                                   * as_map_batch_packed: chunks between the first and the last one (default 2); 100 * d + m =
+                                   * first and last chunk of n / d reads (default 8), m chunks in between */
     int32_t  vote_thread;         /* PART 1 of short reads (<= 8 seeds per phase) by the thread-per-read kernel, the rest by the
                                    * group kernel: -1 = when it applies and the index has at most 2^30 rows (default), 0 = group
                                    * kernel only, 1 = whenever it applies */

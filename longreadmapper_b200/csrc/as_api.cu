@@ -644,11 +644,14 @@ static int plan_chunks_packed(const as_params *p, size_t n, size_t row_bytes, si
      * quarters in between as two chunks (more when the op rows of long reads would not fit); as_params.chunk_tail > 0
      * sets the number of chunks in between (A/B runs).  Measured on c2 (1 M reads, kernels alone 3.9 ms): 4.58 ms with
      * two chunks in between or four equal chunks, 4.6 with three, 4.7 with one or four, 5.0 with six. */
-    size_t edge = n / 8;
+    /* (A/B runs: chunk_tail = 100 * d + m asks for edges of n / d reads and m chunks in between) */
+    const size_t edge_div = p->chunk_tail >= 100 ? (size_t)(p->chunk_tail / 100) : 8;
+    size_t edge = n / (edge_div < 3 ? 3 : edge_div);
     if (edge < min_reads) edge = min_reads;
     if (edge > by_bytes) edge = by_bytes;
     const size_t inner = n - 2 * edge;
-    int mids = p->chunk_tail > 0 ? p->chunk_tail : 2;
+    int mids = p->chunk_tail > 0 ? p->chunk_tail % 100 : 2;
+    if (mids == 0) mids = 2;
     if ((inner + (size_t)mids - 1) / (size_t)mids > by_bytes) mids = (int)((inner + by_bytes - 1) / by_bytes);
     if (mids < 1) mids = 1;
     if (mids > AS_MAX_CHUNKS - 2) mids = AS_MAX_CHUNKS - 2;

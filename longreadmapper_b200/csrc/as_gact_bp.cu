@@ -825,6 +825,7 @@ __global__ void __launch_bounds__(BP_THREADS) k_gact_bp(GactArgs a, uint2 *__res
 __global__ void k_gact_policy(volatile unsigned int *host_band, const unsigned int *cnt, unsigned int cur,
                               const unsigned int *queued, unsigned int n_reads, unsigned long long *stats) {
     if (queued && *queued) atomicAdd(stats + 17, (unsigned long long)*queued);        /* as_stats.gact_queued */
+    if (!host_band) return;                                                            /* fixed band: only the counter */
     const unsigned long long retry = cnt[0], wtiles = cnt[1], half = cnt[2], tiles = cnt[3];
     if (wtiles == 0) return;
     unsigned int kb = cur;
@@ -861,8 +862,8 @@ static int launch_bp(as_gpu *h, GactArgs &a, size_t n, int blocks_per_sm, unsign
                                                                       (uint32_t *)h->gact_tb.p, tb_per_warp);
     h->launches++;
     AS_CUDA(cudaGetLastError());
-    if (a.band == 0) {
-        k_gact_policy<<<1, 1, 0, h->stream>>>(h->d_band, cnt + 1, cur_band, a.retry_count, (unsigned int)n, a.stats);
+    if (a.band == 0 || a.retry_count) {
+        k_gact_policy<<<1, 1, 0, h->stream>>>(a.band == 0 ? h->d_band : nullptr, cnt + 1, cur_band, a.retry_count, (unsigned int)n, a.stats);
         h->launches++;
         AS_CUDA(cudaGetLastError());
     }

@@ -395,7 +395,9 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
             uint64_t kk = 1, ll = ix.N - 1, rr = 0;                             /* alnmain.c:354 */
             bool have_pos = false;                                               /* hit_pos = SA of the seed's one row */
             uint64_t hit_pos = 0;
-            if (m < m_count) {
+            /* (a group whose table overflowed in an earlier round of the phase resolves no more seeds: see below) */
+            const bool gfull = !BIG && c0 > 0 && (__ballot_sync(FULL, !ok) & gmask) != 0;
+            if (m < m_count && !gfull) {
                 const uint64_t seed = as_bases32(pr, j);
                 vote_resolve_seed<SMALL>(ix, a, s_tab, s_tabChi, sl, left0, hmask, seed, false, 0ULL, kk, ll, rr, have_pos, hit_pos,
                                          st_seeds, st_steps, st_fm, st_txt);
@@ -460,11 +462,16 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                 const uint32_t V_max = warp_max_u32(V);
                 /* the overflow pass has one warp per read and four per SM: VU rows per lane are located before any is
                  * inserted, so their SA gathers (and the inserts' first atomics) overlap instead of queueing up */
-                constexpr int VU = BIG ? 4 : 1;
+                constexpr int VU = BIG ? 8 : 1;
                 for (uint32_t v0 = 0; v0 < V_max; v0 += G * VU) {
                     uint64_t vkey[VU];
                     uint32_t vord[VU];
                     bool vok[VU];
+                    /* a group whose table is full leaves the rest of the phase alone: the read goes to the overflow pass
+                     * whatever else it votes, and every further vote would probe the whole table before it failed (c2r:
+                     * 1750 votes of a 250-copy family into 64 slots -- the list pass took 10 ms for that alone) */
+                    const bool full = !BIG && (__ballot_sync(FULL, !ok) & gmask) != 0;
+                    if (full) ok = false;
 #pragma unroll
                     for (int u = 0; u < VU; u++) {
                         const uint32_t v = v0 + (uint32_t)u * G + g;
@@ -481,10 +488,10 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                         const uint32_t opl = __shfl_sync(gmask, (uint32_t)hit_pos, lo, G);
                         const uint32_t oph = __shfl_sync(gmask, (uint32_t)(hit_pos >> 32), lo, G);
                         const bool opk = __shfl_sync(gmask, (int)have_pos, lo, G) != 0;
-                        vok[u] = v < V;
+                        vok[u] = v < V && !full;
                         vkey[u] = 0;
                         vord[u] = 0;
-                        if (v < V) {
+                        if (vok[u]) {
                             const uint32_t om = c0 + lo;
                             const uint32_t oj = (uint32_t)iter + om * (uint32_t)P;
                             const uint32_t off = v - ob;
@@ -494,9 +501,65 @@ __global__ void __launch_bounds__(BIG ? 32 : VOTE_THREADS, BIG ? 1 : (G == 32 ? 
                             st_hits++;
                         }
                     }
+                    if (BIG) {
+                        /* The warp owns the table.  The first compare-and-swap of all VU votes of a lane leaves before any
+                         * answer is back (a vote was four dependent round trips to L2: claim, list slot, and again for the
+                         * next vote; c2r: 23 k cycles per 128 votes); a vote whose slot belongs to another bucket probes on
+                         * by itself; the slots claimed by the batch are appended to the list by ONE addition per batch
+                         * (prefix sum over the lanes' counts) instead of one atomic per claim. */
+                        uint32_t slot[VU];
+                        unsigned long long prev[VU];
 #pragma unroll
-                    for (int u = 0; u < VU; u++)
-                        if (vok[u] && !table_insert<USED_T>(t, vkey[u] >> 4, (uint32_t)vkey[u] & 15u, vord[u])) ok = false;
+                        for (int u = 0; u < VU; u++) {
+                            slot[u] = hash_bucket(vkey[u] >> 4, t.shift);
+                            prev[u] = EMPTY_BUCKET;
+                            if (vok[u]) prev[u] = atomicCAS(t.bucket + slot[u], EMPTY_BUCKET, (unsigned long long)(vkey[u] >> 4));
+                        }
+                        uint32_t newmask = 0;
+#pragma unroll
+                        for (int u = 0; u < VU; u++) {
+                            if (vok[u]) {
+                                const unsigned long long b = (unsigned long long)(vkey[u] >> 4);
+                                unsigned long long pv = prev[u];
+                                uint32_t sl2 = slot[u], probes = 1;
+                                while (pv != EMPTY_BUCKET && pv != b && probes < t.cap) {        /* someone else's slot */
+                                    sl2 = (sl2 + 1) & (t.cap - 1);
+                                    pv = atomicCAS(t.bucket + sl2, EMPTY_BUCKET, b);
+                                    probes++;
+                                }
+                                if (pv == EMPTY_BUCKET || pv == b) {
+                                    slot[u] = sl2;
+                                    if (pv == EMPTY_BUCKET) newmask |= 1u << u;
+                                    atomicAdd(t.val + sl2, 1u);
+                                    atomicMin(t.ord + sl2, vord[u]);
+                                    atomicMin(t.low + sl2, (uint32_t)vkey[u] & 15u);
+                                } else {
+                                    ok = false;
+                                }
+                            }
+                        }
+                        __syncwarp();
+                        uint32_t mine = (uint32_t)__popc(newmask), incl2 = mine;
+#pragma unroll
+                        for (int d = 1; d < 32; d <<= 1) {
+                            const uint32_t o = __shfl_up_sync(FULL, incl2, d);
+                            if ((int)lane >= d) incl2 += o;
+                        }
+                        const uint32_t tot = __shfl_sync(FULL, incl2, 31);
+                        if (tot) {
+                            uint32_t at = *(volatile uint32_t *)t.n_used + incl2 - mine;
+#pragma unroll
+                            for (int u = 0; u < VU; u++)
+                                if (newmask & (1u << u)) t.used[at++] = (USED_T)slot[u];
+                            __syncwarp();
+                            if (lane == 0) *(volatile uint32_t *)t.n_used = *(volatile uint32_t *)t.n_used + tot;
+                            __syncwarp();
+                        }
+                    } else {
+#pragma unroll
+                        for (int u = 0; u < VU; u++)
+                            if (vok[u] && !table_insert<USED_T>(t, vkey[u] >> 4, (uint32_t)vkey[u] & 15u, vord[u])) ok = false;
+                    }
                 }
             }
         }

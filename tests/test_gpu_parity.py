@@ -381,7 +381,7 @@ def test_map_packed_compact_short(native, gpu_repeat, idx_repeat, chunk):
     assert h2d == len(lens) * (4 * ((int(lens.max()) + 15) // 16) + 4) and d2h < len(lens) * 16 + dense.size + 1024
 
 
-@pytest.mark.parametrize("knobs", [dict(), dict(gact_runs=0), dict(chunk_reads=3000), dict(T=64, O=24), dict(band=-1)])
+@pytest.mark.parametrize("knobs", [dict(), dict(gact_runs=0), dict(chunk_reads=3000), dict(T=64, O=24), dict(band=-1), dict(band=16)])
 def test_map_packed_runs_straight_from_gact(native, gpu_repeat, idx_repeat, knobs):
     """Reads of one tile in the short-read kernels (<= 160 bases) leave their run bytes straight from GACT's traceback events
     (GactArgs.emit_runs: no op bytes, no cleared rows, no run-length pass); the reads the one-word band cannot prove exact go
@@ -391,6 +391,7 @@ def test_map_packed_runs_straight_from_gact(native, gpu_repeat, idx_repeat, knob
     ix, gs = idx_repeat
     tk = {k: knobs[k] for k in ("T", "O", "band") if k in knobs}
     kn = {k: v for k, v in knobs.items() if k not in tk}
+    gpu_repeat.stats_reset()
     for seed, (lmin, lmax, emin, emax, sub) in enumerate([(30, 150, 0.0, 0.03, 0.5), (100, 160, 0.05, 0.15, 0.34), (150, 150, 0.0, 0.0, 1.0)]):
         reads, lens, _ = reads_from(native, 660 + seed, gs, 2200, lmin, lmax, emin, emax, sub)
         flags = native.AS_F_RLE_CIGAR | native.AS_F_KEEP_READS
@@ -405,6 +406,8 @@ def test_map_packed_runs_straight_from_gact(native, gpu_repeat, idx_repeat, knob
         assert offs[-1] == dense.size
         for i in range(len(lens)):
             assert np.array_equal(dense[offs[i]:offs[i + 1]], rows[i, : want_n[i]]), (seed, i)
+    if tk == dict(band=16):     # the one-word band cannot prove all of the 5-15 % reads exact
+        assert gpu_repeat.stats()["gact_queued"] > 0, "no read took GACT's retry queue: the test does not reach it"
 
 
 def test_map_packed_compact_long_and_edge(native, gpu_repeat, idx_repeat):
