@@ -138,6 +138,9 @@ typedef struct as_params {
                                    * kernel only, 1 = whenever it applies */
     int32_t  gact_runs;           /* as_map_batch_packed: one-tile reads leave their run bytes straight from GACT's traceback
                                    * (no op bytes, no run-length pass): -1 / 1 = on (default), 0 = off */
+    int32_t  vote_blocks_per_sm;  /* resident blocks per SM of the thread-per-read PART 1 kernel; 0 = occupancy query (default).
+                                   * Its blocks and GACT's are persistent and between them fill an SM's registers: fewer of either
+                                   * lets the two lanes of as_map_batch_packed run PART 1 of one chunk beside GACT of another */
 } as_params;
 #define AS_F_MYERS        1u   /* also run the edlib-equivalent NW distance with k=(int)(0.05*len*2) per read */
 #define AS_F_NO_ALIGN     2u   /* stop after PART 1+2 (no GACT): results carry loc/off/strand/flag only */

@@ -55,7 +55,7 @@ class Params(C.Structure):
     _fields_ = [("seed_len", C.c_uint32), ("thres", C.c_uint32), ("gact_T", C.c_int32), ("gact_O", C.c_int32),
                 ("flags", C.c_uint32), ("gact_band", C.c_int32), ("vote_ectx", C.c_int32), ("gact_order", C.c_int32),
                 ("gact_blocks_per_sm", C.c_int32), ("chunk_reads", C.c_uint32), ("chunk_tail", C.c_int32),
-                ("vote_thread", C.c_int32), ("gact_runs", C.c_int32)]
+                ("vote_thread", C.c_int32), ("gact_runs", C.c_int32), ("vote_blocks_per_sm", C.c_int32)]
 
 
 class OpenOpts(C.Structure):
@@ -380,7 +380,7 @@ class GpuMapper:
         self.L.as_params_default(C.byref(p))
         p.seed_len, p.thres, p.flags = seed_len, thres, flags
         for k, v in knobs.items():
-            if k not in ("vote_ectx", "gact_order", "gact_blocks_per_sm", "chunk_reads", "chunk_tail", "vote_thread", "gact_runs"):
+            if k not in ("vote_ectx", "gact_order", "gact_blocks_per_sm", "chunk_reads", "chunk_tail", "vote_thread", "gact_runs", "vote_blocks_per_sm"):
                 raise TypeError(f"unknown as_params field {k}")
             setattr(p, k, int(v))
         if band is not None:

@@ -27,6 +27,7 @@ extern "C" void as_params_default(as_params *p) {
     p->chunk_tail = -1;
     p->vote_thread = -1;
     p->gact_runs = -1;
+    p->vote_blocks_per_sm = 0;
 }
 
 __global__ void k_rle_ops(uint8_t *__restrict__ ops, size_t stride, as_result *__restrict__ res, size_t n);

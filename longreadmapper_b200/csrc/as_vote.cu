@@ -1156,10 +1156,12 @@ int as_launch_vote(as_gpu *h, const as_params *p, const uint32_t *d_pack, size_t
         uint64_t tb = (n + VT_THREADS - 1) / VT_THREADS;
         if (small) {
             if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_vote_t<true>, VT_THREADS, 0) != cudaSuccess || occ < 1) occ = VT_MIN_BLOCKS;
+            if (p->vote_blocks_per_sm > 0 && p->vote_blocks_per_sm < occ) occ = p->vote_blocks_per_sm;
             const uint64_t cap = (uint64_t)h->sm_count * (uint64_t)occ;
             k_vote_t<true><<<(unsigned)(tb < cap ? tb : cap), VT_THREADS, 0, h->stream>>>(h->ix, a);
         } else {
             if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_vote_t<false>, VT_THREADS, 0) != cudaSuccess || occ < 1) occ = VT_MIN_BLOCKS;
+            if (p->vote_blocks_per_sm > 0 && p->vote_blocks_per_sm < occ) occ = p->vote_blocks_per_sm;
             const uint64_t cap = (uint64_t)h->sm_count * (uint64_t)occ;
             k_vote_t<false><<<(unsigned)(tb < cap ? tb : cap), VT_THREADS, 0, h->stream>>>(h->ix, a);
         }

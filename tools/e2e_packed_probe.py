@@ -19,6 +19,7 @@ ap.add_argument("--reads", type=int, default=0)
 ap.add_argument("--chunks", default="0,125000,250000,333334,500000,1000000")
 ap.add_argument("--reps", type=int, default=8)
 ap.add_argument("--mids", default="")
+ap.add_argument("--knobs", default="", help="as_params knob sets: a=1,b=2;a=3 ...")
 a = ap.parse_args()
 wl = WORKLOADS[a.workload]
 n = a.reads or wl["reads"]
@@ -34,9 +35,12 @@ np.ctypeslib.as_array(C.cast(bufs[0], C.POINTER(C.c_uint32)), shape=(n, wst))[:]
 np.ctypeslib.as_array(C.cast(bufs[1], C.POINTER(C.c_uint32)), shape=(n,))[:] = lens
 got = C.c_uint64(0)
 plans = [dict(chunk_reads=int(x)) for x in a.chunks.split(",") if x] + [dict(chunk_tail=int(x)) for x in a.mids.split(",") if x]
+plans += [dict((kv.split("=")[0], int(kv.split("=")[1])) for kv in ks.split(",")) for ks in a.knobs.split(";") if ks]
 for kn in plans:
     p = m.params(**kn)
     cr = kn.get("chunk_reads", -kn.get("chunk_tail", 0))
+    if any(k not in ("chunk_reads", "chunk_tail") for k in kn):
+        print("knobs", kn, flush=True)
     ts = []
     for k in range(a.reps):
         t0 = time.perf_counter()
