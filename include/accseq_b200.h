@@ -181,11 +181,20 @@ typedef struct as_result {
  *              column (alnmain.c:314-325 uses store_stride = 2*max_read_len); may be NULL.  Columns at and past
  *              results[i].n_cigar_op are unspecified, as in the reference (it never initialises `store`): only the
  *              columns some read of the chunk uses are copied back.
- * The batch is processed in chunks (AS_CHUNK_READS overrides the size) pipelined over three streams; results do
+ * The batch is processed in chunks (as_params.chunk_reads overrides the size) pipelined over three streams; results do
  * not depend on the chunking.
+ * On an error the call returns only after every copy it had enqueued on the caller's buffers has ended, and
+ * as_gpu_last_reads_done says how far it got: reads [0, done) have their results, their CIGAR columns and -- strand 1 --
+ * their in-place reverse complement (alnmain.c:433-438); reads [touched, n) are exactly as the caller passed them and
+ * their results are untouched; the chunk in between (if any) is partly delivered.  Argument errors (a read longer than its
+ * row, a too narrow store_stride) are found before anything is copied back: done = touched = 0.  After a successful call
+ * done = touched = n.
  */
 int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t stride, const uint32_t *lens, size_t n,
                  as_result *results, uint8_t *store_mem, size_t store_stride);
+/* How many leading reads of the last as_map_batch call were delivered to the caller's buffers (see above); the reference has
+ * no counterpart: its loop either finishes or the process dies (alnmain.c:330-479). */
+size_t as_gpu_last_reads_done(as_gpu *h, size_t *touched);
 
 /*
  * as_map_batch_packed -- the same path for hosts that hold reads 2-bit packed (what the FASTQ ingest of libaccseq_host.so

@@ -128,6 +128,8 @@ def cuda_lib():
     L.as_gpu_last_chunk_timeline.argtypes = [vp, i32, C.POINTER(C.c_float * 8)]
     L.as_gpu_last_host_timing.argtypes = [vp, C.POINTER(C.c_double * 3)]
     L.as_gpu_last_transfer.argtypes = [vp, C.POINTER(u64), C.POINTER(u64)]
+    L.as_gpu_last_reads_done.argtypes = [vp, C.POINTER(C.c_size_t)]
+    L.as_gpu_last_reads_done.restype = C.c_size_t
     L.as_lc_aln_batch.argtypes = [vp, vp, i32, sz, vp, vp, vp]
     L.as_fmi_aln_batch.argtypes = [vp, vp, i32, sz, vp, vp, vp]
     L.as_sa_access_batch.argtypes = [vp, vp, sz, vp]
@@ -464,6 +466,12 @@ class GpuMapper:
         a, b = C.c_uint64(0), C.c_uint64(0)
         self._check(self.L.as_gpu_last_transfer(self.h, C.byref(a), C.byref(b)), "as_gpu_last_transfer")
         return int(a.value), int(b.value)
+
+    def last_reads_done(self):
+        """(done, touched) of the last map_batch call: reads [0, done) were delivered, reads [touched, n) are untouched."""
+        t = C.c_size_t(0)
+        d = self.L.as_gpu_last_reads_done(self.h, C.byref(t))
+        return int(d), int(t.value)
 
     # -- single stages ----------------------------------------------------------------------------
     def _aln(self, fn, seeds, qlen):

@@ -335,6 +335,7 @@ static int map_batch_impl(as_gpu *h, const as_params *p, char *reads, size_t str
 
 extern "C" int as_map_batch(as_gpu *h, const as_params *p, char *reads, size_t stride, const uint32_t *lens, size_t n,
                             as_result *results, uint8_t *store_mem, size_t store_stride) {
+    if (h) h->reads_done_last = h->reads_touched_last = 0;
     AS_TRY(check_map_args(h, p, reads, stride, lens, results));
     if (n == 0) return AS_OK;
     AS_CUDA(cudaSetDevice(h->device));
@@ -432,17 +433,23 @@ static int map_batch_impl(as_gpu *h, const as_params *p, char *reads, size_t str
                           d_store ? d_store + r0 * store_stride : nullptr, store_stride, false, nullptr, h->cev[c], r0, n));
         AS_TRY(count_results(h, d_res + r0, cn, h->d_chunk_max + c));
         AS_CUDA(cudaEventRecord(h->cev[c][6], h->stream));
-        if (want_ops && c > 0) AS_TRY(finish_chunk(c - 1));
+        if (want_ops && c > 0) {
+            AS_TRY(finish_chunk(c - 1));
+            h->reads_done_last = cb[c];                      /* chunk c-1: results, reads and columns are all on their way */
+        }
         AS_CUDA(cudaStreamWaitEvent(h->s_d2h, h->cev[c][6], 0));
         if (c == 0) AS_CUDA(cudaEventRecord(h->ev_d2h0, h->s_d2h));
         AS_CUDA(cudaMemcpyAsync(h->h_chunk_max + c, h->d_chunk_max + c, sizeof(int), cudaMemcpyDeviceToHost, h->s_d2h));
         AS_CUDA(cudaEventRecord(h->cev[c][7], h->s_d2h));
+        h->reads_touched_last = cb[c + 1];
         AS_CUDA(cudaMemcpyAsync(results + r0, d_res + r0, cn * sizeof(as_result), cudaMemcpyDeviceToHost, h->s_d2h));
         /* strand-1 reads were reverse-complemented in place (alnmain.c:433-438; the OpenACC copy(reads_mem) :421) */
         if (copy_reads_back)
             AS_CUDA(cudaMemcpyAsync(reads + r0 * stride, d_reads + r0 * stride, cn * stride, cudaMemcpyDeviceToHost, h->s_d2h));
+        if (!want_ops) h->reads_done_last = cb[c + 1];
     }
     if (want_ops) AS_TRY(finish_chunk(nc - 1));
+    h->reads_done_last = n;
     AS_CUDA(cudaEventRecord(h->ev[7], h->s_d2h));
     AS_CUDA(cudaStreamWaitEvent(h->stream, h->ev[7], 0));
     AS_CUDA(cudaEventRecord(h->ev[6], h->stream));
@@ -868,6 +875,11 @@ extern "C" int as_gpu_last_transfer(as_gpu *h, uint64_t *h2d_bytes, uint64_t *d2
     if (h2d_bytes) *h2d_bytes = h->last_h2d_bytes;
     if (d2h_bytes) *d2h_bytes = h->last_d2h_bytes;
     return AS_OK;
+}
+
+extern "C" size_t as_gpu_last_reads_done(as_gpu *h, size_t *touched) {
+    if (touched) *touched = h ? h->reads_touched_last : 0;
+    return h ? h->reads_done_last : 0;
 }
 
 extern "C" int as_gpu_stats(as_gpu *h, as_stats *out) {

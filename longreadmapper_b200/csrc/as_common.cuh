@@ -89,6 +89,7 @@ struct as_gpu {
     cudaEvent_t ev_d2h0 = nullptr;         /* first D2H issued */
     bool cev_ready = false;
     int n_chunks_last = 0;
+    size_t reads_done_last = 0, reads_touched_last = 0;     /* as_map_batch: leading reads whose copies back to the caller were all / partly enqueued */
     uint64_t last_h2d_bytes = 0, last_d2h_bytes = 0;   /* bytes the last as_map_batch moved over PCIe */
     bool timing_pending = false;           /* as_map_batch_device enqueued a call whose events were not read yet */
     int *d_chunk_max = nullptr;            /* per chunk: max n_cigar_op (trims the CIGAR-column D2H) */

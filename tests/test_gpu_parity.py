@@ -437,6 +437,26 @@ def test_map_packed_compact_long_and_edge(native, gpu_repeat, idx_repeat):
     check_packed_equals_full(native, gpu_repeat, ix, edge, el)      # and the handle is fine afterwards
 
 
+def test_map_batch_reports_how_far_it_got(native, gpu_uniform, idx_uniform):
+    """as_gpu_last_reads_done: n after a good call (whatever the chunking); after an argument error found before any copy back
+    (a length its row cannot hold) 0, with the caller's reads and results untouched"""
+    ix, (g,) = idx_uniform
+    reads, lens, _ = reads_from(native, 915, [g], 900, 100, 150, 0.0, 0.03, 0.5)
+    for kn in (dict(), dict(chunk_reads=128)):
+        gpu_uniform.map_batch(reads.copy(), lens, params=gpu_uniform.params(**kn))
+        assert gpu_uniform.last_reads_done() == (len(lens), len(lens))
+        gpu_uniform.map_batch(reads.copy(), lens, params=gpu_uniform.params(**kn), want_ops=False)
+        assert gpu_uniform.last_reads_done() == (len(lens), len(lens))
+    bad = lens.copy()
+    bad[700] = reads.shape[1] + 5
+    mine = reads.copy()
+    with pytest.raises(native.AccSeqError):
+        gpu_uniform.map_batch(mine, bad)
+    assert gpu_uniform.last_reads_done() == (0, 0)
+    assert np.array_equal(mine, reads)
+    compare_map(native, gpu_uniform, ix, reads, lens, reads.shape[1])            # and the handle is fine afterwards
+
+
 def test_map_empty_and_single(native, gpu_uniform, idx_uniform):
     ix, (g,) = idx_uniform
     res, ops = gpu_uniform.map_batch(np.zeros((0, 151), np.uint8), np.zeros(0, np.uint32))
