@@ -737,6 +737,56 @@ int orc_edit_distance_nw(const char *q, int qlen, const char *t, int tlen, int k
     return d;
 }
 
+/* edlib's alignment path, EDLIB_MODE_NW + EDLIB_TASK_PATH (edlib/edlib.cpp:141-260 edlibAlign -> :1110-1150
+ * obtainAlignment -> :909-1108 obtainAlignmentTraceback).  The traceback starts at the last cell and asks, in this
+ * order: is the cell above one less (-> EDLIB_EDOP_INSERT 1, consumes a query base), is the cell to the left one
+ * less (-> EDLIB_EDOP_DELETE 2), else it takes the diagonal (EDLIB_EDOP_MATCH 0 when the diagonal cell is equal,
+ * EDLIB_EDOP_MISMATCH 3 otherwise); on the matrix borders it runs out along the border.  edlib reads those
+ * differences from the stored Pv/Mv words of its block band; cells the band leaves out cost more than the best
+ * score and never satisfy "one less", so the rule is the same on the full matrix, which is what this restatement
+ * fills (plain O(qlen*tlen) DP: test infrastructure for small pairs).  Valid while edlib itself takes this
+ * function, i.e. while its alignment data stays under 1 MiB (:1131-1133: 20 bytes * ceil(qlen/64) * tlen +
+ * 8 * tlen); above that it switches to Hirschberg's divide and conquer (:1143), whose tie-breaks are not restated.
+ * ops: forward order, one code per alignment column; returns the distance, or -1 (no alignment) when k >= 0 and
+ * the distance exceeds k (edlib.cpp:705-708,:196).  An empty sequence is outside what edlibAlign handles. */
+int orc_edit_alignment_nw(const char *q, int qlen, const char *t, int tlen, int k, uint8_t *ops, int *n_ops) {
+    *n_ops = 0;
+    const size_t W = (size_t)tlen + 1;
+    int32_t *D = malloc(sizeof(int32_t) * ((size_t)qlen + 1) * W);
+    if (!D) return -2;
+    for (int j = 0; j <= tlen; j++) D[j] = j;
+    for (int i = 1; i <= qlen; i++) {
+        D[(size_t)i * W] = i;
+        for (int j = 1; j <= tlen; j++) {
+            int d = D[(size_t)(i - 1) * W + (j - 1)] + (q[i - 1] != t[j - 1]);
+            int u = D[(size_t)(i - 1) * W + j] + 1, l = D[(size_t)i * W + (j - 1)] + 1;
+            int m = d < u ? d : u;
+            D[(size_t)i * W + j] = m < l ? m : l;
+        }
+    }
+    const int dist = D[(size_t)qlen * W + tlen];
+    if (k >= 0 && dist > k) { free(D); return -1; }
+    int i = qlen, j = tlen, n = 0;
+    while (i > 0 || j > 0) {
+        uint8_t op;
+        if (i == 0) op = 2;
+        else if (j == 0) op = 1;
+        else {
+            const int cur = D[(size_t)i * W + j];
+            if (D[(size_t)(i - 1) * W + j] + 1 == cur) op = 1;                 /* edlib.cpp:975 */
+            else if (D[(size_t)i * W + (j - 1)] + 1 == cur) op = 2;            /* :1005 */
+            else op = D[(size_t)(i - 1) * W + (j - 1)] == cur ? 0 : 3;         /* :1038-1039 */
+        }
+        ops[n++] = op;
+        i -= (op != 2);
+        j -= (op != 1);
+    }
+    for (int a = 0, b = n - 1; a < b; a++, b--) { uint8_t x = ops[a]; ops[a] = ops[b]; ops[b] = x; }   /* :1106 */
+    *n_ops = n;
+    free(D);
+    return dist;
+}
+
 int orc_parse_cigar(const uint8_t *ops, int n_ops, char *buf, size_t buflen) {
     static const char code[4] = {'M', 'I', 'D', 'M'};   /* EDLIB_CIGAR_STANDARD, edlib.cpp:270-274 */
     size_t w = 0;

@@ -118,6 +118,8 @@ void orc_revcomp(char *seq, uint32_t len);                  /* alnmain.c:27-60 *
 int  orc_gact(const char *q, int qlen, const char *t, int tlen, int T, int O,
               uint8_t *ops, int *n_ops, uint64_t *cells);
 int  orc_edit_distance_nw(const char *q, int qlen, const char *t, int tlen, int k); /* edlib.cpp:694-895 semantics */
+/* edlib's NW alignment path (EDLIB_TASK_PATH, edlib.cpp:909-1108): ops[0..*n_ops) forward order, codes 0 = 1 I 2 D 3 X */
+int  orc_edit_alignment_nw(const char *q, int qlen, const char *t, int tlen, int k, uint8_t *ops, int *n_ops);
 int  orc_parse_cigar(const uint8_t *ops, int n_ops, char *buf, size_t buflen);      /* edlib.cpp:262-311, STANDARD */
 
 /* ---- whole path for one batch (alnmain.c:330-479) ---- */

@@ -65,6 +65,7 @@ def lib():
     L.orc_gact.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
                            C.POINTER(C.c_int), u64p]
     L.orc_edit_distance_nw.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int]
+    L.orc_edit_alignment_nw.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
     L.orc_parse_cigar.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.c_size_t]
     L.orc_map_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_uint32,
                                 C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, u64p]
@@ -342,6 +343,28 @@ def edlib_nw(q, t, k=-1, path=False):
     d = r.editDistance
     E.edlibFreeAlignResult(r)
     return d, cig
+
+
+def edlib_nw_ops(q, t, k=-1):
+    """Reference edlib, NW mode, EDLIB_TASK_PATH: (distance, alignment ops as uint8 array or None)."""
+    E = edlib_ref()
+    r = E.edlibAlign(bytes(q), len(q), bytes(t), len(t), EdlibConfig(k, 0, 2, None, 0))
+    ops = None
+    if r.editDistance >= 0 and r.alignment:
+        ops = np.ctypeslib.as_array(r.alignment, shape=(r.alignmentLength,)).copy()
+    d = r.editDistance
+    E.edlibFreeAlignResult(r)
+    return d, ops
+
+
+def edit_alignment(q, t, k=-1):
+    """oracle: edlib's NW alignment path (orc_edit_alignment_nw): (distance, ops forward order)"""
+    q = np.ascontiguousarray(q, dtype=np.uint8)
+    t = np.ascontiguousarray(t, dtype=np.uint8)
+    ops = np.zeros(q.size + t.size + 1, np.uint8)
+    n = C.c_int(0)
+    d = lib().orc_edit_alignment_nw(q.ctypes.data, q.size, t.ctypes.data, t.size, k, ops.ctypes.data, C.byref(n))
+    return d, ops[: n.value].copy()
 
 
 def run_ref_accidx(fasta_path):

@@ -317,3 +317,75 @@ def test_live_edit_distance_against_edlib():
         for k in (-1, 5, 40):
             want, _ = oracle_lib.edlib_nw(q.tobytes(), t.tobytes(), k)
             assert oracle_lib.edit_distance(q, t, k) == want
+
+
+def _pairs_for_alignment(rng, count):
+    acgt = np.frombuffer(b"ACGT", np.uint8)
+    for it in range(count):
+        n = int(rng.integers(1, 257))
+        q = acgt[rng.integers(0, 4, n)]
+        kind = it % 4
+        if kind == 0:                                   # unrelated
+            t = acgt[rng.integers(0, 4, int(rng.integers(1, 300)))]
+        elif kind == 1:                                 # mutated copy: substitutions, insertions, deletions
+            out = []
+            for c in q:
+                r = rng.random()
+                if r < 0.06:
+                    out.append(acgt[rng.integers(0, 4)])
+                elif r < 0.10:
+                    continue
+                elif r < 0.14:
+                    out += [c, acgt[rng.integers(0, 4)]]
+                else:
+                    out.append(c)
+            t = np.array(out or [q[0]], np.uint8)
+        elif kind == 2:                                 # low complexity: many ties
+            unit = acgt[rng.integers(0, 4, int(rng.integers(1, 4)))]
+            q = np.resize(unit, n)
+            t = np.resize(unit, max(1, n + int(rng.integers(-6, 7))))
+            t = t.copy()
+            t[rng.integers(0, t.size)] = acgt[rng.integers(0, 4)]
+        else:                                           # shifted copy
+            t = np.roll(q, int(rng.integers(1, 9)))[: max(1, n - int(rng.integers(0, 5)))].copy()
+        yield q, t
+
+
+@needs_ref
+def test_live_edit_alignment_against_edlib():
+    """orc_edit_alignment_nw against the reference's own edlibAlign(EDLIB_MODE_NW, EDLIB_TASK_PATH) (libedlib_ref.so =
+    edlib/edlib.cpp compiled as it lies): distance and every op of the path, on unrelated, mutated, low-complexity (tie-rich)
+    and shifted pairs, with and without a bound k; and ed_test.c's known answer"""
+    rng = np.random.default_rng(31)
+    n_paths = 0
+    for q, t in _pairs_for_alignment(rng, 400):
+        for k in (-1, 12):
+            want_d, want_ops = oracle_lib.edlib_nw_ops(q.tobytes(), t.tobytes(), k)
+            got_d, got_ops = oracle_lib.edit_alignment(q, t, k)
+            assert got_d == want_d
+            if want_d >= 0:
+                assert np.array_equal(got_ops, want_ops), (q.tobytes(), t.tobytes(), k)
+                n_paths += 1
+            else:
+                assert got_ops.size == 0
+    assert n_paths > 400
+    d, ops = oracle_lib.edit_alignment(np.frombuffer(b"A" * 100, np.uint8), np.frombuffer(b"A" * 98 + b"TT", np.uint8))
+    assert d == 2 and ops.size == 100                                        # edlib/ed_test.c:14-19: 2, 100M
+
+
+def edlib_golden_pairs():
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "edlib_paths.npz"))
+    qo, to, oo = np.concatenate([[0], np.cumsum(z["qlen"])]), np.concatenate([[0], np.cumsum(z["tlen"])]), np.concatenate([[0], np.cumsum(z["n_ops"])])
+    for i in range(z["qlen"].size):
+        yield (z["q"][qo[i]:qo[i + 1]], z["t"][to[i]:to[i + 1]], int(z["k"][i]), int(z["dist"][i]), z["ops"][oo[i]:oo[i + 1]])
+
+
+def test_edit_alignment_golden():
+    """the oracle against tests/golden/edlib_paths.npz: alignment paths the reference's compiled edlib produced
+    (tests/golden/make_golden_edlib.py); runs without /root/reference"""
+    n = 0
+    for q, t, k, want_d, want_ops in edlib_golden_pairs():
+        d, ops = oracle_lib.edit_alignment(q, t, k)
+        assert d == want_d and np.array_equal(ops, want_ops)
+        n += 1
+    assert n == 120
