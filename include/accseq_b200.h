@@ -309,6 +309,19 @@ int as_cigar_align_batch(as_gpu *h, const as_params *p, const char *q, size_t q_
 int as_edit_distance_batch(as_gpu *h, const char *q, size_t q_stride, const uint32_t *qlens,
                            const char *t, size_t t_stride, const uint32_t *tlens, size_t n,
                            const int32_t *ks, int32_t *dist);
+/* edlib's ALIGNMENT PATH for the same pairs: edlibAlign(EDLIB_MODE_NW, EDLIB_TASK_PATH) (edlib.cpp:141-260 -> obtainAlignment
+ * :1110-1150 -> obtainAlignmentTraceback :909-1108).  ops + i*ops_stride receives the alignment of pair i in forward order, one
+ * EDLIB_EDOP_* code per column (0 match, 1 insert = a query base against a gap, 2 delete, 3 mismatch: what
+ * edlibAlignmentToCigar, edlib.cpp:262-311, turns into a CIGAR); n_ops[i] = its length; dist[i] as as_edit_distance_batch
+ * (-1 and no alignment when ks[i] >= 0 is exceeded, edlib.cpp:705-708).  Tie-breaks are edlib's: from the last cell backwards,
+ * up (insert) before left (delete) before the diagonal.  Range: queries of at most AS_PATH_MAX_QLEN bases and pairs within the
+ * 1 MiB of alignment data below which edlib itself uses this traceback (20 * ceil(qlen/64) * tlen + 8 * tlen < 2^20,
+ * edlib.cpp:1131-1133; beyond it edlib switches to Hirschberg's divide and conquer and the call returns AS_ERANGE);
+ * ops_stride >= qlen + tlen of every pair.  Empty sequences (outside what edlibAlign handles) give all deletes / all inserts. */
+#define AS_PATH_MAX_QLEN 256
+int as_edit_alignment_batch(as_gpu *h, const char *q, size_t q_stride, const uint32_t *qlens,
+                            const char *t, size_t t_stride, const uint32_t *tlens, size_t n,
+                            const int32_t *ks, int32_t *dist, uint8_t *ops, size_t ops_stride, int32_t *n_ops);
 /* The same distances (the same kernel) for callers that cannot allocate -- code under CUDA graph capture, tight serving
  * loops, harnesses that forbid cudaMalloc.  NO COUNTERPART IN THE REFERENCE.
  * Needs no handle and calls no cudaMalloc / cudaFree / allocating routine: the scratch the batched entry takes from the

@@ -136,6 +136,7 @@ def cuda_lib():
     L.as_csa_access_batch.argtypes = [vp, i32, i32, vp, sz, vp]
     L.as_vote_batch.argtypes = [vp, C.POINTER(Params), vp, sz, vp, sz, vp, vp, vp, vp]
     L.as_cigar_align_batch.argtypes = [vp, C.POINTER(Params), vp, sz, vp, vp, sz, vp, sz, vp, sz, vp, vp]
+    L.as_edit_alignment_batch.argtypes = [vp, vp, sz, vp, vp, sz, vp, sz, vp, vp, vp, sz, vp]
     L.as_edit_distance_batch.argtypes = [vp, vp, sz, vp, vp, sz, vp, sz, vp, vp]
     L.as_edit_distance_device_noalloc.argtypes = [vp, vp, sz, vp, vp, sz, vp, sz, vp, vp]
     L.as_edit_distance_device_noalloc.restype = C.c_int
@@ -544,3 +545,18 @@ class GpuMapper:
         self._check(self.L.as_edit_distance_batch(self.h, qb.ctypes.data, qs, ql.ctypes.data, tb.ctypes.data, tstr,
                                                   tl.ctypes.data, n, _ptr(kk), dist.ctypes.data), "as_edit_distance_batch")
         return dist
+
+    def edit_alignment_batch(self, queries, targets, ks=None):
+        """edlib's NW alignment path (EDLIB_TASK_PATH): (dist int32[n], list of uint8 op arrays in forward order)"""
+        n = len(queries)
+        qb, qs, ql = self._pairs(queries)
+        tb, tstr, tl = self._pairs(targets)
+        dist, n_ops = np.zeros(n, np.int32), np.zeros(n, np.int32)
+        stride = int((ql.astype(np.int64) + tl.astype(np.int64)).max()) if n else 1
+        stride = max(16, (stride + 15) & ~15)
+        ops = np.zeros((n, stride), np.uint8)
+        kk = None if ks is None else np.ascontiguousarray(ks, dtype=np.int32)
+        self._check(self.L.as_edit_alignment_batch(self.h, qb.ctypes.data, qs, ql.ctypes.data, tb.ctypes.data, tstr, tl.ctypes.data,
+                                                   n, _ptr(kk), dist.ctypes.data, ops.ctypes.data, stride, n_ops.ctypes.data),
+                    "as_edit_alignment_batch")
+        return dist, [ops[i, : n_ops[i]].copy() for i in range(n)]

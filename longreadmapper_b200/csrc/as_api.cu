@@ -1026,6 +1026,48 @@ extern "C" int as_cigar_align_batch(as_gpu *h, const as_params *p, const char *q
     return AS_OK;
 }
 
+extern "C" int as_edit_alignment_batch(as_gpu *h, const char *q, size_t q_stride, const uint32_t *qlens, const char *t,
+                                       size_t t_stride, const uint32_t *tlens, size_t n, const int32_t *ks, int32_t *dist,
+                                       uint8_t *ops, size_t ops_stride, int32_t *n_ops) {
+    if (!h || !q || !t || !qlens || !tlens || !dist || !ops || !n_ops) return AS_EINVAL;
+    if (n == 0) return AS_OK;
+    AS_CUDA(cudaSetDevice(h->device));
+    uint32_t mq, mt;
+    size_t qws, tws;
+    /* limits first (host scan): the query's words stay in registers, and past 1 MiB of alignment data edlib itself leaves
+     * the traceback for Hirschberg's divide and conquer (edlib.cpp:1131-1143), whose tie-breaks are not this function's */
+    for (size_t i = 0; i < n; i++) {
+        const uint64_t nb = ((uint64_t)qlens[i] + 63) / 64;
+        if (qlens[i] > AS_PATH_MAX_QLEN || 20ull * nb * tlens[i] + 8ull * tlens[i] >= (1ull << 20)) {
+            as_set_error("as_edit_alignment_batch: pair %zu (%u x %u bases) is beyond the traceback's range: query <= %d bases "
+                         "and 20 * ceil(qlen / 64) * tlen + 8 * tlen < 2^20", i, qlens[i], tlens[i], AS_PATH_MAX_QLEN);
+            return AS_ERANGE;
+        }
+        if ((size_t)qlens[i] + tlens[i] > ops_stride) {
+            as_set_error("as_edit_alignment_batch: ops_stride %zu < qlen + tlen of pair %zu", ops_stride, i);
+            return AS_EINVAL;
+        }
+    }
+    AS_TRY(upload_pairs(h, q, q_stride, qlens, t, t_stride, tlens, n, &mq, &mt, &qws, &tws));
+    AS_TRY(pair_offsets(h, n, tws));
+    AS_TRY(as_scratch(h, &h->misc[3], 3 * n * sizeof(int32_t)));
+    AS_TRY(as_scratch(h, &h->store, n * ops_stride));
+    int32_t *d_d = (int32_t *)h->misc[3].p, *d_n = d_d + n;
+    int32_t *d_k = nullptr;
+    if (ks) {
+        d_k = d_d + 2 * n;
+        AS_CUDA(cudaMemcpyAsync(d_k, ks, n * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+    }
+    const uint32_t *d_l = (const uint32_t *)h->misc[2].p;
+    AS_TRY(as_launch_myers_path(h, (const uint32_t *)h->qpack.p, qws, d_l, (const uint32_t *)h->tpack.p, (const uint64_t *)h->toff.p,
+                                d_l + n, n, mq, mt, d_k, d_d, (uint8_t *)h->store.p, ops_stride, d_n));
+    AS_CUDA(cudaMemcpyAsync(dist, d_d, n * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    AS_CUDA(cudaMemcpyAsync(n_ops, d_n, n * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    AS_CUDA(cudaMemcpyAsync(ops, h->store.p, n * ops_stride, cudaMemcpyDeviceToHost, h->stream));
+    AS_CUDA(cudaStreamSynchronize(h->stream));
+    return AS_OK;
+}
+
 extern "C" int as_edit_distance_batch(as_gpu *h, const char *q, size_t q_stride, const uint32_t *qlens, const char *t,
                                       size_t t_stride, const uint32_t *tlens, size_t n, const int32_t *ks, int32_t *dist) {
     if (!h || !q || !t || !qlens || !tlens || !dist) return AS_EINVAL;

@@ -72,6 +72,7 @@ struct as_gpu {
     bool gact_emit_runs = false;         /* run_stages -> as_launch_gact: the caller only reads run bytes (AS_F_RLE_CIGAR, dense gather) */
     ScratchBuf vote_dlist;               /* PART 1: reads the thread-per-read kernel deferred to the group kernel */
     ScratchBuf gact_retry;               /* bit-parallel GACT: one-tile reads the one-word diagonal band could not prove exact */
+    ScratchBuf path_planes;              /* as_edit_alignment_batch: Pv / Ph words of every (column, block) of a slice of pairs */
     ScratchBuf locus_tmp;                /* packed-only long reads: one scratch row per warp for the reverse complement */
     ScratchBuf pack_in, cres, runs, run_tot;   /* as_map_batch_packed: tight packed rows in, compact records + dense run bytes out */
     /* pinned staging for small D2H/H2D */
@@ -139,6 +140,9 @@ struct VoteOut {
 };
 int as_launch_pack(as_gpu *h, const char *d_ascii, size_t stride, const uint32_t *d_lens, size_t n,
                    uint32_t *d_pack, size_t wstride);
+int as_launch_myers_path(as_gpu *h, const uint32_t *d_qpack, size_t q_wstride, const uint32_t *d_qlens, const uint32_t *d_tbase,
+                         const uint64_t *d_toff, const uint32_t *d_tlens, size_t n, uint32_t max_qlen, uint32_t max_tlen,
+                         const int32_t *d_ks, int32_t *d_dist, uint8_t *d_ops, size_t ops_stride, int32_t *d_nops);
 int as_launch_vote(as_gpu *h, const as_params *p, const uint32_t *d_pack, size_t wstride, const uint32_t *d_lens,
                    size_t n, uint32_t max_len, VoteOut *d_vote);
 int as_launch_locus(as_gpu *h, char *d_ascii, size_t stride, const uint32_t *d_lens, size_t n,

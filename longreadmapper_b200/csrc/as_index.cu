@@ -175,7 +175,7 @@ extern "C" void as_gpu_close(as_gpu *h) {
     }
     if (!h->is_twin) free_index(h);
     ScratchBuf *bufs[] = {&h->reads, &h->lens, &h->results, &h->store, &h->qpack, &h->tpack, &h->toff,
-                          &h->vote, &h->counters, &h->ovf_list, &h->ovf_table, &h->gact_planes, &h->gact_tb, &h->gact_order, &h->gact_retry, &h->vote_dlist,
+                          &h->vote, &h->counters, &h->ovf_list, &h->ovf_table, &h->gact_planes, &h->gact_tb, &h->gact_order, &h->gact_retry, &h->path_planes, &h->vote_dlist,
                           &h->locus_tmp, &h->pack_in, &h->cres, &h->runs, &h->run_tot};
     for (ScratchBuf *b : bufs) free_scratch(b);
     for (ScratchBuf &b : h->misc) free_scratch(&b);

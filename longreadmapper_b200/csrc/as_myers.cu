@@ -262,6 +262,150 @@ int as_launch_myers(as_gpu *h, const uint32_t *d_qpack, size_t q_wstride, const 
 }
 
 /* ------------------------------------------------------------------------------------------------------------------------
+ * edlib's alignment path (EDLIB_MODE_NW, EDLIB_TASK_PATH): edlibAlign edlib.cpp:141-260 -> obtainAlignment :1110-1150 ->
+ * obtainAlignmentTraceback :909-1108.  The traceback starts at the last cell and asks, in this order: is the cell above one
+ * less (INSERT 1), is the cell to the left one less (DELETE 2), else the diagonal (MATCH 0 / MISMATCH 3).  "The cell above is
+ * one less" is the vertical delta the column step leaves in Pv, "the cell to the left is one less" the horizontal delta Ph
+ * it computes on the way (before the shift): the fill keeps both words of every (column, block), the walk reads two bits per
+ * step and compares two bases for the diagonal's label.  One thread per pair, queries of at most 256 bases (4 words in
+ * registers), planes [column][block][Pv | Ph][pair of the launch] so that a warp's stores are contiguous.
+ * ---------------------------------------------------------------------------------------------------------------------- */
+struct MyersPathArgs {
+    MyersArgs m;
+    size_t first, count;         /* pairs [first, first + count) of the batch */
+    int nbmax;                   /* blocks of the longest query of the batch */
+    uint64_t *planes;            /* [tlen_max][nbmax][2][count] */
+    uint8_t *ops;                /* row i at ops + i * ops_stride, forward order */
+    size_t ops_stride;
+    int32_t *n_ops;
+};
+
+__global__ void __launch_bounds__(128) k_myers_path(MyersPathArgs pa) {
+    const MyersArgs &a = pa.m;
+    for (size_t li = blockIdx.x * (size_t)blockDim.x + threadIdx.x; li < pa.count; li += (size_t)gridDim.x * blockDim.x) {
+        const size_t i = pa.first + li;
+        const uint64_t toff = a.toff[i];
+        const int qlen = (int)a.qlens[i], tlen = (int)a.tlens[i];
+        const int k = a.ks ? a.ks[i] : -1;
+        const uint32_t *qp = a.qpack + i * a.q_wstride;
+        uint8_t *ops = pa.ops + i * pa.ops_stride;
+        uint64_t *pl = pa.planes + li;
+        const size_t cs = pa.count;                     /* stride between consecutive plane words of one pair */
+        const int nb = (qlen + 63) >> 6;
+        int d;
+        if (qlen == 0) d = tlen;
+        else if (tlen == 0) d = qlen;
+        else {
+            uint64_t p0[4], p1[4], vm[4], Pv[4], Mv[4];
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
+                if (b < nb) query_planes(qp, b, qlen, p0[b], p1[b], vm[b]);
+                else { p0[b] = p1[b] = vm[b] = 0; }
+                Pv[b] = ~0ULL;
+                Mv[b] = 0;
+            }
+            int score = 64 * nb;
+            uint32_t tw = 0;
+            for (int j = 0; j < tlen; j++) {
+                const uint64_t tp = toff + (uint64_t)j;
+                if ((tp & 15u) == 0 || j == 0) tw = __ldg(a.tbase + (tp >> 4));
+                const uint32_t c = (tw >> (2u * ((uint32_t)tp & 15u))) & 3u;
+                int h = 1;
+#pragma unroll
+                for (int b = 0; b < 4; b++) {
+                    if (b < nb) {
+                        /* myers_block, with the horizontal +1 word kept before it is shifted */
+                        uint64_t Eq = eq_mask(c, p0[b], p1[b], vm[b]);
+                        const uint64_t hneg = h < 0 ? 1ULL : 0ULL;
+                        const uint64_t Xv = Eq | Mv[b];
+                        Eq |= hneg;
+                        const uint64_t Xh = (((Eq & Pv[b]) + Pv[b]) ^ Pv[b]) | Eq;
+                        uint64_t Ph = Mv[b] | ~(Xh | Pv[b]);
+                        uint64_t Mh = Pv[b] & Xh;
+                        const uint64_t ph_keep = Ph;
+                        const int hout = (int)(Ph >> 63) - (int)(Mh >> 63);
+                        Ph <<= 1;
+                        Mh <<= 1;
+                        Mh |= hneg;
+                        if (h > 0) Ph |= 1ULL;
+                        Pv[b] = Mh | ~(Xv | Ph);
+                        Mv[b] = Ph & Xv;
+                        h = hout;
+                        uint64_t *w = pl + ((size_t)(j * pa.nbmax + b) * 2) * cs;
+                        w[0] = Pv[b];
+                        w[cs] = ph_keep;
+                    }
+                }
+                score += h;
+            }
+            const int lastbit = (qlen - 1) & 63;
+            const uint64_t above = lastbit == 63 ? 0ULL : (~0ULL << (lastbit + 1));
+            uint64_t pv = Pv[0], mv = Mv[0];
+#pragma unroll
+            for (int b = 1; b < 4; b++)
+                if (b == nb - 1) { pv = Pv[b]; mv = Mv[b]; }
+            d = score - (__popcll(pv & above) - __popcll(mv & above));
+        }
+        const bool over = k >= 0 && d > k;
+        if (a.dist) a.dist[i] = over ? -1 : d;
+        int n = 0;
+        if (!over) {
+            /* two walks: the first counts the columns, the second writes them in forward order */
+            for (int pass = 0; pass < 2; pass++) {
+                int ci = qlen, cj = tlen, m = 0;
+                while (ci > 0 || cj > 0) {
+                    uint32_t op;
+                    if (ci == 0) op = 2u;
+                    else if (cj == 0) op = 1u;
+                    else {
+                        const int b = (ci - 1) >> 6, r = (ci - 1) & 63;
+                        const uint64_t *w = pl + ((size_t)((cj - 1) * pa.nbmax + b) * 2) * cs;
+                        if ((w[0] >> r) & 1ULL) op = 1u;                          /* edlib.cpp:975 */
+                        else if ((w[cs] >> r) & 1ULL) op = 2u;                    /* :1005 */
+                        else op = as_base_at(qp, (uint64_t)(ci - 1)) == as_base_at(a.tbase, toff + (uint64_t)(cj - 1)) ? 0u : 3u;   /* :1038 */
+                    }
+                    if (pass) ops[n - 1 - m] = (uint8_t)op;
+                    m++;
+                    ci -= (op != 2u);
+                    cj -= (op != 1u);
+                }
+                n = m;
+            }
+        }
+        pa.n_ops[i] = n;
+    }
+}
+
+int as_launch_myers_path(as_gpu *h, const uint32_t *d_qpack, size_t q_wstride, const uint32_t *d_qlens, const uint32_t *d_tbase,
+                         const uint64_t *d_toff, const uint32_t *d_tlens, size_t n, uint32_t max_qlen, uint32_t max_tlen,
+                         const int32_t *d_ks, int32_t *d_dist, uint8_t *d_ops, size_t ops_stride, int32_t *d_nops) {
+    if (n == 0) return AS_OK;
+    MyersPathArgs pa;
+    pa.m.qpack = d_qpack; pa.m.q_wstride = q_wstride; pa.m.qlens = d_qlens;
+    pa.m.tbase = d_tbase; pa.m.toff = d_toff; pa.m.tlens = d_tlens; pa.m.n = n;
+    pa.m.ks = d_ks; pa.m.k_from_len = 0; pa.m.dist = d_dist; pa.m.res = nullptr; pa.m.work_counter = nullptr;
+    pa.nbmax = (int)((max_qlen + 63) / 64);
+    if (pa.nbmax < 1) pa.nbmax = 1;
+    pa.ops = d_ops; pa.ops_stride = ops_stride; pa.n_ops = d_nops;
+    /* planes of one pair: max_tlen * nbmax * 16 bytes; the batch goes through in slices of at most 1 GB of them */
+    const size_t per_pair = (size_t)(max_tlen ? max_tlen : 1) * (size_t)pa.nbmax * 16;
+    size_t slice = ((size_t)1 << 30) / per_pair;
+    if (slice < 128) slice = 128;
+    if (slice > n) slice = n;
+    AS_TRY(as_scratch(h, &h->path_planes, slice * per_pair));
+    pa.planes = (uint64_t *)h->path_planes.p;
+    for (size_t first = 0; first < n; first += slice) {
+        pa.first = first;
+        pa.count = n - first < slice ? n - first : slice;
+        uint64_t blocks = (pa.count + 127) / 128, cap = (uint64_t)h->sm_count * 16;
+        k_myers_path<<<(unsigned)(blocks < cap ? blocks : cap), 128, 0, h->stream>>>(pa);
+        h->launches++;
+        AS_CUDA(cudaGetLastError());
+    }
+    return AS_OK;
+}
+
+/* ------------------------------------------------------------------------------------------------------------------------
  * as_edit_distance_device_noalloc: k_myers_short for callers that cannot allocate (code under CUDA graph capture, tight
  * serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
  * The scratch as_edit_distance_batch takes from the handle's growable buffers -- the 2-bit packed queries and

@@ -634,6 +634,42 @@ def test_myers_pairs(orc, gpu_uniform, lmax, emax):
     assert np.array_equal(d, np.where(exp > ks, -1, exp))
 
 
+def test_edit_alignment_path(native, orc, gpu_uniform):
+    """as_edit_alignment_batch = edlib's alignment path (EDLIB_MODE_NW, EDLIB_TASK_PATH; edlib.cpp:909-1108): distance and
+    every op equal (1) the oracle's restatement on seeded pairs -- unrelated, mutated, tie-rich low-complexity, shifted, up to
+    256-base queries against targets of up to 2000 bases, with and without k -- and (2) the golden paths the reference's own
+    compiled edlib produced (tests/golden/edlib_paths.npz); the ops re-read as an alignment consume both sequences and cost
+    the distance; out-of-range pairs are refused"""
+    from test_oracle_vs_ref import _pairs_for_alignment, edlib_golden_pairs
+    rng = np.random.default_rng(77)
+    pairs = list(_pairs_for_alignment(rng, 600))
+    acgt = np.frombuffer(b"ACGT", np.uint8)
+    for L in (1, 2, 63, 64, 65, 128, 129, 255, 256):                     # block boundaries of the query
+        q = acgt[rng.integers(0, 4, L)]
+        pairs.append((q, np.concatenate([q[: L // 2], acgt[rng.integers(0, 4, 3)], q[L // 2:]])))
+        pairs.append((q, acgt[rng.integers(0, 4, 2000)]))
+    qs, ts = [p[0].tobytes() for p in pairs], [p[1].tobytes() for p in pairs]
+    for ks in (None, np.full(len(pairs), 9, np.int32)):
+        dist, ops = gpu_uniform.edit_alignment_batch(qs, ts, ks)
+        for i, (q, t) in enumerate(pairs):
+            d, want = orc.edit_alignment(q, t, -1 if ks is None else int(ks[i]))
+            assert dist[i] == d and np.array_equal(ops[i], want), (i, q.tobytes(), t.tobytes())
+            if d >= 0:
+                o = ops[i]
+                assert (o != 2).sum() == q.size and (o != 1).sum() == t.size and (o != 0).sum() == d
+    gold = list(edlib_golden_pairs())
+    dist, ops = gpu_uniform.edit_alignment_batch([g[0].tobytes() for g in gold], [g[1].tobytes() for g in gold],
+                                                 np.array([g[2] for g in gold], np.int32))
+    for i, g in enumerate(gold):
+        assert dist[i] == g[3] and np.array_equal(ops[i], g[4]), i
+    with pytest.raises(native.AccSeqError, match="beyond the traceback"):
+        gpu_uniform.edit_alignment_batch([b"A" * 257], [b"A" * 10])
+    with pytest.raises(native.AccSeqError, match="beyond the traceback"):
+        gpu_uniform.edit_alignment_batch([b"A" * 256], [b"A" * 12000])
+    dist, ops = gpu_uniform.edit_alignment_batch(qs[:3], ts[:3])            # and the handle is fine afterwards
+    assert all(np.array_equal(ops[i], orc.edit_alignment(pairs[i][0], pairs[i][1], -1)[1]) for i in range(3))
+
+
 # ---------------------------------------------------------------------------------------------------
 # BASELINE config 2 at its full size (4.6 Mbp genome, 1 M reads of 150 bp at 2 %): size-independent properties, plus the
 # oracle on a random sample of the same batch
