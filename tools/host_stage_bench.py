@@ -25,7 +25,7 @@ H = lm.host_lib()
 class Batch(C.Structure):
     _fields_ = [("n", C.c_size_t), ("max_len", C.c_uint32), ("wstride", C.c_size_t), ("packed", C.c_void_p), ("lens", C.c_void_p),
                 ("name", C.c_void_p), ("seq", C.c_void_p), ("qual", C.c_void_p), ("name_len", C.c_void_p), ("text", C.c_void_p),
-                ("text_len", C.c_size_t), ("text_owned", C.c_int)]
+                ("text_len", C.c_size_t), ("text_owned", C.c_int), ("owner", C.c_void_p)]
 
 
 H.as_ingest_open.restype = C.c_void_p
