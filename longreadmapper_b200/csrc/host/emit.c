@@ -48,6 +48,49 @@ static inline char *put_cigar(char *p, const uint8_t *runs, uint32_t n) {
 static const unsigned char COMP[256] = {
     ['A'] = 'T', ['C'] = 'G', ['G'] = 'C', ['T'] = 'A', ['a'] = 'T', ['c'] = 'G', ['g'] = 'C', ['t'] = 'A'};
 
+/* dst[0, len) = reverse complement of src[0, len) (alnmain.c:27-60: either case complements to upper case, anything else
+ * prints 'N').  16 bases per step where the CPU has SSSE3: the low nibble of a byte picks the letter it would have to be and
+ * its complement out of two 16-entry tables (PSHUFB), a byte whose upper-cased value is not that letter becomes 'N', and one
+ * more PSHUFB reverses the 16 bytes.  Same bytes as the table loop on every input. */
+static void revcomp_scalar(char *dst, const char *src, uint32_t len) {
+    for (uint32_t i = 0; i < len; i++) {
+        const unsigned char x = COMP[(unsigned char)src[len - 1 - i]];
+        dst[i] = x ? (char)x : 'N';
+    }
+}
+
+#if defined(__x86_64__) || defined(__i386__)
+#include <immintrin.h>
+__attribute__((target("ssse3"))) static void revcomp_ssse3(char *dst, const char *src, uint32_t len) {
+    /* low nibbles: A/a 1, C/c 3, T/t 4, G/g 7 */
+    const __m128i is = _mm_setr_epi8(0, 'A', 0, 'C', 'T', 0, 0, 'G', 0, 0, 0, 0, 0, 0, 0, 0);
+    const __m128i co = _mm_setr_epi8('N', 'T', 'N', 'G', 'A', 'N', 'N', 'C', 'N', 'N', 'N', 'N', 'N', 'N', 'N', 'N');
+    const __m128i rev = _mm_setr_epi8(15, 14, 13, 12, 11, 10, 9, 8, 7, 6, 5, 4, 3, 2, 1, 0);
+    const __m128i lo4 = _mm_set1_epi8(0x0F), up = _mm_set1_epi8((char)0xDF), en = _mm_set1_epi8('N');
+    uint32_t i = 0;
+    for (; i + 16 <= len; i += 16) {
+        const __m128i x = _mm_loadu_si128((const __m128i *)(src + len - 16 - i));
+        const __m128i nib = _mm_and_si128(x, lo4);
+        const __m128i ok = _mm_cmpeq_epi8(_mm_and_si128(x, up), _mm_shuffle_epi8(is, nib));
+        const __m128i c = _mm_or_si128(_mm_and_si128(ok, _mm_shuffle_epi8(co, nib)), _mm_andnot_si128(ok, en));
+        _mm_storeu_si128((__m128i *)(dst + i), _mm_shuffle_epi8(c, rev));
+    }
+    if (i < len) revcomp_scalar(dst + i, src, len - i);      /* the first len - i bases of src, reversed, finish dst */
+}
+#endif
+
+static void revcomp(char *dst, const char *src, uint32_t len) {
+#if defined(__x86_64__) || defined(__i386__)
+    static int have = -1;
+    if (have < 0) have = __builtin_cpu_supports("ssse3") ? 1 : 0;
+    if (have) {
+        revcomp_ssse3(dst, src, len);
+        return;
+    }
+#endif
+    revcomp_scalar(dst, src, len);
+}
+
 typedef struct {
     char *buf;
     size_t len, cap;
@@ -142,10 +185,7 @@ static inline char *put_record(char *p, const as_host_index *ix, const char *nam
         *p++ = '\t';
     }
     if (AS_RC_STRAND(*c) && seq_id >= 0) {                                    /* strand 1: SEQ is printed reverse-complemented */
-        for (uint32_t i = 0; i < len; i++) {
-            const unsigned char x = COMP[(unsigned char)seq[len - 1 - i]];
-            p[i] = x ? (char)x : 'N';
-        }
+        revcomp(p, seq, len);
     } else {
         memcpy(p, seq, len);
     }
