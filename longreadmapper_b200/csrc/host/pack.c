@@ -16,9 +16,36 @@ static inline uint32_t pack4(uint32_t x) {
 
 static inline uint32_t pack8(uint64_t x) { return pack4((uint32_t)x) | pack4((uint32_t)(x >> 32)) << 8; }
 
+#if defined(__x86_64__) || defined(__i386__)
+#include <immintrin.h>
+/* 16 bases per step: the same codes per byte, then b0 + 4 b1 per byte pair (PMADDUBSW), pairs of pairs + 16 x (PMADDWD), and
+ * the four bytes that result gathered into one word (PSHUFB) */
+__attribute__((target("ssse3"))) static size_t pack_words_ssse3(const char *seq, uint32_t len, uint32_t *out, size_t nwords) {
+    const __m128i m3 = _mm_set1_epi8(3), m1 = _mm_set1_epi8(1);
+    const __m128i w14 = _mm_set1_epi16(0x0401), w116 = _mm_set1_epi32(0x00100001);
+    const __m128i pick = _mm_setr_epi8(0, 4, 8, 12, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1);
+    size_t w = 0;
+    for (uint32_t i = 0; i + 16 <= len && w < nwords; i += 16, w++) {
+        const __m128i x = _mm_loadu_si128((const __m128i *)(seq + i));
+        const __m128i c = _mm_xor_si128(_mm_and_si128(_mm_srli_epi16(x, 1), m3), _mm_and_si128(_mm_srli_epi16(x, 2), m1));
+        const __m128i q = _mm_madd_epi16(_mm_maddubs_epi16(c, w14), w116);
+        out[w] = (uint32_t)_mm_cvtsi128_si32(_mm_shuffle_epi8(q, pick));
+    }
+    return w;
+}
+#endif
+
 void as_pack_read(const char *seq, uint32_t len, uint32_t *out, size_t nwords) {
     size_t w = 0;
     uint32_t i = 0;
+#if defined(__x86_64__) || defined(__i386__)
+    static int have = -1;
+    if (have < 0) have = __builtin_cpu_supports("ssse3") ? 1 : 0;
+    if (have) {
+        w = pack_words_ssse3(seq, len, out, nwords);
+        i = (uint32_t)(16 * w);
+    }
+#endif
     for (; i + 16 <= len && w < nwords; i += 16, w++) {
         uint64_t a, b;
         memcpy(&a, seq + i, 8);
