@@ -111,6 +111,27 @@ def test_parallel_ingest_and_emit_equal_the_serial_reader_and_printer(native, tm
         assert b"host_pipeline_check ok" in p.stdout
 
 
+def test_pack_reads_every_byte_and_length(native):
+    """as_pack_reads (pack.c: 16 bases per step with SSSE3 where the CPU has it, else 8 per multiply) against the per-byte rule of
+    include/accseq_b200.h -- code ((c >> 1) & 3) ^ ((c >> 2) & 1) for EVERY byte value, base j at bits 2(j & 15) of word j >> 4,
+    zero past the length -- on lengths 0..600, row strides wider than needed, and rows that start at any alignment"""
+    rng = np.random.default_rng(12)
+    n, stride = 700, 641
+    reads = rng.integers(0, 256, (n, stride)).astype(np.uint8)
+    acgt = np.frombuffer(b"ACGTacgtN", np.uint8)
+    reads[::2] = acgt[rng.integers(0, 9, (reads[::2].shape))]
+    lens = rng.integers(0, 601, n).astype(np.uint32)
+    lens[:40] = np.arange(40)
+    for wstride in (38, 41):
+        got = native.pack_reads(reads, lens, wstride)
+        code = ((reads >> 1) & 3) ^ ((reads >> 2) & 1)
+        want = np.zeros((n, wstride), np.uint32)
+        for j in range(600):
+            live = lens > j
+            want[live, j >> 4] |= code[live, j].astype(np.uint32) << np.uint32(2 * (j & 15))
+        assert np.array_equal(got, want)
+
+
 def test_params_default(native):
     p = native.Params()
     native.cuda_lib().as_params_default(C.byref(p))
